@@ -1,0 +1,382 @@
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE. See orb_oracle.h.
+// Restatement over flat arrays of the reference's descriptor matchers. Paths relative to
+// /root/reference/external/openvslam/src/openvslam/.
+// Parity status: match/base.h known answers (test/openvslam/match/base.cc:11-57) and match/stereo.cc (compiled unmodified
+// into oracle/_ref) pin the Hamming and stereo paths; robust.cc / projection.cc depend on Eigen + g2o + DBoW2 and cannot be
+// compiled here, so those two restatements are "parity unpinned" beyond line-by-line review and the angle_checker cases.
+#include "orb_oracle.h"
+#include "cvprim.h"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <numeric>
+#include <unordered_set>
+#include <utility>
+#include <vector>
+
+namespace {
+
+constexpr unsigned HAMMING_DIST_THR_LOW = 50;   // match/base.h:13
+constexpr unsigned HAMMING_DIST_THR_HIGH = 100; // match/base.h:14
+constexpr unsigned MAX_HAMMING_DIST = 256;      // match/base.h:15
+
+// match/base.h:18-40 — SWAR popcount on 8 x 32-bit words
+unsigned hamming_32(const uint8_t* a, const uint8_t* b) {
+    const uint32_t* pa = reinterpret_cast<const uint32_t*>(a);
+    const uint32_t* pb = reinterpret_cast<const uint32_t*>(b);
+    unsigned dist = 0;
+    for (int i = 0; i < 8; ++i) {
+        uint32_t v = pa[i] ^ pb[i];
+        v -= (v >> 1) & 0x55555555U;
+        v = (v & 0x33333333U) + ((v >> 2) & 0x33333333U);
+        dist += (((v + (v >> 4)) & 0x0F0F0F0FU) * 0x01010101U) >> 24;
+    }
+    return dist;
+}
+
+// match/base.h:43-63 — SWAR popcount on 4 x 64-bit words
+unsigned hamming_64(const uint8_t* a, const uint8_t* b) {
+    const uint64_t* pa = reinterpret_cast<const uint64_t*>(a);
+    const uint64_t* pb = reinterpret_cast<const uint64_t*>(b);
+    unsigned dist = 0;
+    for (int i = 0; i < 4; ++i) {
+        uint64_t v = pa[i] ^ pb[i];
+        v -= (v >> 1) & 0x5555555555555555ULL;
+        v = (v & 0x3333333333333333ULL) + ((v >> 2) & 0x3333333333333333ULL);
+        dist += static_cast<unsigned>((((v + (v >> 4)) & 0x0F0F0F0F0F0F0F0FULL) * 0x0101010101010101ULL) >> 56);
+    }
+    return dist;
+}
+
+// match/angle_checker.h:60-134, histogram_length = 30, num_bins_thr = 3
+struct AngleHistogram {
+    static constexpr unsigned kLen = 30;
+    static constexpr unsigned kTop = 3;
+    std::vector<std::vector<int>> bins = std::vector<std::vector<int>>(kLen);
+    const float inv_len = 1.0f / kLen;
+
+    void append(float delta, int id) {
+        if (delta < 0.0) delta += 360.0;
+        if (360.0 <= delta) delta -= 360.0;
+        const unsigned bin = static_cast<unsigned>(cvprim::round_half_even(delta * inv_len));
+        bins.at(bin).push_back(id);
+    }
+    std::vector<int> invalid() const {
+        // angle_checker.h:126-134: the same std::sort call on the same container type, so that libstdc++'s handling of
+        // equal bin sizes is reproduced exactly
+        std::vector<unsigned int> order(bins.size());
+        std::iota(order.begin(), order.end(), 0);
+        std::sort(order.begin(), order.end(),
+                  [this](const unsigned int a, const unsigned int b) { return bins.at(a).size() > bins.at(b).size(); });
+        std::vector<int> out;
+        for (unsigned bin = 0; bin < kLen; ++bin) {
+            const bool keep = std::any_of(order.begin(), order.begin() + kTop, [bin](unsigned i) { return bin == i; });
+            if (!keep) out.insert(out.end(), bins[bin].begin(), bins[bin].end());
+        }
+        return out;
+    }
+};
+
+} // namespace
+
+extern "C" {
+
+uint32_t orc_hamming_32(const uint8_t* a, const uint8_t* b) { return hamming_32(a, b); }
+uint32_t orc_hamming_64(const uint8_t* a, const uint8_t* b) { return hamming_64(a, b); }
+
+int orc_angle_invalid(const float* delta_angles, const int32_t* ids, int n, int32_t* invalid_out) {
+    AngleHistogram h;
+    for (int i = 0; i < n; ++i) h.append(delta_angles[i], ids[i]);
+    const auto inv = h.invalid();
+    std::copy(inv.begin(), inv.end(), invalid_out);
+    return static_cast<int>(inv.size());
+}
+
+// match/robust.cc:215-321
+int orc_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* desc_2, uint32_t n2, const uint8_t* valid_2,
+                         const float* angle_1, const float* angle_2, float lowe_ratio, int check_orientation,
+                         int32_t* match_2_in_1) {
+    int num = 0;
+    AngleHistogram hist;
+    std::fill(match_2_in_1, match_2_in_1 + n1, -1);
+    std::vector<uint8_t> claimed(n1, 0);
+    for (uint32_t i2 = 0; i2 < n2; ++i2) {
+        if (valid_2 && !valid_2[i2]) continue; // robust.cc:240-246: no landmark / will be erased
+        const uint8_t* d2 = desc_2 + static_cast<size_t>(i2) * 32;
+        unsigned best = MAX_HAMMING_DIST, second = MAX_HAMMING_DIST;
+        int best_i1 = -1;
+        for (uint32_t i1 = 0; i1 < n1; ++i1) {
+            if (claimed[i1]) continue; // robust.cc:258
+            const unsigned d = hamming_32(d2, desc_1 + static_cast<size_t>(i1) * 32);
+            if (d < best) {
+                second = best;
+                best = d;
+                best_i1 = static_cast<int>(i1);
+            }
+            else if (d < second) {
+                second = d;
+            }
+        }
+        if (HAMMING_DIST_THR_LOW < best) continue;
+        if (best_i1 < 0) continue;
+        if (lowe_ratio * second < static_cast<float>(best)) continue; // robust.cc:285
+        match_2_in_1[best_i1] = static_cast<int32_t>(i2);
+        claimed[best_i1] = 1;
+        if (check_orientation) hist.append(angle_1[best_i1] - angle_2[i2], best_i1);
+        ++num;
+    }
+    if (check_orientation) {
+        for (int id : hist.invalid()) {
+            match_2_in_1[id] = -1;
+            --num;
+        }
+    }
+    return num;
+}
+
+// match/stereo.cc:18-249
+int orc_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r, const int* lw, const int* lh,
+                     const size_t* lpitch_l, const size_t* lpitch_r, int num_levels,
+                     const orc_keypoint* kp_l, uint32_t nl, const orc_keypoint* kp_r, uint32_t nr,
+                     const uint8_t* desc_l, const uint8_t* desc_r, const float* scale_factors,
+                     const float* inv_scale_factors, float focal_x_baseline, float true_baseline,
+                     float* stereo_x_right, float* depths) {
+    (void)num_levels;
+    (void)lh;
+    constexpr unsigned hamm_thr = (HAMMING_DIST_THR_HIGH + HAMMING_DIST_THR_LOW) / 2; // stereo.h:99
+    const float min_disp = 0.0f, max_disp = focal_x_baseline / true_baseline;      // stereo.cc:16
+    // stereo.cc:114-141: right keypoints bucketed by every row within +-2*scale of their y
+    const unsigned rows = static_cast<unsigned>(lh[0]);
+    std::vector<std::vector<unsigned>> in_row(rows);
+    for (unsigned ir = 0; ir < nr; ++ir) {
+        const float y = kp_r[ir].y;
+        const float r = 2.0f * scale_factors[kp_r[ir].octave];
+        const int hi = cvprim::ceil_int(y + r);
+        const int lo = cvprim::floor_int(y - r);
+        for (int row = lo; row <= hi; ++row) in_row.at(row).push_back(ir);
+    }
+    std::fill(stereo_x_right, stereo_x_right + nl, -1.0f);
+    std::fill(depths, depths + nl, -1.0f);
+    std::vector<std::pair<int, int>> corr_idx;
+    for (unsigned il = 0; il < nl; ++il) {
+        const orc_keypoint& kl = kp_l[il];
+        const int oct = kl.octave;
+        const auto& cands = in_row.at(static_cast<size_t>(kl.y));
+        if (cands.empty()) continue;
+        const float min_xr = kl.x - max_disp;
+        const float max_xr = kl.x - min_disp;
+        if (max_xr < 0) continue;
+        // stereo.cc:143-176
+        unsigned best_ir = 0, best_d = hamm_thr;
+        for (unsigned ir : cands) {
+            const orc_keypoint& kr = kp_r[ir];
+            if (kr.octave < oct - 1 || kr.octave > oct + 1) continue;
+            if (kr.x < min_xr || max_xr < kr.x) continue;
+            const unsigned d = hamming_32(desc_l + static_cast<size_t>(il) * 32, desc_r + static_cast<size_t>(ir) * 32);
+            if (d < best_d) {
+                best_ir = ir;
+                best_d = d;
+            }
+        }
+        if (hamm_thr <= best_d) continue;
+        // stereo.cc:178-249 sub-pixel refinement on the pyramid level of the left keypoint
+        const float xr = kp_r[best_ir].x;
+        const float inv_sf = inv_scale_factors[oct];
+        const int sxl = cvprim::round_half_even(kl.x * inv_sf);
+        const int syl = cvprim::round_half_even(kl.y * inv_sf);
+        const int sxr = cvprim::round_half_even(xr * inv_sf);
+        constexpr int win = 5, slide = 5;
+        if (sxr - slide - win < 0 || lw[oct] <= sxr + slide + win) continue;
+        const uint8_t* L = pyr_l[oct];
+        const uint8_t* R = pyr_r[oct];
+        const size_t pl = lpitch_l[oct], pr = lpitch_r[oct];
+        float best_corr = static_cast<float>(UINT_MAX);
+        int best_off = 0;
+        float corr[2 * slide + 1];
+        const float cl = L[static_cast<size_t>(syl) * pl + sxl];
+        for (int off = -slide; off <= slide; ++off) {
+            const float cr = R[static_cast<size_t>(syl) * pr + sxr + off];
+            double sum = 0.0; // cv::norm(NORM_L1) on CV_32F accumulates in double; all terms are integers
+            for (int dy = -win; dy <= win; ++dy)
+                for (int dx = -win; dx <= win; ++dx) {
+                    const float a = static_cast<float>(L[static_cast<size_t>(syl + dy) * pl + sxl + dx]) - cl;
+                    const float b = static_cast<float>(R[static_cast<size_t>(syl + dy) * pr + sxr + off + dx]) - cr;
+                    sum += std::fabs(a - b);
+                }
+            const float c = static_cast<float>(sum);
+            if (c < best_corr) {
+                best_corr = c;
+                best_off = off;
+            }
+            corr[slide + off] = c;
+        }
+        if (best_off == -slide || best_off == slide) continue;
+        const float c1 = corr[slide + best_off - 1], c2 = corr[slide + best_off], c3 = corr[slide + best_off + 1];
+        const float x_delta = static_cast<float>((c1 - c3) / (2.0 * (c1 + c3) - 4.0 * c2));
+        if (x_delta < -1.0 || 1.0 < x_delta) continue;
+        float best_xr = scale_factors[oct] * (static_cast<float>(sxr + best_off) + x_delta);
+        float best_disp = kl.x - best_xr;
+        if (best_disp < min_disp || max_disp <= best_disp) continue;
+        if (best_disp <= 0.0f) {
+            best_disp = 0.01f;
+            best_xr = kl.x - best_disp;
+        }
+        depths[il] = focal_x_baseline / best_disp;
+        stereo_x_right[il] = best_xr;
+        corr_idx.emplace_back(static_cast<int>(best_corr), static_cast<int>(il));
+    }
+    // stereo.cc:94-111: drop matches whose SAD exceeds twice the median
+    std::sort(corr_idx.begin(), corr_idx.end());
+    const size_t mid = corr_idx.size() / 2;
+    const float median = corr_idx.empty() ? 0.0f : static_cast<float>(corr_idx[mid].first);
+    const float thr = static_cast<float>(2.0 * median);
+    int kept = static_cast<int>(corr_idx.size());
+    for (size_t i = mid; i < corr_idx.size(); ++i) {
+        if (thr < corr_idx[i].first) {
+            stereo_x_right[corr_idx[i].second] = -1;
+            depths[corr_idx[i].second] = -1;
+            --kept;
+        }
+    }
+    return kept;
+}
+
+// match/projection.cc:85-208 with data/common.cc:97-186 and camera/perspective.cc:151-169
+int orc_match_projection(const orc_camera* cam, const double* Tc, const double* Tl, uint32_t n_last,
+                         const uint8_t* last_has_lm, const uint8_t* last_outlier, const double* last_pos_w,
+                         const uint8_t* last_lm_desc, const int32_t* last_octave, const float* last_angle,
+                         uint32_t n_curr, const orc_keypoint* kp, const uint8_t* curr_desc, const float* curr_x_right,
+                         const uint8_t* curr_has_observed_lm, const float* scale_factors, float margin,
+                         int check_orientation, int32_t* curr_match_last) {
+    int num = 0;
+    AngleHistogram hist;
+    // data/common.cc:97-118 grid assignment, cell (x, y) -> indices in insertion order
+    const int gc = static_cast<int>(cam->grid_cols), gr = static_cast<int>(cam->grid_rows);
+    std::vector<std::vector<unsigned>> grid(static_cast<size_t>(gc) * gr);
+    for (unsigned i = 0; i < n_curr; ++i) {
+        const int cx = cvprim::round_half_even((kp[i].x - cam->min_x) * cam->inv_cell_width);
+        const int cy = cvprim::round_half_even((kp[i].y - cam->min_y) * cam->inv_cell_height);
+        if (0 <= cx && cx < gc && 0 <= cy && cy < gr) grid[static_cast<size_t>(cx) * gr + cy].push_back(i);
+    }
+    std::vector<uint8_t> taken(curr_has_observed_lm, curr_has_observed_lm + n_curr);
+    std::fill(curr_match_last, curr_match_last + n_curr, -1);
+
+    auto R = [](const double* T, int r, int c) { return T[r * 4 + c]; };
+    // trans_wc = -R_cw^T t_cw ; trans_lc = R_lw trans_wc + t_lw  (projection.cc:90-99)
+    double twc[3];
+    for (int i = 0; i < 3; ++i) twc[i] = -((R(Tc, 0, i) * Tc[3] + R(Tc, 1, i) * Tc[7]) + R(Tc, 2, i) * Tc[11]);
+    const double tlc_z = ((R(Tl, 2, 0) * twc[0] + R(Tl, 2, 1) * twc[1]) + R(Tl, 2, 2) * twc[2]) + Tl[11];
+    const bool forward = cam->is_monocular ? false : tlc_z > cam->true_baseline;
+    const bool backward = cam->is_monocular ? false : -tlc_z > cam->true_baseline;
+
+    std::vector<unsigned> idx;
+    for (unsigned il = 0; il < n_last; ++il) {
+        if (!last_has_lm[il]) continue;
+        if (last_outlier[il]) continue;
+        const double* pw = last_pos_w + 3 * il;
+        // camera/perspective.cc:151-169
+        double pc[3];
+        for (int i = 0; i < 3; ++i) pc[i] = ((R(Tc, i, 0) * pw[0] + R(Tc, i, 1) * pw[1]) + R(Tc, i, 2) * pw[2]) + Tc[i * 4 + 3];
+        if (pc[2] <= 0.0) continue;
+        const double z_inv = 1.0 / pc[2];
+        const double u = cam->fx * pc[0] * z_inv + cam->cx;
+        const double v = cam->fy * pc[1] * z_inv + cam->cy;
+        const float x_right = static_cast<float>(u - cam->focal_x_baseline * z_inv);
+        if (!(cam->min_x < u && u < cam->max_x && cam->min_y < v && v < cam->max_y)) continue;
+
+        const int oct = last_octave[il];
+        int min_level, max_level;
+        if (forward) {
+            min_level = oct;
+            max_level = static_cast<int>(cam->num_scale_levels) - 1;
+        }
+        else if (backward) {
+            min_level = 0;
+            max_level = oct;
+        }
+        else {
+            min_level = oct - 1;
+            max_level = oct + 1;
+        }
+        const float ref_x = static_cast<float>(u), ref_y = static_cast<float>(v);
+        const float m = margin * scale_factors[oct];
+        // data/common.cc:127-186
+        idx.clear();
+        do {
+            const int min_cx = std::max(0, cvprim::floor_int((ref_x - cam->min_x - m) * cam->inv_cell_width));
+            if (gc <= min_cx) break;
+            const int max_cx = std::min(gc - 1, cvprim::ceil_int((ref_x - cam->min_x + m) * cam->inv_cell_width));
+            if (max_cx < 0) break;
+            const int min_cy = std::max(0, cvprim::floor_int((ref_y - cam->min_y - m) * cam->inv_cell_height));
+            if (gr <= min_cy) break;
+            const int max_cy = std::min(gr - 1, cvprim::ceil_int((ref_y - cam->min_y + m) * cam->inv_cell_height));
+            if (max_cy < 0) break;
+            const bool check_level = (0 < min_level) || (0 <= max_level);
+            for (int cx = min_cx; cx <= max_cx; ++cx)
+                for (int cy = min_cy; cy <= max_cy; ++cy)
+                    for (unsigned i : grid[static_cast<size_t>(cx) * gr + cy]) {
+                        if (check_level) {
+                            if (kp[i].octave < min_level) continue;
+                            if (0 <= max_level && max_level < kp[i].octave) continue;
+                        }
+                        const float ddx = kp[i].x - ref_x, ddy = kp[i].y - ref_y;
+                        if (std::abs(ddx) < m && std::abs(ddy) < m) idx.push_back(i);
+                    }
+        } while (false);
+        if (idx.empty()) continue;
+
+        const uint8_t* ld = last_lm_desc + static_cast<size_t>(il) * 32;
+        unsigned best = MAX_HAMMING_DIST;
+        int best_i = -1;
+        for (unsigned i : idx) {
+            if (taken[i]) continue; // projection.cc:163-165 (includes assignments made by earlier iterations)
+            if (curr_x_right[i] > 0) {
+                const float err = std::fabs(x_right - curr_x_right[i]);
+                if (m < err) continue;
+            }
+            const unsigned d = hamming_32(ld, curr_desc + static_cast<size_t>(i) * 32);
+            if (d < best) {
+                best = d;
+                best_i = static_cast<int>(i);
+            }
+        }
+        if (HAMMING_DIST_THR_HIGH < best) continue;
+        curr_match_last[best_i] = static_cast<int32_t>(il);
+        taken[best_i] = 1;
+        ++num;
+        if (check_orientation) hist.append(last_angle[il] - kp[best_i].angle, best_i);
+    }
+    if (check_orientation) {
+        for (int id : hist.invalid()) {
+            curr_match_last[id] = -1;
+            --num;
+        }
+    }
+    return num;
+}
+
+void orc_knn_top2(const uint8_t* q, uint32_t nq, const uint8_t* db, uint64_t ndb, int64_t* best_idx, uint32_t* best_d,
+                  uint32_t* second_d) {
+    for (uint32_t i = 0; i < nq; ++i) {
+        const uint8_t* qi = q + static_cast<size_t>(i) * 32;
+        unsigned b = MAX_HAMMING_DIST, s = MAX_HAMMING_DIST;
+        int64_t bi = -1;
+        for (uint64_t j = 0; j < ndb; ++j) {
+            const unsigned d = hamming_64(qi, db + j * 32);
+            if (d < b) {
+                s = b;
+                b = d;
+                bi = static_cast<int64_t>(j);
+            }
+            else if (d < s) {
+                s = d;
+            }
+        }
+        best_idx[i] = bi;
+        best_d[i] = b;
+        second_d[i] = s;
+    }
+}
+
+} // extern "C"
