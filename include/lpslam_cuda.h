@@ -1,0 +1,218 @@
+/* liblpslam_cuda — C ABI of the B200 (sm_100a) ORB front end for lpslam / OpenVSLAM.
+ *
+ * Every entry point replaces one piece of the reference's CPU path; the reference interface it stands in for is cited
+ * beside it (paths relative to /root/reference/external/openvslam/src/openvslam/). The host-side C++ drop-in classes in
+ * cpp/ (same names and signatures as the reference's) and the Python mirror in lpslam_b200/ both call only this ABI.
+ * No torch / OpenCV / STL types cross it: plain pointers, sizes and POD structs.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative lpslam_status; lpslam_cuda_last_error() gives the text
+ *     (thread-local). There is NO CPU fallback: without a CUDA device the calls fail with LPSLAM_ERR_CUDA.
+ *   - "host" pointers may be pageable or pinned (lpslam_cuda_host_alloc gives pinned memory); "_dev" entry points take
+ *     device pointers on the context's device and enqueue on the context's stream without synchronising.
+ *   - an extractor context may be used by one thread at a time; distinct contexts are independent (own stream, own
+ *     device buffers), which is what the reference's two-thread stereo extraction needs (data/frame.cc:65-68).
+ */
+#ifndef LPSLAM_CUDA_H
+#define LPSLAM_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LPSLAM_CUDA_ABI_VERSION 1
+
+typedef enum {
+    LPSLAM_OK = 0,
+    LPSLAM_ERR_ARG = -1,      /* null pointer, zero size, unsupported parameter */
+    LPSLAM_ERR_CAPACITY = -2, /* caller buffer too small; the needed count is still written to *n_out */
+    LPSLAM_ERR_CUDA = -3,     /* CUDA runtime error (no device, launch failure, out of memory) */
+    LPSLAM_ERR_STATE = -4     /* call order violated (e.g. pyramid requested before any extract) */
+} lpslam_status;
+
+/* == cv::KeyPoint (28 bytes): pt.x, pt.y, size, angle, response, octave, class_id */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} lpslam_keypoint;
+
+/* feature/orb_params.h:9-46. mask_rects = num_mask_rects x (x_min, x_max, y_min, y_max) as fractions of the image. */
+typedef struct {
+    uint32_t max_num_keypts;   /* default 2000 */
+    uint32_t ini_max_num_keypts;
+    float scale_factor;        /* default 1.2 */
+    uint32_t num_levels;       /* default 8 */
+    uint32_t ini_fast_thr;     /* default 20 */
+    uint32_t min_fast_thr;     /* default 7 */
+    const float* mask_rects;
+    uint32_t num_mask_rects;
+} lpslam_orb_params;
+
+typedef struct lpslam_orb_ctx lpslam_orb_ctx; /* one per orb_extractor instance (feature/orb_extractor.h:13-151) */
+
+/* ---------------------------------------------------------------- library ---------------------------------------- */
+int lpslam_cuda_abi_version(void);
+const char* lpslam_cuda_last_error(void);
+int lpslam_cuda_device_count(int* count);
+/* pinned host memory for images / outputs (optional; any host memory is accepted by the host entry points) */
+int lpslam_cuda_host_alloc(void** ptr, size_t bytes);
+int lpslam_cuda_host_free(void* ptr);
+
+/* ---------------------------------------------------------------- ORB extractor ---------------------------------- */
+/* orb_extractor::orb_extractor (feature/orb_extractor.cc:46-69) + initialize() (:208-242). max_batch = number of frames a
+ * single lpslam_orb_extract_batch call may carry (1 for the live tracker). Throws-equivalent: malformed mask
+ * rectangles (feature/orb_params.cc:16-26) return LPSLAM_ERR_ARG. */
+int lpslam_orb_create(lpslam_orb_ctx** ctx, const lpslam_orb_params* params, int device, uint32_t max_batch);
+void lpslam_orb_destroy(lpslam_orb_ctx* ctx);
+
+/* the five setters of feature/orb_extractor.cc:149-206 (max keypoints / scale factor / levels re-run initialize()) */
+typedef enum {
+    LPSLAM_ORB_MAX_NUM_KEYPTS = 0,
+    LPSLAM_ORB_SCALE_FACTOR = 1,
+    LPSLAM_ORB_NUM_LEVELS = 2,
+    LPSLAM_ORB_INI_FAST_THR = 3,
+    LPSLAM_ORB_MIN_FAST_THR = 4
+} lpslam_orb_param_id;
+int lpslam_orb_set_param(lpslam_orb_ctx* ctx, int which, double value);
+int lpslam_orb_get_param(const lpslam_orb_ctx* ctx, int which, double* value);
+
+/* get_scale_factors / get_inv_scale_factors / get_level_sigma_sq / get_inv_level_sigma_sq (feature/orb_extractor.cc:
+ * 176-206 of the getters) and the per-level keypoint quota (:217-226). which: 0..3 as listed, 4 = quota (as float). */
+int lpslam_orb_get_table(const lpslam_orb_ctx* ctx, int which, float* out, uint32_t cap);
+
+/* orb_extractor::extract (feature/orb_extractor.cc:71-147). img: 8UC1, row pitch in bytes. mask: optional 8UC1 image
+ * mask of the same size (0 = masked), NULL selects the rectangle mask of the parameters, if any.
+ * Writes *n_out keypoints (octave order, quadtree order inside an octave) and n_out x 32 descriptor bytes.
+ * An empty image (w or h == 0) returns LPSLAM_OK with *n_out = 0 and outputs untouched (:73-75). */
+int lpslam_orb_extract(lpslam_orb_ctx* ctx, const uint8_t* img, int width, int height, size_t pitch,
+                       const uint8_t* mask, size_t mask_pitch,
+                       lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* n_out);
+
+/* batched replay (config "4096 frames frame-parallel"): n_frames <= max_batch images of identical size, each frame
+ * extracted exactly as by lpslam_orb_extract. Outputs are packed: frame f owns rows [offsets[f], offsets[f+1]).
+ * offsets has n_frames + 1 entries. cap = capacity of kp_out / desc_out in keypoints. */
+int lpslam_orb_extract_batch(lpslam_orb_ctx* ctx, const uint8_t* const* imgs, uint32_t n_frames, int width, int height,
+                             size_t pitch, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets);
+
+/* device-resident variant: imgs_dev = n_frames images stored back to back with row pitch `pitch` and frame stride
+ * pitch*height in device memory; results stay on the device (see lpslam_orb_result_dev). Enqueues only. */
+int lpslam_orb_extract_batch_dev(lpslam_orb_ctx* ctx, const uint8_t* imgs_dev, uint32_t n_frames, int width, int height,
+                                 size_t pitch);
+/* device pointers to the packed results of the last *_dev call (valid until the next call on this context) */
+typedef struct {
+    const lpslam_keypoint* kp;  /* packed keypoints */
+    const uint8_t* desc;        /* packed descriptors, 32 B per row */
+    const uint32_t* offsets;    /* n_frames + 1 */
+    uint32_t capacity;          /* rows available in kp / desc */
+} lpslam_orb_result_dev;
+int lpslam_orb_get_result_dev(lpslam_orb_ctx* ctx, lpslam_orb_result_dev* out);
+/* the context's own level-0 batch buffer (max_batch frames, row pitch *pitch, frame stride *frame_stride) for the
+ * given image size: a producer that writes frames straight into it (decoder, undistortion kernel) and then passes the
+ * same pointer to lpslam_orb_extract_batch_dev avoids the ingest copy. */
+int lpslam_orb_input_dev(lpslam_orb_ctx* ctx, int width, int height, uint8_t** ptr, size_t* pitch, size_t* frame_stride);
+int lpslam_orb_sync(lpslam_orb_ctx* ctx);
+void* lpslam_orb_stream(lpslam_orb_ctx* ctx); /* cudaStream_t of the context */
+
+/* image_pyramid_ (public member, feature/orb_extractor.h:76; consumed by match::stereo, data/frame.cc:78).
+ * Level geometry of the last extract, and a lazy device-to-host copy of one level of frame `frame` of the last call.
+ * blurred != 0 returns the Gaussian-blurred level the descriptors were sampled from (test hook). */
+int lpslam_orb_level_size(const lpslam_orb_ctx* ctx, uint32_t level, int* width, int* height);
+int lpslam_orb_pyramid(lpslam_orb_ctx* ctx, uint32_t frame, uint32_t level, int blurred, uint8_t* dst, size_t pitch);
+
+/* test hooks: intermediates of the last extract for frame `frame` — FAST candidates handed to the quadtree
+ * (feature/orb_extractor.cc:352-369) and the keypoints it selected (:378), as (x, y, score) int32 triplets in
+ * border-relative level coordinates, reference order. Returns the count through *n_out. */
+int lpslam_orb_debug_candidates(lpslam_orb_ctx* ctx, uint32_t frame, uint32_t level, int32_t* xys, uint32_t cap,
+                                uint32_t* n_out);
+int lpslam_orb_debug_selected(lpslam_orb_ctx* ctx, uint32_t frame, uint32_t level, int32_t* xys, uint32_t cap,
+                              uint32_t* n_out);
+
+/* per-stage device time (ms, CUDA events on the context's stream) of the last extract call:
+ * 0 H2D, 1 pyramid, 2 FAST, 3 quadtree, 4 blur, 5 orientation+descriptors, 6 D2H. Returns the number of stages. */
+int lpslam_orb_stage_times(lpslam_orb_ctx* ctx, float* ms, uint32_t cap);
+int lpslam_orb_enable_timing(lpslam_orb_ctx* ctx, int on);
+
+/* ---------------------------------------------------------------- matchers --------------------------------------- */
+/* match::robust::brute_force_match (match/robust.cc:215-321) over flat arrays. desc_1 = frame descriptors (n1 x 32),
+ * desc_2 = keyframe descriptors (n2 x 32); valid_2[i] == 0 marks keyframe keypoints without a live landmark (:240-246),
+ * NULL = all valid. angle_1/angle_2 (degrees) are read only when check_orientation != 0 (match/angle_checker.h).
+ * match_2_in_1[n1] receives the keyframe index matched to each frame keypoint or -1; *n_matches the pair count. */
+int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* desc_2, uint32_t n2, const uint8_t* valid_2,
+                            const float* angle_1, const float* angle_2, float lowe_ratio, int check_orientation,
+                            int32_t* match_2_in_1, uint32_t* n_matches);
+
+/* match::stereo::compute (match/stereo.cc:18-249; ctor match/stereo.h:18-29). Pyramids are arrays of num_levels host
+ * level pointers with per-level width/height/pitch (the extractors' image_pyramid_). Outputs: stereo_x_right[nl],
+ * depths[nl], -1 = no match. */
+int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r, const int* level_w, const int* level_h,
+                        const size_t* pitch_l, const size_t* pitch_r, uint32_t num_levels,
+                        const lpslam_keypoint* kp_l, uint32_t nl, const lpslam_keypoint* kp_r, uint32_t nr,
+                        const uint8_t* desc_l, const uint8_t* desc_r, const float* scale_factors,
+                        const float* inv_scale_factors, float focal_x_baseline, float true_baseline,
+                        float* stereo_x_right, float* depths, uint32_t* n_matches);
+
+/* fused stereo frame: extracts both eyes on the device (two contexts' worth of work on one stream) and runs the row
+ * matcher on the device-resident pyramids — data::frame's stereo constructor (data/frame.cc:55-93) without the 2 x
+ * pyramid round trip. ctx_l / ctx_r are two extractor contexts on the same device. */
+int lpslam_stereo_frame(lpslam_orb_ctx* ctx_l, lpslam_orb_ctx* ctx_r, const uint8_t* img_l, const uint8_t* img_r,
+                        int width, int height, size_t pitch, float focal_x_baseline, float true_baseline,
+                        lpslam_keypoint* kp_l, uint8_t* desc_l, uint32_t* n_l, lpslam_keypoint* kp_r, uint8_t* desc_r,
+                        uint32_t* n_r, uint32_t cap, float* stereo_x_right, float* depths, uint32_t* n_matches);
+
+/* match::projection::match_current_and_last_frames (match/projection.cc:85-208) with the grid query of
+ * data/common.cc:97-186 and the perspective projection of camera/perspective.cc:151-169, over flat arrays. */
+typedef struct {
+    double fx, fy, cx, cy, focal_x_baseline, true_baseline;
+    float min_x, max_x, min_y, max_y; /* camera/base.h image bounds */
+    uint32_t grid_cols, grid_rows;    /* 64 x 48, camera/base.h:62 */
+    double inv_cell_width, inv_cell_height;
+    int32_t is_monocular;
+    uint32_t num_scale_levels;
+} lpslam_camera;
+int lpslam_match_projection(const lpslam_camera* cam, const double* pose_cw_curr /*4x4 row-major*/,
+                            const double* pose_cw_last /*4x4 row-major*/,
+                            uint32_t n_last, const uint8_t* last_has_lm, const uint8_t* last_outlier,
+                            const double* last_pos_w /*n_last x 3*/, const uint8_t* last_lm_desc /*n_last x 32*/,
+                            const int32_t* last_octave, const float* last_angle,
+                            uint32_t n_curr, const lpslam_keypoint* curr_undist_kp, const uint8_t* curr_desc,
+                            const float* curr_x_right, const uint8_t* curr_has_observed_lm, const float* scale_factors,
+                            float margin, int check_orientation, int32_t* curr_match_last, uint32_t* n_matches);
+
+/* ---------------------------------------------------------------- kNN database (relocalisation / loop query) ----- */
+/* Brute-force Hamming top-2 of query descriptors against a device-resident descriptor database (generalises the
+ * best / second-best scan of match/robust.cc:252-274 and the BoW-candidate search of module/relocalizer.cc:31-46).
+ * A database is one shard; index_base is the global row index of its first row. */
+typedef struct lpslam_knn_db lpslam_knn_db;
+int lpslam_knn_create(lpslam_knn_db** db, int device, uint64_t capacity_rows, uint64_t index_base);
+void lpslam_knn_destroy(lpslam_knn_db* db);
+int lpslam_knn_add(lpslam_knn_db* db, const uint8_t* desc_host, uint64_t n_rows);      /* append rows (H2D) */
+int lpslam_knn_add_dev(lpslam_knn_db* db, const uint8_t* desc_dev, uint64_t n_rows);   /* append rows (D2D) */
+int lpslam_knn_size(const lpslam_knn_db* db, uint64_t* n_rows);
+/* host query: best_idx (global row index, -1 if the shard is empty), best_dist, second_dist; ties -> lowest index,
+ * exactly what a sequential strict-< scan gives. */
+int lpslam_knn_query(lpslam_knn_db* db, const uint8_t* q_host, uint32_t nq, int64_t* best_idx, uint32_t* best_dist,
+                     uint32_t* second_dist);
+/* device query: writes per query two packed keys (dist << 40 | global_index), best then second, into keys_dev[nq*2];
+ * empty slots hold LPSLAM_KNN_EMPTY_KEY. Enqueues on `stream` (a cudaStream_t, NULL = default stream). */
+#define LPSLAM_KNN_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
+int lpslam_knn_query_dev(lpslam_knn_db* db, const uint8_t* q_dev, uint32_t nq, uint64_t* keys_dev, void* stream);
+/* merge of n_shards per-shard key blocks (gathered over NCCL): gathered_dev[n_shards][nq][2] -> merged_dev[nq][2] */
+int lpslam_knn_merge_dev(const uint64_t* gathered_dev, uint32_t n_shards, uint32_t nq, uint64_t* merged_dev, void* stream);
+/* fused exchange + merge over NVLink peer memory: every rank passes the device pointers of ALL ranks' key blocks
+ * (peer-mapped); the kernel reads the peers' blocks directly and merges. */
+int lpslam_knn_merge_peer_dev(const uint64_t* const* shard_keys_dev, uint32_t n_shards, uint32_t nq, uint64_t* merged_dev,
+                              void* stream);
+/* unpack merged keys on the device into the host-facing triplets */
+int lpslam_knn_unpack(const uint64_t* merged_dev, uint32_t nq, int64_t* best_idx, uint32_t* best_dist,
+                      uint32_t* second_dist, void* stream);
+
+/* match/base.h:18-63 compute_descriptor_distance_32 / _64 on the device, n pairs (test hook + landmark.cc:153-183) */
+int lpslam_hamming_pairs(const uint8_t* a, const uint8_t* b, uint32_t n, uint32_t* dist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LPSLAM_CUDA_H */

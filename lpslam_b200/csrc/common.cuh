@@ -1,0 +1,141 @@
+// liblpslam_cuda internals shared by all translation units (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/lpslam_cuda.h"
+
+namespace lps {
+
+// ---- constants fixed by the reference (feature/orb_extractor.h:128-133, orb_extractor.cc:285-286) ----
+constexpr int kPatch = 31;
+constexpr int kHalfPatch = 15;
+constexpr int kBorder = 19;
+constexpr int kCell = 64;
+constexpr int kOverlap = 6;
+constexpr int kCellSlots = 1024;  // a 64x64 cell holds at most 32x32 strict 8-neighbourhood maxima
+constexpr int kMaxLevels = 16;
+
+// ---- error plumbing ----
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define LPS_CUDA(call)                                                       \
+    do {                                                                     \
+        cudaError_t e__ = (call);                                            \
+        if (e__ != cudaSuccess) return lps::cuda_fail(e__, #call, __FILE__, __LINE__); \
+    } while (0)
+
+#define LPS_ARG(cond, msg)               \
+    do {                                 \
+        if (!(cond)) {                   \
+            lps::set_error(msg);         \
+            return LPSLAM_ERR_ARG;       \
+        }                                \
+    } while (0)
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// One pyramid level of a batch: frame f lives at base + f * frame_stride (row pitch `pitch`).
+struct LevelGeom {
+    int w, h, pitch;
+    size_t frame_stride;
+    uint8_t* img;   // un-blurred level (level 0 of the batch is a copy of / alias to the input)
+    uint8_t* blur;  // Gaussian-blurred level
+    // resize tables (device), valid for level >= 1: per destination column / row
+    const int* xofs;     // source column
+    const short2* xcoef; // (c0, c1), 11-bit fixed point
+    const int* yofs;
+    const short2* ycoef;
+    int mode;            // 0 = general bilinear, 1 = exact 2x2 decimation (OpenCV routes it to INTER_AREA), 2 = same size copy
+    // FAST cell grid of the level
+    int cell_begin, cell_cols, cell_rows;  // first cell in the per-frame cell table, grid extent (only cells the reference visits)
+    // quadtree
+    unsigned quota;
+    int nx, ny;         // initial node grid
+    double dx, dy;      // initial node extents
+    int depth;          // digits (2 bits each) in the path key
+    int rbits;          // bits of the initial-node index in the key
+    int cand_begin;     // first candidate slot of the level in the per-frame candidate scratch
+    int cand_cap;       // cell_count * kCellSlots
+    int node_begin, node_cap;
+    int sel_begin, sel_cap;
+    float scale, kp_size;
+};
+
+struct CellDesc {
+    short level;
+    short x0, y0;  // top-left of the 70x70 FAST window in level coordinates (>= 19)
+    short cw, ch;  // window size after clipping to the border (<= 70)
+    short j, i;    // cell column / row (candidate coordinates are shifted by 64*j, 64*i)
+};
+
+// Kernel parameter block for one extraction launch sequence (passed by value / from constant memory)
+struct FrameParams {
+    int num_levels;
+    int batch;
+    LevelGeom lv[kMaxLevels];
+};
+
+// ---- launchers (defined in the kernel translation units) ----
+void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaStream_t st);
+void launch_copy_level0(const uint8_t* src, size_t src_pitch, size_t src_frame_stride, const LevelGeom& dst, int batch,
+                        cudaStream_t st);
+void launch_blur(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
+
+struct FastArgs {
+    const LevelGeom* lv;      // device table
+    const CellDesc* cells;    // device table
+    int num_cells;            // per frame
+    int batch;
+    uint32_t ini_thr, min_thr;
+    uint32_t* cell_counts;    // [batch][num_cells]
+    uint32_t* cell_slots;     // [batch][num_cells][kCellSlots] packed lx | ly<<8 | score<<16
+    const uint8_t* mask;      // level-0 mask or nullptr (shared by the batch)
+    size_t mask_pitch;
+};
+void launch_fast(const FastArgs& a, cudaStream_t st);
+
+struct TreeArgs {
+    const LevelGeom* lv;  // device table
+    int num_levels, batch, num_cells;
+    const CellDesc* cells;
+    const uint32_t* cell_counts;
+    const uint32_t* cell_slots;
+    // per-frame scratch (strides in elements)
+    uint32_t* cand_xy;  size_t cand_stride;   // [batch][cand_total]  x | y<<16 (border-relative)
+    uint8_t* cand_sc;                          // [batch][cand_total]
+    uint32_t* keys[2];                         // sort ping-pong, same stride
+    uint32_t* vals[2];
+    uint32_t* cell_base; size_t cell_stride;   // [batch][num_cells]
+    int* node[2][3];     size_t node_stride;   // lo, hi, depth|flags — ping-pong
+    int* tmp[8];                               // per-node temporaries, node_stride
+    uint32_t* cand_count;                      // [batch][levels] candidates per level
+    uint32_t* sel_xys;   size_t sel_stride;    // [batch][sel_total] selected: x | y<<16, score separately
+    uint8_t* sel_sc;
+    uint32_t* sel_count;                       // [batch][levels]
+};
+void launch_quadtree(const TreeArgs& a, const LevelGeom* lv_host, cudaStream_t st);
+
+struct DescribeArgs {
+    const LevelGeom* lv;
+    int num_levels, batch;
+    const uint32_t* sel_xys; size_t sel_stride;
+    const uint8_t* sel_sc;
+    const uint32_t* sel_count;   // [batch][levels]
+    uint32_t* level_off;         // [batch*levels + 1] packed offsets (written by the offsets kernel)
+    uint32_t* frame_off;         // [batch + 1]
+    lpslam_keypoint* kp;         // packed output
+    uint8_t* desc;
+    uint32_t out_cap;
+    uint32_t* overflow;          // set to needed count when out_cap is too small
+};
+void launch_offsets(const DescribeArgs& a, cudaStream_t st);
+void launch_describe(const DescribeArgs& a, cudaStream_t st);
+
+}  // namespace lps

@@ -1,0 +1,369 @@
+// Host side of the extractor context: parameter tables, level / cell / quadtree geometry, device arena, launch sequence.
+#include "ctx.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace lps {
+
+static thread_local std::string g_error;
+
+void set_error(const std::string& msg) { g_error = msg; }
+const std::string& get_error() { return g_error; }
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    g_error = buf;
+    cudaGetLastError();  // clear the sticky-free error state
+    return LPSLAM_ERR_CUDA;
+}
+
+namespace {
+
+int round_half_even(double v) { return (int)std::lrint(v); }
+int floor_int(double v) {
+    const int i = (int)v;
+    return i - (v < i);
+}
+
+// OpenCV resizeGeneric_ coefficient tables for INTER_LINEAR, 8-bit. `clamp_reset` is the
+// horizontal-axis behaviour (offset clamped AND coefficient reset at both ends); rows are only clamped when read.
+void make_axis_tab(int sn, int dn, bool clamp_reset, std::vector<int>& ofs, std::vector<short2>& coef) {
+    ofs.resize(dn);
+    coef.resize(dn);
+    const double scale = (double)sn / dn;
+    for (int d = 0; d < dn; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = floor_int(f);
+        f -= s;
+        if (clamp_reset) {
+            if (s < 0) {
+                s = 0;
+                f = 0.f;
+            }
+            if (s >= sn - 1) {
+                s = sn - 1;
+                f = 0.f;
+            }
+        }
+        ofs[d] = s;
+        short2 c;
+        c.x = (short)round_half_even((1.f - f) * 2048.f);
+        c.y = (short)round_half_even(f * 2048.f);
+        coef[d] = c;
+    }
+}
+
+struct ArenaPlan {
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        const size_t o = off;
+        off = align_up(off + bytes, 256);
+        return o;
+    }
+};
+
+}  // namespace
+}  // namespace lps
+
+using namespace lps;
+
+// feature/orb_params.cc:38-72 (scale tables: float cumulative products) and feature/orb_extractor.cc:208-226 (quota:
+// double geometric series, std::round, last level takes the remainder)
+void lpslam_orb_ctx::initialize_tables() {
+    scale.assign(num_levels, 1.0f);
+    inv_scale.assign(num_levels, 1.0f);
+    sigma_sq.assign(num_levels, 1.0f);
+    inv_sigma_sq.assign(num_levels, 1.0f);
+    float s = 1.0f;
+    for (uint32_t l = 1; l < num_levels; ++l) {
+        scale[l] = scale_factor * scale[l - 1];
+        inv_scale[l] = (1.0f / scale_factor) * inv_scale[l - 1];
+        s = scale_factor * s;
+        sigma_sq[l] = s * s;
+        inv_sigma_sq[l] = 1.0f / (s * s);
+    }
+    quota.assign(num_levels, 0);
+    double desired = max_kpts * (1.0 - 1.0 / scale_factor) / (1.0 - std::pow(1.0 / scale_factor, (double)num_levels));
+    unsigned total = 0;
+    for (uint32_t l = 0; l + 1 < num_levels; ++l) {
+        quota[l] = (unsigned)std::round(desired);
+        total += quota[l];
+        desired *= 1.0 / scale_factor;
+    }
+    quota[num_levels - 1] = (unsigned)std::max((int)max_kpts - (int)total, 0);
+}
+
+void lpslam_orb_ctx::release_geometry() {
+    if (arena) cudaFree(arena);
+    arena = nullptr;
+    arena_bytes = 0;
+    w = h = 0;
+    has_result = false;
+    rect_mask_ready = false;
+}
+
+int lpslam_orb_ctx::configure(int width, int height) {
+    if (width == w && height == h && arena) return LPSLAM_OK;
+    LPS_CUDA(cudaSetDevice(device));
+    LPS_CUDA(cudaStreamSynchronize(stream));
+    release_geometry();
+    const int L = (int)num_levels;
+    LPS_ARG(L >= 1 && L <= kMaxLevels, "num_levels out of range (1..16)");
+    LPS_ARG(width <= 32767 && height <= 32767, "image larger than 32767 px is not supported");
+
+    std::vector<std::vector<int>> xofs(L), yofs(L);
+    std::vector<std::vector<short2>> xc(L), yc(L);
+    cells.clear();
+    memset(lv, 0, sizeof lv);
+    ArenaPlan plan;
+    std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L);
+    int cand_total = 0, node_total = 0, sel_total = 0;
+    for (int l = 0; l < L; ++l) {
+        LevelGeom& g = lv[l];
+        if (l == 0) {
+            g.w = width;
+            g.h = height;
+        }
+        else {
+            // feature/orb_extractor.cc:270-271: size from the ORIGINAL image and the float scale widened to double
+            const double sc = scale[l];
+            g.w = (int)std::round(width * 1.0 / sc);
+            g.h = (int)std::round(height * 1.0 / sc);
+        }
+        LPS_ARG(g.w > 0 && g.h > 0, "pyramid level collapses to zero size");
+        g.pitch = (int)align_up(g.w, 64);
+        g.frame_stride = align_up((size_t)g.pitch * g.h, 256);
+        g.scale = scale[l];
+        g.kp_size = (float)(unsigned)(kPatch * scale[l]);  // orb_extractor.cc:383
+        g.quota = quota[l];
+        off_img[l] = plan.take(g.frame_stride * max_batch);
+        off_blur[l] = plan.take(g.frame_stride * max_batch);
+        if (l > 0) {
+            const LevelGeom& p = lv[l - 1];
+            if (p.w == g.w && p.h == g.h) g.mode = 2;
+            else if (p.w == 2 * g.w && p.h == 2 * g.h) g.mode = 1;
+            else g.mode = 0;
+            make_axis_tab(p.w, g.w, true, xofs[l], xc[l]);
+            make_axis_tab(p.h, g.h, false, yofs[l], yc[l]);
+            off_xo[l] = plan.take(xofs[l].size() * 4);
+            off_xc[l] = plan.take(xc[l].size() * 4);
+            off_yo[l] = plan.take(yofs[l].size() * 4);
+            off_yc[l] = plan.take(yc[l].size() * 4);
+        }
+        // ---- FAST cell grid, feature/orb_extractor.cc:293-332 ----
+        g.cell_begin = (int)cells.size();
+        g.cell_cols = g.cell_rows = 0;
+        if (g.w > 2 * kBorder && g.h > 2 * kBorder) {
+            const unsigned max_bx = g.w - kBorder, max_by = g.h - kBorder;
+            const unsigned width_b = max_bx - kBorder, height_b = max_by - kBorder;
+            const unsigned ncols = width_b / kCell + 1, nrows = height_b / kCell + 1;  // std::ceil of an integer division
+            int rows_inc = 0, cols_inc = 0;
+            for (unsigned i = 0; i < nrows; ++i) {
+                const unsigned y0 = kBorder + i * kCell;
+                if (max_by - kOverlap <= y0) continue;
+                ++rows_inc;
+                const unsigned y1 = std::min(y0 + kCell + kOverlap, max_by);
+                cols_inc = 0;
+                for (unsigned j = 0; j < ncols; ++j) {
+                    const unsigned x0 = kBorder + j * kCell;
+                    if (max_bx - kOverlap <= x0) continue;
+                    ++cols_inc;
+                    const unsigned x1 = std::min(x0 + kCell + kOverlap, max_bx);
+                    CellDesc c;
+                    c.level = (short)l;
+                    c.x0 = (short)x0;
+                    c.y0 = (short)y0;
+                    c.cw = (short)(x1 - x0);
+                    c.ch = (short)(y1 - y0);
+                    c.j = (short)j;
+                    c.i = (short)i;
+                    cells.push_back(c);
+                }
+            }
+            g.cell_cols = cols_inc;
+            g.cell_rows = rows_inc;
+            // ---- quadtree initial grid, feature/orb_extractor.cc:483-503 ----
+            const int min_x = kBorder, max_x = (int)max_bx, min_y = kBorder, max_y = (int)max_by;
+            const double ratio = (double)(max_x - min_x) / (max_y - min_y);
+            if (ratio > 1) {
+                g.nx = (int)std::round(ratio);
+                g.ny = 1;
+                g.dx = (double)(max_x - min_x) / g.nx;
+                g.dy = max_y - min_y;
+            }
+            else {
+                g.nx = 1;
+                g.ny = (int)std::round(1 / ratio);
+                g.dx = max_x - min_y;  // sic, orb_extractor.cc:500
+                g.dy = (double)(max_y - min_y) / g.ny;
+            }
+            int e = std::max((int)std::ceil(g.dx), (int)std::ceil(g.dy)) + 1;
+            int d = 0;
+            while (e > 1) {
+                e = (e + 1) >> 1;
+                ++d;
+            }
+            g.depth = d + 1;
+            g.rbits = 0;
+            while ((1 << g.rbits) < g.nx * g.ny) ++g.rbits;
+            LPS_ARG(2 * g.depth + g.rbits <= 31 && g.nx * g.ny <= 1024, "image aspect ratio / size outside the quadtree key range");
+        }
+        else {
+            g.nx = g.ny = 1;
+            g.dx = g.dy = 1.0;
+            g.depth = 1;
+        }
+        const int ncl = g.cell_cols * g.cell_rows;
+        g.cand_begin = cand_total;
+        g.cand_cap = ncl * kCellSlots;
+        cand_total += g.cand_cap;
+        g.node_begin = node_total;
+        g.node_cap = 4 * std::max<int>((int)g.quota, g.nx * g.ny) + 8;
+        node_total += g.node_cap;
+        g.sel_begin = sel_total;
+        g.sel_cap = g.node_cap;
+        sel_total += g.sel_cap;
+    }
+    num_cells = (int)cells.size();
+    cand_stride = align_up(std::max(cand_total, 1), 64);
+    node_stride = align_up(node_total, 64);
+    sel_stride = align_up(sel_total, 64);
+    out_cap = (uint32_t)std::min<size_t>((size_t)sel_total * max_batch, 0x7FFFFFFFu);
+
+    const size_t B = max_batch;
+    const size_t off_lv = plan.take(sizeof(LevelGeom) * kMaxLevels);
+    const size_t off_cells = plan.take(sizeof(CellDesc) * std::max(num_cells, 1));
+    const size_t off_counts = plan.take(4 * B * std::max(num_cells, 1));
+    const size_t off_slots = plan.take(4 * B * std::max(num_cells, 1) * kCellSlots);
+    const size_t off_cbase = plan.take(4 * B * std::max(num_cells, 1));
+    const size_t off_cxy = plan.take(4 * B * cand_stride);
+    const size_t off_csc = plan.take(1 * B * cand_stride);
+    size_t off_keys[2], off_vals[2], off_node[2][3], off_tmp[8];
+    for (int i = 0; i < 2; ++i) off_keys[i] = plan.take(4 * B * cand_stride);
+    for (int i = 0; i < 2; ++i) off_vals[i] = plan.take(4 * B * cand_stride);
+    for (int i = 0; i < 2; ++i)
+        for (int k = 0; k < 3; ++k) off_node[i][k] = plan.take(4 * B * node_stride);
+    for (int i = 0; i < 8; ++i) off_tmp[i] = plan.take(4 * B * node_stride);
+    const size_t off_ccount = plan.take(4 * B * L);
+    const size_t off_sxy = plan.take(4 * B * sel_stride);
+    const size_t off_ssc = plan.take(1 * B * sel_stride);
+    const size_t off_scount = plan.take(4 * B * L);
+    const size_t off_loff = plan.take(4 * (B * L + 1));
+    const size_t off_foff = plan.take(4 * (B + 2));
+    const size_t off_kp = plan.take(sizeof(lpslam_keypoint) * (size_t)out_cap);
+    const size_t off_desc = plan.take(32 * (size_t)out_cap);
+    const size_t off_mask = plan.take((size_t)width * height);
+    const size_t off_rmask = plan.take((size_t)width * height);
+
+    LPS_CUDA(cudaMalloc(&arena, plan.off));
+    arena_bytes = plan.off;
+    for (int l = 0; l < L; ++l) {
+        lv[l].img = arena + off_img[l];
+        lv[l].blur = arena + off_blur[l];
+        if (l > 0) {
+            lv[l].xofs = (const int*)(arena + off_xo[l]);
+            lv[l].xcoef = (const short2*)(arena + off_xc[l]);
+            lv[l].yofs = (const int*)(arena + off_yo[l]);
+            lv[l].ycoef = (const short2*)(arena + off_yc[l]);
+            LPS_CUDA(cudaMemcpyAsync(arena + off_xo[l], xofs[l].data(), xofs[l].size() * 4, cudaMemcpyHostToDevice, stream));
+            LPS_CUDA(cudaMemcpyAsync(arena + off_xc[l], xc[l].data(), xc[l].size() * 4, cudaMemcpyHostToDevice, stream));
+            LPS_CUDA(cudaMemcpyAsync(arena + off_yo[l], yofs[l].data(), yofs[l].size() * 4, cudaMemcpyHostToDevice, stream));
+            LPS_CUDA(cudaMemcpyAsync(arena + off_yc[l], yc[l].data(), yc[l].size() * 4, cudaMemcpyHostToDevice, stream));
+        }
+    }
+    lv_dev = (LevelGeom*)(arena + off_lv);
+    cells_dev = (CellDesc*)(arena + off_cells);
+    LPS_CUDA(cudaMemcpyAsync(lv_dev, lv, sizeof(LevelGeom) * kMaxLevels, cudaMemcpyHostToDevice, stream));
+    if (num_cells)
+        LPS_CUDA(cudaMemcpyAsync(cells_dev, cells.data(), sizeof(CellDesc) * num_cells, cudaMemcpyHostToDevice, stream));
+    cell_counts = (uint32_t*)(arena + off_counts);
+    cell_slots = (uint32_t*)(arena + off_slots);
+
+    tree = TreeArgs{};
+    tree.lv = lv_dev;
+    tree.num_levels = L;
+    tree.num_cells = num_cells;
+    tree.cells = cells_dev;
+    tree.cell_counts = cell_counts;
+    tree.cell_slots = cell_slots;
+    tree.cand_xy = (uint32_t*)(arena + off_cxy);
+    tree.cand_stride = cand_stride;
+    tree.cand_sc = arena + off_csc;
+    for (int i = 0; i < 2; ++i) {
+        tree.keys[i] = (uint32_t*)(arena + off_keys[i]);
+        tree.vals[i] = (uint32_t*)(arena + off_vals[i]);
+        for (int k = 0; k < 3; ++k) tree.node[i][k] = (int*)(arena + off_node[i][k]);
+    }
+    for (int i = 0; i < 8; ++i) tree.tmp[i] = (int*)(arena + off_tmp[i]);
+    tree.cell_base = (uint32_t*)(arena + off_cbase);
+    tree.cell_stride = std::max(num_cells, 1);
+    tree.node_stride = node_stride;
+    tree.cand_count = (uint32_t*)(arena + off_ccount);
+    tree.sel_xys = (uint32_t*)(arena + off_sxy);
+    tree.sel_stride = sel_stride;
+    tree.sel_sc = arena + off_ssc;
+    tree.sel_count = (uint32_t*)(arena + off_scount);
+
+    desc = DescribeArgs{};
+    desc.lv = lv_dev;
+    desc.num_levels = L;
+    desc.sel_xys = tree.sel_xys;
+    desc.sel_stride = sel_stride;
+    desc.sel_sc = tree.sel_sc;
+    desc.sel_count = tree.sel_count;
+    desc.level_off = (uint32_t*)(arena + off_loff);
+    desc.frame_off = (uint32_t*)(arena + off_foff);
+    desc.overflow = desc.frame_off + B + 1;
+    desc.kp = (lpslam_keypoint*)(arena + off_kp);
+    desc.desc = arena + off_desc;
+    desc.out_cap = out_cap;
+    mask_dev = arena + off_mask;
+    rect_mask_dev = arena + off_rmask;
+    LPS_CUDA(cudaStreamSynchronize(stream));  // the host-side tables go out of scope
+    w = width;
+    h = height;
+    return LPSLAM_OK;
+}
+
+int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, size_t mask_pitch) {
+    const int L = (int)num_levels;
+    const int B = (int)n_frames;
+    int e = 0;
+    auto mark = [&]() {
+        if (timing) cudaEventRecord(ev[e++], stream);
+    };
+    mark();  // 0: start of pyramid
+    for (int l = 1; l < L; ++l) launch_resize(lv[l - 1], lv[l], B, stream);
+    mark();  // 1
+    FastArgs fa;
+    fa.lv = lv_dev;
+    fa.cells = cells_dev;
+    fa.num_cells = num_cells;
+    fa.batch = B;
+    fa.ini_thr = ini_thr;
+    fa.min_thr = min_thr;
+    fa.cell_counts = cell_counts;
+    fa.cell_slots = cell_slots;
+    fa.mask = mask_ptr;
+    fa.mask_pitch = mask_pitch;
+    launch_fast(fa, stream);
+    mark();  // 2
+    tree.batch = B;
+    launch_quadtree(tree, lv, stream);
+    mark();  // 3
+    launch_blur(lv_dev, lv, L, B, stream);
+    mark();  // 4
+    desc.batch = B;
+    LPS_CUDA(cudaMemsetAsync(desc.overflow, 0, 4, stream));
+    launch_offsets(desc, stream);
+    launch_describe(desc, stream);
+    mark();  // 5
+    LPS_CUDA(cudaGetLastError());
+    last_batch = n_frames;
+    has_result = true;
+    return LPSLAM_OK;
+}

@@ -1,0 +1,57 @@
+// Extractor context: host-side state behind lpslam_orb_ctx (one per reference orb_extractor instance).
+#pragma once
+
+#include "common.cuh"
+
+#include <array>
+
+struct lpslam_orb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint32_t max_batch = 1;
+
+    // feature/orb_params.h
+    uint32_t max_kpts = 2000, ini_max_kpts = 2000, num_levels = 8, ini_thr = 20, min_thr = 7;
+    float scale_factor = 1.2f;
+    std::vector<std::array<float, 4>> mask_rects;
+    // feature/orb_params.cc:38-72, orb_extractor.cc:208-226
+    std::vector<float> scale, inv_scale, sigma_sq, inv_sigma_sq;
+    std::vector<unsigned> quota;
+
+    // geometry of the configured image size
+    int w = 0, h = 0;
+    lps::LevelGeom lv[lps::kMaxLevels];
+    lps::LevelGeom* lv_dev = nullptr;
+    std::vector<lps::CellDesc> cells;
+    lps::CellDesc* cells_dev = nullptr;
+    int num_cells = 0;
+    size_t cand_stride = 0, node_stride = 0, sel_stride = 0;
+    uint32_t out_cap = 0;  // packed output rows available on the device
+
+    // device arena (one allocation per geometry)
+    uint8_t* arena = nullptr;
+    size_t arena_bytes = 0;
+    uint32_t* cell_counts = nullptr;
+    uint32_t* cell_slots = nullptr;
+    lps::TreeArgs tree{};
+    lps::DescribeArgs desc{};
+    uint8_t* mask_dev = nullptr;      // user image mask (uploaded per call)
+    uint8_t* rect_mask_dev = nullptr; // rectangle mask, drawn once (orb_extractor.cc:85-88,251-264)
+    bool rect_mask_ready = false;
+    int* tables_dev = nullptr;
+
+    // pinned host staging
+    uint32_t* h_frame_off = nullptr;  // max_batch + 2 (last = overflow flag)
+    uint32_t last_batch = 0;
+    bool has_result = false;
+
+    // optional stage timing
+    bool timing = false;
+    cudaEvent_t ev[8] = {};
+    float stage_ms[7] = {};
+
+    void initialize_tables();
+    int configure(int width, int height);
+    void release_geometry();
+    int run_pipeline(uint32_t n_frames, const uint8_t* mask_dev_ptr, size_t mask_pitch);
+};

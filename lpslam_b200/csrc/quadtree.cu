@@ -1,0 +1,470 @@
+// K3 — quadtree keypoint distribution. Replaces distribute_keypoints_via_tree / initialize_nodes / assign_child_nodes /
+// find_keypoints_with_max_response (feature/orb_extractor.cc:401-593) and orb_extractor_node::divide_node
+// (feature/orb_extractor_node.cc:6-50). One block per (level, frame).
+//
+// The reference walks a std::list of nodes that each own a vector of keypoints. Here the geometry is factored out:
+//   * a node's four children are fixed by its rectangle alone (half extents round up), so the quadrant a keypoint falls
+//     into at every depth is a pure function of its coordinates and its initial node. Each candidate gets a PATH KEY
+//     (initial-node index, then 2 bits per depth: bit0 = right, bit1 = bottom). After one radix sort by that key every
+//     node of every depth is a contiguous range of the sorted array, and "divide" is three binary searches.
+//   * the list discipline (children pushed to the FRONT in order 0..3, parent erased in place, single-keypoint children
+//     not flagged leaf and therefore re-divided, the pool of dividable nodes sorted by (count, address) descending) is
+//     replayed on index arrays with prefix sums: a breadth pass maps node i / child j to position T-1-(P_i + j).
+//   * the address tie-break of the pool sort (orb_extractor.cc:408,455) is pinned as "later created first", which for
+//     nodes created in one pass is "nearer the list front first": a stable sort by count over list order.
+//   * the winner of a node is its first keypoint with the strictly greatest response in candidate order
+//     (orb_extractor.cc:571-593) = arg max of (score, -candidate index).
+#include "common.cuh"
+
+namespace lps {
+
+namespace {
+
+constexpr int QT = 1024;           // threads per block
+constexpr int RADIX_BITS = 4;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int F_LEAF = 1 << 8, F_POOL = 1 << 9, DEPTH_MASK = 0xFF;
+
+struct Scan {
+    unsigned long long* warp_tot;  // 32 entries of shared memory
+    // exclusive block scan of a 64-bit value (three 21-bit fields are packed by the callers); returns the total to all
+    __device__ __forceinline__ unsigned long long excl(unsigned long long v, unsigned long long& total) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        unsigned long long inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const unsigned long long w = warp_tot[lane];
+            unsigned long long wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            warp_tot[lane] = wi - w;
+            if (lane == 31) warp_tot[32] = wi;
+        }
+        __syncthreads();
+        const unsigned long long res = warp_tot[warp] + inc - v;
+        total = warp_tot[32];
+        __syncthreads();
+        return res;
+    }
+};
+
+__device__ __forceinline__ int lower_digit(const uint32_t* __restrict__ keys, int lo, int hi, int shift, unsigned q) {
+    // first index in [lo, hi) whose 2-bit digit at `shift` is >= q (the range shares all higher bits)
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (((keys[mid] >> shift) & 3u) < q) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ void split_node(const uint32_t* __restrict__ keys, int lo, int hi, int d, int D, int (&b)[5]) {
+    b[0] = lo;
+    b[4] = hi;
+    if (hi - lo <= 1 || d >= D) {  // a single keypoint always yields exactly one non-empty child
+        b[1] = b[2] = b[3] = hi;
+        return;
+    }
+    const int shift = 2 * (D - d - 1);
+    b[2] = lower_digit(keys, lo, hi, shift, 2);
+    b[1] = lower_digit(keys, lo, b[2], shift, 1);
+    b[3] = lower_digit(keys, b[2], hi, shift, 3);
+}
+
+__device__ __forceinline__ uint32_t path_key(int x, int y, const LevelGeom& lv) {
+    // initial node: orb_extractor.cc:532-539 (float coordinate / double extent, truncated)
+    const unsigned ix = (unsigned)((double)(float)x / lv.dx);
+    const unsigned iy = (unsigned)((double)(float)y / lv.dy);
+    int bx = (int)(lv.dx * ix), ex = (int)(lv.dx * (ix + 1));
+    int by = (int)(lv.dy * iy), ey = (int)(lv.dy * (iy + 1));
+    uint32_t key = ix + iy * lv.nx;
+    for (int d = 0; d < lv.depth; ++d) {
+        const int hx = (ex - bx + 1) >> 1, hy = (ey - by + 1) >> 1;  // cvCeil(extent / 2.0)
+        uint32_t q = 0;
+        if (bx + hx <= x) { q |= 1; bx += hx; } else { ex = bx + hx; }
+        if (by + hy <= y) { q |= 2; by += hy; } else { ey = by + hy; }
+        key = (key << 2) | q;
+    }
+    return key;
+}
+
+__device__ __forceinline__ int pad_idx(int lin) { return lin + (lin >> 5); }
+
+__global__ void __launch_bounds__(QT, 1) k_quadtree(TreeArgs a) {
+    extern __shared__ uint32_t s_dyn[];  // RADIX * QT counters (padded) during the sort, pool counts afterwards
+    __shared__ unsigned long long s_scan[33];
+    __shared__ int s_i[4];
+
+    const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const LevelGeom lv = a.lv[level];
+    Scan scan{s_scan};
+
+    const uint32_t* cell_counts = a.cell_counts + (size_t)frame * a.num_cells + lv.cell_begin;
+    const uint32_t* cell_slots = a.cell_slots + ((size_t)frame * a.num_cells + lv.cell_begin) * kCellSlots;
+    uint32_t* cell_base = a.cell_base + (size_t)frame * a.cell_stride + lv.cell_begin;
+    uint32_t* cand_xy = a.cand_xy + (size_t)frame * a.cand_stride + lv.cand_begin;
+    uint8_t* cand_sc = a.cand_sc + (size_t)frame * a.cand_stride + lv.cand_begin;
+    uint32_t* keys[2] = {a.keys[0] + (size_t)frame * a.cand_stride + lv.cand_begin,
+                         a.keys[1] + (size_t)frame * a.cand_stride + lv.cand_begin};
+    uint32_t* vals[2] = {a.vals[0] + (size_t)frame * a.cand_stride + lv.cand_begin,
+                         a.vals[1] + (size_t)frame * a.cand_stride + lv.cand_begin};
+    const size_t nofs = (size_t)frame * a.node_stride + lv.node_begin;
+    int* n_lo[2] = {a.node[0][0] + nofs, a.node[1][0] + nofs};
+    int* n_hi[2] = {a.node[0][1] + nofs, a.node[1][1] + nofs};
+    int* n_meta[2] = {a.node[0][2] + nofs, a.node[1][2] + nofs};
+    int* t_b1 = a.tmp[0] + nofs;
+    int* t_b2 = a.tmp[1] + nofs;
+    int* t_b3 = a.tmp[2] + nofs;
+    int* t_p = a.tmp[3] + nofs;   // prefix of non-empty children
+    int* t_l = a.tmp[4] + nofs;   // prefix of carried-over nodes
+    int* t_pl = a.tmp[5] + nofs;  // pool: node index in list order
+    int* t_srt = a.tmp[6] + nofs; // pool sorted: node index
+    int* t_proc = a.tmp[7] + nofs;
+    uint32_t* sel_xy = a.sel_xys + (size_t)frame * a.sel_stride + lv.sel_begin;
+    uint8_t* sel_sc = a.sel_sc + (size_t)frame * a.sel_stride + lv.sel_begin;
+    uint32_t* sel_count = a.sel_count + (size_t)frame * a.num_levels + level;
+    uint32_t* cand_count = a.cand_count + (size_t)frame * a.num_levels + level;
+
+    // ------------------------------------------------------------------ A. candidate list in reference order
+    const int ncl = lv.cell_cols * lv.cell_rows;
+    int N = 0;
+    for (int base = 0; base < ncl; base += QT) {
+        const int i = base + tid;
+        const unsigned v = i < ncl ? cell_counts[i] : 0u;
+        unsigned long long tot;
+        const unsigned ex = (unsigned)scan.excl(v, tot);
+        if (i < ncl) cell_base[i] = N + ex;
+        N += (int)tot;
+    }
+    if (tid == 0) *cand_count = (uint32_t)N;
+    if (N == 0) {
+        if (tid == 0) *sel_count = 0;
+        return;
+    }
+    __syncthreads();
+    for (int ci = warp; ci < ncl; ci += QT / 32) {
+        const CellDesc c = a.cells[lv.cell_begin + ci];
+        const int cnt = (int)cell_counts[ci], base = (int)cell_base[ci];
+        const uint32_t* slots = cell_slots + (size_t)ci * kCellSlots;
+        for (int k = lane; k < cnt; k += 32) {
+            const uint32_t s = slots[k];
+            // window-local + 3 (ring margin) + 64 * cell index, relative to the 19-px border (orb_extractor.cc:362-363)
+            const int x = (int)(s & 255u) + 3 + kCell * c.j;
+            const int y = (int)((s >> 8) & 255u) + 3 + kCell * c.i;
+            cand_xy[base + k] = (uint32_t)x | ((uint32_t)y << 16);
+            cand_sc[base + k] = (uint8_t)(s >> 16);
+            keys[0][base + k] = path_key(x, y, lv);
+            vals[0][base + k] = (uint32_t)(base + k);
+        }
+    }
+    __syncthreads();
+
+    // ------------------------------------------------------------------ B. LSD radix sort by path key (stable)
+    const int keybits = 2 * lv.depth + lv.rbits;
+    const int chunk = (N + QT - 1) / QT;
+    const int my_lo = min(N, tid * chunk), my_hi = min(N, (tid + 1) * chunk);
+    int cur = 0;
+    for (int shift = 0; shift < keybits; shift += RADIX_BITS) {
+        const uint32_t* __restrict__ kin = keys[cur];
+        const uint32_t* __restrict__ vin = vals[cur];
+        uint32_t* __restrict__ kout = keys[cur ^ 1];
+        uint32_t* __restrict__ vout = vals[cur ^ 1];
+#pragma unroll
+        for (int d = 0; d < RADIX; ++d) s_dyn[pad_idx(d * QT + tid)] = 0;
+        for (int k = my_lo; k < my_hi; ++k) s_dyn[pad_idx((int)((kin[k] >> shift) & (RADIX - 1)) * QT + tid)]++;
+        __syncthreads();
+        // exclusive scan over (digit-major, thread-minor): thread j owns linear entries [16 j, 16 j + 16)
+        unsigned loc[RADIX];
+        unsigned sum = 0;
+#pragma unroll
+        for (int e = 0; e < RADIX; ++e) {
+            loc[e] = s_dyn[pad_idx(tid * RADIX + e)];
+            sum += loc[e];
+        }
+        unsigned long long tot;
+        unsigned run = (unsigned)scan.excl(sum, tot);
+#pragma unroll
+        for (int e = 0; e < RADIX; ++e) {
+            s_dyn[pad_idx(tid * RADIX + e)] = run;
+            run += loc[e];
+        }
+        __syncthreads();
+        for (int k = my_lo; k < my_hi; ++k) {
+            const uint32_t key = kin[k];
+            const int slot = pad_idx((int)((key >> shift) & (RADIX - 1)) * QT + tid);
+            const unsigned pos = s_dyn[slot];
+            s_dyn[slot] = pos + 1;
+            kout[pos] = key;
+            vout[pos] = vin[k];
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    const uint32_t* __restrict__ skey = keys[cur];
+    const uint32_t* __restrict__ sval = vals[cur];
+    const int D = lv.depth;
+
+    // ------------------------------------------------------------------ C. initial nodes (orb_extractor.cc:480-553)
+    int m = 0;  // list length, identical in every thread
+    int nb = 0; // node buffer holding the current list
+    {
+        const int ninit = lv.nx * lv.ny;
+        for (int base = 0; base < ninit; base += QT) {
+            const int r = base + tid;
+            int lo = 0, hi = 0;
+            if (r < ninit) {
+                int l = 0, h = N;
+                const int sh = 2 * D;
+                while (l < h) { const int mid = (l + h) >> 1; if ((skey[mid] >> sh) < (unsigned)r) l = mid + 1; else h = mid; }
+                lo = l;
+                h = N;
+                while (l < h) { const int mid = (l + h) >> 1; if ((skey[mid] >> sh) <= (unsigned)r) l = mid + 1; else h = mid; }
+                hi = l;
+            }
+            unsigned long long tot;
+            const int pos = m + (int)scan.excl(hi > lo ? 1u : 0u, tot);
+            if (hi > lo) {
+                n_lo[nb][pos] = lo;
+                n_hi[nb][pos] = hi;
+                n_meta[nb][pos] = (hi - lo == 1) ? F_LEAF : 0;
+            }
+            m += (int)tot;
+        }
+        __syncthreads();
+    }
+
+    const int quota = (int)lv.quota;
+    bool filled = false;
+
+    // ------------------------------------------------------------------ D. breadth passes (orb_extractor.cc:414-445)
+    while (true) {
+        const int prev = m;
+        int T = 0, NL = 0, POOL = 0;
+        for (int base = 0; base < m; base += QT) {
+            const int i = base + tid;
+            unsigned long long v = 0;
+            if (i < m) {
+                const int meta = n_meta[nb][i];
+                if (meta & F_LEAF) {
+                    v = 1ull << 21;
+                }
+                else {
+                    int b[5];
+                    split_node(skey, n_lo[nb][i], n_hi[nb][i], meta & DEPTH_MASK, D, b);
+                    t_b1[i] = b[1];
+                    t_b2[i] = b[2];
+                    t_b3[i] = b[3];
+                    unsigned k = 0, pc = 0;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        k += (b[q + 1] - b[q]) > 0;
+                        pc += (b[q + 1] - b[q]) > 1;
+                    }
+                    v = (unsigned long long)k | ((unsigned long long)pc << 42);
+                }
+            }
+            unsigned long long tot;
+            const unsigned long long ex = scan.excl(v, tot);
+            if (i < m) {
+                t_p[i] = T + (int)(ex & 0x1FFFFF);
+                t_l[i] = NL + (int)((ex >> 21) & 0x1FFFFF);
+            }
+            T += (int)(tot & 0x1FFFFF);
+            NL += (int)((tot >> 21) & 0x1FFFFF);
+            POOL += (int)(tot >> 42);
+        }
+        const int ob = nb ^ 1;
+        for (int i = tid; i < m; i += QT) {
+            const int meta = n_meta[nb][i];
+            const int lo = n_lo[nb][i], hi = n_hi[nb][i];
+            if (meta & F_LEAF) {
+                const int dst = T + t_l[i];
+                n_lo[ob][dst] = lo;
+                n_hi[ob][dst] = hi;
+                n_meta[ob][dst] = meta & ~F_POOL;
+            }
+            else {
+                const int b[5] = {lo, t_b1[i], t_b2[i], t_b3[i], hi};
+                int f = t_p[i];
+                const int dchild = min((meta & DEPTH_MASK) + 1, DEPTH_MASK);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = b[q + 1] - b[q];
+                    if (c > 0) {
+                        const int dst = T - 1 - f;
+                        ++f;
+                        n_lo[ob][dst] = b[q];
+                        n_hi[ob][dst] = b[q + 1];
+                        n_meta[ob][dst] = dchild | (c > 1 ? F_POOL : 0);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        nb = ob;
+        m = T + NL;
+        if (quota <= m || m == prev) {
+            filled = true;
+            break;
+        }
+        if (quota < m + POOL) break;
+    }
+
+    // ------------------------------------------------------------------ E. fullest-first splitting (orb_extractor.cc:447-475)
+    int* s_cnt = reinterpret_cast<int*>(s_dyn);  // pool counts cached in shared memory when they fit
+    const int s_cnt_cap = RADIX * QT;
+    while (!filled) {
+        const int prev = m;
+        // pool = nodes created by the previous pass / round holding more than one keypoint, in list order
+        int np = 0;
+        for (int base = 0; base < m; base += QT) {
+            const int i = base + tid;
+            const bool in_pool = i < m && (n_meta[nb][i] & F_POOL);
+            unsigned long long tot;
+            const int pos = np + (int)scan.excl(in_pool ? 1u : 0u, tot);
+            if (in_pool) {
+                t_pl[pos] = i;
+                if (pos < s_cnt_cap) s_cnt[pos] = n_hi[nb][i] - n_lo[nb][i];
+            }
+            if (i < m) t_proc[i] = -1;
+            np += (int)tot;
+        }
+        __syncthreads();
+        if (np == 0) break;  // nothing dividable: the list cannot grow (size == prev_size)
+        // stable rank sort by count descending (ties: list order = later-created first)
+        for (int x = tid; x < np; x += QT) {
+            const int nx_i = t_pl[x];
+            const int cx = n_hi[nb][nx_i] - n_lo[nb][nx_i];
+            int rank = 0;
+            for (int y = 0; y < np; ++y) {
+                int cy;
+                if (y < s_cnt_cap) cy = s_cnt[y];
+                else { const int ny_i = t_pl[y]; cy = n_hi[nb][ny_i] - n_lo[nb][ny_i]; }
+                rank += (cy > cx) || (cy == cx && y < x);
+            }
+            t_srt[rank] = nx_i;
+        }
+        __syncthreads();
+        // split every pool node (in sorted order), find where the list reaches the quota
+        if (tid == 0) { s_i[0] = 0x7FFFFFFF; }
+        __syncthreads();
+        int K = 0;
+        for (int base = 0; base < np; base += QT) {
+            const int s = base + tid;
+            unsigned k = 0;
+            if (s < np) {
+                const int i = t_srt[s];
+                int b[5];
+                split_node(skey, n_lo[nb][i], n_hi[nb][i], n_meta[nb][i] & DEPTH_MASK, D, b);
+                t_b1[s] = b[1];
+                t_b2[s] = b[2];
+                t_b3[s] = b[3];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) k += (b[q + 1] - b[q]) > 0;
+            }
+            unsigned long long tot;
+            const int exk = (int)scan.excl(k, tot);
+            if (s < np) {
+                t_p[s] = K + exk;
+                // list size after this node has been replaced by its children
+                const int size_after = m + (K + exk + (int)k) - (s + 1);
+                if (quota <= size_after) atomicMin(&s_i[0], s);
+            }
+            K += (int)tot;
+        }
+        __syncthreads();
+        int sstar = s_i[0];
+        if (sstar == 0x7FFFFFFF) sstar = np - 1;
+        else filled = true;
+        __syncthreads();
+        if (tid == 0) {
+            const int i = t_srt[sstar];
+            int b[5] = {n_lo[nb][i], t_b1[sstar], t_b2[sstar], t_b3[sstar], n_hi[nb][i]};
+            int k = 0;
+            for (int q = 0; q < 4; ++q) k += (b[q + 1] - b[q]) > 0;
+            s_i[1] = t_p[sstar] + k;
+        }
+        for (int s = tid; s <= sstar; s += QT) t_proc[t_srt[s]] = s;
+        __syncthreads();
+        const int Tp = s_i[1];
+        const int ob = nb ^ 1;
+        // children of the processed nodes, pushed to the front in processing order
+        for (int s = tid; s <= sstar; s += QT) {
+            const int i = t_srt[s];
+            const int b[5] = {n_lo[nb][i], t_b1[s], t_b2[s], t_b3[s], n_hi[nb][i]};
+            const int dchild = min((n_meta[nb][i] & DEPTH_MASK) + 1, DEPTH_MASK);
+            int f = t_p[s];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = b[q + 1] - b[q];
+                if (c > 0) {
+                    const int dst = Tp - 1 - f;
+                    ++f;
+                    n_lo[ob][dst] = b[q];
+                    n_hi[ob][dst] = b[q + 1];
+                    n_meta[ob][dst] = dchild | (c > 1 ? F_POOL : 0);
+                }
+            }
+        }
+        // every other node keeps its relative order behind them; the pool flag is per round
+        int R = 0;
+        for (int base = 0; base < m; base += QT) {
+            const int i = base + tid;
+            const bool keep = i < m && t_proc[i] < 0;
+            unsigned long long tot;
+            const int pos = Tp + R + (int)scan.excl(keep ? 1u : 0u, tot);
+            if (keep) {
+                n_lo[ob][pos] = n_lo[nb][i];
+                n_hi[ob][pos] = n_hi[nb][i];
+                n_meta[ob][pos] = n_meta[nb][i] & ~F_POOL;
+            }
+            R += (int)tot;
+        }
+        __syncthreads();
+        nb = ob;
+        m = Tp + R;
+        if (filled || quota <= m || m == prev) break;
+    }
+
+    // ------------------------------------------------------------------ F. winner per node, list order
+    for (int i = warp; i < m; i += QT / 32) {
+        const int lo = n_lo[nb][i], hi = n_hi[nb][i];
+        unsigned long long best = 0;
+        for (int k = lo + lane; k < hi; k += 32) {
+            const uint32_t o = sval[k];
+            const unsigned long long cand = ((unsigned long long)cand_sc[o] << 32) | (0xFFFFFFFFu - o);
+            best = cand > best ? cand : best;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long t = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+            best = t > best ? t : best;
+        }
+        if (lane == 0) {
+            const uint32_t o = 0xFFFFFFFFu - (uint32_t)(best & 0xFFFFFFFFu);
+            sel_xy[i] = cand_xy[o];
+            sel_sc[i] = (uint8_t)(best >> 32);
+        }
+    }
+    if (tid == 0) *sel_count = (uint32_t)m;
+}
+
+}  // namespace
+
+void launch_quadtree(const TreeArgs& a, const LevelGeom* lv_host, cudaStream_t st) {
+    (void)lv_host;
+    const size_t smem = (size_t)(RADIX * QT + (RADIX * QT) / 32 + 32) * sizeof(uint32_t);
+    cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_quadtree<<<dim3(a.num_levels, a.batch), QT, smem, st>>>(a);
+}
+
+}  // namespace lps

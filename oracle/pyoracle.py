@@ -26,7 +26,7 @@ def build(force=False):
     """Compile the port (always) and the reference build (when /root/reference is present)."""
     if force or not os.path.exists(PORT_SO):
         subprocess.check_call(["make", "-s", "-f", os.path.join(HERE, "Makefile"), PORT_SO])
-    if os.path.isdir("/root/reference/external/openvslam/src/openvslam/feature"):
+    if os.path.isdir("/root/reference/external/openvslam/src/openvslam/feature") and os.path.exists(os.path.join(HERE, "ref_glue.cc")):
         subprocess.check_call(["make", "-s", "-f", os.path.join(HERE, "Makefile"), "ref"])
 
 

@@ -1,0 +1,77 @@
+"""Pin the oracle's restated OpenCV primitives bit-for-bit against cv2 (the third-party arithmetic the reference calls:
+cv::resize orb_extractor.cc:273, cv::GaussianBlur :136, cv::FAST :343-350, cv::fastAtan2 :633).
+cv2 is only present in the build container; on the GPU box these tests skip and the committed golden vectors
+(tests/golden, test_oracle_golden.py) carry the pin."""
+import numpy as np
+import pytest
+
+from lpslam_b200.synth import noise_image, synth_image
+
+cv2 = pytest.importorskip("cv2")
+
+SIZES = [(480, 640), (720, 1280), (333, 444), (97, 131)]
+
+
+def level_sizes(h, w, n=8, sf=1.2):
+    s = np.float32(1.0)
+    out = [(h, w)]
+    for _ in range(1, n):
+        s = np.float32(sf) * s
+        out.append((int(round(h * 1.0 / float(s))), int(round(w * 1.0 / float(s)))))
+    return out
+
+
+@pytest.mark.parametrize("h,w", SIZES)
+def test_resize_chain(oracle, h, w):
+    img = synth_image(h, w, 1)
+    prev = img
+    for (lh, lw) in level_sizes(h, w)[1:]:
+        if lh < 8 or lw < 8:
+            break
+        want = cv2.resize(prev, (lw, lh), interpolation=cv2.INTER_LINEAR)
+        got = oracle.resize(prev, lw, lh)
+        assert np.array_equal(want, got), (lh, lw, int((want != got).sum()))
+        prev = want
+
+
+def test_resize_half(oracle):
+    img = noise_image(200, 320, 3)
+    want = cv2.resize(img, (160, 100), interpolation=cv2.INTER_LINEAR)
+    assert np.array_equal(want, oracle.resize(img, 160, 100))
+
+
+@pytest.mark.parametrize("h,w", SIZES + [(40, 64), (7, 9)])
+def test_blur(oracle, h, w):
+    for img in (synth_image(h, w, 2), noise_image(h, w, 4)):
+        want = cv2.GaussianBlur(img, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        assert np.array_equal(want, oracle.blur(img))
+
+
+@pytest.mark.parametrize("thr", [20, 7])
+def test_fast(oracle, thr):
+    det = cv2.FastFeatureDetector_create(threshold=thr, nonmaxSuppression=True, type=cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    for img in (synth_image(240, 320, 5), noise_image(70, 70, 6), noise_image(33, 70, 7), synth_image(70, 70, 8)):
+        kps = det.detect(img)
+        want = np.array([[int(k.pt[0]), int(k.pt[1]), int(k.response)] for k in kps], np.int32).reshape(-1, 3)
+        got = oracle.fast(img, thr)
+        assert np.array_equal(want, got)
+
+
+def test_fast_atan2(oracle):
+    rng = np.random.default_rng(9)
+    ys = rng.integers(-3_000_000, 3_000_000, 5000)
+    xs = rng.integers(-3_000_000, 3_000_000, 5000)
+    for y, x in list(zip(ys, xs)) + [(0, 0), (0, 5), (5, 0), (-5, 0), (0, -5), (7, 7), (-7, 7)]:
+        want = cv2.fastAtan2(float(y), float(x))
+        got = oracle.atan2(float(y), float(x))
+        assert np.float32(want) == np.float32(got), (y, x, want, got)
+
+
+def test_rect_fill_matches_line_aa(oracle):
+    m = np.full((100, 120), 255, np.uint8)
+    cv2.rectangle(m, (12, 20), (60, 71), 0, -1, cv2.LINE_AA)
+    # LINE_AA leaves a non-zero anti-aliased fringe; the reference only tests mask == 0 (orb_extractor.cc:281-283),
+    # so the set of zero pixels is what matters: exactly the inclusive rectangle.
+    want = np.zeros((100, 120), bool)
+    want[20:72, 12:61] = True
+    assert np.array_equal(m == 0, want)
