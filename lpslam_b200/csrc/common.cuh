@@ -65,7 +65,7 @@ struct LevelGeom {
     int cand_cap;       // cell_count * kCellSlots
     int node_begin, node_cap;
     int sel_begin, sel_cap;
-    float scale, kp_size;
+    float scale, inv_scale, kp_size;
 };
 
 struct CellDesc {
@@ -136,6 +136,23 @@ struct DescribeArgs {
     uint32_t* overflow;          // set to needed count when out_cap is too small
 };
 void launch_offsets(const DescribeArgs& a, cudaStream_t st);
+
+// match::stereo on device-resident extraction results: frame 2p = left eye, frame 2p + 1 = right eye of pair p
+struct StereoArgs {
+    const LevelGeom* lv;
+    int num_levels, n_pairs;
+    const lpslam_keypoint* kp;   // packed keypoints of all 2 * n_pairs frames
+    const uint8_t* desc;
+    const uint32_t* frame_off;   // [2 * n_pairs + 1]
+    uint32_t max_rows;           // rows in the packed arrays that may be touched
+    uint2* rec;                  // per packed row: (min_r | max_r << 16, octave) of the keypoint as a RIGHT candidate
+    float* x_right;              // per packed row (left-eye rows are meaningful), -1 = no match
+    float* depth;
+    int* corr;                   // best SAD as int, -1 = no match
+    float focal_x_baseline, true_baseline;
+    int rows0;                   // level-0 image rows
+};
+void launch_stereo(const StereoArgs& a, cudaStream_t st);
 void launch_describe(const DescribeArgs& a, cudaStream_t st);
 
 }  // namespace lps

@@ -138,6 +138,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
         g.pitch = (int)align_up(g.w, 64);
         g.frame_stride = align_up((size_t)g.pitch * g.h, 256);
         g.scale = scale[l];
+        g.inv_scale = inv_scale[l];
         g.kp_size = (float)(unsigned)(kPatch * scale[l]);  // orb_extractor.cc:383
         g.quota = quota[l];
         off_img[l] = plan.take(g.frame_stride * max_batch);
