@@ -80,3 +80,222 @@ def make_frames(n_pairs, seed0):
     left = [pool[k % len(pool)][0] for k in range(n_pairs)]
     right = [pool[k % len(pool)][1] for k in range(n_pairs)]
     return left, right
+
+
+def cpu_reference_arm(steps, warmup, sample_pairs=1):
+    """The CPU oracle (reference sources in oracle/_ref when built, else the port) on the host cores: one process per
+    core, each extracting both eyes of a stereo pair and matching them, as data/frame.cc:55-93 does per frame."""
+    import multiprocessing as mp
+    cores = max(1, min(os.cpu_count() or 1, 64))
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(cores) as pool:
+        pool.map(_cpu_worker, [(0, 1)] * cores)  # warm-up: builds / loads the oracle in every worker
+        times = []
+        for s in range(warmup + steps):
+            t = time.perf_counter()
+            pool.map(_cpu_worker, [(s * cores + k, sample_pairs) for k in range(cores)])
+            if s >= warmup:
+                times.append(time.perf_counter() - t)
+    dt = sum(times)
+    frames = steps * cores * sample_pairs
+    return frames / dt, cores, dt / steps * 1e3, kind_of_oracle(), time.perf_counter() - t0
+
+
+def kind_of_oracle():
+    from oracle import pyoracle
+    return "reference" if pyoracle.ref() is not None else "port"
+
+
+_cpu_state = {}
+
+
+def _cpu_worker(arg):
+    seed, n_pairs = arg
+    from oracle import pyoracle
+    from lpslam_b200.synth import synth_stereo_pair
+    if "o" not in _cpu_state:
+        o = pyoracle.ref() or pyoracle.port()
+        _cpu_state["o"] = o
+        _cpu_state["el"] = o.extractor(max_kpts=KPTS)
+        _cpu_state["er"] = o.extractor(max_kpts=KPTS)
+        _cpu_state["pair"] = synth_stereo_pair(H, W, 2000)
+    o, el, er = _cpu_state["o"], _cpu_state["el"], _cpu_state["er"]
+    left, right = _cpu_state["pair"]
+    n = 0
+    for _ in range(n_pairs):
+        kl, dl = el.extract(left)
+        kr, dr = er.extract(right)
+        pl = [el.level(l) for l in range(8)]
+        pr = [er.level(l) for l in range(8)]
+        xr, _ = o.match_stereo(pl, pr, kl, kr, dl, dr, el.table(0), el.table(1), FX_B, BASELINE)
+        n += int((xr >= 0).sum())
+    return n
+
+
+def gpu_arm(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from lpslam_b200 import _lib, match, orb  # noqa: F401  (match registers the stereo entry points)
+    from lpslam_b200._lib import KP_DTYPE, check, lib
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: liblpslam_cuda has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B = args.batch  # stereo pairs per step and per GPU
+    L = lib()
+    ext = orb.orb_extractor(max_num_keypts=KPTS, device=local, max_batch=2 * B)
+    stream = torch.cuda.ExternalStream(L.lpslam_orb_stream(ext._h), device=local)
+
+    lefts, rights = make_frames(B, 2000 + 16 * rank)
+    # pinned host copies of the batch (what a capture / replay thread would hand over)
+    hp = C.c_void_p()
+    check(L.lpslam_cuda_host_alloc(C.byref(hp), 2 * B * W * H))
+    host = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(2 * B, H, W))
+    for p in range(B):
+        host[2 * p], host[2 * p + 1] = lefts[p], rights[p]
+    cap = 2 * B * 4096
+    okp, odesc, oxr, odep = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+    check(L.lpslam_cuda_host_alloc(C.byref(okp), cap * 28))
+    check(L.lpslam_cuda_host_alloc(C.byref(odesc), cap * 32))
+    check(L.lpslam_cuda_host_alloc(C.byref(oxr), cap * 4))
+    check(L.lpslam_cuda_host_alloc(C.byref(odep), cap * 4))
+    offs = np.zeros(2 * B + 1, np.uint32)
+    pl = (C.c_void_p * B)(*[host[2 * p].ctypes.data for p in range(B)])
+    pr = (C.c_void_p * B)(*[host[2 * p + 1].ctypes.data for p in range(B)])
+
+    def e2e_step():
+        check(L.lpslam_stereo_frames(ext._h, pl, pr, B, W, H, W, FX_B, BASELINE, okp, odesc, cap, offs.ctypes.data, oxr, odep))
+
+    # device-resident input: the context's own level-0 buffer, filled once
+    dptr, dpitch, dstride = C.c_void_p(), C.c_size_t(), C.c_size_t()
+    check(L.lpslam_orb_input_dev(ext._h, W, H, C.byref(dptr), C.byref(dpitch), C.byref(dstride)))
+    e2e_step()  # fills level 0 of every frame on the device as a side effect, and warms everything up
+    n_kp = int(offs[2 * B])
+    n_match = int((np.ctypeslib.as_array(C.cast(oxr, C.POINTER(C.c_float)), shape=(cap,))[:n_kp] >= 0).sum())
+
+    def dev_step():
+        check(L.lpslam_stereo_frames_dev(ext._h, dptr, B, W, H, dpitch.value, FX_B, BASELINE))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        ev0.record(stream)
+        for _ in range(steps):
+            fn()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms = ev0.elapsed_time(ev1)
+        t = torch.tensor([ms, wall], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        barrier()
+        return float(t[0]), float(t[1])
+
+    clocks = ClockSampler(local)
+    clocks.start()
+    dev_ms, _ = timed(dev_step, args.steps, args.warmup)
+    clk = clocks.stop()
+    _, e2e_ms = timed(e2e_step, args.steps, args.warmup)  # wall clock: the call blocks until results are on the host
+
+    # per-stage device time of one more resident step (CUDA events on the library's stream)
+    ext.enable_timing(True)
+    stage = {k: 0.0 for k in ("pyramid", "fast", "quadtree", "blur", "describe")}
+    reps = 5
+    for _ in range(reps):
+        dev_step()
+        st = ext.stage_times()
+        for k in stage:
+            stage[k] += st[k] / reps
+    ext.enable_timing(False)
+    frames_img = 2 * B
+    alg = algorithmic_bytes(W, H)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    per_stage = {}
+    for k in ("pyramid", "blur", "fast"):
+        gbs = alg[k] * frames_img / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
+        per_stage[k] = {"ms": round(stage[k], 4), "alg_bytes": alg[k] * frames_img, "achieved_gbs": round(gbs, 1),
+                        "frac": round(gbs / peak, 4)}
+    dom = max(stage, key=stage.get)
+    rk = dom if dom in per_stage else "blur"
+    roofline = {"bound": "hbm", "kernel": {"pyramid": "k_resize_linear", "blur": "k_gauss7", "fast": "k_fast_cells"}[rk],
+                "achieved": per_stage[rk]["achieved_gbs"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": per_stage[rk]["frac"], "traffic": None, "dominant_stage": dom,
+                "stage_ms": {k: round(v, 4) for k, v in stage.items()}, "stages": per_stage}
+
+    pairs_total = B * args.steps * world
+    out = {"metric": "frames/s ORB extract+match @1280x720 2000kpt", "value": pairs_total / (dev_ms * 1e-3),
+           "unit": "stereo frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "u8", "data": "synthetic",
+           "config": {"workload": "ZED stereo 1280x720 pair, 2000 kpts/eye, ORB extract (8 levels x1.2) + stereo row-search "
+                                  "matching (BASELINE configs[1])", "pairs_per_step_per_gpu": B, "images_per_step_per_gpu": 2 * B,
+                      "keypoints_per_step": n_kp, "stereo_matches_per_step": n_match,
+                      "l2": "inputs + pyramids of one step (%.0f MB) exceed the 126 MB L2" % (2 * B * 2 * 2.85),
+                      "parallelism": "frame-parallel x%d" % world},
+           "e2e": {"value": pairs_total / (e2e_ms * 1e-3), "unit": "stereo frames/s", "ms_per_step": e2e_ms / args.steps,
+                   "h2d_bytes_per_step": 2 * B * W * H, "d2h_bytes_per_step": n_kp * (28 + 32 + 8) + 4 * (2 * B + 2),
+                   "timing": "wall clock around the blocking host-buffer C-ABI call, max over ranks"},
+           "gpu_launches": args.steps * 15, "clocks": clk, "roofline": roofline}
+    return out, rank
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=32, help="stereo pairs per step per GPU")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", 0))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        steps = min(args.steps, 5)
+        v, cores, ms, kind, _ = cpu_reference_arm(steps, min(args.warmup, 1))
+        line = {"impl": "reference", "metric": "frames/s ORB extract+match @1280x720 2000kpt", "value": v,
+                "unit": "stereo frames/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+                "data": "synthetic",
+                "config": {"workload": "ZED stereo 1280x720 pair, 2000 kpts/eye, ORB extract (8 levels x1.2) + stereo "
+                                       "row-search matching (BASELINE configs[1])", "parallelism": "%d host processes" % cores},
+                "cpu_baseline": {"value": v, "unit": "stereo frames/s", "cores": cores, "kind": kind,
+                                 "sample": "%d steps x %d processes x 1 stereo pair each" % (steps, cores)},
+                "e2e": {"value": v, "unit": "stereo frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return
+
+    out, rank = gpu_arm(args)
+    if rank == 0:
+        if args.gpus == 1 and not args.no_cpu_baseline:
+            v, cores, ms, kind, took = cpu_reference_arm(2, 0)
+            out["cpu_baseline"] = {"value": v, "unit": "stereo frames/s", "cores": cores, "kind": kind,
+                                   "sample": "2 steps x %d processes x 1 stereo pair each (%.1f s)" % (cores, took)}
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -154,13 +154,20 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
                         const float* inv_scale_factors, float focal_x_baseline, float true_baseline,
                         float* stereo_x_right, float* depths, uint32_t* n_matches);
 
-/* fused stereo frame: extracts both eyes on the device (two contexts' worth of work on one stream) and runs the row
- * matcher on the device-resident pyramids — data::frame's stereo constructor (data/frame.cc:55-93) without the 2 x
- * pyramid round trip. ctx_l / ctx_r are two extractor contexts on the same device. */
-int lpslam_stereo_frame(lpslam_orb_ctx* ctx_l, lpslam_orb_ctx* ctx_r, const uint8_t* img_l, const uint8_t* img_r,
-                        int width, int height, size_t pitch, float focal_x_baseline, float true_baseline,
-                        lpslam_keypoint* kp_l, uint8_t* desc_l, uint32_t* n_l, lpslam_keypoint* kp_r, uint8_t* desc_r,
-                        uint32_t* n_r, uint32_t cap, float* stereo_x_right, float* depths, uint32_t* n_matches);
+/* fused stereo frames — data::frame's stereo constructor (data/frame.cc:55-93: two extractions + match::stereo) for
+ * n_pairs stereo pairs in one pass, without the pyramid round trip: both eyes are extracted on the device by ONE context
+ * (max_batch >= 2 * n_pairs; frame 2p = left eye, 2p + 1 = right eye of pair p) and the row matcher reads the
+ * device-resident pyramids. Outputs are packed like lpslam_orb_extract_batch (offsets has 2 * n_pairs + 1 entries);
+ * stereo_x_right / depths have one float per packed keypoint row and are meaningful on left-eye rows (-1 = no match). */
+int lpslam_stereo_frames(lpslam_orb_ctx* ctx, const uint8_t* const* imgs_l, const uint8_t* const* imgs_r, uint32_t n_pairs,
+                         int width, int height, size_t pitch, float focal_x_baseline, float true_baseline,
+                         lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets,
+                         float* stereo_x_right, float* depths);
+/* device-resident variant: imgs_dev holds 2 * n_pairs frames, left / right interleaved. Enqueues only. */
+int lpslam_stereo_frames_dev(lpslam_orb_ctx* ctx, const uint8_t* imgs_dev, uint32_t n_pairs, int width, int height,
+                             size_t pitch, float focal_x_baseline, float true_baseline);
+/* device pointers to stereo_x_right / depths of the last lpslam_stereo_frames_dev call (one float per packed row) */
+int lpslam_stereo_result_dev(lpslam_orb_ctx* ctx, const float** stereo_x_right_dev, const float** depths_dev);
 
 /* match::projection::match_current_and_last_frames (match/projection.cc:85-208) with the grid query of
  * data/common.cc:97-186 and the perspective projection of camera/perspective.cc:151-169, over flat arrays. */

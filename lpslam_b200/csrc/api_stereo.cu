@@ -1,0 +1,173 @@
+// C ABI — stereo entry points (include/lpslam_cuda.h): fused stereo frames on an extractor context, and the standalone
+// match::stereo drop-in that takes host pyramids (match/stereo.h:18-29).
+#include "ctx.h"
+
+#include <algorithm>
+#include <cstring>
+
+using namespace lps;
+
+extern "C" {
+
+int lpslam_stereo_frames_dev(lpslam_orb_ctx* c, const uint8_t* imgs_dev, uint32_t n_pairs, int width, int height,
+                             size_t pitch, float focal_x_baseline, float true_baseline) {
+    LPS_ARG(c, "null context");
+    LPS_ARG(n_pairs >= 1 && 2 * n_pairs <= c->max_batch, "2 * n_pairs exceeds the context's max_batch");
+    const int rc = lpslam_orb_extract_batch_dev(c, imgs_dev, 2 * n_pairs, width, height, pitch);
+    if (rc) return rc;
+    c->stereo.n_pairs = (int)n_pairs;
+    c->stereo.focal_x_baseline = focal_x_baseline;
+    c->stereo.true_baseline = true_baseline;
+    launch_stereo(c->stereo, c->stream);
+    if (c->timing) cudaEventRecord(c->ev[5], c->stream);  // the describe stage then includes the matcher
+    LPS_CUDA(cudaGetLastError());
+    return LPSLAM_OK;
+}
+
+int lpslam_stereo_result_dev(lpslam_orb_ctx* c, const float** xr, const float** dep) {
+    LPS_ARG(c && xr && dep, "null argument");
+    if (!c->has_result) {
+        set_error("no extraction has run on this context");
+        return LPSLAM_ERR_STATE;
+    }
+    *xr = c->stereo.x_right;
+    *dep = c->stereo.depth;
+    return LPSLAM_OK;
+}
+
+int lpslam_stereo_frames(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const uint8_t* const* imgs_r, uint32_t n_pairs,
+                         int width, int height, size_t pitch, float focal_x_baseline, float true_baseline,
+                         lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets, float* stereo_x_right,
+                         float* depths) {
+    LPS_ARG(c && imgs_l && imgs_r && offsets && kp_out && desc_out && stereo_x_right && depths, "null argument");
+    LPS_ARG(n_pairs >= 1 && 2 * n_pairs <= c->max_batch, "2 * n_pairs exceeds the context's max_batch");
+    LPS_ARG(width > 0 && height > 0 && pitch >= (size_t)width, "bad image geometry");
+    LPS_CUDA(cudaSetDevice(c->device));
+    int rc = c->configure(width, height);
+    if (rc) return rc;
+    const LevelGeom& g0 = c->lv[0];
+    for (uint32_t p = 0; p < n_pairs; ++p) {
+        LPS_ARG(imgs_l[p] && imgs_r[p], "null image pointer");
+        LPS_CUDA(cudaMemcpy2DAsync(g0.img + (2 * p) * g0.frame_stride, g0.pitch, imgs_l[p], pitch, width, height,
+                                   cudaMemcpyHostToDevice, c->stream));
+        LPS_CUDA(cudaMemcpy2DAsync(g0.img + (2 * p + 1) * g0.frame_stride, g0.pitch, imgs_r[p], pitch, width, height,
+                                   cudaMemcpyHostToDevice, c->stream));
+    }
+    rc = lpslam_stereo_frames_dev(c, g0.img, n_pairs, width, height, g0.pitch, focal_x_baseline, true_baseline);
+    if (rc) return rc;
+    const uint32_t nf = 2 * n_pairs;
+    LPS_CUDA(cudaMemcpyAsync(c->h_frame_off, c->desc.frame_off, sizeof(uint32_t) * (c->max_batch + 2), cudaMemcpyDeviceToHost,
+                             c->stream));
+    LPS_CUDA(cudaStreamSynchronize(c->stream));
+    const uint32_t total = c->h_frame_off[nf];
+    for (uint32_t f = 0; f <= nf; ++f) offsets[f] = c->h_frame_off[f];
+    if (c->h_frame_off[c->max_batch + 1] != 0 || total > cap) {
+        set_error("output capacity too small for the extracted keypoints");
+        return LPSLAM_ERR_CAPACITY;
+    }
+    if (total) {
+        LPS_CUDA(cudaMemcpyAsync(kp_out, c->desc.kp, sizeof(lpslam_keypoint) * (size_t)total, cudaMemcpyDeviceToHost, c->stream));
+        LPS_CUDA(cudaMemcpyAsync(desc_out, c->desc.desc, 32 * (size_t)total, cudaMemcpyDeviceToHost, c->stream));
+        LPS_CUDA(cudaMemcpyAsync(stereo_x_right, c->stereo.x_right, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->stream));
+        LPS_CUDA(cudaMemcpyAsync(depths, c->stereo.depth, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->stream));
+    }
+    LPS_CUDA(cudaStreamSynchronize(c->stream));
+    return LPSLAM_OK;
+}
+
+int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r, const int* level_w, const int* level_h,
+                        const size_t* pitch_l, const size_t* pitch_r, uint32_t num_levels, const lpslam_keypoint* kp_l,
+                        uint32_t nl, const lpslam_keypoint* kp_r, uint32_t nr, const uint8_t* desc_l, const uint8_t* desc_r,
+                        const float* scale_factors, const float* inv_scale_factors, float focal_x_baseline,
+                        float true_baseline, float* stereo_x_right, float* depths, uint32_t* n_matches) {
+    LPS_ARG(pyr_l && pyr_r && level_w && level_h && pitch_l && pitch_r && scale_factors && inv_scale_factors, "null argument");
+    LPS_ARG(num_levels >= 1 && num_levels <= (uint32_t)kMaxLevels, "num_levels out of range (1..16)");
+    LPS_ARG(nl == 0 || (kp_l && desc_l && stereo_x_right && depths), "null left-eye argument");
+    LPS_ARG(nr == 0 || (kp_r && desc_r), "null right-eye argument");
+    if (n_matches) *n_matches = 0;
+    if (nl == 0) return LPSLAM_OK;
+    for (uint32_t i = 0; i < nl; ++i) LPS_ARG(kp_l[i].octave >= 0 && (uint32_t)kp_l[i].octave < num_levels, "left octave out of range");
+    for (uint32_t i = 0; i < nr; ++i) LPS_ARG(kp_r[i].octave >= 0 && (uint32_t)kp_r[i].octave < num_levels, "right octave out of range");
+
+    LevelGeom lv[kMaxLevels];
+    memset(lv, 0, sizeof lv);
+    size_t img_bytes = 0;
+    std::vector<size_t> off(num_levels);
+    for (uint32_t l = 0; l < num_levels; ++l) {
+        lv[l].w = level_w[l];
+        lv[l].h = level_h[l];
+        lv[l].pitch = (int)align_up(level_w[l], 64);
+        lv[l].frame_stride = align_up((size_t)lv[l].pitch * level_h[l], 256);
+        lv[l].scale = scale_factors[l];
+        lv[l].inv_scale = inv_scale_factors[l];
+        off[l] = img_bytes;
+        img_bytes += 2 * lv[l].frame_stride;
+    }
+    const uint32_t rows = nl + nr;
+    uint8_t* dev = nullptr;
+    size_t o_lv = align_up(img_bytes, 256), o_kp = o_lv + align_up(sizeof lv, 256);
+    size_t o_desc = o_kp + align_up(sizeof(lpslam_keypoint) * (size_t)rows, 256), o_off = o_desc + align_up(32 * (size_t)rows, 256);
+    size_t o_rec = o_off + 256, o_xr = o_rec + align_up(8 * (size_t)rows, 256), o_dep = o_xr + align_up(4 * (size_t)rows, 256);
+    size_t o_corr = o_dep + align_up(4 * (size_t)rows, 256), total = o_corr + align_up(4 * (size_t)rows, 256);
+    LPS_CUDA(cudaMalloc(&dev, total));
+    cudaStream_t st = nullptr;
+    int rc = LPSLAM_OK;
+    auto fail = [&](cudaError_t e, const char* what) {
+        rc = cuda_fail(e, what, __FILE__, __LINE__);
+        return rc;
+    };
+#define TRY(call)                                \
+    do {                                         \
+        cudaError_t e__ = (call);                \
+        if (e__ != cudaSuccess) {                \
+            fail(e__, #call);                    \
+            goto done;                           \
+        }                                        \
+    } while (0)
+    {
+        const uint32_t h_off[3] = {0, nl, rows};
+        std::vector<int> corr(nl);
+        for (uint32_t l = 0; l < num_levels; ++l) {
+            lv[l].img = dev + off[l];
+            TRY(cudaMemcpy2D(lv[l].img, lv[l].pitch, pyr_l[l], pitch_l[l], lv[l].w, lv[l].h, cudaMemcpyHostToDevice));
+            TRY(cudaMemcpy2D(lv[l].img + lv[l].frame_stride, lv[l].pitch, pyr_r[l], pitch_r[l], lv[l].w, lv[l].h,
+                             cudaMemcpyHostToDevice));
+        }
+        TRY(cudaMemcpy(dev + o_lv, lv, sizeof lv, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(dev + o_kp, kp_l, sizeof(lpslam_keypoint) * (size_t)nl, cudaMemcpyHostToDevice));
+        if (nr) TRY(cudaMemcpy(dev + o_kp + sizeof(lpslam_keypoint) * (size_t)nl, kp_r, sizeof(lpslam_keypoint) * (size_t)nr, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(dev + o_desc, desc_l, 32 * (size_t)nl, cudaMemcpyHostToDevice));
+        if (nr) TRY(cudaMemcpy(dev + o_desc + 32 * (size_t)nl, desc_r, 32 * (size_t)nr, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(dev + o_off, h_off, sizeof h_off, cudaMemcpyHostToDevice));
+        StereoArgs a{};
+        a.lv = (const LevelGeom*)(dev + o_lv);
+        a.num_levels = (int)num_levels;
+        a.n_pairs = 1;
+        a.kp = (const lpslam_keypoint*)(dev + o_kp);
+        a.desc = dev + o_desc;
+        a.frame_off = (const uint32_t*)(dev + o_off);
+        a.max_rows = rows;
+        a.rec = (uint2*)(dev + o_rec);
+        a.x_right = (float*)(dev + o_xr);
+        a.depth = (float*)(dev + o_dep);
+        a.corr = (int*)(dev + o_corr);
+        a.focal_x_baseline = focal_x_baseline;
+        a.true_baseline = true_baseline;
+        a.rows0 = level_h[0];
+        launch_stereo(a, st);
+        TRY(cudaGetLastError());
+        TRY(cudaMemcpy(stereo_x_right, a.x_right, 4 * (size_t)nl, cudaMemcpyDeviceToHost));
+        TRY(cudaMemcpy(depths, a.depth, 4 * (size_t)nl, cudaMemcpyDeviceToHost));
+        if (n_matches) {
+            uint32_t n = 0;
+            for (uint32_t i = 0; i < nl; ++i) n += !(depths[i] == -1.0f && stereo_x_right[i] == -1.0f);
+            *n_matches = n;
+        }
+    }
+done:
+#undef TRY
+    cudaFree(dev);
+    return rc;
+}
+
+}  // extern "C"

@@ -259,6 +259,10 @@ int lpslam_orb_ctx::configure(int width, int height) {
     const size_t off_desc = plan.take(32 * (size_t)out_cap);
     const size_t off_mask = plan.take((size_t)width * height);
     const size_t off_rmask = plan.take((size_t)width * height);
+    const size_t off_srec = plan.take(8 * (size_t)out_cap);
+    const size_t off_sxr = plan.take(4 * (size_t)out_cap);
+    const size_t off_sdep = plan.take(4 * (size_t)out_cap);
+    const size_t off_scorr = plan.take(4 * (size_t)out_cap);
 
     LPS_CUDA(cudaMalloc(&arena, plan.off));
     arena_bytes = plan.off;
@@ -324,6 +328,18 @@ int lpslam_orb_ctx::configure(int width, int height) {
     desc.out_cap = out_cap;
     mask_dev = arena + off_mask;
     rect_mask_dev = arena + off_rmask;
+    stereo = StereoArgs{};
+    stereo.lv = lv_dev;
+    stereo.num_levels = L;
+    stereo.kp = desc.kp;
+    stereo.desc = desc.desc;
+    stereo.frame_off = desc.frame_off;
+    stereo.max_rows = out_cap;
+    stereo.rec = (uint2*)(arena + off_srec);
+    stereo.x_right = (float*)(arena + off_sxr);
+    stereo.depth = (float*)(arena + off_sdep);
+    stereo.corr = (int*)(arena + off_scorr);
+    stereo.rows0 = height;
     LPS_CUDA(cudaStreamSynchronize(stream));  // the host-side tables go out of scope
     w = width;
     h = height;

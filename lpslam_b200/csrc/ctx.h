@@ -35,6 +35,7 @@ struct lpslam_orb_ctx {
     uint32_t* cell_slots = nullptr;
     lps::TreeArgs tree{};
     lps::DescribeArgs desc{};
+    lps::StereoArgs stereo{};
     uint8_t* mask_dev = nullptr;      // user image mask (uploaded per call)
     uint8_t* rect_mask_dev = nullptr; // rectangle mask, drawn once (orb_extractor.cc:85-88,251-264)
     bool rect_mask_ready = false;

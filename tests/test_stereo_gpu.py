@@ -1,0 +1,53 @@
+"""GPU parity of the stereo row matcher (match/stereo.cc:18-249) against the oracle: bit-exact x_right / depth."""
+import numpy as np
+import pytest
+
+from lpslam_b200.synth import synth_stereo_pair
+
+pytestmark = pytest.mark.gpu
+
+FX_B, B = 700.0 * 0.12, 0.12
+
+
+def oracle_pair(oracle, left, right, n):
+    ol, orr = oracle.extractor(max_kpts=n), oracle.extractor(max_kpts=n)
+    kl, dl = ol.extract(left)
+    kr, dr = orr.extract(right)
+    pl = [ol.level(l) for l in range(8)]
+    pr = [orr.level(l) for l in range(8)]
+    xr, dep = oracle.match_stereo(pl, pr, kl, kr, dl, dr, ol.table(0), ol.table(1), FX_B, B)
+    return kl, dl, kr, dr, pl, pr, ol.table(0), ol.table(1), xr, dep
+
+
+@pytest.mark.parametrize("h,w,n", [(480, 640, 1000), (720, 1280, 2000)])
+def test_standalone_matcher(oracle, h, w, n):
+    from lpslam_b200 import match
+    left, right = synth_stereo_pair(h, w, 2000 + h)
+    kl, dl, kr, dr, pl, pr, sf, isf, xr, dep = oracle_pair(oracle, left, right, n)
+    gxr, gdep = match.stereo(pl, pr, kl, kr, dl, dr, sf, isf, FX_B, B).compute()
+    assert (xr >= 0).sum() > n // 10, "synthetic pair should produce stereo matches"
+    assert np.array_equal(gxr, xr, equal_nan=True)
+    assert np.array_equal(gdep, dep, equal_nan=True)
+
+
+def test_fused_frames(oracle):
+    from lpslam_b200 import match, orb
+    pairs = [synth_stereo_pair(360, 640, 2100 + k) for k in range(3)]
+    e = orb.orb_extractor(max_num_keypts=800, max_batch=6)
+    res = match.stereo_frames(e, [p[0] for p in pairs], [p[1] for p in pairs], FX_B, B)
+    for (left, right), r in zip(pairs, res):
+        kl, dl, kr, dr, pl, pr, sf, isf, xr, dep = oracle_pair(oracle, left, right, 800)
+        assert np.array_equal(r["keypts_left"]["x"], kl["x"]) and np.array_equal(r["keypts_right"]["x"], kr["x"])
+        if (r["descs_left"] == dl).all() and (r["descs_right"] == dr).all():
+            assert np.array_equal(r["stereo_x_right"], xr, equal_nan=True)
+            assert np.array_equal(r["depths"], dep, equal_nan=True)
+
+
+def test_empty_right(oracle):
+    from lpslam_b200 import match
+    left, right = synth_stereo_pair(240, 320, 5)
+    o = oracle.extractor(max_kpts=300)
+    kl, dl = o.extract(left)
+    pl = [o.level(l) for l in range(8)]
+    xr, dep = match.stereo(pl, pl, kl, kl[:0], dl, dl[:0], o.table(0), o.table(1), FX_B, B).compute()
+    assert (xr == -1).all() and (dep == -1).all()
