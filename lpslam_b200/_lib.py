@@ -83,6 +83,10 @@ SIGNATURES = {
 
 def register(name, restype, argtypes):
     SIGNATURES[name] = (restype, argtypes)
+    if _lib is not None:  # library already loaded: bind the late registration now
+        fn = getattr(_lib, name)
+        fn.restype = restype
+        fn.argtypes = argtypes
 
 
 def lib():
