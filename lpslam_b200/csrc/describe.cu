@@ -10,7 +10,8 @@ namespace lps {
 
 namespace {
 
-__constant__ signed char c_pattern[1024] = {
+// rBRIEF pattern in global memory: every lane reads ITS 8 pairs once (lane-divergent constant-bank reads would serialise)
+__device__ const signed char g_pattern[1024] = {
 #include "rbrief_pattern.inc"
 };
 // u_max_ of feature/orb_extractor.cc:228-241 for a half patch of 15
@@ -109,6 +110,15 @@ __global__ void __launch_bounds__(256) k_describe(DescribeArgs a) {
     const int warps_total = gridDim.x * (blockDim.x >> 5);
     const int n_seg = a.batch * a.num_levels;
     const unsigned total = min(a.level_off[n_seg], a.out_cap);
+    float pat[32];  // this lane's 8 point pairs: x0, y0, x1, y1 each
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const char4 q = reinterpret_cast<const char4*>(g_pattern)[lane * 8 + i];
+        pat[4 * i] = (float)q.x;
+        pat[4 * i + 1] = (float)q.y;
+        pat[4 * i + 2] = (float)q.z;
+        pat[4 * i + 3] = (float)q.w;
+    }
     for (unsigned k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < total; k += warps_total) {
         // segment (frame, level) holding packed row k
         int lo = 0, hi = n_seg;
@@ -131,14 +141,20 @@ __global__ void __launch_bounds__(256) k_describe(DescribeArgs a) {
         const int u = lane - kHalfPatch;
         const int au = abs(u);
         if (lane < kPatch) {
-#pragma unroll 1
-            for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-                if (au <= c_umax[abs(v)]) {
-                    const int val = __ldg(c0 + v * pitch + u);
-                    m10 += u * val;
-                    m01 += v * val;
-                }
+            // 31 independent predicated byte loads in flight (rows v = -15..15 of this lane's column)
+            int val[kPatch];
+#pragma unroll
+            for (int i = 0; i < kPatch; ++i) {
+                const int v = i - kHalfPatch;
+                val[i] = (au <= c_umax[v < 0 ? -v : v]) ? (int)__ldg(c0 + v * pitch + u) : 0;
             }
+            int colsum = 0;
+#pragma unroll
+            for (int i = 0; i < kPatch; ++i) {
+                colsum += val[i];
+                m01 += (i - kHalfPatch) * val[i];
+            }
+            m10 = u * colsum;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -155,9 +171,7 @@ __global__ void __launch_bounds__(256) k_describe(DescribeArgs a) {
         unsigned byte = 0;
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
-            const int base = (lane * 8 + b) * 4;
-            const float x0 = (float)c_pattern[base], y0 = (float)c_pattern[base + 1];
-            const float x1 = (float)c_pattern[base + 2], y1 = (float)c_pattern[base + 3];
+            const float x0 = pat[4 * b], y0 = pat[4 * b + 1], x1 = pat[4 * b + 2], y1 = pat[4 * b + 3];
             const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
             const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
             const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));

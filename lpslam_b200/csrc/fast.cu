@@ -43,10 +43,12 @@ __device__ __forceinline__ int arc9_maxmin(const int (&d)[16]) {
 
 __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
     __shared__ __align__(16) uint8_t s_win[WIN][WP];
-    __shared__ uint8_t s_best[kCell + 2][BP];  // [1 + ly][1 + lx], zero apron
+    __shared__ __align__(16) uint8_t s_best[kCell + 2][BP];  // [1 + ly][1 + lx], zero apron
     __shared__ uint32_t s_bits[kCell][2];      // kept-pixel bitmap per interior row
     __shared__ uint32_t s_rowbase[kCell + 1];
     __shared__ int s_total;
+    __shared__ int s_nlist;
+    __shared__ uint16_t s_list[kCell * kCell];
 
     const int cell_id = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
     const CellDesc c = a.cells[cell_id];
@@ -65,50 +67,70 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
     }
 
     const uint8_t* __restrict__ img = lv.img + frame * lv.frame_stride;
-    // ---- stage the window ----
-    for (int idx = tid; idx < WIN * (WP / 4); idx += 256) {
-        const int r = idx / (WP / 4), q = idx % (WP / 4);
-        uint32_t v = 0;
-        if (r < c.ch) {
-            const uint8_t* row = img + (size_t)(c.y0 + r) * lv.pitch + c.x0;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int x = 4 * q + k;
-                if (x < c.cw) v |= (uint32_t)__ldg(row + x) << (8 * k);
-            }
-        }
-        *reinterpret_cast<uint32_t*>(&s_win[r][4 * q]) = v;
+    // ---- stage the window: the 16-byte aligned span [x0 - 3, x0 + 77) of every window row (x0 = 19 + 64 j) ----
+    for (int idx = tid; idx < WIN * (WP / 16); idx += 256) {
+        const int r = idx / (WP / 16), q = idx % (WP / 16);
+        uint4 v = make_uint4(0, 0, 0, 0);
+        const int gx = c.x0 - 3 + 16 * q;
+        if (r < c.ch && gx + 16 <= lv.pitch) v = __ldg(reinterpret_cast<const uint4*>(img + (size_t)(c.y0 + r) * lv.pitch + gx));
+        *reinterpret_cast<uint4*>(&s_win[r][16 * q]) = v;
     }
-    for (int idx = tid; idx < (kCell + 2) * BP; idx += 256) (&s_best[0][0])[idx] = 0;
+    for (int idx = tid; idx < (kCell + 2) * BP / 4; idx += 256) reinterpret_cast<uint32_t*>(&s_best[0][0])[idx] = 0;
+    if (tid == 0) s_nlist = 0;
     __syncthreads();
 
     // ---- best for every interior pixel with a full ring inside the window ----
+    // Pass 1 (cheap, divergent): four compass pixels. An arc of 9 always holds two ADJACENT compass points, so a corner
+    // at threshold t needs such a pair both brighter or both darker than the centre by more than t; everything else
+    // has best <= t and keeps the zero already in s_best. Survivors are compacted into a list so that pass 2 (the
+    // full 16-pixel ring, ~200 integer ops) runs with every lane busy.
     const int vw = c.cw - 6, vh = c.ch - 6;  // valid interior extent (<= 64)
     const int quick_thr = (int)min(a.ini_thr, a.min_thr);
     {
         const int lx = tid & 63;
-        for (int ly = tid >> 6; ly < vh; ly += 4) {
-            if (lx >= vw) continue;
-            const uint8_t* p = &s_win[ly + 3][lx + 3];
+        const int lane_ = tid & 31;
+        for (int ly = tid >> 6; ly < kCell; ly += 4) {
+            bool pass = false;
+            if (lx < vw && ly < vh) {
+                const uint8_t* p = &s_win[ly + 3][lx + 6];
+                const int v = p[0];
+                const int d0 = v - p[3 * WP], d4 = v - p[3], d8 = v - p[-3 * WP], d12 = v - p[-3];
+                const unsigned hi = (d0 > quick_thr) | ((d4 > quick_thr) << 1) | ((d8 > quick_thr) << 2) | ((d12 > quick_thr) << 3);
+                const unsigned lo = (d0 < -quick_thr) | ((d4 < -quick_thr) << 1) | ((d8 < -quick_thr) << 2) | ((d12 < -quick_thr) << 3);
+                // adjacent pairs (0,4) (4,8) (8,12) (12,0): bit i and bit (i+1) mod 4
+                const unsigned hr = ((hi >> 1) | (hi << 3)) & 15u, lr = ((lo >> 1) | (lo << 3)) & 15u;
+                pass = ((hi & hr) | (lo & lr)) != 0;
+            }
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
+            if (m) {
+                int base = 0;
+                if (lane_ == 0) base = atomicAdd(&s_nlist, __popc(m));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (pass) s_list[base + __popc(m & ((1u << lane_) - 1))] = (uint16_t)(ly * 64 + lx);
+            }
+        }
+    }
+    __syncthreads();
+    {
+        const int n = s_nlist;
+        for (int i = tid; i < n; i += 256) {
+            const int id = s_list[i], lx = id & 63, ly = id >> 6;
+            const uint8_t* p = &s_win[ly + 3][lx + 6];
             const int v = p[0];
             int d[16];
             d[0] = v - p[3 * WP];
-            d[8] = v - p[-3 * WP];
-            d[4] = v - p[3];
-            d[12] = v - p[-3];
-            // any arc of 9 holds one pixel of each antipodal pair: both within +-t => best <= t, never a corner
-            const bool flat_v = (abs(d[0]) <= quick_thr) && (abs(d[8]) <= quick_thr);
-            const bool flat_h = (abs(d[4]) <= quick_thr) && (abs(d[12]) <= quick_thr);
-            if (flat_v || flat_h) continue;
             d[1] = v - p[3 * WP + 1];
             d[2] = v - p[2 * WP + 2];
             d[3] = v - p[WP + 3];
+            d[4] = v - p[3];
             d[5] = v - p[-WP + 3];
             d[6] = v - p[-2 * WP + 2];
             d[7] = v - p[-3 * WP + 1];
+            d[8] = v - p[-3 * WP];
             d[9] = v - p[-3 * WP - 1];
             d[10] = v - p[-2 * WP - 2];
             d[11] = v - p[-WP - 3];
+            d[12] = v - p[-3];
             d[13] = v - p[WP - 3];
             d[14] = v - p[2 * WP - 2];
             d[15] = v - p[3 * WP - 1];
@@ -116,8 +138,7 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
 #pragma unroll
             for (int k = 0; k < 16; ++k) d[k] = -d[k];
             const int neg = arc9_maxmin(d);
-            const int best = max(pos, neg);
-            s_best[ly + 1][lx + 1] = (uint8_t)max(best, 0);
+            s_best[ly + 1][lx + 1] = (uint8_t)max(max(pos, neg), 0);
         }
     }
     __syncthreads();
