@@ -48,6 +48,8 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
     __shared__ uint32_t s_rowbase[kCell + 1];
     __shared__ int s_total;
     __shared__ int s_nlist;
+    __shared__ uint32_t s_pass[kCell][2];
+    __shared__ int s_wbase[2 * kCell];
     __shared__ uint16_t s_list[kCell * kCell];
 
     const int cell_id = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
@@ -76,94 +78,141 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
         *reinterpret_cast<uint4*>(&s_win[r][16 * q]) = v;
     }
     for (int idx = tid; idx < (kCell + 2) * BP / 4; idx += 256) reinterpret_cast<uint32_t*>(&s_best[0][0])[idx] = 0;
-    if (tid == 0) s_nlist = 0;
+    if (tid < 2 * kCell) (&s_bits[0][0])[tid] = 0;
     __syncthreads();
 
-    // ---- best for every interior pixel with a full ring inside the window ----
-    // Pass 1 (cheap, divergent): four compass pixels. An arc of 9 always holds two ADJACENT compass points, so a corner
-    // at threshold t needs such a pair both brighter or both darker than the centre by more than t; everything else
-    // has best <= t and keeps the zero already in s_best. Survivors are compacted into a list so that pass 2 (the
-    // full 16-pixel ring, ~200 integer ops) runs with every lane busy.
+    // ---- corner strength, suppression, ordered counts: at ini_fast_thr, then once more at min_fast_thr if the cell is empty ----
+    // Per attempt (threshold T):
+    //   1. compass pre-test, 4 pixels per thread as packed 16-bit lanes: an arc of 9 always holds two ADJACENT compass
+    //      points, so best > T needs max over the 4 adjacent pairs of min(d_i, d_i+1) > T or min of max < -T.
+    //      Survivors go into a bitmap, the bitmap into a compact list.
+    //   2. exact best for listed pixels only, two pixels per thread in 16x2 SIMD (VIMNMX.U16x2), every lane busy.
+    //   3. non-max suppression only around listed pixels with best > T (everything unlisted scores 0).
     const int vw = c.cw - 6, vh = c.ch - 6;  // valid interior extent (<= 64)
-    const int quick_thr = (int)min(a.ini_thr, a.min_thr);
-    {
-        const int lx = tid & 63;
-        const int lane_ = tid & 31;
-        for (int ly = tid >> 6; ly < kCell; ly += 4) {
-            bool pass = false;
-            if (lx < vw && ly < vh) {
-                const uint8_t* p = &s_win[ly + 3][lx + 6];
-                const int v = p[0];
-                const int d0 = v - p[3 * WP], d4 = v - p[3], d8 = v - p[-3 * WP], d12 = v - p[-3];
-                const unsigned hi = (d0 > quick_thr) | ((d4 > quick_thr) << 1) | ((d8 > quick_thr) << 2) | ((d12 > quick_thr) << 3);
-                const unsigned lo = (d0 < -quick_thr) | ((d4 < -quick_thr) << 1) | ((d8 < -quick_thr) << 2) | ((d12 < -quick_thr) << 3);
-                // adjacent pairs (0,4) (4,8) (8,12) (12,0): bit i and bit (i+1) mod 4
-                const unsigned hr = ((hi >> 1) | (hi << 3)) & 15u, lr = ((lo >> 1) | (lo << 3)) & 15u;
-                pass = ((hi & hr) | (lo & lr)) != 0;
-            }
-            const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
-            if (m) {
-                int base = 0;
-                if (lane_ == 0) base = atomicAdd(&s_nlist, __popc(m));
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (pass) s_list[base + __popc(m & ((1u << lane_) - 1))] = (uint16_t)(ly * 64 + lx);
-            }
-        }
-    }
-    __syncthreads();
-    {
-        const int n = s_nlist;
-        for (int i = tid; i < n; i += 256) {
-            const int id = s_list[i], lx = id & 63, ly = id >> 6;
-            const uint8_t* p = &s_win[ly + 3][lx + 6];
-            const int v = p[0];
-            int d[16];
-            d[0] = v - p[3 * WP];
-            d[1] = v - p[3 * WP + 1];
-            d[2] = v - p[2 * WP + 2];
-            d[3] = v - p[WP + 3];
-            d[4] = v - p[3];
-            d[5] = v - p[-WP + 3];
-            d[6] = v - p[-2 * WP + 2];
-            d[7] = v - p[-3 * WP + 1];
-            d[8] = v - p[-3 * WP];
-            d[9] = v - p[-3 * WP - 1];
-            d[10] = v - p[-2 * WP - 2];
-            d[11] = v - p[-WP - 3];
-            d[12] = v - p[-3];
-            d[13] = v - p[WP - 3];
-            d[14] = v - p[2 * WP - 2];
-            d[15] = v - p[3 * WP - 1];
-            const int pos = arc9_maxmin(d);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) d[k] = -d[k];
-            const int neg = arc9_maxmin(d);
-            s_best[ly + 1][lx + 1] = (uint8_t)max(max(pos, neg), 0);
-        }
-    }
-    __syncthreads();
-
-    // ---- suppression at `thr`, retried once at the lower threshold when nothing survives ----
     const int warp = tid >> 5, lane = tid & 31;
     int thr = (int)a.ini_thr;
     int total = 0;
     for (int attempt = 0; attempt < 2; ++attempt) {
-        // warp w handles rows w, w+8, ...; two ballots (column halves) per row
-        for (int ly = warp; ly < kCell; ly += 8) {
+        {   // 1a. pre-test -> s_pass
+            const int w = tid & 15, lx = 4 * w;
+            const uint32_t kC = 0x01000100u;
+            const uint32_t kHi = (uint32_t)(0x7FFF - 256 - thr) * 0x00010001u;   // bit15 set iff half >= 257 + thr
+            const uint32_t kLo = (uint32_t)(0x8000 + 255 - thr) * 0x00010001u;   // bit15 set iff half <= 255 - thr
+            const int nv = vw - lx;
+            const uint32_t vmask = nv >= 4 ? 0xFu : (nv <= 0 ? 0u : ((1u << nv) - 1u));
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const int lx = half * 32 + lane;
-                const uint8_t* b = &s_best[ly + 1][lx + 1];
-                const int best = b[0];
-                bool keep = false;
-                if (best > thr) {
-                    const int s = best - 1;
-                    auto sc = [thr](int v) { return v > thr ? v - 1 : 0; };
-                    keep = s > sc(b[-1]) && s > sc(b[1]) && s > sc(b[-BP - 1]) && s > sc(b[-BP]) && s > sc(b[-BP + 1])
-                           && s > sc(b[BP - 1]) && s > sc(b[BP]) && s > sc(b[BP + 1]);
+            for (int it = 0; it < 4; ++it) {
+                const int ly = (tid >> 4) + 16 * it;
+                uint32_t nib = 0;
+                if (ly < vh && vmask) {
+                    const uint32_t* rc = reinterpret_cast<const uint32_t*>(&s_win[ly + 3][0]) + w;
+                    const uint32_t* rn = reinterpret_cast<const uint32_t*>(&s_win[ly + 6][0]) + w;
+                    const uint32_t* rs = reinterpret_cast<const uint32_t*>(&s_win[ly][0]) + w;
+                    const uint32_t w0 = rc[0], w1 = rc[1], w2 = rc[2], w3 = rc[3];
+                    // pixel lx sits at staged byte lx + 6
+                    const uint32_t C = __funnelshift_r(w1, w2, 16), E = __funnelshift_r(w2, w3, 8), Wt = __funnelshift_r(w0, w1, 24);
+                    const uint32_t N = __funnelshift_r(rn[1], rn[2], 16), S = __funnelshift_r(rs[1], rs[2], 16);
+                    uint32_t f[2];
+#pragma unroll
+                    for (int hf = 0; hf < 2; ++hf) {
+                        const uint32_t sel = hf ? 0x4342u : 0x4140u;
+                        const uint32_t c16 = __byte_perm(C, 0, sel) + kC;
+                        const uint32_t d0 = c16 - __byte_perm(N, 0, sel), d4 = c16 - __byte_perm(E, 0, sel);
+                        const uint32_t d8 = c16 - __byte_perm(S, 0, sel), d12 = c16 - __byte_perm(Wt, 0, sel);
+                        const uint32_t mm = __vmaxu2(__vmaxu2(__vminu2(d0, d4), __vminu2(d4, d8)), __vmaxu2(__vminu2(d8, d12), __vminu2(d12, d0)));
+                        const uint32_t nm = __vminu2(__vminu2(__vmaxu2(d0, d4), __vmaxu2(d4, d8)), __vminu2(__vmaxu2(d8, d12), __vmaxu2(d12, d0)));
+                        f[hf] = ((mm + kHi) | (kLo - nm)) & 0x80008000u;
+                    }
+                    nib = ((f[0] >> 15) & 1u) | ((f[0] >> 30) & 2u) | ((f[1] >> 13) & 4u) | ((f[1] >> 28) & 8u);
+                    nib &= vmask;
                 }
-                const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
-                if (lane == 0) s_bits[ly][half] = m;
+                uint32_t word = nib << (4 * (w & 7));
+                word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
+                word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
+                word |= __shfl_xor_sync(0xFFFFFFFFu, word, 4);
+                if ((w & 7) == 0) s_pass[ly][w >> 3] = word;
+            }
+        }
+        __syncthreads();
+        if (warp == 0) {  // 1b. bitmap -> per-word list offsets
+            const uint32_t* pw = &s_pass[0][0];
+            const int c0 = __popc(pw[4 * lane]), c1 = __popc(pw[4 * lane + 1]), c2 = __popc(pw[4 * lane + 2]), c3 = __popc(pw[4 * lane + 3]);
+            int inc = c0 + c1 + c2 + c3;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            int ex = inc - (c0 + c1 + c2 + c3);
+            s_wbase[4 * lane] = ex;
+            s_wbase[4 * lane + 1] = ex + c0;
+            s_wbase[4 * lane + 2] = ex + c0 + c1;
+            s_wbase[4 * lane + 3] = ex + c0 + c1 + c2;
+            if (lane == 31) s_nlist = inc;
+        }
+        __syncthreads();
+        if (tid < 128) {
+            uint32_t m = (&s_pass[0][0])[tid];
+            int o = s_wbase[tid];
+            const int idbase = (tid >> 1) * 64 + (tid & 1) * 32;
+            while (m) {
+                const int bit = __ffs(m) - 1;
+                m &= m - 1;
+                s_list[o++] = (uint16_t)(idbase + bit);
+            }
+        }
+        __syncthreads();
+        const int n = s_nlist;
+        // 2. exact best, two listed pixels per thread
+        for (int i = tid; 2 * i < n; i += 256) {
+            const int ida = s_list[2 * i], idb = (2 * i + 1 < n) ? s_list[2 * i + 1] : ida;
+            const uint8_t* pa = &s_win[(ida >> 6) + 3][(ida & 63) + 6];
+            const uint8_t* pb = &s_win[(idb >> 6) + 3][(idb & 63) + 6];
+            const uint32_t C = ((uint32_t)pa[0] + 256u) | (((uint32_t)pb[0] + 256u) << 16);
+            uint32_t d[16];
+#define RING(k, off) d[k] = C - ((uint32_t)pa[off] | ((uint32_t)pb[off] << 16))
+            RING(0, 3 * WP);      RING(1, 3 * WP + 1);   RING(2, 2 * WP + 2);   RING(3, WP + 3);
+            RING(4, 3);           RING(5, -WP + 3);      RING(6, -2 * WP + 2);  RING(7, -3 * WP + 1);
+            RING(8, -3 * WP);     RING(9, -3 * WP - 1);  RING(10, -2 * WP - 2); RING(11, -WP - 3);
+            RING(12, -3);         RING(13, WP - 3);      RING(14, 2 * WP - 2);  RING(15, 3 * WP - 1);
+#undef RING
+            uint32_t lo2[16], hi2[16], lo4[16], hi4[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                lo2[k] = __vminu2(d[k], d[(k + 1) & 15]);
+                hi2[k] = __vmaxu2(d[k], d[(k + 1) & 15]);
+            }
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                lo4[k] = __vminu2(lo2[k], lo2[(k + 2) & 15]);
+                hi4[k] = __vmaxu2(hi2[k], hi2[(k + 2) & 15]);
+            }
+            uint32_t A = 0u, Bm = 0xFFFFFFFFu;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const uint32_t lo9 = __vminu2(__vminu2(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
+                const uint32_t hi9 = __vmaxu2(__vmaxu2(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
+                A = __vmaxu2(A, lo9);
+                Bm = __vminu2(Bm, hi9);
+            }
+            // halves hold d + 256: best = max(A - 256, 256 - Bm)
+            const int ba = max((int)(A & 0xFFFFu) - 256, 256 - (int)(Bm & 0xFFFFu));
+            const int bb = max((int)(A >> 16) - 256, 256 - (int)(Bm >> 16));
+            s_best[(ida >> 6) + 1][(ida & 63) + 1] = (uint8_t)max(ba, 0);
+            s_best[(idb >> 6) + 1][(idb & 63) + 1] = (uint8_t)max(bb, 0);
+        }
+        __syncthreads();
+        // 3. suppression around listed pixels
+        for (int i = tid; i < n; i += 256) {
+            const int id = s_list[i], lx = id & 63, ly = id >> 6;
+            const uint8_t* b = &s_best[ly + 1][lx + 1];
+            const int best = b[0];
+            if (best > thr) {
+                const int s = best - 1;
+                auto sc = [thr](int v) { return v > thr ? v - 1 : 0; };
+                const bool keep = s > sc(b[-1]) && s > sc(b[1]) && s > sc(b[-BP - 1]) && s > sc(b[-BP]) && s > sc(b[-BP + 1])
+                                  && s > sc(b[BP - 1]) && s > sc(b[BP]) && s > sc(b[BP + 1]);
+                if (keep) atomicOr(&s_bits[ly][lx >> 5], 1u << (lx & 31));
             }
         }
         __syncthreads();
@@ -190,9 +239,8 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
         }
         __syncthreads();
         total = s_total;
-        if (total > 0 || (int)a.min_thr == thr) break;
-        thr = (int)a.min_thr;
-        __syncthreads();
+        if (total > 0 || (int)a.min_thr >= thr) break;
+        thr = (int)a.min_thr;  // nothing survived: every s_bits word is still zero, s_best is recomputed as a superset
     }
 
     // ---- ordered emission (raster order inside the cell), own-pixel mask applied after the emptiness decision ----
