@@ -184,6 +184,8 @@ int lpslam_match_projection(const lpslam_camera* cam, const double* pose_cw_curr
                             uint32_t n_last, const uint8_t* last_has_lm, const uint8_t* last_outlier,
                             const double* last_pos_w /*n_last x 3*/, const uint8_t* last_lm_desc /*n_last x 32*/,
                             const int32_t* last_octave, const float* last_angle,
+                            const uint8_t* last_lm_has_observation /* nullable = all 1: a matched keypoint blocks later
+                               landmarks only if the landmark it now holds has observations (projection.cc:163-165) */,
                             uint32_t n_curr, const lpslam_keypoint* curr_undist_kp, const uint8_t* curr_desc,
                             const float* curr_x_right, const uint8_t* curr_has_observed_lm, const float* scale_factors,
                             float margin, int check_orientation, int32_t* curr_match_last, uint32_t* n_matches);

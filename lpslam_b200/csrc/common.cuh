@@ -41,6 +41,16 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// bump planner for one-shot device scratch (offsets aligned to 256 bytes)
+struct ArenaBump {
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        const size_t o = off;
+        off = align_up(off + (bytes ? bytes : 1), 256);
+        return o;
+    }
+};
+
 // One pyramid level of a batch: frame f lives at base + f * frame_stride (row pitch `pitch`).
 struct LevelGeom {
     int w, h, pitch;

@@ -1,0 +1,270 @@
+// K7 + K8 — brute-force Hamming matcher with ratio test. Replaces match::robust::brute_force_match (match/robust.cc:215-321)
+// and carries the Hamming primitive of match/base.h:18-63.
+//
+// The reference scans keyframe rows in order; each row takes the best and second-best frame descriptor AMONG THOSE NOT YET
+// CLAIMED by an earlier row (strict <, so the lowest index wins ties), accepts on best <= 50 and ratio * second >= best,
+// and claims its best. The claim makes the loop order-dependent, so the work is split:
+//   k_bf_topk     all rows in parallel: the 4 smallest keys (distance << 16 | index) of every row ignoring claims.
+//                 In key order, "best / second among unclaimed" is simply the first two unclaimed keys.
+//   k_bf_resolve  one warp replays the rows in order against a shared-memory claim bitmap. A row whose top-4 list runs
+//                 out of unclaimed entries before the decision is certain is rescanned exactly by the warp.
+#include "common.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <numeric>
+
+namespace lps {
+
+namespace {
+
+constexpr int K = 4;
+constexpr unsigned HAMMING_DIST_THR_LOW = 50, MAX_HAMMING_DIST = 256;  // match/base.h:13-15
+constexpr uint32_t EMPTY = 0xFFFFFFFFu;
+
+__device__ __forceinline__ unsigned hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x)
+           + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__device__ __forceinline__ void insert4(uint32_t (&t)[K], uint32_t key) {
+    // keep t sorted ascending
+    if (key < t[3]) {
+        t[3] = key;
+        if (t[3] < t[2]) { const uint32_t x = t[2]; t[2] = t[3]; t[3] = x; }
+        if (t[2] < t[1]) { const uint32_t x = t[1]; t[1] = t[2]; t[2] = x; }
+        if (t[1] < t[0]) { const uint32_t x = t[0]; t[0] = t[1]; t[1] = x; }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_bf_topk(const uint8_t* __restrict__ desc_1, uint32_t n1, const uint8_t* __restrict__ desc_2,
+                                                 uint32_t n2, const uint8_t* __restrict__ valid_2, uint4* __restrict__ topk) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= n2) return;
+    if (valid_2 && !valid_2[row]) {
+        if (lane == 0) topk[row] = make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        return;
+    }
+    const uint4* d2 = reinterpret_cast<const uint4*>(desc_2 + (size_t)row * 32);
+    const uint4 a0 = __ldg(d2), a1 = __ldg(d2 + 1);
+    uint32_t t[K] = {EMPTY, EMPTY, EMPTY, EMPTY};
+    for (uint32_t i = lane; i < n1; i += 32) {
+        const uint4* d1 = reinterpret_cast<const uint4*>(desc_1 + (size_t)i * 32);
+        const unsigned d = hamming256(a0, a1, __ldg(d1), __ldg(d1 + 1));
+        insert4(t, (d << 16) | i);
+    }
+    // warp merge: four rounds of "smallest head wins and pops"
+    uint32_t out[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        uint32_t m = t[0];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+        out[r] = m;
+        if (t[0] == m && m != EMPTY) {  // keys are unique (index in the low bits)
+            t[0] = t[1];
+            t[1] = t[2];
+            t[2] = t[3];
+            t[3] = EMPTY;
+        }
+    }
+    if (lane == 0) topk[row] = make_uint4(out[0], out[1], out[2], out[3]);
+}
+
+// one warp, rows in reference order
+__global__ void __launch_bounds__(32) k_bf_resolve(const uint8_t* __restrict__ desc_1, uint32_t n1, const uint8_t* __restrict__ desc_2,
+                                                   uint32_t n2, const uint4* __restrict__ topk, float lowe_ratio,
+                                                   int32_t* __restrict__ match_2_in_1, uint32_t* __restrict__ n_matches) {
+    extern __shared__ uint32_t s_claim[];  // bitmap over frame keypoints
+    const int lane = threadIdx.x;
+    const uint32_t words = (n1 + 31) / 32;
+    for (uint32_t i = lane; i < words; i += 32) s_claim[i] = 0;
+    for (uint32_t i = lane; i < n1; i += 32) match_2_in_1[i] = -1;
+    __syncwarp();
+    uint32_t num = 0;
+    for (uint32_t base = 0; base < n2; base += 32) {
+        const uint32_t mine = base + lane;
+        const uint4 mk = mine < n2 ? topk[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const uint32_t active = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 16) <= HAMMING_DIST_THR_LOW);
+        uint32_t todo = active;
+        while (todo) {  // rows whose unconditional best is already > 50 can never match and claim nothing
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
+            uint32_t k[K];
+            k[0] = __shfl_sync(0xFFFFFFFFu, mk.x, j);
+            k[1] = __shfl_sync(0xFFFFFFFFu, mk.y, j);
+            k[2] = __shfl_sync(0xFFFFFFFFu, mk.z, j);
+            k[3] = __shfl_sync(0xFFFFFFFFu, mk.w, j);
+            // first two unclaimed keys of the list (every lane computes the same thing)
+            uint32_t best = EMPTY, second = EMPTY;
+            int seen = 0;
+#pragma unroll
+            for (int q = 0; q < K; ++q) {
+                if (k[q] == EMPTY) continue;
+                const uint32_t i1 = k[q] & 0xFFFFu;
+                const bool claimed = (s_claim[i1 >> 5] >> (i1 & 31)) & 1u;
+                if (!claimed) {
+                    if (seen == 0) best = k[q];
+                    else if (seen == 1) second = k[q];
+                    ++seen;
+                }
+            }
+            const bool list_complete = (k[K - 1] == EMPTY);  // fewer than K frame keypoints exist: nothing beyond the list
+            bool exact = (seen >= 2) || list_complete;
+            if (!exact && seen == 1) {
+                // second >= the list's last distance; if the ratio test passes with that bound it passes with the truth
+                const unsigned lb = k[K - 1] >> 16, bd = best >> 16;
+                if (bd > HAMMING_DIST_THR_LOW) exact = true;  // rejected whatever the second is
+                else if (!(__fmul_rn(lowe_ratio, (float)lb) < (float)bd)) {
+                    exact = true;
+                    second = lb << 16;
+                }
+            }
+            if (!exact) {
+                // exact rescan of this row over the unclaimed frame keypoints (reference inner loop, match/robust.cc:252-274)
+                const uint32_t row = base + j;
+                const uint4* d2 = reinterpret_cast<const uint4*>(desc_2 + (size_t)row * 32);
+                const uint4 a0 = __ldg(d2), a1 = __ldg(d2 + 1);
+                uint32_t b = EMPTY, s = EMPTY;
+                for (uint32_t i = lane; i < n1; i += 32) {
+                    if ((s_claim[i >> 5] >> (i & 31)) & 1u) continue;
+                    const uint4* d1 = reinterpret_cast<const uint4*>(desc_1 + (size_t)i * 32);
+                    const uint32_t key = (hamming256(a0, a1, __ldg(d1), __ldg(d1 + 1)) << 16) | i;
+                    if (key < b) { s = b; b = key; }
+                    else if (key < s) s = key;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, b, o), os = __shfl_xor_sync(0xFFFFFFFFu, s, o);
+                    const uint32_t nb = min(b, ob);
+                    const uint32_t ns = min(max(b, ob), min(s, os));
+                    b = nb;
+                    s = ns;
+                }
+                best = b;
+                second = s;
+            }
+            if (best == EMPTY) continue;  // best_idx_1 < 0
+            const unsigned bd = best >> 16;
+            const unsigned sd = second == EMPTY ? MAX_HAMMING_DIST : (second >> 16);
+            if (HAMMING_DIST_THR_LOW < bd) continue;
+            if (__fmul_rn(lowe_ratio, (float)sd) < (float)bd) continue;  // match/robust.cc:285
+            const uint32_t i1 = best & 0xFFFFu;
+            if (lane == 0) {
+                s_claim[i1 >> 5] |= 1u << (i1 & 31);
+                match_2_in_1[i1] = (int32_t)(base + j);
+            }
+            ++num;
+            __syncwarp();
+        }
+    }
+    if (lane == 0) *n_matches = num;
+}
+
+__global__ void k_hamming_pairs(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, uint32_t n, uint32_t* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4* pa = reinterpret_cast<const uint4*>(a + (size_t)i * 32);
+    const uint4* pb = reinterpret_cast<const uint4*>(b + (size_t)i * 32);
+    out[i] = hamming256(__ldg(pa), __ldg(pa + 1), __ldg(pb), __ldg(pb + 1));
+}
+
+}  // namespace
+
+// match/angle_checker.h:60-134 (histogram_length 30, num_bins_thr 3) — the same std::sort call on the same container as
+// the reference, so libstdc++'s treatment of equal bin sizes is reproduced. Host-side: <= n1 scalar entries.
+std::vector<int> angle_invalid_matches(const std::vector<std::pair<float, int>>& delta_and_id) {
+    constexpr unsigned kLen = 30, kTop = 3;
+    const float inv_len = 1.0f / kLen;
+    std::vector<std::vector<int>> bins(kLen);
+    for (const auto& e : delta_and_id) {
+        float delta = e.first;
+        if (delta < 0.0) delta += 360.0;
+        if (360.0 <= delta) delta -= 360.0;
+        const unsigned bin = (unsigned)std::lrint((double)(delta * inv_len));
+        bins.at(bin).push_back(e.second);
+    }
+    std::vector<unsigned int> order(kLen);
+    std::iota(order.begin(), order.end(), 0);
+    std::sort(order.begin(), order.end(), [&bins](const unsigned int a, const unsigned int b) { return bins.at(a).size() > bins.at(b).size(); });
+    std::vector<int> out;
+    for (unsigned bin = 0; bin < kLen; ++bin) {
+        const bool keep = std::any_of(order.begin(), order.begin() + kTop, [bin](unsigned i) { return bin == i; });
+        if (!keep) out.insert(out.end(), bins[bin].begin(), bins[bin].end());
+    }
+    return out;
+}
+
+}  // namespace lps
+
+using namespace lps;
+
+extern "C" {
+
+int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* desc_2, uint32_t n2, const uint8_t* valid_2,
+                            const float* angle_1, const float* angle_2, float lowe_ratio, int check_orientation,
+                            int32_t* match_2_in_1, uint32_t* n_matches) {
+    LPS_ARG(n_matches, "n_matches is null");
+    *n_matches = 0;
+    LPS_ARG(n1 == 0 || (desc_1 && match_2_in_1), "null frame-side argument");
+    LPS_ARG(n2 == 0 || desc_2, "null keyframe descriptors");
+    LPS_ARG(n1 <= 65535, "more than 65535 frame keypoints are not supported by this matcher");
+    LPS_ARG(!check_orientation || (angle_1 && angle_2), "angles required for the orientation check");
+    for (uint32_t i = 0; i < n1; ++i) match_2_in_1[i] = -1;
+    if (n1 == 0 || n2 == 0) return LPSLAM_OK;
+    uint8_t* dev = nullptr;
+    const size_t o_d1 = 0, o_d2 = align_up(32 * (size_t)n1, 256), o_v = o_d2 + align_up(32 * (size_t)n2, 256);
+    const size_t o_top = o_v + align_up(n2, 256), o_m = o_top + align_up(16 * (size_t)n2, 256), o_n = o_m + align_up(4 * (size_t)n1, 256);
+    LPS_CUDA(cudaMalloc(&dev, o_n + 256));
+    int rc = LPSLAM_OK;
+    cudaError_t e;
+    do {
+        if ((e = cudaMemcpy(dev + o_d1, desc_1, 32 * (size_t)n1, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(dev + o_d2, desc_2, 32 * (size_t)n2, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        if (valid_2 && (e = cudaMemcpy(dev + o_v, valid_2, n2, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        k_bf_topk<<<(n2 + 7) / 8, 256>>>(dev + o_d1, n1, dev + o_d2, n2, valid_2 ? dev + o_v : nullptr, (uint4*)(dev + o_top));
+        k_bf_resolve<<<1, 32, ((n1 + 31) / 32) * 4>>>(dev + o_d1, n1, dev + o_d2, n2, (const uint4*)(dev + o_top), lowe_ratio,
+                                                      (int32_t*)(dev + o_m), (uint32_t*)(dev + o_n));
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(match_2_in_1, dev + o_m, 4 * (size_t)n1, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(n_matches, dev + o_n, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+    } while (false);
+    if (e != cudaSuccess) rc = cuda_fail(e, "lpslam_match_bruteforce", __FILE__, __LINE__);
+    cudaFree(dev);
+    if (rc == LPSLAM_OK && check_orientation) {
+        // appended in keyframe-row order, as the reference does while it scans (match/robust.cc:293-297)
+        std::vector<std::pair<int, int>> by_row;
+        for (uint32_t i = 0; i < n1; ++i)
+            if (match_2_in_1[i] >= 0) by_row.emplace_back(match_2_in_1[i], (int)i);
+        std::sort(by_row.begin(), by_row.end());
+        std::vector<std::pair<float, int>> deltas;
+        for (const auto& p : by_row) deltas.emplace_back(angle_1[p.second] - angle_2[p.first], p.second);
+        for (int id : angle_invalid_matches(deltas)) {
+            match_2_in_1[id] = -1;
+            --*n_matches;
+        }
+    }
+    return rc;
+}
+
+int lpslam_hamming_pairs(const uint8_t* a, const uint8_t* b, uint32_t n, uint32_t* dist) {
+    LPS_ARG(n == 0 || (a && b && dist), "null argument");
+    if (n == 0) return LPSLAM_OK;
+    uint8_t* dev = nullptr;
+    const size_t sz = align_up(32 * (size_t)n, 256);
+    LPS_CUDA(cudaMalloc(&dev, 2 * sz + 4 * (size_t)n));
+    cudaError_t e;
+    do {
+        if ((e = cudaMemcpy(dev, a, 32 * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(dev + sz, b, 32 * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        k_hamming_pairs<<<(n + 255) / 256, 256>>>(dev, dev + sz, n, (uint32_t*)(dev + 2 * sz));
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        e = cudaMemcpy(dist, dev + 2 * sz, 4 * (size_t)n, cudaMemcpyDeviceToHost);
+    } while (false);
+    cudaFree(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_hamming_pairs", __FILE__, __LINE__);
+    return LPSLAM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,441 @@
+// K10 — frame-to-frame projection matcher. Replaces match::projection::match_current_and_last_frames
+// (match/projection.cc:85-208) together with the grid of data/common.cc:97-186 / data/common.h:59-64 and the perspective
+// reprojection of camera/perspective.cc:151-169, over flat arrays.
+//
+//   k_grid_*        assign_keypoints_to_grid: CSR lists per cell, indices ascending inside a cell (= insertion order)
+//   k_proj_topk     one thread per last-frame landmark: reproject (double, no FMA), walk the cells x-outer / y-inner like
+//                   get_keypoints_in_cell, apply the octave / window / x_right gates and keep the 4 best (distance, visit order)
+//   k_proj_resolve  one warp replays the landmarks in order against the "already holds an observed landmark" bitmap; that
+//                   bitmap changes as matches are made (projection.cc:163-165,189), which is what makes the loop sequential.
+//                   A landmark whose 4 candidates are all taken is rescanned exactly.
+#include "common.cuh"
+
+#include <algorithm>
+
+namespace lps {
+
+std::vector<int> angle_invalid_matches(const std::vector<std::pair<float, int>>& delta_and_id);  // match_bf.cu
+
+namespace {
+
+constexpr int K = 4;
+constexpr unsigned HAMMING_DIST_THR_HIGH = 100, MAX_HAMMING_DIST = 256;  // match/base.h:14-15
+constexpr uint32_t EMPTY = 0xFFFFFFFFu;
+
+struct ProjArgs {
+    lpslam_camera cam;
+    double Tc[16], Tl[16];
+    uint32_t n_last, n_curr;
+    const uint8_t* last_has_lm;
+    const uint8_t* last_outlier;
+    const double* last_pos_w;
+    const uint8_t* last_desc;
+    const int32_t* last_octave;
+    const uint8_t* last_obs;  // nullable
+    const lpslam_keypoint* kp;
+    const uint8_t* desc;
+    const float* x_right;
+    const uint8_t* curr_taken;
+    const float* scale;
+    float margin;
+    // grid (CSR over cx * rows + cy)
+    uint32_t* cell_count;
+    uint32_t* cell_start;
+    uint32_t* cell_fill;
+    uint32_t* cell_items;
+    // per-landmark candidates
+    uint4* top_key;
+    int4* top_idx;
+    // results
+    int32_t* curr_match_last;
+    int2* events;  // (idx_last, idx_curr) in match order
+    uint32_t* n_events;
+};
+
+__device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
+__device__ __forceinline__ int cv_floor(double v) { return __double2int_rd(v); }
+__device__ __forceinline__ int cv_ceil(double v) { return __double2int_ru(v); }
+
+__device__ __forceinline__ unsigned hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x)
+           + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__device__ __forceinline__ bool cell_of(const ProjArgs& a, const lpslam_keypoint& k, int& cx, int& cy) {
+    cx = cv_round(__dmul_rn((double)__fsub_rn(k.x, a.cam.min_x), a.cam.inv_cell_width));
+    cy = cv_round(__dmul_rn((double)__fsub_rn(k.y, a.cam.min_y), a.cam.inv_cell_height));
+    return 0 <= cx && cx < (int)a.cam.grid_cols && 0 <= cy && cy < (int)a.cam.grid_rows;
+}
+
+__global__ void k_grid_count(ProjArgs a) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n_curr) return;
+    int cx, cy;
+    if (cell_of(a, a.kp[i], cx, cy)) atomicAdd(&a.cell_count[cx * a.cam.grid_rows + cy], 1u);
+}
+
+__global__ void __launch_bounds__(1024) k_grid_scan(ProjArgs a) {
+    __shared__ uint32_t s_w[33];
+    const uint32_t n = a.cam.grid_cols * a.cam.grid_rows;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + tid;
+        const uint32_t v = i < n ? a.cell_count[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_w[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = s_w[lane];
+            uint32_t wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            s_w[lane] = wi - w;
+            if (lane == 31) s_w[32] = wi;
+        }
+        __syncthreads();
+        if (i < n) {
+            a.cell_start[i] = carry + s_w[warp] + inc - v;
+            a.cell_fill[i] = 0;
+        }
+        carry += s_w[32];
+        __syncthreads();
+    }
+    if (tid == 0) a.cell_start[n] = carry;
+}
+
+__global__ void k_grid_fill(ProjArgs a) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n_curr) return;
+    int cx, cy;
+    if (cell_of(a, a.kp[i], cx, cy)) {
+        const uint32_t c = cx * a.cam.grid_rows + cy;
+        a.cell_items[a.cell_start[c] + atomicAdd(&a.cell_fill[c], 1u)] = i;
+    }
+}
+
+__global__ void k_grid_sort(ProjArgs a) {
+    // push_back order = ascending keypoint index; cells hold a handful of entries
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= a.cam.grid_cols * a.cam.grid_rows) return;
+    const uint32_t b = a.cell_start[c], e = a.cell_start[c + 1];
+    for (uint32_t i = b + 1; i < e; ++i) {
+        const uint32_t v = a.cell_items[i];
+        uint32_t j = i;
+        while (j > b && a.cell_items[j - 1] > v) {
+            a.cell_items[j] = a.cell_items[j - 1];
+            --j;
+        }
+        a.cell_items[j] = v;
+    }
+}
+
+struct Projected {
+    bool ok;
+    float ref_x, ref_y, x_right, m;
+    int min_cx, max_cx, min_cy, max_cy, min_level, max_level;
+};
+
+__device__ Projected project(const ProjArgs& a, uint32_t il, bool forward, bool backward) {
+    Projected p;
+    p.ok = false;
+    if (!a.last_has_lm[il] || a.last_outlier[il]) return p;
+    const double* pw = a.last_pos_w + 3 * (size_t)il;
+    double pc[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+        pc[i] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(a.Tc[i * 4], pw[0]), __dmul_rn(a.Tc[i * 4 + 1], pw[1])), __dmul_rn(a.Tc[i * 4 + 2], pw[2])),
+                          a.Tc[i * 4 + 3]);
+    if (pc[2] <= 0.0) return p;
+    const double z_inv = __ddiv_rn(1.0, pc[2]);
+    const double u = __dadd_rn(__dmul_rn(__dmul_rn(a.cam.fx, pc[0]), z_inv), a.cam.cx);
+    const double v = __dadd_rn(__dmul_rn(__dmul_rn(a.cam.fy, pc[1]), z_inv), a.cam.cy);
+    p.x_right = (float)__dsub_rn(u, __dmul_rn(a.cam.focal_x_baseline, z_inv));
+    if (!((double)a.cam.min_x < u && u < (double)a.cam.max_x && (double)a.cam.min_y < v && v < (double)a.cam.max_y)) return p;
+    const int oct = a.last_octave[il];
+    if (forward) {
+        p.min_level = oct;
+        p.max_level = (int)a.cam.num_scale_levels - 1;
+    }
+    else if (backward) {
+        p.min_level = 0;
+        p.max_level = oct;
+    }
+    else {
+        p.min_level = oct - 1;
+        p.max_level = oct + 1;
+    }
+    p.ref_x = (float)u;
+    p.ref_y = (float)v;
+    p.m = __fmul_rn(a.margin, a.scale[oct]);
+    const int gc = (int)a.cam.grid_cols, gr = (int)a.cam.grid_rows;
+    p.min_cx = max(0, cv_floor(__dmul_rn((double)__fsub_rn(__fsub_rn(p.ref_x, a.cam.min_x), p.m), a.cam.inv_cell_width)));
+    if (gc <= p.min_cx) return p;
+    p.max_cx = min(gc - 1, cv_ceil(__dmul_rn((double)__fadd_rn(__fsub_rn(p.ref_x, a.cam.min_x), p.m), a.cam.inv_cell_width)));
+    if (p.max_cx < 0) return p;
+    p.min_cy = max(0, cv_floor(__dmul_rn((double)__fsub_rn(__fsub_rn(p.ref_y, a.cam.min_y), p.m), a.cam.inv_cell_height)));
+    if (gr <= p.min_cy) return p;
+    p.max_cy = min(gr - 1, cv_ceil(__dmul_rn((double)__fadd_rn(__fsub_rn(p.ref_y, a.cam.min_y), p.m), a.cam.inv_cell_height)));
+    if (p.max_cy < 0) return p;
+    p.ok = true;
+    return p;
+}
+
+// visits the candidates of landmark il in reference order; f(seq, idx, dist) for every candidate that passes the gates
+template <typename F>
+__device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const uint32_t* taken_bits, F f) {
+    const uint4* dl = reinterpret_cast<const uint4*>(a.last_desc + (size_t)il * 32);
+    const uint4 l0 = __ldg(dl), l1 = __ldg(dl + 1);
+    const bool check_level = (0 < p.min_level) || (0 <= p.max_level);
+    uint32_t seq = 0;
+    for (int cx = p.min_cx; cx <= p.max_cx; ++cx)
+        for (int cy = p.min_cy; cy <= p.max_cy; ++cy) {
+            const uint32_t c = cx * a.cam.grid_rows + cy;
+            for (uint32_t q = a.cell_start[c]; q < a.cell_start[c + 1]; ++q) {
+                const uint32_t i = a.cell_items[q];
+                const lpslam_keypoint k = a.kp[i];
+                if (check_level) {
+                    if (k.octave < p.min_level) continue;
+                    if (0 <= p.max_level && p.max_level < k.octave) continue;
+                }
+                if (!(fabsf(__fsub_rn(k.x, p.ref_x)) < p.m && fabsf(__fsub_rn(k.y, p.ref_y)) < p.m)) continue;
+                ++seq;
+                if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
+                const float xr = a.x_right[i];
+                if (xr > 0) {
+                    if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
+                }
+                const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
+                f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)));
+            }
+        }
+}
+
+__device__ __forceinline__ void motion_flags(const ProjArgs& a, bool& forward, bool& backward) {
+    // projection.cc:90-109: trans_wc = -R_cw^T t_cw, trans_lc = R_lw trans_wc + t_lw
+    double twc[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+        twc[i] = -__dadd_rn(__dadd_rn(__dmul_rn(a.Tc[i], a.Tc[3]), __dmul_rn(a.Tc[4 + i], a.Tc[7])), __dmul_rn(a.Tc[8 + i], a.Tc[11]));
+    const double z = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(a.Tl[8], twc[0]), __dmul_rn(a.Tl[9], twc[1])), __dmul_rn(a.Tl[10], twc[2])), a.Tl[11]);
+    forward = a.cam.is_monocular ? false : z > a.cam.true_baseline;
+    backward = a.cam.is_monocular ? false : -z > a.cam.true_baseline;
+}
+
+__global__ void k_proj_topk(ProjArgs a) {
+    const uint32_t il = blockIdx.x * blockDim.x + threadIdx.x;
+    if (il >= a.n_last) return;
+    bool fw, bw;
+    motion_flags(a, fw, bw);
+    const Projected p = project(a, il, fw, bw);
+    uint32_t key[K] = {EMPTY, EMPTY, EMPTY, EMPTY};
+    int idx[K] = {-1, -1, -1, -1};
+    if (p.ok) {
+        visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d) {
+            const uint32_t kk = (d << 20) | seq;
+            if (kk < key[3]) {
+                key[3] = kk;
+                idx[3] = (int)i;
+#pragma unroll
+                for (int q = 3; q > 0; --q)
+                    if (key[q] < key[q - 1]) {
+                        const uint32_t tk = key[q]; key[q] = key[q - 1]; key[q - 1] = tk;
+                        const int ti = idx[q]; idx[q] = idx[q - 1]; idx[q - 1] = ti;
+                    }
+            }
+        });
+    }
+    a.top_key[il] = make_uint4(key[0], key[1], key[2], key[3]);
+    a.top_idx[il] = make_int4(idx[0], idx[1], idx[2], idx[3]);
+}
+
+__global__ void __launch_bounds__(32) k_proj_resolve(ProjArgs a) {
+    extern __shared__ uint32_t s_taken[];
+    const int lane = threadIdx.x;
+    const uint32_t words = (a.n_curr + 31) / 32;
+    for (uint32_t w = lane; w < words; w += 32) {
+        uint32_t bits = 0;
+        for (uint32_t b = 0; b < 32 && w * 32 + b < a.n_curr; ++b) bits |= (a.curr_taken[w * 32 + b] ? 1u : 0u) << b;
+        s_taken[w] = bits;
+    }
+    for (uint32_t i = lane; i < a.n_curr; i += 32) a.curr_match_last[i] = -1;
+    __syncwarp();
+    bool fw, bw;
+    motion_flags(a, fw, bw);
+    uint32_t num = 0;
+    for (uint32_t base = 0; base < a.n_last; base += 32) {
+        const uint32_t mine = base + lane;
+        const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
+        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_HIGH);
+        while (todo) {
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t il = base + j;
+            const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
+                                   __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
+            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j), __shfl_sync(0xFFFFFFFFu, mi.y, j),
+                               __shfl_sync(0xFFFFFFFFu, mi.z, j), __shfl_sync(0xFFFFFFFFu, mi.w, j)};
+            uint32_t best = EMPTY;
+            int best_i = -1;
+#pragma unroll
+            for (int q = K - 1; q >= 0; --q) {
+                if (k[q] == EMPTY) continue;
+                if (!((s_taken[ix[q] >> 5] >> (ix[q] & 31)) & 1u)) {
+                    best = k[q];
+                    best_i = ix[q];
+                }
+            }
+            if (best_i < 0 && k[K - 1] != EMPTY) {
+                // all four taken and the list may be longer: exact rescan in reference order by lane 0
+                uint32_t b = EMPTY;
+                int bi = -1;
+                if (lane == 0) {
+                    const Projected p = project(a, il, fw, bw);
+                    visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d) {
+                        const uint32_t kk = (d << 20) | seq;
+                        if (kk < b) {
+                            b = kk;
+                            bi = (int)i;
+                        }
+                    });
+                }
+                best = __shfl_sync(0xFFFFFFFFu, b, 0);
+                best_i = __shfl_sync(0xFFFFFFFFu, bi, 0);
+            }
+            if (best_i < 0) continue;
+            if (HAMMING_DIST_THR_HIGH < (best >> 20)) continue;
+            if (lane == 0) {
+                a.curr_match_last[best_i] = (int32_t)il;
+                // projection.cc:163-165 re-tests has_observation() of the landmark the keypoint holds now
+                const bool blocks = a.last_obs ? a.last_obs[il] != 0 : true;
+                if (blocks) s_taken[best_i >> 5] |= 1u << (best_i & 31);
+                a.events[num] = make_int2((int)il, best_i);
+            }
+            ++num;
+            __syncwarp();
+        }
+    }
+    if (lane == 0) *a.n_events = num;
+}
+
+}  // namespace
+}  // namespace lps
+
+using namespace lps;
+
+extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* pose_cw_curr, const double* pose_cw_last,
+                                       uint32_t n_last, const uint8_t* last_has_lm, const uint8_t* last_outlier,
+                                       const double* last_pos_w, const uint8_t* last_lm_desc, const int32_t* last_octave,
+                                       const float* last_angle, const uint8_t* last_lm_has_observation, uint32_t n_curr,
+                                       const lpslam_keypoint* curr_undist_kp, const uint8_t* curr_desc, const float* curr_x_right,
+                                       const uint8_t* curr_has_observed_lm, const float* scale_factors, float margin,
+                                       int check_orientation, int32_t* curr_match_last, uint32_t* n_matches) {
+    LPS_ARG(cam && pose_cw_curr && pose_cw_last && n_matches && scale_factors, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n_curr == 0 || (curr_undist_kp && curr_desc && curr_x_right && curr_has_observed_lm && curr_match_last), "null current-frame argument");
+    LPS_ARG(n_last == 0 || (last_has_lm && last_outlier && last_pos_w && last_lm_desc && last_octave), "null last-frame argument");
+    LPS_ARG(!check_orientation || last_angle, "last-frame angles required for the orientation check");
+    LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1 && cam->num_scale_levels >= 1 && cam->num_scale_levels <= (uint32_t)kMaxLevels,
+            "bad camera grid / level count");
+    LPS_ARG(n_curr < (1u << 20), "too many current keypoints");
+    for (uint32_t i = 0; i < n_curr; ++i) curr_match_last[i] = -1;
+    if (n_curr == 0 || n_last == 0) return LPSLAM_OK;
+    for (uint32_t i = 0; i < n_last; ++i)
+        LPS_ARG(last_octave[i] >= 0 && (uint32_t)last_octave[i] < cam->num_scale_levels, "last-frame octave out of range");
+
+    const uint32_t ncell = cam->grid_cols * cam->grid_rows;
+    ArenaBump ar;
+    const size_t o_has = ar.take(n_last), o_out = ar.take(n_last), o_pos = ar.take(24 * (size_t)n_last), o_ld = ar.take(32 * (size_t)n_last);
+    const size_t o_oct = ar.take(4 * (size_t)n_last), o_obs = ar.take(n_last), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_curr);
+    const size_t o_desc = ar.take(32 * (size_t)n_curr), o_xr = ar.take(4 * (size_t)n_curr), o_tk = ar.take(n_curr);
+    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_curr), o_tkey = ar.take(16 * (size_t)n_last);
+    const size_t o_tidx = ar.take(16 * (size_t)n_last), o_m = ar.take(4 * (size_t)n_curr), o_ev = ar.take(8 * (size_t)n_last);
+    const size_t o_ne = ar.take(4);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    int rc = LPSLAM_OK;
+    cudaError_t e = cudaSuccess;
+    std::vector<int2> events;
+    uint32_t n_ev = 0;
+    do {
+#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
+        UP(o_has, last_has_lm, n_last);
+        UP(o_out, last_outlier, n_last);
+        UP(o_pos, last_pos_w, 24 * (size_t)n_last);
+        UP(o_ld, last_lm_desc, 32 * (size_t)n_last);
+        UP(o_oct, last_octave, 4 * (size_t)n_last);
+        if (last_lm_has_observation) UP(o_obs, last_lm_has_observation, n_last);
+        UP(o_kp, curr_undist_kp, sizeof(lpslam_keypoint) * (size_t)n_curr);
+        UP(o_desc, curr_desc, 32 * (size_t)n_curr);
+        UP(o_xr, curr_x_right, 4 * (size_t)n_curr);
+        UP(o_tk, curr_has_observed_lm, n_curr);
+        UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+#undef UP
+        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        ProjArgs a;
+        a.cam = *cam;
+        for (int i = 0; i < 16; ++i) {
+            a.Tc[i] = pose_cw_curr[i];
+            a.Tl[i] = pose_cw_last[i];
+        }
+        a.n_last = n_last;
+        a.n_curr = n_curr;
+        a.last_has_lm = dev + o_has;
+        a.last_outlier = dev + o_out;
+        a.last_pos_w = (const double*)(dev + o_pos);
+        a.last_desc = dev + o_ld;
+        a.last_octave = (const int32_t*)(dev + o_oct);
+        a.last_obs = last_lm_has_observation ? dev + o_obs : nullptr;
+        a.kp = (const lpslam_keypoint*)(dev + o_kp);
+        a.desc = dev + o_desc;
+        a.x_right = (const float*)(dev + o_xr);
+        a.curr_taken = dev + o_tk;
+        a.scale = (const float*)(dev + o_sc);
+        a.margin = margin;
+        a.cell_count = (uint32_t*)(dev + o_cc);
+        a.cell_start = (uint32_t*)(dev + o_cs);
+        a.cell_fill = (uint32_t*)(dev + o_cf);
+        a.cell_items = (uint32_t*)(dev + o_ci);
+        a.top_key = (uint4*)(dev + o_tkey);
+        a.top_idx = (int4*)(dev + o_tidx);
+        a.curr_match_last = (int32_t*)(dev + o_m);
+        a.events = (int2*)(dev + o_ev);
+        a.n_events = (uint32_t*)(dev + o_ne);
+        k_grid_count<<<(n_curr + 255) / 256, 256>>>(a);
+        k_grid_scan<<<1, 1024>>>(a);
+        k_grid_fill<<<(n_curr + 255) / 256, 256>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
+        k_proj_topk<<<(n_last + 127) / 128, 128>>>(a);
+        k_proj_resolve<<<1, 32, ((n_curr + 31) / 32) * 4>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(curr_match_last, dev + o_m, 4 * (size_t)n_curr, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (check_orientation && n_ev) {
+            events.resize(n_ev);
+            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        }
+    } while (false);
+    if (e != cudaSuccess) rc = cuda_fail(e, "lpslam_match_projection", __FILE__, __LINE__);
+    cudaFree(dev);
+    if (rc) return rc;
+    *n_matches = n_ev;
+    if (check_orientation) {
+        std::vector<std::pair<float, int>> deltas;
+        for (const int2& ev : events) deltas.emplace_back(last_angle[ev.x] - curr_undist_kp[ev.y].angle, ev.y);
+        for (int id : angle_invalid_matches(deltas)) {
+            curr_match_last[id] = -1;
+            --*n_matches;
+        }
+    }
+    return LPSLAM_OK;
+}

@@ -77,3 +77,98 @@ def stereo_frames(extractor, lefts, rights, focal_x_baseline, true_baseline, cap
         out.append(dict(keypts_left=kp[a:b].copy(), descs_left=desc[a:b].copy(), keypts_right=kp[b:c].copy(),
                         descs_right=desc[b:c].copy(), stereo_x_right=xr[a:b].copy(), depths=dep[a:b].copy()))
     return out
+
+
+register("lpslam_match_bruteforce", C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_float, C.c_int, C.c_void_p, _lib.u32p])
+register("lpslam_hamming_pairs", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p])
+register("lpslam_match_projection", C.c_int, [C.POINTER(_lib.Camera), C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p,
+                                              _lib.u32p])
+
+
+def compute_descriptor_distance_32(desc_1, desc_2):
+    """match/base.h:18-40 on the device, row-wise over (N, 32) uint8 arrays (or a single pair)."""
+    a = np.ascontiguousarray(np.atleast_2d(desc_1), np.uint8)
+    b = np.ascontiguousarray(np.atleast_2d(desc_2), np.uint8)
+    assert a.shape == b.shape and a.shape[1] == 32
+    out = np.zeros(len(a), np.uint32)
+    check(lib().lpslam_hamming_pairs(a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data))
+    return out if np.ndim(desc_1) == 2 else int(out[0])
+
+
+compute_descriptor_distance_64 = compute_descriptor_distance_32  # match/base.h:43-63: same value, 64-bit words
+
+
+class robust:
+    """match::robust (match/robust.h:19-30)."""
+
+    def __init__(self, lowe_ratio=0.8, check_orientation=False):
+        self.lowe_ratio_, self.check_orientation_ = float(lowe_ratio), bool(check_orientation)
+
+    def brute_force_match(self, frm_descs, keyfrm_descs, keyfrm_valid=None, frm_angles=None, keyfrm_angles=None):
+        """match/robust.cc:215-321 over flat arrays: returns the (idx_1, idx_2) pairs sorted by idx_1."""
+        d1 = np.ascontiguousarray(frm_descs, np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(keyfrm_descs, np.uint8).reshape(-1, 32)
+        valid = None if keyfrm_valid is None else np.ascontiguousarray(keyfrm_valid, np.uint8)
+        a1 = None if frm_angles is None else np.ascontiguousarray(frm_angles, np.float32)
+        a2 = None if keyfrm_angles is None else np.ascontiguousarray(keyfrm_angles, np.float32)
+        out = np.full(len(d1), -1, np.int32)
+        n = C.c_uint32(0)
+        check(lib().lpslam_match_bruteforce(d1.ctypes.data, len(d1), d2.ctypes.data, len(d2), _lib.ptr(valid), _lib.ptr(a1),
+                                            _lib.ptr(a2), self.lowe_ratio_, int(self.check_orientation_), out.ctypes.data,
+                                            C.byref(n)))
+        idx_1 = np.nonzero(out >= 0)[0]
+        matches = np.stack([idx_1, out[idx_1]], axis=1).astype(np.int32)
+        assert len(matches) == n.value
+        return matches, out
+
+
+class projection:
+    """match::projection (match/projection.h:21-30)."""
+
+    def __init__(self, lowe_ratio=0.6, check_orientation=True):
+        self.lowe_ratio_, self.check_orientation_ = float(lowe_ratio), bool(check_orientation)
+
+    def match_current_and_last_frames(self, cam, pose_cw_curr, pose_cw_last, last_has_lm, last_outlier, last_pos_w, last_lm_desc,
+                                      last_octave, last_angle, curr_undist_keypts, curr_descs, curr_stereo_x_right,
+                                      curr_has_observed_lm, scale_factors, margin, last_lm_has_observation=None):
+        """match/projection.cc:85-208 over flat arrays: returns (curr_match_last, num_matches)."""
+        Tc = np.ascontiguousarray(pose_cw_curr, np.float64)
+        Tl = np.ascontiguousarray(pose_cw_last, np.float64)
+        has = np.ascontiguousarray(last_has_lm, np.uint8)
+        outl = np.ascontiguousarray(last_outlier, np.uint8)
+        pos = np.ascontiguousarray(last_pos_w, np.float64)
+        ld = np.ascontiguousarray(last_lm_desc, np.uint8)
+        loct = np.ascontiguousarray(last_octave, np.int32)
+        lang = np.ascontiguousarray(last_angle, np.float32)
+        obs = None if last_lm_has_observation is None else np.ascontiguousarray(last_lm_has_observation, np.uint8)
+        kp = np.ascontiguousarray(curr_undist_keypts, KP_DTYPE)
+        cd = np.ascontiguousarray(curr_descs, np.uint8)
+        xr = np.ascontiguousarray(curr_stereo_x_right, np.float32)
+        tk = np.ascontiguousarray(curr_has_observed_lm, np.uint8)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        out = np.full(len(kp), -1, np.int32)
+        n = C.c_uint32(0)
+        check(lib().lpslam_match_projection(C.byref(cam), Tc.ctypes.data, Tl.ctypes.data, len(has), has.ctypes.data,
+                                            outl.ctypes.data, pos.ctypes.data, ld.ctypes.data, loct.ctypes.data, lang.ctypes.data,
+                                            _lib.ptr(obs), len(kp), kp.ctypes.data, cd.ctypes.data, xr.ctypes.data,
+                                            tk.ctypes.data, sf.ctypes.data, float(margin), int(self.check_orientation_),
+                                            out.ctypes.data, C.byref(n)))
+        return out, int(n.value)
+
+
+def make_camera(fx, fy, cx, cy, cols, rows, focal_x_baseline=0.0, true_baseline=1.0, is_monocular=False, num_levels=8,
+                grid_cols=64, grid_rows=48):
+    """camera::perspective without distortion (camera/perspective.cc:20-31, camera/base.h:62,118-131)."""
+    cam = _lib.Camera()
+    cam.fx, cam.fy, cam.cx, cam.cy = fx, fy, cx, cy
+    cam.focal_x_baseline, cam.true_baseline = focal_x_baseline, true_baseline
+    cam.min_x, cam.max_x, cam.min_y, cam.max_y = 0.0, float(cols), 0.0, float(rows)
+    cam.grid_cols, cam.grid_rows = grid_cols, grid_rows
+    cam.inv_cell_width = float(grid_cols) / (np.float32(cols) - np.float32(0))
+    cam.inv_cell_height = float(grid_rows) / (np.float32(rows) - np.float32(0))
+    cam.is_monocular = int(is_monocular)
+    cam.num_scale_levels = num_levels
+    return cam

@@ -248,7 +248,7 @@ int orc_match_projection(const orc_camera* cam, const double* Tc, const double* 
                          const uint8_t* last_lm_desc, const int32_t* last_octave, const float* last_angle,
                          uint32_t n_curr, const orc_keypoint* kp, const uint8_t* curr_desc, const float* curr_x_right,
                          const uint8_t* curr_has_observed_lm, const float* scale_factors, float margin,
-                         int check_orientation, int32_t* curr_match_last) {
+                         int check_orientation, const uint8_t* last_lm_has_observation, int32_t* curr_match_last) {
     int num = 0;
     AngleHistogram hist;
     // data/common.cc:97-118 grid assignment, cell (x, y) -> indices in insertion order
@@ -343,7 +343,9 @@ int orc_match_projection(const orc_camera* cam, const double* Tc, const double* 
         }
         if (HAMMING_DIST_THR_HIGH < best) continue;
         curr_match_last[best_i] = static_cast<int32_t>(il);
-        taken[best_i] = 1;
+        // projection.cc:163-165 re-tests has_observation() of whatever landmark the keypoint holds NOW: a temporary
+        // (stereo VO) landmark without observations does not block later rows
+        taken[best_i] = last_lm_has_observation ? last_lm_has_observation[il] : 1;
         ++num;
         if (check_orientation) hist.append(last_angle[il] - kp[best_i].angle, best_i);
     }

@@ -90,6 +90,7 @@ int orc_match_projection(const orc_camera* cam, const double* pose_cw_curr /*4x4
                          uint32_t n_curr, const orc_keypoint* curr_undist_kp, const uint8_t* curr_desc,
                          const float* curr_x_right, const uint8_t* curr_has_observed_lm, const float* scale_factors,
                          float margin, int check_orientation,
+                         const uint8_t* last_lm_has_observation /* n_last, NULL = all landmarks have observations */,
                          int32_t* curr_match_last /* n_curr: index of the last-frame landmark or -1 */);
 
 /* exact brute-force top-2 (reference semantics of a sequential strict-< scan): per query best index, best and second distance */

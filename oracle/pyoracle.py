@@ -102,7 +102,7 @@ class Oracle:
             L.orc_match_bruteforce.argtypes = [u8p, C.c_uint32, u8p, C.c_uint32, u8p, f32p, f32p, C.c_float, C.c_int, i32p]
             L.orc_match_projection.argtypes = [C.POINTER(_CameraStruct), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                                C.c_uint32, u8p, u8p, C.POINTER(C.c_double), u8p, i32p, f32p,
-                                               C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, C.c_float, C.c_int, i32p]
+                                               C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, C.c_float, C.c_int, u8p, i32p]
             L.orc_knn_top2.argtypes = [u8p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_int64), C.POINTER(C.c_uint32),
                                        C.POINTER(C.c_uint32)]
 
@@ -186,7 +186,7 @@ class Oracle:
 
     def match_projection(self, cam, pose_curr, pose_last, last_has_lm, last_outlier, last_pos_w, last_lm_desc, last_octave,
                          last_angle, curr_kp, curr_desc, curr_x_right, curr_has_observed_lm, scale, margin,
-                         check_orientation=True):
+                         check_orientation=True, last_lm_has_observation=None):
         dp = C.POINTER(C.c_double)
         pose_curr = np.ascontiguousarray(pose_curr, np.float64)
         pose_last = np.ascontiguousarray(pose_last, np.float64)
@@ -207,7 +207,9 @@ class Oracle:
                                           _ptr(last_lm_desc, u8p), _ptr(last_octave, i32p), _ptr(last_angle, f32p),
                                           len(curr_kp), curr_kp.ctypes.data, _ptr(curr_desc, u8p),
                                           _ptr(curr_x_right, f32p), _ptr(curr_has, u8p), _ptr(scale, f32p),
-                                          margin, int(check_orientation), _ptr(out, i32p))
+                                          margin, int(check_orientation),
+                                          None if last_lm_has_observation is None else _ptr(np.ascontiguousarray(last_lm_has_observation, np.uint8), u8p),
+                                          _ptr(out, i32p))
         return out, n
 
     def knn_top2(self, q, db):

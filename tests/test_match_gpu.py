@@ -1,0 +1,117 @@
+"""GPU parity of the Hamming matchers against the oracle: match indices and distances bit-exact given identical descriptors."""
+import numpy as np
+import pytest
+
+from lpslam_b200.synth import synth_descriptors, synth_image
+
+pytestmark = pytest.mark.gpu
+
+
+def test_hamming_known_answers():
+    # test/openvslam/match/base.cc:11-57
+    from lpslam_b200 import match
+    a = np.zeros(32, np.uint8)
+    assert match.compute_descriptor_distance_32(a, a) == 0
+    assert match.compute_descriptor_distance_32(a, ~a) == 256
+    assert match.compute_descriptor_distance_32(np.full(32, 0x66, np.uint8), np.full(32, 0x3C, np.uint8)) == 128
+    rng = np.random.default_rng(1)
+    x = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    y = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    want = np.unpackbits(x ^ y, axis=1).sum(axis=1)
+    assert np.array_equal(match.compute_descriptor_distance_32(x, y), want)
+
+
+def frame_pair(n1, n2, seed, flip=0.06):
+    """keyframe descriptors = noisy copies of frame descriptors (so matches exist), shuffled, plus duplicates to force
+    claim conflicts."""
+    rng = np.random.default_rng(seed)
+    d1 = rng.integers(0, 256, (n1, 32), dtype=np.uint8)
+    src = rng.integers(0, n1, n2)
+    src[: n2 // 5] = rng.integers(0, max(n1 // 20, 1), n2 // 5)   # many rows fight for a few frame keypoints
+    flips = rng.random((n2, 256)) < flip
+    d2 = d1[src] ^ np.packbits(flips, axis=1, bitorder="little")
+    return d1, d2
+
+
+@pytest.mark.parametrize("n1,n2,seed", [(1000, 1000, 1), (2000, 2000, 2), (4000, 4000, 3), (37, 500, 4), (500, 3, 5), (3, 40, 6)])
+def test_bruteforce(oracle, n1, n2, seed):
+    from lpslam_b200 import match
+    d1, d2 = frame_pair(n1, n2, seed)
+    rng = np.random.default_rng(seed + 100)
+    valid = (rng.random(n2) < 0.8).astype(np.uint8)
+    a1 = rng.uniform(0, 360, n1).astype(np.float32)
+    a2 = rng.uniform(0, 360, n2).astype(np.float32)
+    for chk in (False, True):
+        want, nw = oracle.match_bruteforce(d1, d2, valid, a1, a2, 0.8, chk)
+        pairs, got = match.robust(0.8, chk).brute_force_match(d1, d2, valid, a1, a2)
+        assert np.array_equal(got, want)
+        assert len(pairs) == nw
+    if n1 >= 1000:
+        assert nw > 10
+
+
+def test_bruteforce_exhaustion(oracle):
+    """every keyframe row is a near copy of the same 3 frame descriptors: top-4 lists run dry and the exact rescan runs"""
+    from lpslam_b200 import match
+    rng = np.random.default_rng(7)
+    d1 = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    d1[3:40] = d1[0] ^ np.packbits(rng.random((37, 256)) < 0.03, axis=1, bitorder="little")
+    d2 = d1[rng.integers(0, 3, 200)] ^ np.packbits(rng.random((200, 256)) < 0.02, axis=1, bitorder="little")
+    for ratio in (0.8, 1.0, 3.0):
+        want, _ = oracle.match_bruteforce(d1, d2, None, None, None, ratio, False)
+        _, got = match.robust(ratio, False).brute_force_match(d1, d2)
+        assert np.array_equal(got, want)
+
+
+def test_bruteforce_on_extracted_frames(oracle):
+    from lpslam_b200 import match
+    a = synth_image(480, 640, 50)
+    b = np.roll(a, (3, 5), axis=(0, 1))
+    o = oracle.extractor(max_kpts=1000)
+    ka, da = o.extract(a)
+    kb, db = o.extract(b)
+    want, nw = oracle.match_bruteforce(da, db, None, ka["angle"], kb["angle"], 0.8, True)
+    _, got = match.robust(0.8, True).brute_force_match(da, db, None, ka["angle"], kb["angle"])
+    assert nw > 50 and np.array_equal(got, want)
+
+
+def projection_case(oracle, seed, stereo, with_temporaries):
+    from oracle import pyoracle
+    rng = np.random.default_rng(seed)
+    img = synth_image(480, 640, 60 + seed)
+    o = oracle.extractor(max_kpts=1000)
+    kp, desc = o.extract(img)
+    n = len(kp)
+    fx = fy = 500.0
+    cx, cy = 320.0, 240.0
+    args = dict(fx=fx, fy=fy, cx=cx, cy=cy, cols=640, rows=480, focal_x_baseline=50.0 if stereo else 0.0, true_baseline=0.1,
+                is_monocular=not stereo)
+    depth = rng.uniform(2.0, 8.0, n)
+    pos = np.stack([(kp["x"] - cx) / fx * depth, (kp["y"] - cy) / fy * depth, depth], axis=1)  # world = last camera
+    Tl = np.eye(4)
+    Tc = np.eye(4)
+    Tc[:3, 3] = [0.02, -0.01, -0.3 if stereo else 0.05]   # forward motion for the stereo case
+    has = (rng.random(n) < 0.85).astype(np.uint8)
+    outl = (rng.random(n) < 0.05).astype(np.uint8)
+    ldesc = desc ^ np.packbits(rng.random((n, 256)) < 0.05, axis=1, bitorder="little")
+    xr = np.where(rng.random(n) < 0.5, kp["x"] - 50.0 / depth, -1.0).astype(np.float32) if stereo else np.full(n, -1.0, np.float32)
+    taken = (rng.random(n) < 0.1).astype(np.uint8)
+    obs = (rng.random(n) < 0.5).astype(np.uint8) if with_temporaries else None
+    sf = o.table(0)
+    return args, Tc, Tl, has, outl, pos, ldesc, kp["octave"], kp["angle"], kp, desc, xr, taken, sf, obs
+
+
+@pytest.mark.parametrize("seed,stereo,temps", [(1, False, False), (2, True, False), (3, True, True), (4, False, True)])
+def test_projection(oracle, seed, stereo, temps):
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    args, Tc, Tl, has, outl, pos, ldesc, loct, lang, kp, desc, xr, taken, sf, obs = projection_case(oracle, seed, stereo, temps)
+    for margin in (10.0, 20.0, 40.0):
+        for chk in (True, False):
+            want, nw = oracle.match_projection(pyoracle.make_camera(**args), Tc, Tl, has, outl, pos, ldesc, loct, lang, kp, desc,
+                                               xr, taken, sf, margin, chk, obs)
+            got, ng = match.projection(0.9, chk).match_current_and_last_frames(match.make_camera(**args), Tc, Tl, has, outl, pos,
+                                                                              ldesc, loct, lang, kp, desc, xr, taken, sf, margin,
+                                                                              obs)
+            assert np.array_equal(got, want) and ng == nw
+    assert nw > 50
