@@ -5,8 +5,8 @@
 //
 // Tie-break pin: the reference sorts std::pair<int, orb_extractor_node*> (orb_extractor.cc:408,455), i.e. equal keypoint
 // counts are ordered by HEAP ADDRESS of the std::list nodes. The operator new below hands out list nodes of exactly that
-// size from a monotonic arena (reset per extract call), so a later-created node always has the higher address: the
-// documented pin "later created first" that both the port and the CUDA kernel implement.
+// size from monotonic chunks (rewound between calls only when empty), so within one call a later-created node always has
+// the higher address: the documented pin "later created first" that both the port and the CUDA kernel implement.
 #include <algorithm>
 #include <array>
 #include <cstdint>
@@ -28,22 +28,54 @@
 namespace {
 
 constexpr size_t kNodeSize = sizeof(std::_List_node<openvslam::feature::orb_extractor_node>);
-constexpr size_t kArenaBytes = size_t(256) << 20;
-char* g_arena = nullptr;
-size_t g_arena_off = 0;
+constexpr size_t kChunkBytes = size_t(64) << 20;
+constexpr size_t kLowWater = size_t(8) << 20;
 
-inline bool in_arena(void* p) { return g_arena && p >= g_arena && p < g_arena + kArenaBytes; }
+// Monotonic chunks. Anything of exactly kNodeSize bytes lands here (list nodes, but also e.g. a 3-element
+// vector<vector<KeyPoint>>), so a chunk is only rewound when nothing allocated from it is still alive; otherwise the
+// offset keeps growing and a fresh chunk is started when the current one runs low (the old one stays valid).
+struct Chunk {
+    char* base;
+    size_t off;
+    long live;
+};
+Chunk g_chunks[64];
+int g_nchunks = 0;
+
+inline Chunk* chunk_of(void* p) {
+    for (int i = g_nchunks - 1; i >= 0; --i)
+        if (p >= g_chunks[i].base && p < g_chunks[i].base + kChunkBytes) return &g_chunks[i];
+    return nullptr;
+}
+
+// called at the start of every reference call that builds a quadtree
+void arena_begin_call() {
+    if (g_nchunks == 0) return;
+    Chunk& c = g_chunks[g_nchunks - 1];
+    if (c.live == 0) c.off = 0;
+    else if (kChunkBytes - c.off < kLowWater && g_nchunks < 64) {
+        char* b = static_cast<char*>(std::malloc(kChunkBytes));
+        if (b) g_chunks[g_nchunks++] = Chunk{b, 0, 0};
+    }
+}
 
 }  // namespace
 
 void* operator new(size_t n) {
     if (n == kNodeSize) {
-        if (!g_arena) g_arena = static_cast<char*>(std::malloc(kArenaBytes));
+        if (g_nchunks == 0) {
+            char* b = static_cast<char*>(std::malloc(kChunkBytes));
+            if (b) g_chunks[g_nchunks++] = Chunk{b, 0, 0};
+        }
         const size_t need = (n + 15) & ~size_t(15);
-        if (g_arena && g_arena_off + need <= kArenaBytes) {
-            void* p = g_arena + g_arena_off;
-            g_arena_off += need;
-            return p;
+        if (g_nchunks) {
+            Chunk& c = g_chunks[g_nchunks - 1];
+            if (c.off + need <= kChunkBytes) {
+                void* p = c.base + c.off;
+                c.off += need;
+                ++c.live;
+                return p;
+            }
         }
     }
     void* p = std::malloc(n ? n : 1);
@@ -51,7 +83,11 @@ void* operator new(size_t n) {
     return p;
 }
 void operator delete(void* p) noexcept {
-    if (!p || in_arena(p)) return;
+    if (!p) return;
+    if (Chunk* c = chunk_of(p)) {
+        --c->live;
+        return;
+    }
     std::free(p);
 }
 void operator delete(void* p, size_t) noexcept { operator delete(p); }
@@ -108,7 +144,7 @@ int ref_get_table(const ref_extractor* e, int which, float* out, int cap) {
 int ref_extract(ref_extractor* e, const uint8_t* img, int w, int h, size_t pitch, const uint8_t* mask, size_t mask_pitch,
                 orc_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* n_out) {
     *n_out = 0;
-    g_arena_off = 0;  // no list node outlives an extract call
+    arena_begin_call();
     e->have_sel = false;
     if (!img || w <= 0 || h <= 0) return 0;
     e->image = cv::Mat(h, w, CV_8UC1, const_cast<uint8_t*>(img), pitch).clone();
@@ -144,7 +180,7 @@ int ref_level_selected(ref_extractor* e, int level, int32_t* xys, int cap) {
     if (level < 0 || level >= static_cast<int>(e->ex->get_num_scale_levels())) return -1;
     if (!e->have_sel) {
         // re-run the private FAST + quadtree step on the pyramid of the last extract (same mask priority as :93-107)
-        g_arena_off = 0;
+        arena_begin_call();
         e->sel.clear();
         if (!e->mask.empty()) e->ex->compute_fast_keypoints(e->sel, e->mask);
         else if (!e->ex->rect_mask_.empty()) e->ex->compute_fast_keypoints(e->sel, e->ex->rect_mask_);

@@ -79,6 +79,14 @@ struct Range {
     int start, end;
 };
 
+// cv::MatExpr of Mat::zeros / Mat::ones: assigning it to a Mat that already has the right size and type fills that Mat's
+// buffer IN PLACE (MatOp_Initializer::assign -> Mat::create keeps the allocation). feature/orb_extractor.cc:637 relies
+// on this: `descriptors = cv::Mat::zeros(...)` must keep writing into the rows of the caller's output matrix.
+struct MatInit {
+    int rows, cols, type;
+    double value;
+};
+
 class Mat {
 public:
     int rows = 0, cols = 0;
@@ -157,8 +165,18 @@ public:
             for (int x = 0; x < cols; ++x) at<float>(y, x) -= o.at<float>(y, x);
         return *this;
     }
-    static Mat zeros(int r, int c, int type) { return Mat(r, c, type, Scalar(0)); }
-    static Mat ones(int r, int c, int type) { return Mat(r, c, type, Scalar(1)); }
+    static MatInit zeros(int r, int c, int type) { return MatInit{r, c, type, 0.0}; }
+    static MatInit ones(int r, int c, int type) { return MatInit{r, c, type, 1.0}; }
+    Mat(const MatInit& e) {
+        create(e.rows, e.cols, e.type);
+        fill(e.value);
+    }
+    Mat& operator=(const MatInit& e) {
+        // same geometry: keep the buffer (even a non-owned row range of another matrix), exactly like cv::Mat::create
+        if (!(rows == e.rows && cols == e.cols && type_ == e.type && data)) create(e.rows, e.cols, e.type);
+        fill(e.value);
+        return *this;
+    }
 
 private:
     void fill(double v) {
@@ -179,6 +197,8 @@ inline Mat operator*(float s, const Mat& m) {
     return out;
 }
 inline Mat operator*(double s, const Mat& m) { return static_cast<float>(s) * m; }
+inline Mat operator*(float s, const MatInit& e) { return s * Mat(e); }
+inline Mat operator*(double s, const MatInit& e) { return static_cast<float>(s) * Mat(e); }
 
 // cv::norm(a, b, NORM_L1) on CV_32F: absolute differences accumulated in double
 inline double norm(const Mat& a, const Mat& b, int /*type*/) {

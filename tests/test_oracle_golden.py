@@ -1,0 +1,108 @@
+"""CPU: the oracle port (oracle/*.cc) — and the reference build (oracle/_ref) where it exists — against the committed
+golden vectors, which tools/gen_golden.py produced from the reference's own sources. Also the known-answer cases the
+reference's unit tests hold for this path (test/openvslam/match/base.cc, match/angle_checker.cc, util/trigonometric.cc,
+feature/orb_extractor.cc)."""
+import math
+
+import numpy as np
+import pytest
+
+from golden_util import EXTRACT_FIXTURES, STEREO_FIXTURES, case_input, crc, load, stereo_input
+
+FX_B, B = 700.0 * 0.12, 0.12
+
+
+def check_extract(o, name, is_port):
+    g = load(name)
+    img, mask, params = case_input(g)
+    e = o.extractor(**params)
+    kp, desc = e.extract(img, mask)
+    assert kp.tobytes() == g["kp"].tobytes(), "keypoints differ from the reference"
+    assert np.array_equal(desc.reshape(-1, 32), g["desc"].reshape(-1, 32)), "descriptors differ from the reference"
+    for l in range(params["num_levels"]):
+        assert crc(e.level(l)) == int(g["pyr_crc"][l]), f"pyramid level {l}"
+        assert np.array_equal(e.selected(l), g[f"sel_l{l}"]), f"quadtree selection level {l}"
+        if is_port:
+            c = e.candidates(l)
+            assert len(c) == int(g["cand_n"][l]) and crc(c.astype(np.int32)) == int(g["cand_crc"][l]), f"FAST candidates level {l}"
+            if int(g["blur_crc"][l]) >= 0:
+                assert crc(e.level(l, blurred=True)) == int(g["blur_crc"][l]), f"blurred level {l}"
+
+
+@pytest.mark.parametrize("name", EXTRACT_FIXTURES)
+def test_port_extract(oracle, name):
+    check_extract(oracle, name, True)
+
+
+@pytest.mark.parametrize("name", EXTRACT_FIXTURES)
+def test_reference_build_extract(ref_oracle, name):
+    check_extract(ref_oracle, name, False)
+
+
+def check_stereo(o, name):
+    g = load(name)
+    (left, right), n = stereo_input(g)
+    el, er = o.extractor(max_kpts=n), o.extractor(max_kpts=n)
+    kl, dl = el.extract(left)
+    kr, dr = er.extract(right)
+    assert np.array_equal(np.stack([kl["x"], kl["y"]], 1), g["kp_l_xy"]) and np.array_equal(np.stack([kr["x"], kr["y"]], 1), g["kp_r_xy"])
+    assert crc(dl) == int(g["desc_l_crc"]) and crc(dr) == int(g["desc_r_crc"])
+    xr, dep = o.match_stereo([el.level(l) for l in range(8)], [er.level(l) for l in range(8)], kl, kr, dl, dr,
+                             el.table(0), el.table(1), FX_B, B)
+    assert np.array_equal(xr, g["stereo_x_right"]) and np.array_equal(dep, g["depths"])
+
+
+@pytest.mark.parametrize("name", STEREO_FIXTURES)
+def test_port_stereo(oracle, name):
+    check_stereo(oracle, name)
+
+
+@pytest.mark.parametrize("name", STEREO_FIXTURES[:1])
+def test_reference_build_stereo(ref_oracle, name):
+    check_stereo(ref_oracle, name)
+
+
+def test_toy_corner_property():
+    # test/openvslam/feature/orb_extractor.cc:24-49: every keypoint within 2 * scale of the single corner (300, 300)
+    g = load("toy_corner_600x600")
+    kp = g["kp"]
+    assert len(kp) > 0
+    sf = np.float32(1.2) ** kp["octave"].astype(np.float32)
+    assert (np.abs(kp["x"] - 300) <= 2.0 * sf + 1e-3).all() and (np.abs(kp["y"] - 300) <= 2.0 * sf + 1e-3).all()
+
+
+def test_mask_properties():
+    # test/openvslam/feature/orb_extractor.cc:116-332: no keypoint inside a masked region
+    g = load("imgmask_640x480")
+    kp = g["kp"]
+    inside = (kp["x"] >= 200) & (kp["x"] < 500) & (kp["y"] >= 100) & (kp["y"] < 300)
+    assert len(kp) > 0 and not inside.any()
+    g = load("rectmask_640x480")
+    kp = g["kp"]
+    for x0, x1, y0, y1 in g["p_mask_rects"]:
+        inside = (kp["x"] > 640 * x0 + 1) & (kp["x"] < 640 * x1 - 1) & (kp["y"] > 480 * y0 + 1) & (kp["y"] < 480 * y1 - 1)
+        assert not inside.any()
+
+
+def test_hamming_known_answers(oracle):
+    # test/openvslam/match/base.cc:11-57
+    cases = [(0b01010101, 0b01010101, 0), (0b01010101, 0b10101010, 256), (0b01100110, 0b00111100, 128)]
+    for a, b, want in cases:
+        da, db = np.full(32, a, np.uint8), np.full(32, b, np.uint8)
+        assert oracle.hamming(da, db, 32) == want and oracle.hamming(da, db, 64) == want
+
+
+def test_trigonometric_tolerance(oracle):
+    # test/openvslam/util/trigonometric.cc:8-20
+    for deg in range(0, 3601):
+        rad = float(np.float32(np.float32(deg / 10.0) * np.float32(math.pi) / np.float32(180.0)))
+        assert abs(math.cos(rad) - oracle.lib.orc_cos(rad)) < 1e-3
+        assert abs(math.sin(rad) - oracle.lib.orc_sin(rad)) < 1e-3
+
+
+def test_angle_checker_top3(oracle):
+    # test/openvslam/match/angle_checker.cc:106-145 (histogram length 30, three fullest bins kept)
+    deltas = [34.8, 34.9, 35.0, 35.1, 35.2, 323.8, 323.9, 324.1, 324.2, 126.9, 127.0, 127.1, 0.0, 90.0, 180.0, 270.0]
+    ids = [35] * 5 + [324] * 4 + [127] * 3 + [0, 60, 180, 270]
+    inv = oracle.angle_invalid(deltas, ids)
+    assert sorted(inv.tolist()) == [0, 60, 180, 270]
