@@ -1,20 +1,135 @@
 // K5 — 7x7 Gaussian blur, sigma 2, BORDER_REFLECT_101. Replaces cv::GaussianBlur at feature/orb_extractor.cc:135-136.
-// Arithmetic: separable integer kernel [18 34 48 56 48 34 18] (sum 256); the horizontal pass keeps
-// full 16-bit sums, the vertical pass is Q16.16 with round-half-up: dst = (V + 32768) >> 16. Bit-exact with OpenCV 4.x.
+// Arithmetic: separable integer kernel k = [18 34 48 56 48 34 18] (sum 256); OpenCV's fixed-point
+// path keeps the full 16-bit horizontal sums and rounds once: dst = (sum_ij k_i k_j p_ij + 32768) >> 16. Nothing is
+// rounded in between, so this is one exact integer 2-D convolution and it is bit-exact with OpenCV 4.x.
 //
-// One launch blurs every level of every frame of the batch: blockIdx.x walks the concatenated tile lists of the levels,
-// blockIdx.y is the frame. A block stages a (128+32) x (32+6) byte window in shared memory with 128-bit loads, runs the
-// horizontal pass into a 16-bit shared buffer and the vertical pass out of it; global traffic is one read and one write
-// per pixel plus the 6-row / 16-byte halo.
+// Design (B200): the kernel is bound by the integer pipes, not by HBM, unless the instruction count per pixel is cut to
+// ~10, so everything here is about that count.
+//   * every level image carries a reflected apron (k_pad_borders, below), so no thread ever mirrors an index;
+//   * a thread owns a strip of 8 columns and walks DOWN it; all loads are plain 32/64-bit global loads (the three
+//     neighbouring words of a row are shared with the adjacent lanes through L1), there is no shared memory and no
+//     barrier, and a warp reads 256 contiguous bytes per row;
+//   * horizontal pass: the 7 taps of one pixel are two IDP.4A (4-way byte dot product) on byte quads cut from the row
+//     words with PRMT: H(x) = dp4a(p[x-3..x], (18,34,48,56)) + dp4a(p[x+1..x+4], (48,34,18,0));
+//   * the 16-bit H values of rows 2m and 2m+1 are packed into one register (a "row pair");
+//   * vertical pass: the 7 taps of one output pixel are four IDP.2A (2-way 16-bit x 8-bit dot product) over four row
+//     pairs, the rounding constant 32768 rides in as the first accumulator, and the output byte is byte 2 of the sum.
+//   per pixel: 2 IDP.4A + 4 IDP.2A + ~2.4 PRMT + 0.5 load/store  (was ~56 instructions per pixel with the staged version)
 #include "common.cuh"
 
 namespace lps {
 
 namespace {
 
-constexpr int TW = 128, TH = 32, HALO = 3;
-constexpr int IN_W = TW + 32;        // bytes per staged row: [tx0 - 16, tx0 + 144), 16-byte aligned in global memory
-constexpr int IN_H = TH + 2 * HALO;  // 38 rows
+constexpr int SW = 8;           // strip width (pixels per thread-row)
+constexpr int MACRO_ROWS = 10;  // rows per macro iteration: 5 row pairs = one full rotation of the pair window
+constexpr int BLUR_THREADS = 128;
+
+struct BlurTable {
+    int num_levels;
+    int rows_per_thread;               // multiple of MACRO_ROWS
+    int item_begin[kMaxLevels + 1];    // first (strip, row block) item of each level
+    int strips[kMaxLevels];            // strips per row
+};
+
+constexpr uint32_t W_A = 0x30221200u;  // bytes ( 0, 18, 34, 48)
+constexpr uint32_t W_B = 0x12223038u;  // bytes (56, 48, 34, 18)
+constexpr uint32_t W_C = 0x38302212u;  // bytes (18, 34, 48, 56)
+constexpr uint32_t W_D = 0x00122230u;  // bytes (48, 34, 18,  0)
+
+// horizontal sums of the 8 pixels at rp[0..8) (apron makes rp[-4..12) readable), started from `init`
+__device__ __forceinline__ void hrow(const uint8_t* __restrict__ rp, uint32_t (&h)[SW]) {
+    const uint32_t wm = __ldg(reinterpret_cast<const uint32_t*>(rp - 4));
+    const uint2 w01 = __ldg(reinterpret_cast<const uint2*>(rp));
+    const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(rp + 8));
+    uint32_t q[12];  // q[k] = bytes p[k-3 .. k]
+    q[3] = w01.x;
+    q[7] = w01.y;
+    q[11] = w2;
+    q[0] = __byte_perm(wm, w01.x, 0x4321);
+    q[1] = __byte_perm(wm, w01.x, 0x5432);
+    q[2] = __byte_perm(wm, w01.x, 0x6543);
+    q[4] = __byte_perm(w01.x, w01.y, 0x4321);
+    q[5] = __byte_perm(w01.x, w01.y, 0x5432);
+    q[6] = __byte_perm(w01.x, w01.y, 0x6543);
+    q[8] = __byte_perm(w01.y, w2, 0x4321);
+    q[9] = __byte_perm(w01.y, w2, 0x5432);
+    q[10] = __byte_perm(w01.y, w2, 0x6543);
+#pragma unroll
+    for (int k = 0; k < SW; ++k) h[k] = __dp4a(q[k + 4], W_D, __dp4a(q[k], W_C, 0u));
+}
+
+__device__ __forceinline__ uint32_t pack4(uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
+    // byte 2 of each sum (sum < 2^24) -> one word
+    return __byte_perm(__byte_perm(r0, r1, 0x6262), __byte_perm(r2, r3, 0x6262), 0x5410);
+}
+
+__global__ void __launch_bounds__(BLUR_THREADS) k_gauss7(const LevelGeom* __restrict__ lvs, BlurTable tab) {
+    const int item = blockIdx.x * BLUR_THREADS + threadIdx.x;
+    if (item >= tab.item_begin[tab.num_levels]) return;
+    int level = 0;
+    while (item >= tab.item_begin[level + 1]) ++level;
+    const int w = lvs[level].w, h = lvs[level].h, pitch = lvs[level].pitch;
+    (void)w;
+    const size_t fofs = blockIdx.y * lvs[level].frame_stride;
+    const int local = item - tab.item_begin[level];
+    const int strips = tab.strips[level];
+    const int rb = local / strips, s = local - rb * strips;
+    const int y0 = rb * tab.rows_per_thread;
+    const uint8_t* __restrict__ src = lvs[level].img + fofs + s * SW;
+    uint8_t* __restrict__ dst = lvs[level].blur + fofs + s * SW;
+    const int last_row = h + 3;  // the apron holds rows -4 .. h + 3
+
+    // row pair m (virtual rows 2m, 2m + 1) of this strip
+    auto load_pair = [&](int m, uint32_t (&p)[SW]) {
+        const int ra = min(2 * m, last_row), rbw = min(2 * m + 1, last_row);
+        uint32_t he[SW], ho[SW];
+        hrow(src + (ptrdiff_t)ra * pitch, he);
+        hrow(src + (ptrdiff_t)rbw * pitch, ho);
+#pragma unroll
+        for (int k = 0; k < SW; ++k) p[k] = __byte_perm(he[k], ho[k], 0x5410);
+    };
+
+    uint32_t P[5][SW];  // window of row pairs j-2 .. j+2 (rotating: pair m lives in slot m mod 5, relative to the start)
+    const int j0 = y0 >> 1;
+    load_pair(j0 - 2, P[0]);
+    load_pair(j0 - 1, P[1]);
+    load_pair(j0, P[2]);
+    load_pair(j0 + 1, P[3]);
+
+    const int macros = tab.rows_per_thread / MACRO_ROWS;
+    for (int mi = 0; mi < macros; ++mi) {
+        const int jb = j0 + mi * (MACRO_ROWS / 2);
+        if (2 * jb >= h) break;
+#pragma unroll
+        for (int u = 0; u < MACRO_ROWS / 2; ++u) {
+            const int j = jb + u;
+            uint32_t(&A)[SW] = P[u % 5];
+            uint32_t(&B)[SW] = P[(u + 1) % 5];
+            uint32_t(&C)[SW] = P[(u + 2) % 5];
+            uint32_t(&D)[SW] = P[(u + 3) % 5];
+            uint32_t(&E)[SW] = P[(u + 4) % 5];
+            load_pair(j + 2, E);
+            uint32_t re[SW], ro[SW];
+#pragma unroll
+            for (int k = 0; k < SW; ++k) {
+                uint32_t a = __dp2a_lo(A[k], W_A, 32768u);  // rows 2j-4 (x0), 2j-3 (x18)
+                a = __dp2a_hi(B[k], W_A, a);                // 2j-2 (x34), 2j-1 (x48)
+                a = __dp2a_lo(C[k], W_B, a);                // 2j (x56), 2j+1 (x48)
+                re[k] = __dp2a_hi(D[k], W_B, a);            // 2j+2 (x34), 2j+3 (x18)
+                uint32_t b = __dp2a_lo(B[k], W_C, 32768u);  // 2j-2 (x18), 2j-1 (x34)
+                b = __dp2a_hi(C[k], W_C, b);                // 2j (x48), 2j+1 (x56)
+                b = __dp2a_lo(D[k], W_D, b);                // 2j+2 (x48), 2j+3 (x34)
+                ro[k] = __dp2a_hi(E[k], W_D, b);            // 2j+4 (x18), 2j+5 (x0)
+            }
+            const int y = 2 * j;
+            if (y < h)
+                *reinterpret_cast<uint2*>(dst + (size_t)y * pitch) = make_uint2(pack4(re[0], re[1], re[2], re[3]), pack4(re[4], re[5], re[6], re[7]));
+            if (y + 1 < h)
+                *reinterpret_cast<uint2*>(dst + (size_t)(y + 1) * pitch) = make_uint2(pack4(ro[0], ro[1], ro[2], ro[3]), pack4(ro[4], ro[5], ro[6], ro[7]));
+        }
+    }
+}
 
 __device__ __forceinline__ int reflect101(int p, int len) {
     if ((unsigned)p < (unsigned)len) return p;
@@ -25,116 +140,56 @@ __device__ __forceinline__ int reflect101(int p, int len) {
     return p;
 }
 
-struct BlurTable {
-    int num_levels;
-    int tile_begin[kMaxLevels + 1];
-    int tiles_x[kMaxLevels];
-};
-
-__global__ void __launch_bounds__(256) k_gauss7(const LevelGeom* __restrict__ lvs, BlurTable tab) {
-    __shared__ __align__(16) uint8_t s_in[IN_H][IN_W];
-    __shared__ __align__(16) uint16_t s_h[IN_H][TW];
-
-    int level = 0;
-    while (level + 1 < tab.num_levels && (int)blockIdx.x >= tab.tile_begin[level + 1]) ++level;
-    const LevelGeom lv = lvs[level];
-    const int tile = blockIdx.x - tab.tile_begin[level];
-    const int tx0 = (tile % tab.tiles_x[level]) * TW;
-    const int ty0 = (tile / tab.tiles_x[level]) * TH;
-    const uint8_t* __restrict__ src = lv.img + blockIdx.y * lv.frame_stride;
-    uint8_t* __restrict__ dst = lv.blur + blockIdx.y * lv.frame_stride;
-    const int tid = threadIdx.x;
-
-    // ---- stage the window (rows reflect at the top/bottom, columns at the left/right) ----
-    for (int idx = tid; idx < IN_H * (IN_W / 16); idx += 256) {
-        const int r = idx / (IN_W / 16), v = idx % (IN_W / 16);
-        const int gy = reflect101(ty0 - HALO + r, lv.h);
-        const int gx = tx0 - 16 + 16 * v;
-        const uint8_t* row = src + (size_t)gy * lv.pitch;
-        uint4 val;
-        if (gx >= 0 && gx + 16 <= lv.w) {
-            val = __ldg(reinterpret_cast<const uint4*>(row + gx));
-        }
-        else {
-            uint32_t w4[4] = {0, 0, 0, 0};
-#pragma unroll
-            for (int k = 0; k < 16; ++k) w4[k >> 2] |= (uint32_t)row[reflect101(gx + k, lv.w)] << (8 * (k & 3));
-            val = make_uint4(w4[0], w4[1], w4[2], w4[3]);
-        }
-        *reinterpret_cast<uint4*>(&s_in[r][16 * v]) = val;
+// Writes the BORDER_REFLECT_101 apron (kApron rows above / below, kApron columns left / right) of every level of every
+// frame, so that the blur never mirrors an index. One block per (level, frame).
+__global__ void __launch_bounds__(256) k_pad_borders(const LevelGeom* __restrict__ lvs) {
+    const LevelGeom lv = lvs[blockIdx.x];
+    if (lv.w <= 0 || lv.h <= 0) return;
+    uint8_t* __restrict__ img = lv.img + blockIdx.y * lv.frame_stride;
+    const int w = lv.w, h = lv.h, pitch = lv.pitch;
+    // left / right columns of the real rows
+    for (int i = threadIdx.x; i < h * 2 * kApron; i += 256) {
+        const int y = i / (2 * kApron), c = i % (2 * kApron);
+        const int x = c < kApron ? c - kApron : w + (c - kApron);
+        img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)y * pitch + reflect101(x, w)];
     }
     __syncthreads();
-
-    // ---- horizontal pass: 4 outputs per thread-iteration from 12 staged bytes ----
-    for (int idx = tid; idx < IN_H * (TW / 4); idx += 256) {
-        const int r = idx / (TW / 4), cg = idx % (TW / 4);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(&s_in[r][4 * cg + 12]);
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-        int p[12];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            p[k] = (w0 >> (8 * k)) & 255;
-            p[4 + k] = (w1 >> (8 * k)) & 255;
-            p[8 + k] = (w2 >> (8 * k)) & 255;
-        }
-        // output x (local 4cg + o) is centred on staged byte 16 + 4cg + o = p[4 + o]; taps p[1 + o .. 7 + o]
-        uint32_t h[4];
-#pragma unroll
-        for (int o = 0; o < 4; ++o)
-            h[o] = 18 * (p[1 + o] + p[7 + o]) + 34 * (p[2 + o] + p[6 + o]) + 48 * (p[3 + o] + p[5 + o]) + 56 * p[4 + o];
-        *reinterpret_cast<uint2*>(&s_h[r][4 * cg]) = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
-    }
-    __syncthreads();
-
-    // ---- vertical pass: each thread produces a 4-wide x 4-tall patch ----
-    const int cg = tid % 32, band = tid / 32;
-    const int x = tx0 + 4 * cg;
-    if (x >= lv.w) return;
-    uint32_t hv[10][4];
-#pragma unroll
-    for (int i = 0; i < 10; ++i) {
-        const uint2 q = *reinterpret_cast<const uint2*>(&s_h[band * 4 + i][4 * cg]);
-        hv[i][0] = q.x & 0xFFFF;
-        hv[i][1] = q.x >> 16;
-        hv[i][2] = q.y & 0xFFFF;
-        hv[i][3] = q.y >> 16;
-    }
-#pragma unroll
-    for (int rr = 0; rr < 4; ++rr) {
-        const int y = ty0 + band * 4 + rr;
-        if (y >= lv.h) break;
-        uint32_t packed = 0;
-#pragma unroll
-        for (int o = 0; o < 4; ++o) {
-            const uint32_t v = 18u * (hv[rr][o] + hv[rr + 6][o]) + 34u * (hv[rr + 1][o] + hv[rr + 5][o])
-                               + 48u * (hv[rr + 2][o] + hv[rr + 4][o]) + 56u * hv[rr + 3][o];
-            packed |= ((v + 32768u) >> 16) << (8 * o);
-        }
-        uint8_t* o = dst + (size_t)y * lv.pitch + x;
-        if (x + 4 <= lv.w) {
-            *reinterpret_cast<uint32_t*>(o) = packed;
-        }
-        else {
-            for (int k = 0; x + k < lv.w; ++k) o[k] = (uint8_t)(packed >> (8 * k));
-        }
+    // rows above / below, apron columns included (reads only real rows, whose column apron is complete)
+    const int span = w + 2 * kApron;
+    for (int i = threadIdx.x; i < 2 * kApron * span; i += 256) {
+        const int r = i / span, x = i % span - kApron;
+        const int y = r < kApron ? r - kApron : h + (r - kApron);
+        img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)reflect101(y, h) * pitch + x];
     }
 }
 
 }  // namespace
 
+void launch_pad_borders(const LevelGeom* lv_dev, int num_levels, int batch, cudaStream_t st) {
+    k_pad_borders<<<dim3(num_levels, batch), 256, 0, st>>>(lv_dev);
+}
+
 void launch_blur(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st) {
     BlurTable tab;
     tab.num_levels = num_levels;
+    // rows per thread: long strips amortise the 8-row prologue; short ones keep a small batch spread over the SMs
+    long px = 0;
+    for (int l = 0; l < num_levels; ++l) px += (long)lv_host[l].w * lv_host[l].h;
+    const long threads_at_10 = px * batch / (SW * MACRO_ROWS);
+    int macros = (int)(threads_at_10 / (148L * 2048));
+    macros = macros < 1 ? 1 : (macros > 4 ? 4 : macros);
+    tab.rows_per_thread = macros * MACRO_ROWS;
     int total = 0;
     for (int l = 0; l < num_levels; ++l) {
-        tab.tile_begin[l] = total;
-        const int tx = (lv_host[l].w + TW - 1) / TW, ty = (lv_host[l].h + TH - 1) / TH;
-        tab.tiles_x[l] = tx > 0 ? tx : 1;
-        total += (lv_host[l].w > 0 && lv_host[l].h > 0) ? tx * ty : 0;
+        tab.item_begin[l] = total;
+        const int strips = (lv_host[l].w + SW - 1) / SW;
+        const int blocks = (lv_host[l].h + tab.rows_per_thread - 1) / tab.rows_per_thread;
+        tab.strips[l] = strips > 0 ? strips : 1;
+        total += (lv_host[l].w > 0 && lv_host[l].h > 0) ? strips * blocks : 0;
     }
-    tab.tile_begin[num_levels] = total;
+    for (int l = num_levels; l <= kMaxLevels; ++l) tab.item_begin[l] = total;
     if (total == 0) return;
-    k_gauss7<<<dim3(total, batch), 256, 0, st>>>(lv_dev, tab);
+    k_gauss7<<<dim3((total + BLUR_THREADS - 1) / BLUR_THREADS, batch), BLUR_THREADS, 0, st>>>(lv_dev, tab);
 }
 
 }  // namespace lps

@@ -20,6 +20,11 @@ constexpr int kCell = 64;
 constexpr int kOverlap = 6;
 constexpr int kCellSlots = 1024;  // a 64x64 cell holds at most 32x32 strict 8-neighbourhood maxima
 constexpr int kMaxLevels = 16;
+// Level images live inside a reflected apron (BORDER_REFLECT_101, written by k_pad_borders): kApron rows above and below,
+// kPadLeft bytes left of pixel 0 and at least kPadLeft bytes right of the last pixel of every row. LevelGeom::img / blur
+// point at pixel (0, 0); [-kPadLeft, pitch - kPadLeft) of every row from -kApron to h + kApron - 1 is readable.
+constexpr int kApron = 4;
+constexpr int kPadLeft = 16;
 
 // ---- error plumbing ----
 void set_error(const std::string& msg);
@@ -96,6 +101,7 @@ struct FrameParams {
 void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaStream_t st);
 void launch_copy_level0(const uint8_t* src, size_t src_pitch, size_t src_frame_stride, const LevelGeom& dst, int batch,
                         cudaStream_t st);
+void launch_pad_borders(const LevelGeom* lv_dev_table, int num_levels, int batch, cudaStream_t st);
 void launch_blur(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
 
 struct FastArgs {

@@ -135,8 +135,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
             g.h = (int)std::round(height * 1.0 / sc);
         }
         LPS_ARG(g.w > 0 && g.h > 0, "pyramid level collapses to zero size");
-        g.pitch = (int)align_up(g.w, 64);
-        g.frame_stride = align_up((size_t)g.pitch * g.h, 256);
+        g.pitch = (int)align_up(g.w + 2 * kPadLeft, 64);
+        g.frame_stride = align_up((size_t)g.pitch * (g.h + 2 * kApron), 256);
         g.scale = scale[l];
         g.inv_scale = inv_scale[l];
         g.kp_size = (float)(unsigned)(kPatch * scale[l]);  // orb_extractor.cc:383
@@ -267,8 +267,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
     LPS_CUDA(cudaMalloc(&arena, plan.off));
     arena_bytes = plan.off;
     for (int l = 0; l < L; ++l) {
-        lv[l].img = arena + off_img[l];
-        lv[l].blur = arena + off_blur[l];
+        lv[l].img = arena + off_img[l] + (size_t)kApron * lv[l].pitch + kPadLeft;
+        lv[l].blur = arena + off_blur[l] + (size_t)kApron * lv[l].pitch + kPadLeft;
         if (l > 0) {
             lv[l].xofs = (const int*)(arena + off_xo[l]);
             lv[l].xcoef = (const short2*)(arena + off_xc[l]);
@@ -372,6 +372,7 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     tree.batch = B;
     launch_quadtree(tree, lv, stream);
     mark();  // 3
+    launch_pad_borders(lv_dev, L, B, stream);
     launch_blur(lv_dev, lv, L, B, stream);
     mark();  // 4
     desc.batch = B;

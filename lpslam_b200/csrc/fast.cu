@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
         const int r = idx / (WP / 16), q = idx % (WP / 16);
         uint4 v = make_uint4(0, 0, 0, 0);
         const int gx = c.x0 - 3 + 16 * q;
-        if (r < c.ch && gx + 16 <= lv.pitch) v = __ldg(reinterpret_cast<const uint4*>(img + (size_t)(c.y0 + r) * lv.pitch + gx));
+        if (r < c.ch && gx + 16 <= lv.pitch - kPadLeft) v = __ldg(reinterpret_cast<const uint4*>(img + (size_t)(c.y0 + r) * lv.pitch + gx));
         *reinterpret_cast<uint4*>(&s_win[r][16 * q]) = v;
     }
     for (int idx = tid; idx < (kCell + 2) * BP / 4; idx += 256) reinterpret_cast<uint32_t*>(&s_best[0][0])[idx] = 0;
