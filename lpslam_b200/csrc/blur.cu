@@ -37,24 +37,35 @@ constexpr uint32_t W_B = 0x12223038u;  // bytes (56, 48, 34, 18)
 constexpr uint32_t W_C = 0x38302212u;  // bytes (18, 34, 48, 56)
 constexpr uint32_t W_D = 0x00122230u;  // bytes (48, 34, 18,  0)
 
-// horizontal sums of the 8 pixels at rp[0..8) (apron makes rp[-4..12) readable), started from `init`
-__device__ __forceinline__ void hrow(const uint8_t* __restrict__ rp, uint32_t (&h)[SW]) {
-    const uint32_t wm = __ldg(reinterpret_cast<const uint32_t*>(rp - 4));
+// the four words of a strip row: rp[-4 .. 12) (the apron makes them readable on every strip)
+struct RowWords {
+    uint32_t wm, w0, w1, w2;
+};
+__device__ __forceinline__ RowWords load_row(const uint8_t* __restrict__ rp) {
+    RowWords r;
+    r.wm = __ldg(reinterpret_cast<const uint32_t*>(rp - 4));
     const uint2 w01 = __ldg(reinterpret_cast<const uint2*>(rp));
-    const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(rp + 8));
+    r.w0 = w01.x;
+    r.w1 = w01.y;
+    r.w2 = __ldg(reinterpret_cast<const uint32_t*>(rp + 8));
+    return r;
+}
+
+// horizontal sums of the 8 pixels of a strip row
+__device__ __forceinline__ void hrow(const RowWords& r, uint32_t (&h)[SW]) {
     uint32_t q[12];  // q[k] = bytes p[k-3 .. k]
-    q[3] = w01.x;
-    q[7] = w01.y;
-    q[11] = w2;
-    q[0] = __byte_perm(wm, w01.x, 0x4321);
-    q[1] = __byte_perm(wm, w01.x, 0x5432);
-    q[2] = __byte_perm(wm, w01.x, 0x6543);
-    q[4] = __byte_perm(w01.x, w01.y, 0x4321);
-    q[5] = __byte_perm(w01.x, w01.y, 0x5432);
-    q[6] = __byte_perm(w01.x, w01.y, 0x6543);
-    q[8] = __byte_perm(w01.y, w2, 0x4321);
-    q[9] = __byte_perm(w01.y, w2, 0x5432);
-    q[10] = __byte_perm(w01.y, w2, 0x6543);
+    q[3] = r.w0;
+    q[7] = r.w1;
+    q[11] = r.w2;
+    q[0] = __byte_perm(r.wm, r.w0, 0x4321);
+    q[1] = __byte_perm(r.wm, r.w0, 0x5432);
+    q[2] = __byte_perm(r.wm, r.w0, 0x6543);
+    q[4] = __byte_perm(r.w0, r.w1, 0x4321);
+    q[5] = __byte_perm(r.w0, r.w1, 0x5432);
+    q[6] = __byte_perm(r.w0, r.w1, 0x6543);
+    q[8] = __byte_perm(r.w1, r.w2, 0x4321);
+    q[9] = __byte_perm(r.w1, r.w2, 0x5432);
+    q[10] = __byte_perm(r.w1, r.w2, 0x6543);
 #pragma unroll
     for (int k = 0; k < SW; ++k) h[k] = __dp4a(q[k + 4], W_D, __dp4a(q[k], W_C, 0u));
 }
@@ -80,22 +91,30 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_gauss7(const LevelGeom* __rest
     uint8_t* __restrict__ dst = lvs[level].blur + fofs + s * SW;
     const int last_row = h + 3;  // the apron holds rows -4 .. h + 3
 
-    // row pair m (virtual rows 2m, 2m + 1) of this strip
-    auto load_pair = [&](int m, uint32_t (&p)[SW]) {
-        const int ra = min(2 * m, last_row), rbw = min(2 * m + 1, last_row);
+    // row pair m (virtual rows 2m, 2m + 1) of this strip: the words are fetched one iteration ahead of their use
+    auto fetch_pair = [&](int m, RowWords& a, RowWords& b) {
+        a = load_row(src + (ptrdiff_t)min(2 * m, last_row) * pitch);
+        b = load_row(src + (ptrdiff_t)min(2 * m + 1, last_row) * pitch);
+    };
+    auto make_pair = [&](const RowWords& a, const RowWords& b, uint32_t (&p)[SW]) {
         uint32_t he[SW], ho[SW];
-        hrow(src + (ptrdiff_t)ra * pitch, he);
-        hrow(src + (ptrdiff_t)rbw * pitch, ho);
+        hrow(a, he);
+        hrow(b, ho);
 #pragma unroll
         for (int k = 0; k < SW; ++k) p[k] = __byte_perm(he[k], ho[k], 0x5410);
     };
 
     uint32_t P[5][SW];  // window of row pairs j-2 .. j+2 (rotating: pair m lives in slot m mod 5, relative to the start)
     const int j0 = y0 >> 1;
-    load_pair(j0 - 2, P[0]);
-    load_pair(j0 - 1, P[1]);
-    load_pair(j0, P[2]);
-    load_pair(j0 + 1, P[3]);
+    RowWords na, nb;  // words of the pair the next iteration consumes
+    {
+        RowWords r[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) fetch_pair(j0 - 2 + i, r[2 * i], r[2 * i + 1]);
+        fetch_pair(j0 + 2, na, nb);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) make_pair(r[2 * i], r[2 * i + 1], P[i]);
+    }
 
     const int macros = tab.rows_per_thread / MACRO_ROWS;
     for (int mi = 0; mi < macros; ++mi) {
@@ -109,7 +128,9 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_gauss7(const LevelGeom* __rest
             uint32_t(&C)[SW] = P[(u + 2) % 5];
             uint32_t(&D)[SW] = P[(u + 3) % 5];
             uint32_t(&E)[SW] = P[(u + 4) % 5];
-            load_pair(j + 2, E);
+            const RowWords ca = na, cb = nb;
+            fetch_pair(j + 3, na, nb);
+            make_pair(ca, cb, E);
             uint32_t re[SW], ro[SW];
 #pragma unroll
             for (int k = 0; k < SW; ++k) {
@@ -141,32 +162,39 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 // Writes the BORDER_REFLECT_101 apron (kApron rows above / below, kApron columns left / right) of every level of every
-// frame, so that the blur never mirrors an index. One block per (level, frame).
-__global__ void __launch_bounds__(256) k_pad_borders(const LevelGeom* __restrict__ lvs) {
-    const LevelGeom lv = lvs[blockIdx.x];
-    if (lv.w <= 0 || lv.h <= 0) return;
-    uint8_t* __restrict__ img = lv.img + blockIdx.y * lv.frame_stride;
-    const int w = lv.w, h = lv.h, pitch = lv.pitch;
-    // left / right columns of the real rows
-    for (int i = threadIdx.x; i < h * 2 * kApron; i += 256) {
-        const int y = i / (2 * kApron), c = i % (2 * kApron);
+// frame, so that the blur never mirrors an index. grid = (row chunk, level, frame); every value is read from a real
+// pixel, so the blocks are independent.
+constexpr int PAD_ROWS = 32;
+__global__ void __launch_bounds__(128) k_pad_borders(const LevelGeom* __restrict__ lvs) {
+    const int w = lvs[blockIdx.y].w, h = lvs[blockIdx.y].h, pitch = lvs[blockIdx.y].pitch;
+    const int r0 = (int)blockIdx.x * PAD_ROWS - kApron;
+    if (w <= 0 || h <= 0 || r0 >= h + kApron) return;
+    uint8_t* __restrict__ img = lvs[blockIdx.y].img + blockIdx.z * lvs[blockIdx.y].frame_stride;
+    const int r1 = min(r0 + PAD_ROWS, h + kApron);
+    // left / right apron columns of rows r0 .. r1 (apron rows included)
+    for (int i = threadIdx.x; i < (r1 - r0) * 2 * kApron; i += 128) {
+        const int y = r0 + i / (2 * kApron), c = i % (2 * kApron);
         const int x = c < kApron ? c - kApron : w + (c - kApron);
-        img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)y * pitch + reflect101(x, w)];
+        img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)reflect101(y, h) * pitch + reflect101(x, w)];
     }
-    __syncthreads();
-    // rows above / below, apron columns included (reads only real rows, whose column apron is complete)
-    const int span = w + 2 * kApron;
-    for (int i = threadIdx.x; i < 2 * kApron * span; i += 256) {
-        const int r = i / span, x = i % span - kApron;
-        const int y = r < kApron ? r - kApron : h + (r - kApron);
-        img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)reflect101(y, h) * pitch + x];
+    // apron rows: mirrored copies of real rows
+    for (int y = r0; y < r1; ++y) {
+        if (y >= 0 && y < h) continue;
+        const uint8_t* __restrict__ s = img + (ptrdiff_t)reflect101(y, h) * pitch;
+        uint8_t* __restrict__ d = img + (ptrdiff_t)y * pitch;
+        for (int x4 = threadIdx.x; x4 < w / 4; x4 += 128)  // rows start 16-byte aligned
+            reinterpret_cast<uint32_t*>(d)[x4] = reinterpret_cast<const uint32_t*>(s)[x4];
+        if (threadIdx.x < (w & 3)) d[(w & ~3) + threadIdx.x] = s[(w & ~3) + threadIdx.x];
     }
 }
 
 }  // namespace
 
-void launch_pad_borders(const LevelGeom* lv_dev, int num_levels, int batch, cudaStream_t st) {
-    k_pad_borders<<<dim3(num_levels, batch), 256, 0, st>>>(lv_dev);
+void launch_pad_borders(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st) {
+    int hmax = 0;
+    for (int l = 0; l < num_levels; ++l) hmax = lv_host[l].h > hmax ? lv_host[l].h : hmax;
+    if (hmax <= 0) return;
+    k_pad_borders<<<dim3((hmax + 2 * kApron + PAD_ROWS - 1) / PAD_ROWS, num_levels, batch), 128, 0, st>>>(lv_dev);
 }
 
 void launch_blur(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st) {
@@ -175,9 +203,9 @@ void launch_blur(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_leve
     // rows per thread: long strips amortise the 8-row prologue; short ones keep a small batch spread over the SMs
     long px = 0;
     for (int l = 0; l < num_levels; ++l) px += (long)lv_host[l].w * lv_host[l].h;
-    const long threads_at_10 = px * batch / (SW * MACRO_ROWS);
-    int macros = (int)(threads_at_10 / (148L * 2048));
-    macros = macros < 1 ? 1 : (macros > 4 ? 4 : macros);
+    const long threads_at_10 = px * batch / (SW * MACRO_ROWS);  // threads if every thread took one macro
+    int macros = (int)(threads_at_10 / (148L * 1024));
+    macros = macros < 1 ? 1 : (macros > 8 ? 8 : macros);
     tab.rows_per_thread = macros * MACRO_ROWS;
     int total = 0;
     for (int l = 0; l < num_levels; ++l) {

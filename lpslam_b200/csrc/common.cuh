@@ -101,7 +101,7 @@ struct FrameParams {
 void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaStream_t st);
 void launch_copy_level0(const uint8_t* src, size_t src_pitch, size_t src_frame_stride, const LevelGeom& dst, int batch,
                         cudaStream_t st);
-void launch_pad_borders(const LevelGeom* lv_dev_table, int num_levels, int batch, cudaStream_t st);
+void launch_pad_borders(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
 void launch_blur(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
 
 struct FastArgs {

@@ -372,7 +372,7 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     tree.batch = B;
     launch_quadtree(tree, lv, stream);
     mark();  // 3
-    launch_pad_borders(lv_dev, L, B, stream);
+    launch_pad_borders(lv_dev, lv, L, B, stream);
     launch_blur(lv_dev, lv, L, B, stream);
     mark();  // 4
     desc.batch = B;
