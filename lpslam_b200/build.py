@@ -10,7 +10,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "liblpslam_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall",
-         "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+         "--expt-relaxed-constexpr", "-Xptxas", "-v"] + os.environ.get("LPSLAM_NVCC_FLAGS", "").split()
 
 
 def sources():

@@ -143,11 +143,9 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_gauss7(const LevelGeom* __rest
                 b = __dp2a_lo(D[k], W_D, b);                // 2j+2 (x48), 2j+3 (x34)
                 ro[k] = __dp2a_hi(E[k], W_D, b);            // 2j+4 (x18), 2j+5 (x0)
             }
-            const int y = 2 * j;
-            if (y < h)
-                *reinterpret_cast<uint2*>(dst + (size_t)y * pitch) = make_uint2(pack4(re[0], re[1], re[2], re[3]), pack4(re[4], re[5], re[6], re[7]));
-            if (y + 1 < h)
-                *reinterpret_cast<uint2*>(dst + (size_t)(y + 1) * pitch) = make_uint2(pack4(ro[0], ro[1], ro[2], ro[3]), pack4(ro[4], ro[5], ro[6], ro[7]));
+            // rows past the image are parked in apron row h of the blurred level: no branch in the loop body
+            *reinterpret_cast<uint2*>(dst + (size_t)min(2 * j, h) * pitch) = make_uint2(pack4(re[0], re[1], re[2], re[3]), pack4(re[4], re[5], re[6], re[7]));
+            *reinterpret_cast<uint2*>(dst + (size_t)min(2 * j + 1, h) * pitch) = make_uint2(pack4(ro[0], ro[1], ro[2], ro[3]), pack4(ro[4], ro[5], ro[6], ro[7]));
         }
     }
 }
@@ -162,39 +160,65 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 // Writes the BORDER_REFLECT_101 apron (kApron rows above / below, kApron columns left / right) of every level of every
-// frame, so that the blur never mirrors an index. grid = (row chunk, level, frame); every value is read from a real
-// pixel, so the blocks are independent.
-constexpr int PAD_ROWS = 32;
-__global__ void __launch_bounds__(128) k_pad_borders(const LevelGeom* __restrict__ lvs) {
+// frame, so that the blur never mirrors an index. grid = (row block | apron row, level, frame). Every value is read from a
+// real pixel, so blocks are independent: in the first `row_blocks` blocks a thread owns one row (apron rows included) and
+// writes its 2 x kApron apron bytes; each of the last 2 x kApron blocks copies one mirrored apron row.
+constexpr int PAD_THREADS = 128;
+__global__ void __launch_bounds__(PAD_THREADS) k_pad_borders(const LevelGeom* __restrict__ lvs, int row_blocks, uint32_t level_mask) {
+    if (!((level_mask >> blockIdx.y) & 1u)) return;
     const int w = lvs[blockIdx.y].w, h = lvs[blockIdx.y].h, pitch = lvs[blockIdx.y].pitch;
-    const int r0 = (int)blockIdx.x * PAD_ROWS - kApron;
-    if (w <= 0 || h <= 0 || r0 >= h + kApron) return;
+    if (w <= 0 || h <= 0) return;
     uint8_t* __restrict__ img = lvs[blockIdx.y].img + blockIdx.z * lvs[blockIdx.y].frame_stride;
-    const int r1 = min(r0 + PAD_ROWS, h + kApron);
-    // left / right apron columns of rows r0 .. r1 (apron rows included)
-    for (int i = threadIdx.x; i < (r1 - r0) * 2 * kApron; i += 128) {
-        const int y = r0 + i / (2 * kApron), c = i % (2 * kApron);
-        const int x = c < kApron ? c - kApron : w + (c - kApron);
-        img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)reflect101(y, h) * pitch + reflect101(x, w)];
-    }
-    // apron rows: mirrored copies of real rows
-    for (int y = r0; y < r1; ++y) {
-        if (y >= 0 && y < h) continue;
+    if ((int)blockIdx.x < row_blocks) {
+        const int y = (int)blockIdx.x * PAD_THREADS + threadIdx.x - kApron;
+        if (y >= h + kApron) return;
         const uint8_t* __restrict__ s = img + (ptrdiff_t)reflect101(y, h) * pitch;
         uint8_t* __restrict__ d = img + (ptrdiff_t)y * pitch;
-        for (int x4 = threadIdx.x; x4 < w / 4; x4 += 128)  // rows start 16-byte aligned
-            reinterpret_cast<uint32_t*>(d)[x4] = reinterpret_cast<const uint32_t*>(s)[x4];
-        if (threadIdx.x < (w & 3)) d[(w & ~3) + threadIdx.x] = s[(w & ~3) + threadIdx.x];
+        uint8_t l[kApron], r[kApron];
+        if (w > kApron + 1) {  // the usual case: no repeated mirroring
+#pragma unroll
+            for (int c = 0; c < kApron; ++c) {
+                l[c] = s[1 + c];
+                r[c] = s[w - 2 - c];
+            }
+        }
+        else {
+#pragma unroll
+            for (int c = 0; c < kApron; ++c) {
+                l[c] = s[reflect101(-1 - c, w)];
+                r[c] = s[reflect101(w + c, w)];
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < kApron; ++c) {
+            d[-1 - c] = l[c];
+            d[w + c] = r[c];
+        }
+        return;
     }
+    const int a = (int)blockIdx.x - row_blocks;  // 0 .. 2 * kApron - 1
+    const int y = a < kApron ? a - kApron : h + (a - kApron);
+    const uint8_t* __restrict__ s = img + (ptrdiff_t)reflect101(y, h) * pitch;
+    uint8_t* __restrict__ d = img + (ptrdiff_t)y * pitch;
+    for (int x4 = threadIdx.x; x4 < w / 4; x4 += PAD_THREADS)  // rows start 16-byte aligned
+        reinterpret_cast<uint32_t*>(d)[x4] = reinterpret_cast<const uint32_t*>(s)[x4];
+    if ((int)threadIdx.x < (w & 3)) d[(w & ~3) + threadIdx.x] = s[(w & ~3) + threadIdx.x];
 }
 
 }  // namespace
 
-void launch_pad_borders(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st) {
-    int hmax = 0;
-    for (int l = 0; l < num_levels; ++l) hmax = lv_host[l].h > hmax ? lv_host[l].h : hmax;
+void launch_pad_borders(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_levels, uint32_t level_mask, int batch,
+                        cudaStream_t st) {
+    int hmax = 0, top = 0;
+    for (int l = 0; l < num_levels; ++l)
+        if ((level_mask >> l) & 1u) {
+            hmax = lv_host[l].h > hmax ? lv_host[l].h : hmax;
+            top = l + 1;
+        }
+    num_levels = top;
     if (hmax <= 0) return;
-    k_pad_borders<<<dim3((hmax + 2 * kApron + PAD_ROWS - 1) / PAD_ROWS, num_levels, batch), 128, 0, st>>>(lv_dev);
+    const int row_blocks = (hmax + 2 * kApron + PAD_THREADS - 1) / PAD_THREADS;
+    k_pad_borders<<<dim3(row_blocks + 2 * kApron, num_levels, batch), PAD_THREADS, 0, st>>>(lv_dev, row_blocks, level_mask);
 }
 
 void launch_blur(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st) {
@@ -205,7 +229,7 @@ void launch_blur(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_leve
     for (int l = 0; l < num_levels; ++l) px += (long)lv_host[l].w * lv_host[l].h;
     const long threads_at_10 = px * batch / (SW * MACRO_ROWS);  // threads if every thread took one macro
     int macros = (int)(threads_at_10 / (148L * 1024));
-    macros = macros < 1 ? 1 : (macros > 8 ? 8 : macros);
+    macros = macros < 1 ? 1 : (macros > 4 ? 4 : macros);
     tab.rows_per_thread = macros * MACRO_ROWS;
     int total = 0;
     for (int l = 0; l < num_levels; ++l) {

@@ -67,6 +67,9 @@ struct LevelGeom {
     const short2* xcoef; // (c0, c1), 11-bit fixed point
     const int* yofs;
     const short2* ycoef;
+    // row schedule of the column-walk resize over the apron-extended rows v = -kApron .. h + kApron + 1 (index v + kApron):
+    // x = lower source row, y = upper source row (both clamped), z = b0 | b1 << 16, w = 1 when x differs from the upper row of v - 1
+    const int4* rowtab;
     int mode;            // 0 = general bilinear, 1 = exact 2x2 decimation (OpenCV routes it to INTER_AREA), 2 = same size copy
     // FAST cell grid of the level
     int cell_begin, cell_cols, cell_rows;  // first cell in the per-frame cell table, grid extent (only cells the reference visits)
@@ -101,7 +104,10 @@ struct FrameParams {
 void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaStream_t st);
 void launch_copy_level0(const uint8_t* src, size_t src_pitch, size_t src_frame_stride, const LevelGeom& dst, int batch,
                         cudaStream_t st);
-void launch_pad_borders(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
+// apron of the levels in `level_mask` (bit l); the column-walk resize writes the apron of its own output
+void launch_pad_borders(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, uint32_t level_mask, int batch,
+                        cudaStream_t st);
+bool resize_writes_apron(const LevelGeom& src, const LevelGeom& dst);
 void launch_blur(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
 
 struct FastArgs {

@@ -120,7 +120,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
     cells.clear();
     memset(lv, 0, sizeof lv);
     ArenaPlan plan;
-    std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L);
+    std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L), off_rt(L);
+    std::vector<std::vector<int4>> rowtab(L);
     int cand_total = 0, node_total = 0, sel_total = 0;
     for (int l = 0; l < L; ++l) {
         LevelGeom& g = lv[l];
@@ -154,6 +155,25 @@ int lpslam_orb_ctx::configure(int width, int height) {
             off_xc[l] = plan.take(xc[l].size() * 4);
             off_yo[l] = plan.take(yofs[l].size() * 4);
             off_yc[l] = plan.take(yc[l].size() * 4);
+            // apron-extended row schedule (mirrored rows use the tables of the row they mirror)
+            auto mirror = [](int v, int n) {
+                if (n == 1) return 0;
+                while (v < 0 || v >= n) v = v < 0 ? -v : 2 * (n - 1) - v;
+                return v;
+            };
+            rowtab[l].resize(g.h + 2 * kApron + 2);
+            int prev_up = -1;
+            for (int i = 0; i < (int)rowtab[l].size(); ++i) {
+                const int v = mirror(std::min(i - kApron, g.h + kApron - 1), g.h);
+                int4 e;
+                e.x = std::min(std::max(yofs[l][v], 0), p.h - 1);
+                e.y = std::min(std::max(yofs[l][v] + 1, 0), p.h - 1);
+                e.z = (int)((uint32_t)(uint16_t)yc[l][v].x | ((uint32_t)(uint16_t)yc[l][v].y << 16));
+                e.w = e.x != prev_up;
+                prev_up = e.y;
+                rowtab[l][i] = e;
+            }
+            off_rt[l] = plan.take(rowtab[l].size() * sizeof(int4));
         }
         // ---- FAST cell grid, feature/orb_extractor.cc:293-332 ----
         g.cell_begin = (int)cells.size();
@@ -274,6 +294,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
             lv[l].xcoef = (const short2*)(arena + off_xc[l]);
             lv[l].yofs = (const int*)(arena + off_yo[l]);
             lv[l].ycoef = (const short2*)(arena + off_yc[l]);
+            lv[l].rowtab = (const int4*)(arena + off_rt[l]);
+            LPS_CUDA(cudaMemcpyAsync(arena + off_rt[l], rowtab[l].data(), rowtab[l].size() * sizeof(int4), cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_xo[l], xofs[l].data(), xofs[l].size() * 4, cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_xc[l], xc[l].data(), xc[l].size() * 4, cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_yo[l], yofs[l].data(), yofs[l].size() * 4, cudaMemcpyHostToDevice, stream));
@@ -354,7 +376,11 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
         if (timing) cudaEventRecord(ev[e++], stream);
     };
     mark();  // 0: start of pyramid
+    uint32_t pad_mask = 1u;  // level 0 arrives without its apron; so do levels made by the exact-half / copy / wide-ratio paths
+    for (int l = 1; l < L; ++l)
+        if (!resize_writes_apron(lv[l - 1], lv[l])) pad_mask |= 1u << l;
     for (int l = 1; l < L; ++l) launch_resize(lv[l - 1], lv[l], B, stream);
+    launch_pad_borders(lv_dev, lv, L, pad_mask, B, stream);
     mark();  // 1
     FastArgs fa;
     fa.lv = lv_dev;
@@ -372,7 +398,6 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     tree.batch = B;
     launch_quadtree(tree, lv, stream);
     mark();  // 3
-    launch_pad_borders(lv_dev, lv, L, B, stream);
     launch_blur(lv_dev, lv, L, B, stream);
     mark();  // 4
     desc.batch = B;

@@ -77,6 +77,140 @@ __global__ void __launch_bounds__(256) k_resize_linear(LevelGeom src, LevelGeom 
     }
 }
 
+// ---- column-walk bilinear kernel (the production path for scale factors below 3) -------------------------------------
+// Instruction diet (budget at 60 % of HBM: ~22 issue slots per destination pixel, the first version spent ~46):
+//   * a thread owns 4 destination columns (two 2-pixel windows) and walks down a band of destination rows; the row
+//     schedule (which source rows a destination row needs, the row coefficients) depends on the block only, so it runs
+//     on the uniform datapath and branches never diverge;
+//   * the two source bytes of a destination pixel sit in a thread-private 8-byte window (two aligned words, loop
+//     invariant offset); one PRMT cuts them out and one IDP.2A applies the coefficient pair (c0, c1);
+//   * horizontal sums are kept as H >> 4 and reused by the next destination row when it shares the source row;
+//   * vertical: two IMUL, one PRMT that gathers both products' upper halves ((b * Hs) >> 16) and one IDP.2A with weights
+//     (64, 64) and addend 128 = ((t0 + t1 + 2) << 6): the output byte is byte 1 of that sum, no clamp is needed;
+//   * the words of the source rows the NEXT destination row needs are fetched before the current row is computed.
+__device__ __forceinline__ int reflect101(int p, int len) {
+    if ((unsigned)p < (unsigned)len) return p;
+    if (len == 1) return 0;
+    do {
+        p = p < 0 ? -p : 2 * (len - 1) - p;
+    } while ((unsigned)p >= (unsigned)len);
+    return p;
+}
+
+#ifndef LPS_RW_PX
+#define LPS_RW_PX 8
+#endif
+constexpr int RW_PX = LPS_RW_PX;  // destination pixels per thread (4 or 8)
+constexpr int RW_NW = RW_PX / 2;  // 2-pixel windows per thread
+
+struct Window {  // loop-invariant description of one 2-pixel window
+    int base;            // byte offset of the first aligned word inside a source row
+    uint32_t sel0, sel1; // PRMT selectors cutting (p[sx], p[sx + 1]) out of the two words
+    uint32_t c0, c1;     // coefficient pairs (c0 | c1 << 16)
+};
+struct RowW {  // the words of one source row for all windows of a thread
+    uint32_t lo[RW_NW], hi[RW_NW];
+};
+
+__global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom dst, int rows_per_block) {
+    // The destination domain is the level PLUS its reflected apron: columns [-RW_PX, w + kApron), rows [-kApron, h + kApron).
+    // An apron pixel is computed like the real pixel it mirrors (same tables, same arithmetic), so no separate border
+    // pass and no divergent edge code is needed.
+    const int strip = blockIdx.x * blockDim.x + threadIdx.x;
+    const int x0 = (strip - 1) * RW_PX;
+    const bool live = x0 < dst.w + kApron;
+    const uint8_t* __restrict__ s = src.img + blockIdx.z * src.frame_stride;
+    uint8_t* __restrict__ d = dst.img + blockIdx.z * dst.frame_stride + x0;
+    const int spitch = src.pitch, dpitch = dst.pitch;
+
+    Window wd[RW_NW];
+#pragma unroll
+    for (int g = 0; g < RW_NW; ++g) {
+        const int xa = reflect101(x0 + 2 * g, dst.w), xb = reflect101(x0 + 2 * g + 1, dst.w);
+        const int sa = dst.xofs[xa], sb = dst.xofs[xb];
+        const short2 ca = dst.xcoef[xa], cb = dst.xcoef[xb];
+        const int base = min(sa, sb) & ~3;
+        wd[g].base = base;
+        const uint32_t oa = (uint32_t)min(sa - base, 6), ob = (uint32_t)min(sb - base, 6);  // the launcher guarantees <= 6
+        wd[g].sel0 = oa | ((oa + 1) << 4);
+        wd[g].sel1 = ob | ((ob + 1) << 4);
+        wd[g].c0 = (uint32_t)(uint16_t)ca.x | ((uint32_t)(uint16_t)ca.y << 16);
+        wd[g].c1 = (uint32_t)(uint16_t)cb.x | ((uint32_t)(uint16_t)cb.y << 16);
+    }
+    const int y0 = blockIdx.y * rows_per_block - kApron;
+    const int y1 = min(y0 + rows_per_block, dst.h + kApron);
+    const int4* __restrict__ rt = dst.rowtab + kApron;  // rt[v]: schedule of (apron-extended) destination row v
+
+    auto fetch = [&](int r, RowW& w) {
+        const uint32_t off = (uint32_t)r * (uint32_t)spitch;
+#pragma unroll
+        for (int g = 0; g < RW_NW; ++g) {
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(s + (off + wd[g].base));  // 4-byte aligned window
+            w.lo[g] = __ldg(wp);
+            w.hi[g] = __ldg(wp + 1);
+        }
+    };
+    auto hsum = [&](const RowW& w, uint32_t (&h)[RW_PX]) {  // H >> 4 of the thread's pixels on one source row
+#pragma unroll
+        for (int g = 0; g < RW_NW; ++g) {
+            h[2 * g] = __dp2a_lo(wd[g].c0, __byte_perm(w.lo[g], w.hi[g], wd[g].sel0), 0u) >> 4;
+            h[2 * g + 1] = __dp2a_lo(wd[g].c1, __byte_perm(w.lo[g], w.hi[g], wd[g].sel1), 0u) >> 4;
+        }
+    };
+
+    // One step = one destination row. L / U hold H >> 4 of its lower / upper source row. Every step flips the roles of
+    // the two register sets: after a step the old U is the new L (the usual case, the source advances by one row) and
+    // the old L receives the new upper row, whose words were fetched two steps earlier. When the source advances
+    // differently (about one step in six at scale 1.2, in the mirrored apron rows, at the clamped bottom), the new L is
+    // reloaded as well. e1 = schedule of row y + 1; the schedule of y + 2 is read here and handed to the next step.
+    auto step = [&](int y, uint32_t coef, const int4 e1, int4& e2, uint32_t (&L)[RW_PX], uint32_t (&U)[RW_PX], RowW& up_next,
+                    RowW& up_after) {
+        e2 = __ldg(rt + y + 2);
+        fetch(e2.y, up_after);  // upper row of y + 2, consumed at the end of the next step
+        const uint32_t b0 = coef & 0xFFFFu, b1 = coef >> 16;
+        uint32_t sum[RW_PX];
+#pragma unroll
+        for (int k = 0; k < RW_PX; ++k)
+            sum[k] = __dp2a_lo(__byte_perm(b0 * L[k], b1 * U[k], 0x7632), 0x4040u, 128u);  // (t0 + t1 + 2) << 6
+        if (live) {  // columns past w + kApron of the last strip land in the unused part of the row pad
+#pragma unroll
+            for (int q = 0; q < RW_PX / 4; ++q)
+                reinterpret_cast<uint32_t*>(d + (ptrdiff_t)y * dpitch)[q] =
+                    __byte_perm(__byte_perm(sum[4 * q], sum[4 * q + 1], 0x5151), __byte_perm(sum[4 * q + 2], sum[4 * q + 3], 0x5151), 0x5410);
+        }
+        hsum(up_next, L);  // roles for y + 1: L' = U, U' = L
+        if (e1.w) {        // block-uniform, rare
+            RowW lw;
+            fetch(e1.x, lw);
+            hsum(lw, U);
+        }
+    };
+
+    uint32_t A[RW_PX], B[RW_PX];
+    RowW w0, w1;
+    int4 ea = __ldg(rt + y0), eb = __ldg(rt + y0 + 1);
+    {
+        RowW wa, wb;
+        fetch(ea.x, wa);
+        fetch(ea.y, wb);
+        fetch(eb.y, w0);
+        hsum(wa, A);
+        hsum(wb, B);
+    }
+    int y = y0;
+    for (; y + 1 < y1; y += 2) {
+        int4 ec, ed;
+        step(y, (uint32_t)ea.z, eb, ec, A, B, w0, w1);
+        step(y + 1, (uint32_t)eb.z, ec, ed, B, A, w1, w0);
+        ea = ec;
+        eb = ed;
+    }
+    if (y < y1) {
+        int4 ec;
+        step(y, (uint32_t)ea.z, eb, ec, A, B, w0, w1);
+    }
+}
+
 // exact 2x decimation: OpenCV's INTER_LINEAR takes the INTER_AREA fast path, (a + b + c + d + 2) >> 2
 __global__ void __launch_bounds__(256) k_resize_half(LevelGeom src, LevelGeom dst) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -107,6 +241,8 @@ __global__ void __launch_bounds__(256) k_copy2d(const uint8_t* __restrict__ src,
 
 }  // namespace
 
+bool resize_writes_apron(const LevelGeom& src, const LevelGeom& dst) { return dst.mode == 0 && src.w < 3 * dst.w; }
+
 void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaStream_t st) {
     if (dst.w <= 0 || dst.h <= 0) return;
     if (dst.mode == 2) {
@@ -117,6 +253,26 @@ void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaSt
         dim3 blk(32, 8);
         dim3 grd((dst.w + 31) / 32, (dst.h + 7) / 8, batch);
         k_resize_half<<<grd, blk, 0, st>>>(src, dst);
+        return;
+    }
+    if (src.w < 3 * dst.w) {
+        // block width: the candidate that wastes the fewest lanes on the last column tile
+        const int strips = 1 + (dst.w + kApron + RW_PX - 1) / RW_PX;  // one strip left of column 0 for the left apron
+        const int vrows = dst.h + 2 * kApron;
+        int best_t = 128, best_waste = 1 << 30;
+        for (int t = 64; t <= 256; t += 32) {
+            const int waste = (strips + t - 1) / t * t - strips;
+            if (waste < best_waste || (waste == best_waste && t == 128)) {
+                best_waste = waste;
+                best_t = t;
+            }
+        }
+        // band height: long walks amortise the per-thread set-up, short ones keep a small batch spread over the SMs
+        const long threads_per_row_of_bands = (long)((strips + best_t - 1) / best_t) * best_t * batch;
+        int rows = 64;
+        while (rows > 8 && threads_per_row_of_bands * ((vrows + rows - 1) / rows) < 148L * 2048) rows >>= 1;
+        dim3 grd((strips + best_t - 1) / best_t, (vrows + rows - 1) / rows, batch);
+        k_resize_walk<<<grd, best_t, 0, st>>>(src, dst, rows);
         return;
     }
     dim3 blk(32, 8);
