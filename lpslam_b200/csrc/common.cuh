@@ -67,9 +67,10 @@ struct LevelGeom {
     const short2* xcoef; // (c0, c1), 11-bit fixed point
     const int* yofs;
     const short2* ycoef;
-    // row schedule of the column-walk resize over the apron-extended rows v = -kApron .. h + kApron + 1 (index v + kApron):
-    // x = lower source row, y = upper source row (both clamped), z = b0 | b1 << 16, w = 1 when x differs from the upper row of v - 1
-    const int4* rowtab;
+    // schedule of the column-walk resize, indexed by SOURCE row r = 0 .. src.h (r = src.h stands for the clamped row
+    // src.h - 1): x = destination row completed by the source rows (r - 1, r), or -1; y = its row coefficients b0 | b1 << 16
+    const int2* srctab;
+    int walk_ok;         // the column-walk kernel applies (down-scaling by less than 3 in x, monotonic rows)
     int mode;            // 0 = general bilinear, 1 = exact 2x2 decimation (OpenCV routes it to INTER_AREA), 2 = same size copy
     // FAST cell grid of the level
     int cell_begin, cell_cols, cell_rows;  // first cell in the per-frame cell table, grid extent (only cells the reference visits)

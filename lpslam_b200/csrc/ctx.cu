@@ -121,7 +121,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
     memset(lv, 0, sizeof lv);
     ArenaPlan plan;
     std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L), off_rt(L);
-    std::vector<std::vector<int4>> rowtab(L);
+    std::vector<std::vector<int2>> rowtab(L);
     int cand_total = 0, node_total = 0, sel_total = 0;
     for (int l = 0; l < L; ++l) {
         LevelGeom& g = lv[l];
@@ -155,25 +155,18 @@ int lpslam_orb_ctx::configure(int width, int height) {
             off_xc[l] = plan.take(xc[l].size() * 4);
             off_yo[l] = plan.take(yofs[l].size() * 4);
             off_yc[l] = plan.take(yc[l].size() * 4);
-            // apron-extended row schedule (mirrored rows use the tables of the row they mirror)
-            auto mirror = [](int v, int n) {
-                if (n == 1) return 0;
-                while (v < 0 || v >= n) v = v < 0 ? -v : 2 * (n - 1) - v;
-                return v;
-            };
-            rowtab[l].resize(g.h + 2 * kApron + 2);
-            int prev_up = -1;
-            for (int i = 0; i < (int)rowtab[l].size(); ++i) {
-                const int v = mirror(std::min(i - kApron, g.h + kApron - 1), g.h);
-                int4 e;
-                e.x = std::min(std::max(yofs[l][v], 0), p.h - 1);
-                e.y = std::min(std::max(yofs[l][v] + 1, 0), p.h - 1);
-                e.z = (int)((uint32_t)(uint16_t)yc[l][v].x | ((uint32_t)(uint16_t)yc[l][v].y << 16));
-                e.w = e.x != prev_up;
-                prev_up = e.y;
-                rowtab[l][i] = e;
+            // source-row schedule of the column-walk resize
+            rowtab[l].assign(p.h + 2, make_int2(-1, 0));
+            g.walk_ok = g.mode == 0 && p.w < 3 * g.w && p.h >= g.h && g.h > kApron + 1 && g.w > 1;
+            for (int y = 0; y < g.h && g.walk_ok; ++y) {
+                const int r = yofs[l][y] + 1;
+                if (yofs[l][y] < 0 || r > p.h || rowtab[l][r].x >= 0) {
+                    g.walk_ok = 0;
+                    break;
+                }
+                rowtab[l][r] = make_int2(y, (int)((uint32_t)(uint16_t)yc[l][y].x | ((uint32_t)(uint16_t)yc[l][y].y << 16)));
             }
-            off_rt[l] = plan.take(rowtab[l].size() * sizeof(int4));
+            off_rt[l] = plan.take(rowtab[l].size() * sizeof(int2));
         }
         // ---- FAST cell grid, feature/orb_extractor.cc:293-332 ----
         g.cell_begin = (int)cells.size();
@@ -294,8 +287,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
             lv[l].xcoef = (const short2*)(arena + off_xc[l]);
             lv[l].yofs = (const int*)(arena + off_yo[l]);
             lv[l].ycoef = (const short2*)(arena + off_yc[l]);
-            lv[l].rowtab = (const int4*)(arena + off_rt[l]);
-            LPS_CUDA(cudaMemcpyAsync(arena + off_rt[l], rowtab[l].data(), rowtab[l].size() * sizeof(int4), cudaMemcpyHostToDevice, stream));
+            lv[l].srctab = (const int2*)(arena + off_rt[l]);
+            LPS_CUDA(cudaMemcpyAsync(arena + off_rt[l], rowtab[l].data(), rowtab[l].size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_xo[l], xofs[l].data(), xofs[l].size() * 4, cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_xc[l], xc[l].data(), xc[l].size() * 4, cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_yo[l], yofs[l].data(), yofs[l].size() * 4, cudaMemcpyHostToDevice, stream));

@@ -97,6 +97,9 @@ __device__ __forceinline__ int reflect101(int p, int len) {
     return p;
 }
 
+#ifndef LPS_RW_MIN_THREADS
+#define LPS_RW_MIN_THREADS (148L * 2048)
+#endif
 #ifndef LPS_RW_PX
 #define LPS_RW_PX 8
 #endif
@@ -104,7 +107,7 @@ constexpr int RW_PX = LPS_RW_PX;  // destination pixels per thread (4 or 8)
 constexpr int RW_NW = RW_PX / 2;  // 2-pixel windows per thread
 
 struct Window {  // loop-invariant description of one 2-pixel window
-    int base;            // byte offset of the first aligned word inside a source row
+    const uint8_t* ptr;  // first aligned word of the window in source row 0 of this frame
     uint32_t sel0, sel1; // PRMT selectors cutting (p[sx], p[sx + 1]) out of the two words
     uint32_t c0, c1;     // coefficient pairs (c0 | c1 << 16)
 };
@@ -116,36 +119,47 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
     // The destination domain is the level PLUS its reflected apron: columns [-RW_PX, w + kApron), rows [-kApron, h + kApron).
     // An apron pixel is computed like the real pixel it mirrors (same tables, same arithmetic), so no separate border
     // pass and no divergent edge code is needed.
-    const int strip = blockIdx.x * blockDim.x + threadIdx.x;
-    const int x0 = (strip - 1) * RW_PX;
-    const bool live = x0 < dst.w + kApron;
+    // Lane mapping: a warp owns RW_PX * 32 consecutive destination columns; window g of lane i covers the two columns
+    // 64 g + 2 i (+1) of them, so that ONE warp-wide load touches the source bytes of 64 consecutive destination columns
+    // (77 contiguous bytes at scale 1.2: a single L1 wavefront instead of three or four).
+    const int warp_x0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (RW_PX * 32) - 2 * kApron;
+    const int lane2 = 2 * (int)(threadIdx.x & 31);
     const uint8_t* __restrict__ s = src.img + blockIdx.z * src.frame_stride;
-    uint8_t* __restrict__ d = dst.img + blockIdx.z * dst.frame_stride + x0;
+    uint8_t* __restrict__ d = dst.img + blockIdx.z * dst.frame_stride + warp_x0 + lane2;  // window g stores at d + 64 g
     const int spitch = src.pitch, dpitch = dst.pitch;
+    bool live[RW_NW];
 
     Window wd[RW_NW];
 #pragma unroll
     for (int g = 0; g < RW_NW; ++g) {
-        const int xa = reflect101(x0 + 2 * g, dst.w), xb = reflect101(x0 + 2 * g + 1, dst.w);
+        const int xg = warp_x0 + 64 * g + lane2;
+        live[g] = xg < dst.w + kApron;
+        const int xa = reflect101(xg, dst.w), xb = reflect101(xg + 1, dst.w);
         const int sa = dst.xofs[xa], sb = dst.xofs[xb];
         const short2 ca = dst.xcoef[xa], cb = dst.xcoef[xb];
         const int base = min(sa, sb) & ~3;
-        wd[g].base = base;
+        wd[g].ptr = s + base;
         const uint32_t oa = (uint32_t)min(sa - base, 6), ob = (uint32_t)min(sb - base, 6);  // the launcher guarantees <= 6
         wd[g].sel0 = oa | ((oa + 1) << 4);
         wd[g].sel1 = ob | ((ob + 1) << 4);
         wd[g].c0 = (uint32_t)(uint16_t)ca.x | ((uint32_t)(uint16_t)ca.y << 16);
         wd[g].c1 = (uint32_t)(uint16_t)cb.x | ((uint32_t)(uint16_t)cb.y << 16);
     }
-    const int y0 = blockIdx.y * rows_per_block - kApron;
-    const int y1 = min(y0 + rows_per_block, dst.h + kApron);
-    const int4* __restrict__ rt = dst.rowtab + kApron;  // rt[v]: schedule of (apron-extended) destination row v
+    // Band of destination rows [y0, y1). The walk is over SOURCE rows: every iteration consumes one source row (its
+    // words were fetched two iterations earlier), writes its H >> 4 into the register set that held the row before
+    // last, and, when the schedule says that (r - 1, r) completes a destination row, emits it. The two sets swap roles
+    // every iteration, so nothing is ever moved, and the control flow is the same for the whole block.
+    const int y0 = blockIdx.y * rows_per_block;
+    const int y1 = min(y0 + rows_per_block, dst.h);
+    const int smax = src.h - 1;
+    const int r_first = dst.yofs[y0], r_last = dst.yofs[y1 - 1] + 1;
+    const int2* __restrict__ tab = dst.srctab;
 
     auto fetch = [&](int r, RowW& w) {
-        const uint32_t off = (uint32_t)r * (uint32_t)spitch;
+        const uint32_t off = (uint32_t)min(r, smax) * (uint32_t)spitch;
 #pragma unroll
         for (int g = 0; g < RW_NW; ++g) {
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(s + (off + wd[g].base));  // 4-byte aligned window
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(wd[g].ptr + off);  // 4-byte aligned window
             w.lo[g] = __ldg(wp);
             w.hi[g] = __ldg(wp + 1);
         }
@@ -157,58 +171,50 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
             h[2 * g + 1] = __dp2a_lo(wd[g].c1, __byte_perm(w.lo[g], w.hi[g], wd[g].sel1), 0u) >> 4;
         }
     };
-
-    // One step = one destination row. L / U hold H >> 4 of its lower / upper source row. Every step flips the roles of
-    // the two register sets: after a step the old U is the new L (the usual case, the source advances by one row) and
-    // the old L receives the new upper row, whose words were fetched two steps earlier. When the source advances
-    // differently (about one step in six at scale 1.2, in the mirrored apron rows, at the clamped bottom), the new L is
-    // reloaded as well. e1 = schedule of row y + 1; the schedule of y + 2 is read here and handed to the next step.
-    auto step = [&](int y, uint32_t coef, const int4 e1, int4& e2, uint32_t (&L)[RW_PX], uint32_t (&U)[RW_PX], RowW& up_next,
-                    RowW& up_after) {
-        e2 = __ldg(rt + y + 2);
-        fetch(e2.y, up_after);  // upper row of y + 2, consumed at the end of the next step
-        const uint32_t b0 = coef & 0xFFFFu, b1 = coef >> 16;
-        uint32_t sum[RW_PX];
+    // source row r arrives in `buf`; Lo holds row r - 1; Up receives row r
+    auto step = [&](int r, uint32_t (&Lo)[RW_PX], uint32_t (&Up)[RW_PX], RowW& buf) {
+        hsum(buf, Up);
+        fetch(r + 2, buf);
+        const int2 e = __ldg(tab + r);
+        if (e.x >= y0 && e.x < y1) {  // block-uniform
+            const uint32_t b0 = (uint32_t)e.y & 0xFFFFu, b1 = (uint32_t)e.y >> 16;
+            uint32_t sum[RW_PX];
+            uint16_t out[RW_NW];
 #pragma unroll
-        for (int k = 0; k < RW_PX; ++k)
-            sum[k] = __dp2a_lo(__byte_perm(b0 * L[k], b1 * U[k], 0x7632), 0x4040u, 128u);  // (t0 + t1 + 2) << 6
-        if (live) {  // columns past w + kApron of the last strip land in the unused part of the row pad
+            for (int k = 0; k < RW_PX; ++k)
+                sum[k] = __dp2a_lo(__byte_perm(b0 * Lo[k], b1 * Up[k], 0x7632), 0x4040u, 128u);  // (t0 + t1 + 2) << 6
 #pragma unroll
-            for (int q = 0; q < RW_PX / 4; ++q)
-                reinterpret_cast<uint32_t*>(d + (ptrdiff_t)y * dpitch)[q] =
-                    __byte_perm(__byte_perm(sum[4 * q], sum[4 * q + 1], 0x5151), __byte_perm(sum[4 * q + 2], sum[4 * q + 3], 0x5151), 0x5410);
-        }
-        hsum(up_next, L);  // roles for y + 1: L' = U, U' = L
-        if (e1.w) {        // block-uniform, rare
-            RowW lw;
-            fetch(e1.x, lw);
-            hsum(lw, U);
+            for (int g = 0; g < RW_NW; ++g) out[g] = (uint16_t)__byte_perm(sum[2 * g], sum[2 * g + 1], 0x4451);  // byte 1 of each
+            const int y = e.x;
+            // apron rows are copies of the real rows they mirror (BORDER_REFLECT_101: row -k = row k, row h-1+k = row h-1-k)
+            const bool top = y >= 1 && y <= kApron, bot = y >= dst.h - 1 - kApron && y <= dst.h - 2;
+#pragma unroll
+            for (int g = 0; g < RW_NW; ++g) {
+                if (live[g]) {  // columns past w + kApron land in the unused part of the row pad or are skipped
+                    uint8_t* o = d + 64 * g;
+                    *reinterpret_cast<uint16_t*>(o + (ptrdiff_t)y * dpitch) = out[g];
+                    if (top) *reinterpret_cast<uint16_t*>(o - (ptrdiff_t)y * dpitch) = out[g];
+                    if (bot) *reinterpret_cast<uint16_t*>(o + (ptrdiff_t)(2 * (dst.h - 1) - y) * dpitch) = out[g];
+                }
+            }
         }
     };
 
     uint32_t A[RW_PX], B[RW_PX];
     RowW w0, w1;
-    int4 ea = __ldg(rt + y0), eb = __ldg(rt + y0 + 1);
     {
-        RowW wa, wb;
-        fetch(ea.x, wa);
-        fetch(ea.y, wb);
-        fetch(eb.y, w0);
+        RowW wa;
+        fetch(r_first, wa);
+        fetch(r_first + 1, w0);
+        fetch(r_first + 2, w1);
         hsum(wa, A);
-        hsum(wb, B);
     }
-    int y = y0;
-    for (; y + 1 < y1; y += 2) {
-        int4 ec, ed;
-        step(y, (uint32_t)ea.z, eb, ec, A, B, w0, w1);
-        step(y + 1, (uint32_t)eb.z, ec, ed, B, A, w1, w0);
-        ea = ec;
-        eb = ed;
+    int r = r_first + 1;
+    for (; r + 1 <= r_last; r += 2) {
+        step(r, A, B, w0);
+        step(r + 1, B, A, w1);
     }
-    if (y < y1) {
-        int4 ec;
-        step(y, (uint32_t)ea.z, eb, ec, A, B, w0, w1);
-    }
+    if (r <= r_last) step(r, A, B, w0);
 }
 
 // exact 2x decimation: OpenCV's INTER_LINEAR takes the INTER_AREA fast path, (a + b + c + d + 2) >> 2
@@ -241,7 +247,10 @@ __global__ void __launch_bounds__(256) k_copy2d(const uint8_t* __restrict__ src,
 
 }  // namespace
 
-bool resize_writes_apron(const LevelGeom& src, const LevelGeom& dst) { return dst.mode == 0 && src.w < 3 * dst.w; }
+bool resize_writes_apron(const LevelGeom& src, const LevelGeom& dst) {
+    (void)src;
+    return dst.walk_ok != 0;
+}
 
 void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaStream_t st) {
     if (dst.w <= 0 || dst.h <= 0) return;
@@ -255,10 +264,11 @@ void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaSt
         k_resize_half<<<grd, blk, 0, st>>>(src, dst);
         return;
     }
-    if (src.w < 3 * dst.w) {
+    if (dst.walk_ok) {
         // block width: the candidate that wastes the fewest lanes on the last column tile
-        const int strips = 1 + (dst.w + kApron + RW_PX - 1) / RW_PX;  // one strip left of column 0 for the left apron
-        const int vrows = dst.h + 2 * kApron;
+        // columns -2 kApron .. w + kApron in units of a thread's RW_PX pixels (a warp owns RW_PX * 32 consecutive columns)
+        const int strips = ((dst.w + 3 * kApron + RW_PX * 32 - 1) / (RW_PX * 32)) * 32;
+        const int vrows = dst.h;
         int best_t = 128, best_waste = 1 << 30;
         for (int t = 64; t <= 256; t += 32) {
             const int waste = (strips + t - 1) / t * t - strips;
@@ -270,7 +280,7 @@ void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaSt
         // band height: long walks amortise the per-thread set-up, short ones keep a small batch spread over the SMs
         const long threads_per_row_of_bands = (long)((strips + best_t - 1) / best_t) * best_t * batch;
         int rows = 64;
-        while (rows > 8 && threads_per_row_of_bands * ((vrows + rows - 1) / rows) < 148L * 2048) rows >>= 1;
+        while (rows > 8 && threads_per_row_of_bands * ((vrows + rows - 1) / rows) < LPS_RW_MIN_THREADS) rows >>= 1;
         dim3 grd((strips + best_t - 1) / best_t, (vrows + rows - 1) / rows, batch);
         k_resize_walk<<<grd, best_t, 0, st>>>(src, dst, rows);
         return;
