@@ -1,0 +1,54 @@
+"""GPU: the C++ drop-in layer (cpp/openvslam/feature/orb_extractor.h + orb_extractor_cuda.cc, match/stereo_cuda.cc) driven
+exactly as the reference drives its own classes (tracking_module.cc:78-94, data/frame.cc:55-93), compared with the oracle.
+The harness binary is built by cpp/Makefile in the build container (it needs the reference headers) and travels with gpurun."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from lpslam_b200.synth import synth_stereo_pair
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "cpp", "build", "dropin_smoke")
+FX_B, B = 700.0 * 0.12, 0.12
+KP = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+
+
+def test_dropin_classes_match_oracle(oracle, tmp_path):
+    if not os.path.exists(BIN):
+        pytest.skip("cpp/build/dropin_smoke not built (needs /root/reference at build time)")
+    h, w, n = 360, 640, 800
+    left, right = synth_stereo_pair(h, w, 4242)
+    lp, rp, out = tmp_path / "l.raw", tmp_path / "r.raw", tmp_path / "out.bin"
+    left.tofile(lp)
+    right.tofile(rp)
+    r = subprocess.run([BIN, str(w), str(h), str(n), str(lp), str(rp), str(out), repr(FX_B), repr(B)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    raw = open(out, "rb").read()
+    nl, nr = np.frombuffer(raw, np.uint32, 2)
+    o = 8
+    kl = np.frombuffer(raw, KP, nl, o); o += 28 * nl
+    dl = np.frombuffer(raw, np.uint8, 32 * nl, o).reshape(-1, 32); o += 32 * nl
+    kr = np.frombuffer(raw, KP, nr, o); o += 28 * nr
+    dr = np.frombuffer(raw, np.uint8, 32 * nr, o).reshape(-1, 32); o += 32 * nr
+    xr = np.frombuffer(raw, np.float32, nl, o); o += 4 * nl
+    dep = np.frombuffer(raw, np.float32, nl, o); o += 4 * nl
+    pw, ph = np.frombuffer(raw, np.int32, 2, o); o += 8
+    p3 = np.frombuffer(raw, np.uint8, pw * ph, o).reshape(ph, pw)
+
+    ol, orr = oracle.extractor(max_kpts=n), oracle.extractor(max_kpts=n)
+    okl, odl = ol.extract(left)
+    okr, odr = orr.extract(right)
+    assert nl == len(okl) and nr == len(okr)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(kl[f], okl[f]) and np.array_equal(kr[f], okr[f]), f
+    assert np.abs(kl["angle"] - okl["angle"]).max() <= 1e-4 * 180 / np.pi
+    assert (dl == odl).all(axis=1).mean() >= 0.999 and (dr == odr).all(axis=1).mean() >= 0.999
+    assert np.array_equal(p3, ol.level(3))  # image_pyramid_ side effect (orb_extractor.h:76)
+    oxr, odep = oracle.match_stereo([ol.level(l) for l in range(8)], [orr.level(l) for l in range(8)], okl, okr, odl, odr,
+                                    ol.table(0), ol.table(1), FX_B, B)
+    if (dl == odl).all() and (dr == odr).all():
+        assert np.array_equal(xr, oxr) and np.array_equal(dep, odep)
+    assert (xr >= 0).sum() > 50
