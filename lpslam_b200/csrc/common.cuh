@@ -80,6 +80,12 @@ struct LevelGeom {
     double dx, dy;      // initial node extents
     int depth;          // digits (2 bits each) in the path key
     int rbits;          // bits of the initial-node index in the key
+    // integer-only statement of the initial-node assignment (orb_extractor.cc:532-539): node column of every border-relative
+    // x (qix[x] = unsigned(float(x) / dx)), node row of every y, and the node boundaries int(dx * i), int(dy * i)
+    const uint16_t* qix;
+    const uint16_t* qiy;
+    const int* qbx;     // nx + 1 entries
+    const int* qby;     // ny + 1 entries
     int cand_begin;     // first candidate slot of the level in the per-frame candidate scratch
     int cand_cap;       // cell_count * kCellSlots
     int node_begin, node_cap;

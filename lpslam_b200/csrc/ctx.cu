@@ -122,6 +122,9 @@ int lpslam_orb_ctx::configure(int width, int height) {
     ArenaPlan plan;
     std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L), off_rt(L);
     std::vector<std::vector<int2>> rowtab(L);
+    std::vector<std::vector<uint16_t>> qix(L), qiy(L);
+    std::vector<std::vector<int>> qbx(L), qby(L);
+    std::vector<size_t> off_qix(L), off_qiy(L), off_qbx(L), off_qby(L);
     int cand_total = 0, node_total = 0, sel_total = 0;
     for (int l = 0; l < L; ++l) {
         LevelGeom& g = lv[l];
@@ -231,6 +234,22 @@ int lpslam_orb_ctx::configure(int width, int height) {
             g.dx = g.dy = 1.0;
             g.depth = 1;
         }
+        {   // initial-node lookup tables: the double division of the reference, done once on the host
+            const int ext_x = std::max(g.w - 2 * kBorder, 1), ext_y = std::max(g.h - 2 * kBorder, 1);
+            qix[l].resize(ext_x + 1);
+            qiy[l].resize(ext_y + 1);
+            for (int x = 0; x <= ext_x; ++x) qix[l][x] = (uint16_t)std::min<unsigned>((unsigned)((double)(float)x / g.dx), 65535u);
+            for (int y = 0; y <= ext_y; ++y) qiy[l][y] = (uint16_t)std::min<unsigned>((unsigned)((double)(float)y / g.dy), 65535u);
+            const int maxix = *std::max_element(qix[l].begin(), qix[l].end()), maxiy = *std::max_element(qiy[l].begin(), qiy[l].end());
+            qbx[l].resize(std::max(g.nx, maxix + 1) + 1);
+            qby[l].resize(std::max(g.ny, maxiy + 1) + 1);
+            for (size_t i = 0; i < qbx[l].size(); ++i) qbx[l][i] = (int)(g.dx * (unsigned)i);
+            for (size_t i = 0; i < qby[l].size(); ++i) qby[l][i] = (int)(g.dy * (unsigned)i);
+            off_qix[l] = plan.take(qix[l].size() * 2);
+            off_qiy[l] = plan.take(qiy[l].size() * 2);
+            off_qbx[l] = plan.take(qbx[l].size() * 4);
+            off_qby[l] = plan.take(qby[l].size() * 4);
+        }
         const int ncl = g.cell_cols * g.cell_rows;
         g.cand_begin = cand_total;
         g.cand_cap = ncl * kCellSlots;
@@ -282,6 +301,14 @@ int lpslam_orb_ctx::configure(int width, int height) {
     for (int l = 0; l < L; ++l) {
         lv[l].img = arena + off_img[l] + (size_t)kApron * lv[l].pitch + kPadLeft;
         lv[l].blur = arena + off_blur[l] + (size_t)kApron * lv[l].pitch + kPadLeft;
+        lv[l].qix = (const uint16_t*)(arena + off_qix[l]);
+        lv[l].qiy = (const uint16_t*)(arena + off_qiy[l]);
+        lv[l].qbx = (const int*)(arena + off_qbx[l]);
+        lv[l].qby = (const int*)(arena + off_qby[l]);
+        LPS_CUDA(cudaMemcpyAsync(arena + off_qix[l], qix[l].data(), qix[l].size() * 2, cudaMemcpyHostToDevice, stream));
+        LPS_CUDA(cudaMemcpyAsync(arena + off_qiy[l], qiy[l].data(), qiy[l].size() * 2, cudaMemcpyHostToDevice, stream));
+        LPS_CUDA(cudaMemcpyAsync(arena + off_qbx[l], qbx[l].data(), qbx[l].size() * 4, cudaMemcpyHostToDevice, stream));
+        LPS_CUDA(cudaMemcpyAsync(arena + off_qby[l], qby[l].data(), qby[l].size() * 4, cudaMemcpyHostToDevice, stream));
         if (l > 0) {
             lv[l].xofs = (const int*)(arena + off_xo[l]);
             lv[l].xcoef = (const short2*)(arena + off_xc[l]);

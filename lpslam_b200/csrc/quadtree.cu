@@ -21,8 +21,9 @@ namespace lps {
 namespace {
 
 constexpr int QT = 1024;           // threads per block
-constexpr int RADIX_BITS = 4;
+constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int POOL_CACHE = 16 * 1024;  // pool counts cached in shared memory (words)
 constexpr int F_LEAF = 1 << 8, F_POOL = 1 << 9, DEPTH_MASK = 0xFF;
 
 struct Scan {
@@ -81,11 +82,10 @@ __device__ __forceinline__ void split_node(const uint32_t* __restrict__ keys, in
 }
 
 __device__ __forceinline__ uint32_t path_key(int x, int y, const LevelGeom& lv) {
-    // initial node: orb_extractor.cc:532-539 (float coordinate / double extent, truncated)
-    const unsigned ix = (unsigned)((double)(float)x / lv.dx);
-    const unsigned iy = (unsigned)((double)(float)y / lv.dy);
-    int bx = (int)(lv.dx * ix), ex = (int)(lv.dx * (ix + 1));
-    int by = (int)(lv.dy * iy), ey = (int)(lv.dy * (iy + 1));
+    // initial node: orb_extractor.cc:532-539 (float coordinate / double extent, truncated) through the host-built tables
+    const unsigned ix = lv.qix[x], iy = lv.qiy[y];
+    int bx = lv.qbx[ix], ex = lv.qbx[ix + 1];
+    int by = lv.qby[iy], ey = lv.qby[iy + 1];
     uint32_t key = ix + iy * lv.nx;
     for (int d = 0; d < lv.depth; ++d) {
         const int hx = (ex - bx + 1) >> 1, hy = (ey - by + 1) >> 1;  // cvCeil(extent / 2.0)
@@ -169,42 +169,66 @@ __global__ void __launch_bounds__(QT, 1) k_quadtree(TreeArgs a) {
     __syncthreads();
 
     // ------------------------------------------------------------------ B. LSD radix sort by path key (stable)
+    // 8 bits per pass. Warp w owns the contiguous segment [w * seg, (w + 1) * seg) and walks it 32 keys at a time with
+    // coalesced loads; inside a round the rank of a key among the equal digits of its warp comes from __match_any_sync,
+    // so order is preserved: earlier segments, earlier rounds, lower lanes first. Counters live in shared memory as
+    // [digit][warp] (pitch 33: leaders of one warp hit different banks).
     const int keybits = 2 * lv.depth + lv.rbits;
-    const int chunk = (N + QT - 1) / QT;
-    const int my_lo = min(N, tid * chunk), my_hi = min(N, (tid + 1) * chunk);
+    const int seg = ((N + QT - 1) / QT) * 32;
+    const int seg_lo = min(N, warp * seg), seg_hi = min(N, (warp + 1) * seg);
+    uint32_t* s_cntr = s_dyn;  // RADIX * 33 words
     int cur = 0;
     for (int shift = 0; shift < keybits; shift += RADIX_BITS) {
         const uint32_t* __restrict__ kin = keys[cur];
         const uint32_t* __restrict__ vin = vals[cur];
         uint32_t* __restrict__ kout = keys[cur ^ 1];
         uint32_t* __restrict__ vout = vals[cur ^ 1];
-#pragma unroll
-        for (int d = 0; d < RADIX; ++d) s_dyn[pad_idx(d * QT + tid)] = 0;
-        for (int k = my_lo; k < my_hi; ++k) s_dyn[pad_idx((int)((kin[k] >> shift) & (RADIX - 1)) * QT + tid)]++;
+        for (int i = tid; i < RADIX * 33; i += QT) s_cntr[i] = 0;
         __syncthreads();
-        // exclusive scan over (digit-major, thread-minor): thread j owns linear entries [16 j, 16 j + 16)
-        unsigned loc[RADIX];
-        unsigned sum = 0;
-#pragma unroll
-        for (int e = 0; e < RADIX; ++e) {
-            loc[e] = s_dyn[pad_idx(tid * RADIX + e)];
-            sum += loc[e];
-        }
-        unsigned long long tot;
-        unsigned run = (unsigned)scan.excl(sum, tot);
-#pragma unroll
-        for (int e = 0; e < RADIX; ++e) {
-            s_dyn[pad_idx(tid * RADIX + e)] = run;
-            run += loc[e];
+        for (int base = seg_lo; base < seg_hi; base += 32) {
+            const int k = base + lane;
+            const bool ok = k < seg_hi;
+            const unsigned d = ok ? ((kin[k] >> shift) & (RADIX - 1)) : RADIX;  // inactive lanes form their own group
+            const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
+            if (ok && (peers & ((1u << lane) - 1)) == 0) s_cntr[d * 33 + warp] += __popc(peers);
+            __syncwarp();
         }
         __syncthreads();
-        for (int k = my_lo; k < my_hi; ++k) {
-            const uint32_t key = kin[k];
-            const int slot = pad_idx((int)((key >> shift) & (RADIX - 1)) * QT + tid);
-            const unsigned pos = s_dyn[slot];
-            s_dyn[slot] = pos + 1;
-            kout[pos] = key;
-            vout[pos] = vin[k];
+        // exclusive scan in (digit major, warp minor) order: thread t owns digit t / 4, warps 8 (t % 4) .. + 8
+        {
+            const int d = tid >> 2, w0 = (tid & 3) * 8;
+            unsigned loc[8], sum = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                loc[e] = s_cntr[d * 33 + w0 + e];
+                sum += loc[e];
+            }
+            unsigned long long tot;
+            unsigned run = (unsigned)scan.excl(sum, tot);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                s_cntr[d * 33 + w0 + e] = run;
+                run += loc[e];
+            }
+        }
+        __syncthreads();
+        for (int base = seg_lo; base < seg_hi; base += 32) {
+            const int k = base + lane;
+            const bool ok = k < seg_hi;
+            const uint32_t key = ok ? kin[k] : 0u;
+            const uint32_t val = ok ? vin[k] : 0u;
+            const unsigned d = ok ? ((key >> shift) & (RADIX - 1)) : RADIX;
+            const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
+            const unsigned before = __popc(peers & ((1u << lane) - 1));
+            unsigned pos = 0;
+            if (ok) pos = s_cntr[d * 33 + warp] + before;
+            __syncwarp();
+            if (ok) {
+                if (before == 0) s_cntr[d * 33 + warp] += __popc(peers);
+                kout[pos] = key;
+                vout[pos] = val;
+            }
+            __syncwarp();
         }
         __syncthreads();
         cur ^= 1;
@@ -321,7 +345,7 @@ __global__ void __launch_bounds__(QT, 1) k_quadtree(TreeArgs a) {
 
     // ------------------------------------------------------------------ E. fullest-first splitting (orb_extractor.cc:447-475)
     int* s_cnt = reinterpret_cast<int*>(s_dyn);  // pool counts cached in shared memory when they fit
-    const int s_cnt_cap = RADIX * QT;
+    const int s_cnt_cap = POOL_CACHE;
     while (!filled) {
         const int prev = m;
         // pool = nodes created by the previous pass / round holding more than one keypoint, in list order
@@ -462,7 +486,7 @@ __global__ void __launch_bounds__(QT, 1) k_quadtree(TreeArgs a) {
 
 void launch_quadtree(const TreeArgs& a, const LevelGeom* lv_host, cudaStream_t st) {
     (void)lv_host;
-    const size_t smem = (size_t)(RADIX * QT + (RADIX * QT) / 32 + 32) * sizeof(uint32_t);
+    const size_t smem = (size_t)(POOL_CACHE > RADIX * 33 ? POOL_CACHE : RADIX * 33) * sizeof(uint32_t);
     cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_quadtree<<<dim3(a.num_levels, a.batch), QT, smem, st>>>(a);
 }
