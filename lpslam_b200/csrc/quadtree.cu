@@ -20,7 +20,10 @@ namespace lps {
 
 namespace {
 
-constexpr int QT = 1024;           // threads per block
+#ifndef LPS_QT_THREADS
+#define LPS_QT_THREADS 512
+#endif
+constexpr int QT = LPS_QT_THREADS;  // threads per block (two resident blocks per SM at 512)
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int POOL_CACHE = 16 * 1024;  // pool counts cached in shared memory (words)
@@ -40,7 +43,7 @@ struct Scan {
         if (lane == 31) warp_tot[warp] = inc;
         __syncthreads();
         if (warp == 0) {
-            const unsigned long long w = warp_tot[lane];
+            const unsigned long long w = lane < (int)(blockDim.x >> 5) ? warp_tot[lane] : 0ull;
             unsigned long long wi = w;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -99,12 +102,13 @@ __device__ __forceinline__ uint32_t path_key(int x, int y, const LevelGeom& lv) 
 
 __device__ __forceinline__ int pad_idx(int lin) { return lin + (lin >> 5); }
 
-__global__ void __launch_bounds__(QT, 1) k_quadtree(TreeArgs a) {
+__global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(TreeArgs a) {
     extern __shared__ uint32_t s_dyn[];  // RADIX * QT counters (padded) during the sort, pool counts afterwards
     __shared__ unsigned long long s_scan[33];
     __shared__ int s_i[4];
 
-    const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // grid = (frame, level): the blocks of the fullest level (0) are scheduled first, the light ones fill the tail
+    const int level = blockIdx.y, frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LevelGeom lv = a.lv[level];
     Scan scan{s_scan};
 
@@ -196,7 +200,7 @@ __global__ void __launch_bounds__(QT, 1) k_quadtree(TreeArgs a) {
         __syncthreads();
         // exclusive scan in (digit major, warp minor) order: thread t owns digit t / 4, warps 8 (t % 4) .. + 8
         {
-            const int d = tid >> 2, w0 = (tid & 3) * 8;
+            const int d = tid / (QT / RADIX), w0 = (tid % (QT / RADIX)) * 8;  // (QT / 32) warps = (QT / RADIX) threads x 8
             unsigned loc[8], sum = 0;
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -488,7 +492,7 @@ void launch_quadtree(const TreeArgs& a, const LevelGeom* lv_host, cudaStream_t s
     (void)lv_host;
     const size_t smem = (size_t)(POOL_CACHE > RADIX * 33 ? POOL_CACHE : RADIX * 33) * sizeof(uint32_t);
     cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_quadtree<<<dim3(a.num_levels, a.batch), QT, smem, st>>>(a);
+    k_quadtree<<<dim3(a.batch, a.num_levels), QT, smem, st>>>(a);
 }
 
 }  // namespace lps
