@@ -41,7 +41,10 @@ __device__ __forceinline__ int arc9_maxmin(const int (&d)[16]) {
     return best;
 }
 
-__global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
+#ifndef LPS_FAST_MINBLOCKS
+#define LPS_FAST_MINBLOCKS 6
+#endif
+__global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs a) {
     __shared__ __align__(16) uint8_t s_win[WIN][WP];
     __shared__ __align__(16) uint8_t s_best[kCell + 2][BP];  // [1 + ly][1 + lx], zero apron
     __shared__ uint32_t s_bits[kCell][2];      // kept-pixel bitmap per interior row
@@ -51,6 +54,8 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
     __shared__ uint32_t s_pass[kCell][2];
     __shared__ int s_wbase[2 * kCell];
     __shared__ uint16_t s_list[kCell * kCell];
+    __shared__ uint16_t s_corner[kCell * kCell];
+    __shared__ int s_ncorner;
 
     const int cell_id = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
     const CellDesc c = a.cells[cell_id];
@@ -148,7 +153,10 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
             s_wbase[4 * lane + 1] = ex + c0;
             s_wbase[4 * lane + 2] = ex + c0 + c1;
             s_wbase[4 * lane + 3] = ex + c0 + c1 + c2;
-            if (lane == 31) s_nlist = inc;
+            if (lane == 31) {
+                s_nlist = inc;
+                s_ncorner = 0;
+            }
         }
         __syncthreads();
         if (tid < 128) {
@@ -176,44 +184,47 @@ __global__ void __launch_bounds__(256) k_fast_cells(FastArgs a) {
             RING(8, -3 * WP);     RING(9, -3 * WP - 1);  RING(10, -2 * WP - 2); RING(11, -WP - 3);
             RING(12, -3);         RING(13, WP - 3);      RING(14, 2 * WP - 2);  RING(15, 3 * WP - 1);
 #undef RING
-            uint32_t lo2[16], hi2[16], lo4[16], hi4[16];
+            // min / max over every window of 9 consecutive ring values = 3-input min / max of three triples
+            uint32_t lo3[16], hi3[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) {
-                lo2[k] = __vminu2(d[k], d[(k + 1) & 15]);
-                hi2[k] = __vmaxu2(d[k], d[(k + 1) & 15]);
+                lo3[k] = __vimin3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+                hi3[k] = __vimax3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
             }
+            uint32_t lo9[16], hi9[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) {
-                lo4[k] = __vminu2(lo2[k], lo2[(k + 2) & 15]);
-                hi4[k] = __vmaxu2(hi2[k], hi2[(k + 2) & 15]);
+                lo9[k] = __vimin3_u16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+                hi9[k] = __vimax3_u16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
             }
-            uint32_t A = 0u, Bm = 0xFFFFFFFFu;
+            uint32_t A = __vimax3_u16x2(lo9[0], lo9[1], lo9[2]), Bm = __vimin3_u16x2(hi9[0], hi9[1], hi9[2]);
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const uint32_t lo9 = __vminu2(__vminu2(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
-                const uint32_t hi9 = __vmaxu2(__vmaxu2(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
-                A = __vmaxu2(A, lo9);
-                Bm = __vminu2(Bm, hi9);
+            for (int k = 3; k < 15; k += 2) {
+                A = __vimax3_u16x2(A, lo9[k], lo9[k + 1]);
+                Bm = __vimin3_u16x2(Bm, hi9[k], hi9[k + 1]);
             }
+            A = __vmaxu2(A, lo9[15]);
+            Bm = __vminu2(Bm, hi9[15]);
             // halves hold d + 256: best = max(A - 256, 256 - Bm)
             const int ba = max((int)(A & 0xFFFFu) - 256, 256 - (int)(Bm & 0xFFFFu));
             const int bb = max((int)(A >> 16) - 256, 256 - (int)(Bm >> 16));
             s_best[(ida >> 6) + 1][(ida & 63) + 1] = (uint8_t)max(ba, 0);
             s_best[(idb >> 6) + 1][(idb & 63) + 1] = (uint8_t)max(bb, 0);
+            // corners go into a second list: only they are looked at by the suppression
+            if (ba > thr) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)ida;
+            if (bb > thr && 2 * i + 1 < n) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)idb;
         }
         __syncthreads();
-        // 3. suppression around listed pixels
-        for (int i = tid; i < n; i += 256) {
-            const int id = s_list[i], lx = id & 63, ly = id >> 6;
+        // 3. suppression around the corners (every other pixel scores 0)
+        const int nc = s_ncorner;
+        for (int i = tid; i < nc; i += 256) {
+            const int id = s_corner[i], lx = id & 63, ly = id >> 6;
             const uint8_t* b = &s_best[ly + 1][lx + 1];
-            const int best = b[0];
-            if (best > thr) {
-                const int s = best - 1;
-                auto sc = [thr](int v) { return v > thr ? v - 1 : 0; };
-                const bool keep = s > sc(b[-1]) && s > sc(b[1]) && s > sc(b[-BP - 1]) && s > sc(b[-BP]) && s > sc(b[-BP + 1])
-                                  && s > sc(b[BP - 1]) && s > sc(b[BP]) && s > sc(b[BP + 1]);
-                if (keep) atomicOr(&s_bits[ly][lx >> 5], 1u << (lx & 31));
-            }
+            const int s = b[0] - 1;
+            auto sc = [thr](int v) { return v > thr ? v - 1 : 0; };
+            const bool keep = s > sc(b[-1]) && s > sc(b[1]) && s > sc(b[-BP - 1]) && s > sc(b[-BP]) && s > sc(b[-BP + 1])
+                              && s > sc(b[BP - 1]) && s > sc(b[BP]) && s > sc(b[BP + 1]);
+            if (keep) atomicOr(&s_bits[ly][lx >> 5], 1u << (lx & 31));
         }
         __syncthreads();
         if (tid < 32) {
