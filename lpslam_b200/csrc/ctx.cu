@@ -295,6 +295,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
     const size_t off_sxr = plan.take(4 * (size_t)out_cap);
     const size_t off_sdep = plan.take(4 * (size_t)out_cap);
     const size_t off_scorr = plan.take(4 * (size_t)out_cap);
+    const size_t off_sperm = plan.take(4 * (size_t)out_cap);
+    const size_t off_srows = plan.take(4 * (size_t)(height + 1) * ((max_batch + 1) / 2));
 
     LPS_CUDA(cudaMalloc(&arena, plan.off));
     arena_bytes = plan.off;
@@ -381,6 +383,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
     stereo.x_right = (float*)(arena + off_sxr);
     stereo.depth = (float*)(arena + off_sdep);
     stereo.corr = (int*)(arena + off_scorr);
+    stereo.perm = (uint32_t*)(arena + off_sperm);
+    stereo.row_start = (uint32_t*)(arena + off_srows);
     stereo.rows0 = height;
     LPS_CUDA(cudaStreamSynchronize(stream));  // the host-side tables go out of scope
     w = width;

@@ -42,6 +42,57 @@ __global__ void __launch_bounds__(256) k_stereo_prep(StereoArgs a) {
     }
 }
 
+// Right-eye keypoints of one pair ordered by image row (counting sort on floor(y)): the candidates of a left keypoint at row
+// y are then a contiguous slice of `perm` (rows y - R .. y + R, R = the largest half interval), not the whole right eye.
+__global__ void __launch_bounds__(1024) k_stereo_rows(StereoArgs a) {
+    extern __shared__ uint32_t s_rows[];  // rows0 + 1 counters, then cursors
+    __shared__ uint32_t s_part[33];
+    const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t rbeg = min(a.frame_off[2 * pair + 1], a.max_rows), rend = min(a.frame_off[2 * pair + 2], a.max_rows);
+    const int rows = a.rows0;
+    for (int r = tid; r <= rows; r += 1024) s_rows[r] = 0;
+    __syncthreads();
+    for (uint32_t k = rbeg + tid; k < rend; k += 1024) atomicAdd(&s_rows[min(max((int)a.kp[k].y, 0), rows - 1)], 1u);
+    __syncthreads();
+    // exclusive scan over rows: every thread owns a contiguous chunk
+    const int chunk = (rows + 1 + 1023) / 1024;
+    const int c0 = min(tid * chunk, rows + 1), c1 = min(c0 + chunk, rows + 1);
+    uint32_t sum = 0;
+    for (int r = c0; r < c1; ++r) sum += s_rows[r];
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_part[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = s_part[lane];
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        s_part[lane] = wi - w;
+    }
+    __syncthreads();
+    uint32_t run = s_part[warp] + inc - sum;
+    uint32_t* __restrict__ rs = a.row_start + (size_t)pair * (rows + 1);
+    for (int r = c0; r < c1; ++r) {
+        const uint32_t c = s_rows[r];
+        s_rows[r] = run;
+        rs[r] = run;
+        run += c;
+    }
+    __syncthreads();
+    for (uint32_t k = rbeg + tid; k < rend; k += 1024) {
+        const uint32_t pos = atomicAdd(&s_rows[min(max((int)a.kp[k].y, 0), rows - 1)], 1u);
+        a.perm[rbeg + pos] = k;
+    }
+}
+
 __device__ __forceinline__ unsigned hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
     return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x)
            + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
@@ -53,6 +104,8 @@ __global__ void __launch_bounds__(256) k_stereo_match(StereoArgs a) {
     const int n_frames = 2 * a.n_pairs;
     const uint32_t total = min(a.frame_off[n_frames], a.max_rows);
     const float max_disp = __fdiv_rn(a.focal_x_baseline, a.true_baseline), min_disp = 0.0f;  // match/stereo.cc:16
+    // a right keypoint at y covers rows floor(y - 2 s) .. ceil(y + 2 s): at most ceil(2 s_max) + 1 rows from floor(y)
+    const int reach = __float2int_ru(__fmul_rn(2.0f, a.lv[a.num_levels - 1].scale)) + 1;
     for (uint32_t k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < total; k += warps_total) {
         const int f = frame_of_row(a.frame_off, n_frames, k);
         if (f & 1) continue;  // right-eye row
@@ -64,7 +117,12 @@ __global__ void __launch_bounds__(256) k_stereo_match(StereoArgs a) {
         const uint4* dl = reinterpret_cast<const uint4*>(a.desc + (size_t)k * 32);
         const uint4 l0 = __ldg(dl), l1 = __ldg(dl + 1);
         uint32_t best = (kHammThr << 16);  // (distance << 16 | right index): strict < in index order == minimum key
-        for (uint32_t ir = rbeg + lane; ir < rend; ir += 32) {
+        // candidates: right keypoints whose row interval contains `row`; they sit within `reach` rows of it in the row order
+        const int pair = f >> 1;
+        const uint32_t* __restrict__ rs = a.row_start + (size_t)pair * (a.rows0 + 1);
+        const uint32_t s_lo = rs[max(row - reach, 0)], s_hi = rs[min(row + reach + 1, a.rows0)];
+        for (uint32_t s = s_lo + lane; s < s_hi; s += 32) {
+            const uint32_t ir = a.perm[rbeg + s];
             const uint2 rec = a.rec[ir];
             const int min_r = (int)(rec.x & 0xFFFFu), max_r = (int)(rec.x >> 16), oct = (int)rec.y;
             if (row < min_r || row > max_r) continue;
@@ -217,6 +275,7 @@ void launch_stereo(const StereoArgs& a, cudaStream_t st) {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     k_stereo_prep<<<sms * 2, 256, 0, st>>>(a);
+    k_stereo_rows<<<a.n_pairs, 1024, (size_t)(a.rows0 + 1) * sizeof(uint32_t), st>>>(a);
     k_stereo_match<<<sms * 8, 256, 0, st>>>(a);
     k_stereo_median<<<a.n_pairs, 1024, 0, st>>>(a);
 }
