@@ -57,7 +57,7 @@ class KnnDatabase:
         self.device = device
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # `lib` is already gone at interpreter shutdown
             lib().lpslam_knn_destroy(self._h)
             self._h = None
 

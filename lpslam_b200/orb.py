@@ -50,7 +50,7 @@ class orb_extractor:
         self.image_pyramid_ = _Pyramid(self)
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # `lib` is already gone at interpreter shutdown
             lib().lpslam_orb_destroy(self._h)
             self._h = None
 
