@@ -132,12 +132,19 @@ def _cpu_worker(arg):
     return n
 
 
+KERNEL_OF_STAGE = {"pyramid": "k_resize_walk", "blur": "k_gauss7", "fast": "k_fast_cells", "quadtree": "k_quadtree",
+                   "describe": "k_describe+k_stereo_match"}
+LAUNCHES_PER_STEP = 17  # 7 x k_resize_walk, k_pad_borders, k_fast_cells, k_quadtree, k_gauss7, k_offsets, k_describe, 4 x k_stereo_*
+KNN_ROWS_PER_GPU, KNN_QUERIES = 1_250_000, 2000  # BASELINE configs[4]: 10 M rows over 8 GPUs, 2000 queries
+
+
 def gpu_arm(args):
+    import concurrent.futures as cf
     import ctypes as C
     import torch
     import torch.distributed as dist
-    from lpslam_b200 import _lib, match, orb  # noqa: F401  (match registers the stereo entry points)
-    from lpslam_b200._lib import KP_DTYPE, check, lib
+    from lpslam_b200 import _lib, knn, match, orb  # noqa: F401  (match / knn register their entry points)
+    from lpslam_b200._lib import check, lib
 
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -158,25 +165,56 @@ def gpu_arm(args):
     host = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(2 * B, H, W))
     for p in range(B):
         host[2 * p], host[2 * p + 1] = lefts[p], rights[p]
-    cap = 2 * B * 4096
-    okp, odesc, oxr, odep = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
-    check(L.lpslam_cuda_host_alloc(C.byref(okp), cap * 28))
-    check(L.lpslam_cuda_host_alloc(C.byref(odesc), cap * 32))
-    check(L.lpslam_cuda_host_alloc(C.byref(oxr), cap * 4))
-    check(L.lpslam_cuda_host_alloc(C.byref(odep), cap * 4))
-    offs = np.zeros(2 * B + 1, np.uint32)
-    pl = (C.c_void_p * B)(*[host[2 * p].ctypes.data for p in range(B)])
-    pr = (C.c_void_p * B)(*[host[2 * p + 1].ctypes.data for p in range(B)])
+
+    def pinned(nbytes):
+        q = C.c_void_p()
+        check(L.lpslam_cuda_host_alloc(C.byref(q), nbytes))
+        return q
+
+    # ---- end to end: the replay a user runs. Two extractor contexts per GPU, each fed by its own host thread with half
+    # of the step's pairs through the blocking host-buffer entry point, so one context's PCIe copies overlap the other's
+    # kernels (the reference also extracts on two threads, data/frame.cc:65-66).
+    halves = []
+    Bh = max(B // 2, 1)
+    for hx in range(2):
+        lo = hx * Bh
+        n = Bh if hx == 0 else B - Bh
+        if n <= 0:
+            continue
+        e = orb.orb_extractor(max_num_keypts=KPTS, device=local, max_batch=2 * n)
+        cap = 2 * n * 4096
+        bufs = dict(kp=pinned(cap * 28), desc=pinned(cap * 32), xr=pinned(cap * 4), dep=pinned(cap * 4))
+        offs = np.zeros(2 * n + 1, np.uint32)
+        pl = (C.c_void_p * n)(*[host[2 * (lo + p)].ctypes.data for p in range(n)])
+        pr = (C.c_void_p * n)(*[host[2 * (lo + p) + 1].ctypes.data for p in range(n)])
+        halves.append((e, n, cap, bufs, offs, pl, pr))
+
+    def run_half(hf):
+        e, n, cap, bufs, offs, pl, pr = hf
+        check(L.lpslam_stereo_frames(e._h, pl, pr, n, W, H, W, FX_B, BASELINE, bufs["kp"], bufs["desc"], cap, offs.ctypes.data,
+                                     bufs["xr"], bufs["dep"]))
+        return int(offs[2 * n])
+
+    pool = cf.ThreadPoolExecutor(max_workers=2)
 
     def e2e_step():
-        check(L.lpslam_stereo_frames(ext._h, pl, pr, B, W, H, W, FX_B, BASELINE, okp, odesc, cap, offs.ctypes.data, oxr, odep))
+        return sum(pool.map(run_half, halves))
 
-    # device-resident input: the context's own level-0 buffer, filled once
+    n_kp = e2e_step()
+    n_match = 0
+    for e, n, cap, bufs, offs, pl, pr in halves:
+        xr = np.ctypeslib.as_array(C.cast(bufs["xr"], C.POINTER(C.c_float)), shape=(cap,))[:int(offs[2 * n])]
+        n_match += int((xr >= 0).sum())
+
+    # ---- device resident: the context's own level-0 buffer, filled once through the host entry point ----
+    okp, odesc, oxr, odep = pinned(2 * B * 4096 * 28), pinned(2 * B * 4096 * 32), pinned(2 * B * 4096 * 4), pinned(2 * B * 4096 * 4)
+    offs_all = np.zeros(2 * B + 1, np.uint32)
+    pl_all = (C.c_void_p * B)(*[host[2 * p].ctypes.data for p in range(B)])
+    pr_all = (C.c_void_p * B)(*[host[2 * p + 1].ctypes.data for p in range(B)])
+    check(L.lpslam_stereo_frames(ext._h, pl_all, pr_all, B, W, H, W, FX_B, BASELINE, okp, odesc, 2 * B * 4096, offs_all.ctypes.data,
+                                 oxr, odep))
     dptr, dpitch, dstride = C.c_void_p(), C.c_size_t(), C.c_size_t()
     check(L.lpslam_orb_input_dev(ext._h, W, H, C.byref(dptr), C.byref(dpitch), C.byref(dstride)))
-    e2e_step()  # fills level 0 of every frame on the device as a side effect, and warms everything up
-    n_kp = int(offs[2 * B])
-    n_match = int((np.ctypeslib.as_array(C.cast(oxr, C.POINTER(C.c_float)), shape=(cap,))[:n_kp] >= 0).sum())
 
     def dev_step():
         check(L.lpslam_stereo_frames_dev(ext._h, dptr, B, W, H, dpitch.value, FX_B, BASELINE))
@@ -187,16 +225,16 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, on_stream):
         for _ in range(warmup):
             fn()
         barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
-        ev0.record(stream)
+        ev0.record(on_stream)
         for _ in range(steps):
             fn()
-        ev1.record(stream)
+        ev1.record(on_stream)
         torch.cuda.synchronize()
         wall = (time.perf_counter() - t0) * 1e3
         ms = ev0.elapsed_time(ev1)
@@ -208,11 +246,11 @@ def gpu_arm(args):
 
     clocks = ClockSampler(local)
     clocks.start()
-    dev_ms, _ = timed(dev_step, args.steps, args.warmup)
+    dev_ms, _ = timed(dev_step, args.steps, args.warmup, stream)
     clk = clocks.stop()
-    _, e2e_ms = timed(e2e_step, args.steps, args.warmup)  # wall clock: the call blocks until results are on the host
+    _, e2e_ms = timed(e2e_step, args.steps, args.warmup, stream)  # wall clock: the calls block until results are on the host
 
-    # per-stage device time of one more resident step (CUDA events on the library's stream)
+    # ---- per-stage device time of a few more resident steps (CUDA events on the library's stream) ----
     ext.enable_timing(True)
     stage = {k: 0.0 for k in ("pyramid", "fast", "quadtree", "blur", "describe")}
     reps = 5
@@ -224,23 +262,50 @@ def gpu_arm(args):
     ext.enable_timing(False)
     frames_img = 2 * B
     alg = algorithmic_bytes(W, H)
-    peaks = {}
+    peaks, traffic = {}, {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
         pass
-    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))  # dram bytes per launch, ncu --set full
+    except OSError:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs") if "hbm_gbs" in peaks else (6650.0, "B200_PROFILING.md fallback")
     per_stage = {}
     for k in ("pyramid", "blur", "fast"):
         gbs = alg[k] * frames_img / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
-        per_stage[k] = {"ms": round(stage[k], 4), "alg_bytes": alg[k] * frames_img, "achieved_gbs": round(gbs, 1),
-                        "frac": round(gbs / peak, 4)}
+        per_stage[k] = {"kernel": KERNEL_OF_STAGE[k], "ms": round(stage[k], 4), "alg_bytes": alg[k] * frames_img,
+                        "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4), "traffic": traffic.get(KERNEL_OF_STAGE[k])}
     dom = max(stage, key=stage.get)
     rk = dom if dom in per_stage else "blur"
-    roofline = {"bound": "hbm", "kernel": {"pyramid": "k_resize_linear", "blur": "k_gauss7", "fast": "k_fast_cells"}[rk],
-                "achieved": per_stage[rk]["achieved_gbs"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": per_stage[rk]["frac"], "traffic": None, "dominant_stage": dom,
-                "stage_ms": {k: round(v, 4) for k, v in stage.items()}, "stages": per_stage}
+    roofline = {"bound": "hbm", "kernel": per_stage[rk]["kernel"], "achieved": per_stage[rk]["achieved_gbs"], "peak": peak,
+                "peak_source": peak_src, "unit": "GB/s", "frac": per_stage[rk]["frac"], "traffic": per_stage[rk]["traffic"],
+                "dominant_stage": dom, "stage_ms": {k: round(v, 4) for k, v in stage.items()}, "stages": per_stage,
+                "note": "k_fast_cells reads each level once (algorithmic bytes = sum of level pixels) but is bound by the "
+                        "integer compare pipe, not by HBM; the HBM-bound kernels are k_resize_walk and k_gauss7 (stages)"}
+
+    # ---- relocalisation kNN (BASELINE configs[4]): one database shard per GPU, NCCL all_gather of the top-2 keys, merge ----
+    g = torch.Generator(device="cuda").manual_seed(5 + rank)
+    shard = torch.randint(0, 256, (KNN_ROWS_PER_GPU, 32), dtype=torch.uint8, device="cuda", generator=g)
+    gq = torch.Generator(device="cuda").manual_seed(99)
+    queries = torch.randint(0, 256, (KNN_QUERIES, 32), dtype=torch.uint8, device="cuda", generator=gq)
+    db = knn.KnnDatabase(KNN_ROWS_PER_GPU, device=local, index_base=rank * KNN_ROWS_PER_GPU)
+    db.add_dev(shard.data_ptr(), KNN_ROWS_PER_GPU)
+    cur = torch.cuda.current_stream()
+
+    def knn_step():
+        knn.sharded_query(db, queries, KNN_QUERIES, cur.cuda_stream)
+
+    knn_ms, _ = timed(knn_step, max(args.steps, 5), 3, cur)
+    knn_steps = max(args.steps, 5)
+    cmp_per_step = KNN_QUERIES * KNN_ROWS_PER_GPU * world
+    knn_out = {"metric": "Gdesc-cmp/s kNN", "value": cmp_per_step * knn_steps / (knn_ms * 1e-3) / 1e9, "unit": "1e9 256-bit comparisons/s",
+               "ms_per_query_batch": knn_ms / knn_steps, "queries": KNN_QUERIES, "db_rows_total": KNN_ROWS_PER_GPU * world,
+               "db_rows_per_gpu": KNN_ROWS_PER_GPU, "exchange": "nccl all_gather of 2 keys/query + device merge" if world > 1 else "none",
+               "popc_roofline_gcmp_per_gpu": 578.0,
+               "note": "popc pipe measured at 16 lanes/clk/SM (profiles/r1_pipe_rates.txt): 8 POPC per comparison caps a GPU at 578 "
+                       "Gcmp/s; the carry-save-adder scan needs 4"}
 
     pairs_total = B * args.steps * world
     out = {"metric": "frames/s ORB extract+match @1280x720 2000kpt", "value": pairs_total / (dev_ms * 1e-3),
@@ -254,8 +319,12 @@ def gpu_arm(args):
                       "parallelism": "frame-parallel x%d" % world},
            "e2e": {"value": pairs_total / (e2e_ms * 1e-3), "unit": "stereo frames/s", "ms_per_step": e2e_ms / args.steps,
                    "h2d_bytes_per_step": 2 * B * W * H, "d2h_bytes_per_step": n_kp * (28 + 32 + 8) + 4 * (2 * B + 2),
-                   "timing": "wall clock around the blocking host-buffer C-ABI call, max over ranks"},
-           "gpu_launches": args.steps * 15, "clocks": clk, "roofline": roofline}
+                   "timing": "wall clock around the blocking host-buffer C-ABI calls (2 contexts x 1 host thread each per GPU), max over ranks"},
+           "gpu_launches": args.steps * LAUNCHES_PER_STEP, "clocks": clk, "roofline": roofline, "knn": knn_out}
+    pool.shutdown()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     return out, rank
 
 

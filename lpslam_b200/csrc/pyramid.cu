@@ -97,6 +97,11 @@ __device__ __forceinline__ int reflect101(int p, int len) {
     return p;
 }
 
+// predicated 16-bit store (keeps the store a single predicated instruction instead of a branch around it)
+__device__ __forceinline__ void st_u16_if(uint8_t* p, uint16_t v, bool pred) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q st.global.u16 [%0], %1;\n\t}" ::"l"(p), "h"(v), "r"((uint32_t)pred) : "memory");
+}
+
 #ifndef LPS_RW_MIN_THREADS
 #define LPS_RW_MIN_THREADS (148L * 2048)
 #endif
@@ -186,15 +191,24 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
 #pragma unroll
             for (int g = 0; g < RW_NW; ++g) out[g] = (uint16_t)__byte_perm(sum[2 * g], sum[2 * g + 1], 0x4451);  // byte 1 of each
             const int y = e.x;
+            uint8_t* o = d + (ptrdiff_t)y * dpitch;  // window g stores at o + 64 g (immediate offsets)
+#pragma unroll
+            for (int g = 0; g < RW_NW; ++g)
+                st_u16_if(o + 64 * g, out[g], live[g]);
             // apron rows are copies of the real rows they mirror (BORDER_REFLECT_101: row -k = row k, row h-1+k = row h-1-k)
             const bool top = y >= 1 && y <= kApron, bot = y >= dst.h - 1 - kApron && y <= dst.h - 2;
+            if (top || bot) {  // block-uniform, 8 rows per level
+                if (top) {
+                    uint8_t* o2 = d - (ptrdiff_t)y * dpitch;
 #pragma unroll
-            for (int g = 0; g < RW_NW; ++g) {
-                if (live[g]) {  // columns past w + kApron land in the unused part of the row pad or are skipped
-                    uint8_t* o = d + 64 * g;
-                    *reinterpret_cast<uint16_t*>(o + (ptrdiff_t)y * dpitch) = out[g];
-                    if (top) *reinterpret_cast<uint16_t*>(o - (ptrdiff_t)y * dpitch) = out[g];
-                    if (bot) *reinterpret_cast<uint16_t*>(o + (ptrdiff_t)(2 * (dst.h - 1) - y) * dpitch) = out[g];
+                    for (int g = 0; g < RW_NW; ++g)
+                        st_u16_if(o2 + 64 * g, out[g], live[g]);
+                }
+                if (bot) {
+                    uint8_t* o2 = d + (ptrdiff_t)(2 * (dst.h - 1) - y) * dpitch;
+#pragma unroll
+                    for (int g = 0; g < RW_NW; ++g)
+                        st_u16_if(o2 + 64 * g, out[g], live[g]);
                 }
             }
         }
