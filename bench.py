@@ -152,6 +152,7 @@ def gpu_arm(args):
         raise RuntimeError("bench.py needs a CUDA device: liblpslam_cuda has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"  # the version banner would otherwise land on stdout next to the JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch  # stereo pairs per step and per GPU
     L = lib()

@@ -106,7 +106,7 @@ __device__ __forceinline__ void st_u16_if(uint8_t* p, uint16_t v, bool pred) {
 #define LPS_RW_MIN_THREADS (148L * 2048)
 #endif
 #ifndef LPS_RW_PX
-#define LPS_RW_PX 8
+#define LPS_RW_PX 4
 #endif
 constexpr int RW_PX = LPS_RW_PX;  // destination pixels per thread (4 or 8)
 constexpr int RW_NW = RW_PX / 2;  // 2-pixel windows per thread
