@@ -160,7 +160,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
             off_yc[l] = plan.take(yc[l].size() * 4);
             // source-row schedule of the column-walk resize
             rowtab[l].assign(p.h + 2, make_int2(-1, 0));
-            g.walk_ok = g.mode == 0 && p.w < 3 * g.w && p.h >= g.h && g.h > kApron + 1 && g.w > 1;
+            g.walk_ok = g.mode == 0 && p.w < 3 * g.w && p.h >= g.h && p.h < 24 * g.h && g.h > 2 * kApron + 1 && g.w > 1;
             for (int y = 0; y < g.h && g.walk_ok; ++y) {
                 const int r = yofs[l][y] + 1;
                 if (yofs[l][y] < 0 || r > p.h || rowtab[l][r].x >= 0) {

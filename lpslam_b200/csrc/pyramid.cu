@@ -120,6 +120,13 @@ struct RowW {  // the words of one source row for all windows of a thread
     uint32_t lo[RW_NW], hi[RW_NW];
 };
 
+struct TabE {  // block-local copy of the source-row schedule (one entry per source row of the band)
+    int y;            // destination row completed by source rows (r - 1, r); -1 = none inside this band
+    uint32_t b0, b1;  // row coefficients
+    int dup;          // byte offset (in rows) of the apron row that mirrors y, 0 = none
+};
+constexpr int kTabMax = 224;  // source rows per band the shared schedule can hold (launcher keeps bands below it)
+
 __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom dst, int rows_per_block) {
     // The destination domain is the level PLUS its reflected apron: columns [-RW_PX, w + kApron), rows [-kApron, h + kApron).
     // An apron pixel is computed like the real pixel it mirrors (same tables, same arithmetic), so no separate border
@@ -127,13 +134,35 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
     // Lane mapping: a warp owns RW_PX * 32 consecutive destination columns; window g of lane i covers the two columns
     // 64 g + 2 i (+1) of them, so that ONE warp-wide load touches the source bytes of 64 consecutive destination columns
     // (77 contiguous bytes at scale 1.2: a single L1 wavefront instead of three or four).
+    __shared__ TabE s_tab[kTabMax];
+    // programmatic dependent launch: the next level's blocks may start their set-up (tables only) while this grid drains
+    asm volatile("griddepcontrol.launch_dependents;");
     const int warp_x0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (RW_PX * 32) - 2 * kApron;
     const int lane2 = 2 * (int)(threadIdx.x & 31);
     const uint8_t* __restrict__ s = src.img + blockIdx.z * src.frame_stride;
-    uint8_t* __restrict__ d = dst.img + blockIdx.z * dst.frame_stride + warp_x0 + lane2;  // window g stores at d + 64 g
     const int spitch = src.pitch, dpitch = dst.pitch;
-    bool live[RW_NW];
+    // Band of destination rows [y0, y1). The walk is over SOURCE rows: every iteration consumes one source row (its
+    // words were fetched two iterations earlier), writes its H >> 4 into the register set that held the row before
+    // last, and, when the schedule says that (r - 1, r) completes a destination row, emits it. The two sets swap roles
+    // every iteration, so nothing is ever moved, and the control flow is the same for the whole block.
+    const int y0 = blockIdx.y * rows_per_block;
+    const int y1 = min(y0 + rows_per_block, dst.h);
+    const int r_first = dst.yofs[y0], r_last = dst.yofs[y1 - 1] + 1;
+    for (int i = threadIdx.x; i <= r_last - r_first; i += blockDim.x) {
+        const int2 e = __ldg(dst.srctab + r_first + i);
+        TabE t;
+        const bool in = e.x >= y0 && e.x < y1;
+        t.y = in ? e.x : -1;
+        t.b0 = (uint32_t)e.y & 0xFFFFu;
+        t.b1 = (uint32_t)e.y >> 16;
+        // apron rows are copies of the real rows they mirror (BORDER_REFLECT_101: row -k = row k, row h-1+k = row h-1-k)
+        t.dup = 0;
+        if (e.x >= 1 && e.x <= kApron) t.dup = -2 * e.x;
+        if (e.x >= dst.h - 1 - kApron && e.x <= dst.h - 2) t.dup = 2 * (dst.h - 1 - e.x);
+        s_tab[i] = t;
+    }
 
+    bool live[RW_NW];
     Window wd[RW_NW];
 #pragma unroll
     for (int g = 0; g < RW_NW; ++g) {
@@ -143,30 +172,28 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
         const int sa = dst.xofs[xa], sb = dst.xofs[xb];
         const short2 ca = dst.xcoef[xa], cb = dst.xcoef[xb];
         const int base = min(sa, sb) & ~3;
-        wd[g].ptr = s + base;
+        wd[g].ptr = s + base + (ptrdiff_t)r_first * spitch;
         const uint32_t oa = (uint32_t)min(sa - base, 6), ob = (uint32_t)min(sb - base, 6);  // the launcher guarantees <= 6
         wd[g].sel0 = oa | ((oa + 1) << 4);
         wd[g].sel1 = ob | ((ob + 1) << 4);
         wd[g].c0 = (uint32_t)(uint16_t)ca.x | ((uint32_t)(uint16_t)ca.y << 16);
         wd[g].c1 = (uint32_t)(uint16_t)cb.x | ((uint32_t)(uint16_t)cb.y << 16);
     }
-    // Band of destination rows [y0, y1). The walk is over SOURCE rows: every iteration consumes one source row (its
-    // words were fetched two iterations earlier), writes its H >> 4 into the register set that held the row before
-    // last, and, when the schedule says that (r - 1, r) completes a destination row, emits it. The two sets swap roles
-    // every iteration, so nothing is ever moved, and the control flow is the same for the whole block.
-    const int y0 = blockIdx.y * rows_per_block;
-    const int y1 = min(y0 + rows_per_block, dst.h);
-    const int smax = src.h - 1;
-    const int r_first = dst.yofs[y0], r_last = dst.yofs[y1 - 1] + 1;
-    const int2* __restrict__ tab = dst.srctab;
+    uint8_t* d = dst.img + blockIdx.z * dst.frame_stride + warp_x0 + lane2;  // window g stores at d + 64 g
+    asm volatile("" : "+l"(d));  // not to be rematerialised from the kernel parameters at every emitted row
+    __syncthreads();
+    asm volatile("griddepcontrol.wait;" ::: "memory");  // the source level is complete and visible from here on
+    // (the image must be read with ordinary loads: ptxas schedules non-coherent ld.global.nc loads above the wait)
 
-    auto fetch = [&](int r, RowW& w) {
-        const uint32_t off = (uint32_t)min(r, smax) * (uint32_t)spitch;
+    // fetch the words of the next unread source row (rows below the image are apron rows: readable, and only ever
+    // multiplied by a zero coefficient) and advance the window pointers
+    auto fetch = [&](RowW& w) {
 #pragma unroll
         for (int g = 0; g < RW_NW; ++g) {
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(wd[g].ptr + off);  // 4-byte aligned window
-            w.lo[g] = __ldg(wp);
-            w.hi[g] = __ldg(wp + 1);
+            // 4-byte aligned window; ordinary (coherent, L1-cached) loads, kept below the dependency wait
+            asm volatile("ld.global.u32 %0, [%2];\n\tld.global.u32 %1, [%2 + 4];" : "=r"(w.lo[g]), "=r"(w.hi[g]) : "l"(wd[g].ptr));
+            wd[g].ptr += spitch;
+            asm volatile("" : "+l"(wd[g].ptr));  // keep a running 64-bit pointer (no per-row re-derivation from a 32-bit offset)
         }
     };
     auto hsum = [&](const RowW& w, uint32_t (&h)[RW_PX]) {  // H >> 4 of the thread's pixels on one source row
@@ -176,40 +203,26 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
             h[2 * g + 1] = __dp2a_lo(wd[g].c1, __byte_perm(w.lo[g], w.hi[g], wd[g].sel1), 0u) >> 4;
         }
     };
-    // source row r arrives in `buf`; Lo holds row r - 1; Up receives row r
-    auto step = [&](int r, uint32_t (&Lo)[RW_PX], uint32_t (&Up)[RW_PX], RowW& buf) {
+    // source row r_first + i arrives in `buf`; Lo holds row r - 1; Up receives row r
+    auto step = [&](int i, uint32_t (&Lo)[RW_PX], uint32_t (&Up)[RW_PX], RowW& buf) {
         hsum(buf, Up);
-        fetch(r + 2, buf);
-        const int2 e = __ldg(tab + r);
-        if (e.x >= y0 && e.x < y1) {  // block-uniform
-            const uint32_t b0 = (uint32_t)e.y & 0xFFFFu, b1 = (uint32_t)e.y >> 16;
+        fetch(buf);
+        const TabE e = s_tab[i];
+        if (e.y >= 0) {  // block-uniform
             uint32_t sum[RW_PX];
             uint16_t out[RW_NW];
 #pragma unroll
             for (int k = 0; k < RW_PX; ++k)
-                sum[k] = __dp2a_lo(__byte_perm(b0 * Lo[k], b1 * Up[k], 0x7632), 0x4040u, 128u);  // (t0 + t1 + 2) << 6
+                sum[k] = __dp2a_lo(__byte_perm(e.b0 * Lo[k], e.b1 * Up[k], 0x7632), 0x4040u, 128u);  // (t0 + t1 + 2) << 6
 #pragma unroll
             for (int g = 0; g < RW_NW; ++g) out[g] = (uint16_t)__byte_perm(sum[2 * g], sum[2 * g + 1], 0x4451);  // byte 1 of each
-            const int y = e.x;
-            uint8_t* o = d + (ptrdiff_t)y * dpitch;  // window g stores at o + 64 g (immediate offsets)
+            uint8_t* o = d + (ptrdiff_t)e.y * dpitch;  // window g stores at o + 64 g (immediate offsets)
 #pragma unroll
-            for (int g = 0; g < RW_NW; ++g)
-                st_u16_if(o + 64 * g, out[g], live[g]);
-            // apron rows are copies of the real rows they mirror (BORDER_REFLECT_101: row -k = row k, row h-1+k = row h-1-k)
-            const bool top = y >= 1 && y <= kApron, bot = y >= dst.h - 1 - kApron && y <= dst.h - 2;
-            if (top || bot) {  // block-uniform, 8 rows per level
-                if (top) {
-                    uint8_t* o2 = d - (ptrdiff_t)y * dpitch;
+            for (int g = 0; g < RW_NW; ++g) st_u16_if(o + 64 * g, out[g], live[g]);
+            if (e.dup) {  // block-uniform, 8 rows per level
+                uint8_t* o2 = o + (ptrdiff_t)e.dup * dpitch;
 #pragma unroll
-                    for (int g = 0; g < RW_NW; ++g)
-                        st_u16_if(o2 + 64 * g, out[g], live[g]);
-                }
-                if (bot) {
-                    uint8_t* o2 = d + (ptrdiff_t)(2 * (dst.h - 1) - y) * dpitch;
-#pragma unroll
-                    for (int g = 0; g < RW_NW; ++g)
-                        st_u16_if(o2 + 64 * g, out[g], live[g]);
-                }
+                for (int g = 0; g < RW_NW; ++g) st_u16_if(o2 + 64 * g, out[g], live[g]);
             }
         }
     };
@@ -218,17 +231,18 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
     RowW w0, w1;
     {
         RowW wa;
-        fetch(r_first, wa);
-        fetch(r_first + 1, w0);
-        fetch(r_first + 2, w1);
+        fetch(wa);
+        fetch(w0);
+        fetch(w1);
         hsum(wa, A);
     }
-    int r = r_first + 1;
-    for (; r + 1 <= r_last; r += 2) {
-        step(r, A, B, w0);
-        step(r + 1, B, A, w1);
+    const int n = r_last - r_first;  // source rows r_first + 1 .. r_last are walked
+    int i = 1;
+    for (; i + 1 <= n; i += 2) {
+        step(i, A, B, w0);
+        step(i + 1, B, A, w1);
     }
-    if (r <= r_last) step(r, A, B, w0);
+    if (i <= n) step(i, A, B, w0);
 }
 
 // exact 2x decimation: OpenCV's INTER_LINEAR takes the INTER_AREA fast path, (a + b + c + d + 2) >> 2
@@ -295,8 +309,19 @@ void launch_resize(const LevelGeom& src, const LevelGeom& dst, int batch, cudaSt
         const long threads_per_row_of_bands = (long)((strips + best_t - 1) / best_t) * best_t * batch;
         int rows = 64;
         while (rows > 8 && threads_per_row_of_bands * ((vrows + rows - 1) / rows) < LPS_RW_MIN_THREADS) rows >>= 1;
+        // the band's source rows must fit the shared schedule (ctx.cu only sets walk_ok when they do at 8 rows)
+        while (rows > 8 && (long)rows * src.h / dst.h + 4 > kTabMax) rows >>= 1;
         dim3 grd((strips + best_t - 1) / best_t, (vrows + rows - 1) / rows, batch);
-        k_resize_walk<<<grd, best_t, 0, st>>>(src, dst, rows);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grd;
+        cfg.blockDim = dim3(best_t);
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, k_resize_walk, src, dst, rows);
         return;
     }
     dim3 blk(32, 8);
