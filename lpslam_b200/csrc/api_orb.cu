@@ -64,6 +64,9 @@ int lpslam_orb_create(lpslam_orb_ctx** out, const lpslam_orb_params* p, int devi
         c->mask_rects.push_back({p->mask_rects[4 * i], p->mask_rects[4 * i + 1], p->mask_rects[4 * i + 2], p->mask_rects[4 * i + 3]});
     c->initialize_tables();
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_frame_off, sizeof(uint32_t) * (max_batch + 2), cudaHostAllocDefault);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
     if (e != cudaSuccess) {
@@ -78,7 +81,11 @@ void lpslam_orb_destroy(lpslam_orb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->side) cudaStreamSynchronize(c->side);
     c->release_geometry();
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->side) cudaStreamDestroy(c->side);
     if (c->h_frame_off) cudaFreeHost(c->h_frame_off);
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);

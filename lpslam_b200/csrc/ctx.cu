@@ -404,7 +404,20 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     for (int l = 1; l < L; ++l)
         if (!resize_writes_apron(lv[l - 1], lv[l])) pad_mask |= 1u << l;
     for (int l = 1; l < L; ++l) launch_resize(lv[l - 1], lv[l], B, stream);
-    launch_pad_borders(lv_dev, lv, L, pad_mask, B, stream);
+    // The blur and the apron of level 0 depend on the pyramid only: outside of stage timing they run on the side stream,
+    // next to FAST and the quadtree (memory-bound work beside compare-pipe-bound and latency-bound work), and are joined
+    // before the descriptors. With stage timing on, everything stays on one stream so that each stage is timed alone.
+    const bool fork = !timing && side && pad_mask == 1u;
+    if (fork) {
+        LPS_CUDA(cudaEventRecord(ev_fork, stream));
+        LPS_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        launch_pad_borders(lv_dev, lv, L, pad_mask, B, side);
+        launch_blur(lv_dev, lv, L, B, side);
+        LPS_CUDA(cudaEventRecord(ev_join, side));
+    }
+    else {
+        launch_pad_borders(lv_dev, lv, L, pad_mask, B, stream);
+    }
     mark();  // 1
     FastArgs fa;
     fa.lv = lv_dev;
@@ -422,7 +435,10 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     tree.batch = B;
     launch_quadtree(tree, lv, stream);
     mark();  // 3
-    launch_blur(lv_dev, lv, L, B, stream);
+    if (fork)
+        LPS_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+    else
+        launch_blur(lv_dev, lv, L, B, stream);
     mark();  // 4
     desc.batch = B;
     LPS_CUDA(cudaMemsetAsync(desc.overflow, 0, 4, stream));

@@ -8,6 +8,9 @@
 struct lpslam_orb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    // side stream: level-0 apron + blur run beside FAST and the quadtree (they only depend on the pyramid)
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     uint32_t max_batch = 1;
 
     // feature/orb_params.h

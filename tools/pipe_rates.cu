@@ -9,10 +9,11 @@ constexpr int CH = 8;      // independent chains per thread
 constexpr int UNROLL = 16; // ops per chain per loop trip
 constexpr int ITERS = 512;
 
-enum Op { IMAD, IADD3, LOP3, PRMT, SHF, DP4A, DP2A, POPC, VMNMX, XORPOPCADD, DP4A_PRMT, DP2A_PRMT, IMAD_PRMT, IMAD_IADD, POPC_LOP, NOPS };
+enum Op { IMAD, IADD3, LOP3, PRMT, SHF, DP4A, DP2A, POPC, VMNMX, XORPOPCADD, DP4A_PRMT, DP2A_PRMT, IMAD_PRMT, IMAD_IADD, POPC_LOP, IMADHI, IMADWIDE, DP2A_IMAD, DP2A_SHF, SHF_PRMT, VABSDIFF4, IMADHI_PRMT, NOPS };
 const char* names[NOPS] = {"IMAD", "IADD3", "LOP3", "PRMT", "SHF", "IDP.4A", "IDP.2A", "POPC", "VIMNMX.U16x2", "LOP3+POPC+IADD (hamming word)",
-                           "IDP.4A+PRMT 1:1", "IDP.2A+PRMT 1:1", "IMAD+PRMT 1:1", "IMAD+IADD3 1:1", "POPC+LOP3 1:1"};
-const int per_step[NOPS] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 3, 2, 2, 2, 2, 2};
+                           "IDP.4A+PRMT 1:1", "IDP.2A+PRMT 1:1", "IMAD+PRMT 1:1", "IMAD+IADD3 1:1", "POPC+LOP3 1:1",
+                           "IMAD.HI", "IMAD.WIDE", "IDP.2A+IMAD 1:1", "IDP.2A+SHF 1:1", "SHF+PRMT 1:1", "VABSDIFF4", "IMAD.HI+PRMT 1:1"};
+const int per_step[NOPS] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 3, 2, 2, 2, 2, 2, 1, 1, 2, 2, 2, 1, 2};
 
 template <int OP>
 __device__ __forceinline__ void step(unsigned& a, unsigned b, unsigned c) {
@@ -46,6 +47,29 @@ __device__ __forceinline__ void step(unsigned& a, unsigned b, unsigned c) {
     if (OP == IMAD_IADD) {
         asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
         asm volatile("add.u32 %0, %0, %1;" : "+r"(a) : "r"(b));
+    }
+    if (OP == IMADHI) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+    if (OP == IMADWIDE) {
+        unsigned long long w;
+        asm volatile("mad.wide.u32 %0, %1, %2, %3;" : "=l"(w) : "r"(a), "r"(b), "l"((unsigned long long)c << 20));
+        a = (unsigned)(w >> 8);  // compiles to a byte permute at most; counted as one step (upper bound on the cost)
+    }
+    if (OP == DP2A_IMAD) {
+        asm volatile("dp2a.lo.u32.u32 %0, %1, %2, %0;" : "+r"(a) : "r"(b), "r"(c));
+        asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+    }
+    if (OP == DP2A_SHF) {
+        asm volatile("dp2a.lo.u32.u32 %0, %1, %2, %0;" : "+r"(a) : "r"(b), "r"(c));
+        asm volatile("shf.r.wrap.b32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+    }
+    if (OP == SHF_PRMT) {
+        asm volatile("shf.r.wrap.b32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+        asm volatile("prmt.b32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+    }
+    if (OP == VABSDIFF4) asm volatile("vabsdiff4.u32.u32.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+    if (OP == IMADHI_PRMT) {
+        asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
+        asm volatile("prmt.b32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c));
     }
     if (OP == POPC_LOP) {
         asm volatile("popc.b32 %0, %0;" : "+r"(a));
@@ -115,5 +139,6 @@ int main() {
     const int s = p.multiProcessorCount;
     run<IMAD>(s); run<IADD3>(s); run<LOP3>(s); run<PRMT>(s); run<SHF>(s); run<DP4A>(s); run<DP2A>(s); run<POPC>(s); run<VMNMX>(s);
     run<XORPOPCADD>(s); run<DP4A_PRMT>(s); run<DP2A_PRMT>(s); run<IMAD_PRMT>(s); run<IMAD_IADD>(s); run<POPC_LOP>(s);
+    run<IMADHI>(s); run<IMADWIDE>(s); run<DP2A_IMAD>(s); run<DP2A_SHF>(s); run<SHF_PRMT>(s); run<VABSDIFF4>(s); run<IMADHI_PRMT>(s);
     return 0;
 }
