@@ -190,6 +190,20 @@ int lpslam_match_projection(const lpslam_camera* cam, const double* pose_cw_curr
                             const float* curr_x_right, const uint8_t* curr_has_observed_lm, const float* scale_factors,
                             float margin, int check_orientation, int32_t* curr_match_last, uint32_t* n_matches);
 
+/* match::projection::match_frame_and_landmarks (match/projection.cc:11-83), the local-map search run on every tracked
+ * frame (module/local_map_updater + tracking_module::search_local_landmarks), over flat arrays. Each local landmark brings
+ * the reprojection the tracker cached on it (data/landmark.h:112-115: reproj_in_tracking_, x_right_in_tracking_,
+ * scale_level_in_tracking_); lm_active = is_observable_in_tracking_ && !will_be_erased(). kp_has_observed_lm[i] != 0 when
+ * frm.landmarks_[i] exists and has observations (projection.cc:41-43); a keypoint matched by this call blocks later
+ * landmarks only if the landmark it now holds has observations (lm_has_observation, nullable = all 1).
+ * kp_match_lm[i] = index of the landmark written to frm.landmarks_[i] by this call, or -1 (unchanged). */
+int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, const uint8_t* lm_active,
+                           const double* lm_reproj /*n_lm x 2*/, const float* lm_x_right, const int32_t* lm_scale_level,
+                           const uint8_t* lm_desc /*n_lm x 32*/, const uint8_t* lm_has_observation,
+                           uint32_t n_kp, const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const float* kp_x_right,
+                           const uint8_t* kp_has_observed_lm, const float* scale_factors, float margin, float lowe_ratio,
+                           int32_t* kp_match_lm, uint32_t* n_matches);
+
 /* ---------------------------------------------------------------- kNN database (relocalisation / loop query) ----- */
 /* Brute-force Hamming top-2 of query descriptors against a device-resident descriptor database (generalises the
  * best / second-best scan of match/robust.cc:252-274 and the BoW-candidate search of module/relocalizer.cc:31-46).

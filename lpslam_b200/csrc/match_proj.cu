@@ -50,6 +50,12 @@ struct ProjArgs {
     int32_t* curr_match_last;
     int2* events;  // (idx_last, idx_curr) in match order
     uint32_t* n_events;
+    // mode 1 = match_frame_and_landmarks (projection.cc:11-83): the "last frame" arrays describe local landmarks that come
+    // with their cached reprojection (data/landmark.h:112-115); last_has_lm = is_observable_in_tracking_ && !will_be_erased()
+    int mode;
+    const double* lm_reproj;   // n_last x 2
+    const float* lm_x_right;   // n_last
+    float lowe_ratio;
 };
 
 __device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
@@ -144,9 +150,22 @@ struct Projected {
     int min_cx, max_cx, min_cy, max_cy, min_level, max_level;
 };
 
+__device__ Projected cell_window(const ProjArgs& a, Projected p);
+
 __device__ Projected project(const ProjArgs& a, uint32_t il, bool forward, bool backward) {
     Projected p;
     p.ok = false;
+    if (a.mode == 1) {
+        if (!a.last_has_lm[il]) return p;
+        const int level = a.last_octave[il];
+        p.min_level = level - 1;  // projection.cc:27-29
+        p.max_level = level;
+        p.ref_x = (float)a.lm_reproj[2 * (size_t)il];
+        p.ref_y = (float)a.lm_reproj[2 * (size_t)il + 1];
+        p.x_right = a.lm_x_right[il];
+        p.m = __fmul_rn(a.margin, a.scale[level]);
+        return cell_window(a, p);
+    }
     if (!a.last_has_lm[il] || a.last_outlier[il]) return p;
     const double* pw = a.last_pos_w + 3 * (size_t)il;
     double pc[3];
@@ -176,6 +195,12 @@ __device__ Projected project(const ProjArgs& a, uint32_t il, bool forward, bool 
     p.ref_x = (float)u;
     p.ref_y = (float)v;
     p.m = __fmul_rn(a.margin, a.scale[oct]);
+    return cell_window(a, p);
+}
+
+// data/common.cc:135-153: the cell range of the query window; ok = false when it misses the grid
+__device__ Projected cell_window(const ProjArgs& a, Projected p) {
+    p.ok = false;
     const int gc = (int)a.cam.grid_cols, gr = (int)a.cam.grid_rows;
     p.min_cx = max(0, cv_floor(__dmul_rn((double)__fsub_rn(__fsub_rn(p.ref_x, a.cam.min_x), p.m), a.cam.inv_cell_width)));
     if (gc <= p.min_cx) return p;
@@ -327,6 +352,91 @@ __global__ void __launch_bounds__(32) k_proj_resolve(ProjArgs a) {
     if (lane == 0) *a.n_events = num;
 }
 
+// match_frame_and_landmarks (projection.cc:31-79): like k_proj_resolve, but the decision needs the best AND the second
+// best candidate that is still free (Lowe ratio, applied only when both sit on the same scale level). In a list ordered by
+// (distance, visit order) those are the first two free entries (strict '<' updates, projection.cc:55-66).
+__global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
+    extern __shared__ uint32_t s_taken[];
+    const int lane = threadIdx.x;
+    const uint32_t words = (a.n_curr + 31) / 32;
+    for (uint32_t w = lane; w < words; w += 32) {
+        uint32_t bits = 0;
+        for (uint32_t b = 0; b < 32 && w * 32 + b < a.n_curr; ++b) bits |= (a.curr_taken[w * 32 + b] ? 1u : 0u) << b;
+        s_taken[w] = bits;
+    }
+    for (uint32_t i = lane; i < a.n_curr; i += 32) a.curr_match_last[i] = -1;
+    __syncwarp();
+    uint32_t num = 0;
+    for (uint32_t base = 0; base < a.n_last; base += 32) {
+        const uint32_t mine = base + lane;
+        const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
+        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_HIGH);
+        while (todo) {
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t il = base + j;
+            const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
+                                   __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
+            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j), __shfl_sync(0xFFFFFFFFu, mi.y, j),
+                               __shfl_sync(0xFFFFFFFFu, mi.z, j), __shfl_sync(0xFFFFFFFFu, mi.w, j)};
+            uint32_t b1 = EMPTY, b2 = EMPTY;
+            int i1 = -1, i2 = -1;
+#pragma unroll
+            for (int q = 0; q < K; ++q) {
+                if (k[q] == EMPTY) continue;
+                if ((s_taken[ix[q] >> 5] >> (ix[q] & 31)) & 1u) continue;
+                if (i1 < 0) {
+                    b1 = k[q];
+                    i1 = ix[q];
+                }
+                else if (i2 < 0) {
+                    b2 = k[q];
+                    i2 = ix[q];
+                }
+            }
+            if (i2 < 0 && k[K - 1] != EMPTY) {
+                // fewer than two free entries among the four kept and the list may be longer: exact rescan by lane 0
+                uint32_t r1 = EMPTY, r2 = EMPTY;
+                int ri1 = -1, ri2 = -1;
+                if (lane == 0) {
+                    const Projected p = project(a, il, false, false);
+                    visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d) {
+                        const uint32_t kk = (d << 20) | seq;
+                        if (kk < r1) {
+                            r2 = r1;
+                            ri2 = ri1;
+                            r1 = kk;
+                            ri1 = (int)i;
+                        }
+                        else if (kk < r2) {
+                            r2 = kk;
+                            ri2 = (int)i;
+                        }
+                    });
+                }
+                b1 = __shfl_sync(0xFFFFFFFFu, r1, 0);
+                i1 = __shfl_sync(0xFFFFFFFFu, ri1, 0);
+                b2 = __shfl_sync(0xFFFFFFFFu, r2, 0);
+                i2 = __shfl_sync(0xFFFFFFFFu, ri2, 0);
+            }
+            if (i1 < 0) continue;
+            const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
+            if (HAMMING_DIST_THR_HIGH < best) continue;
+            const int best_level = a.kp[i1].octave, second_level = i2 >= 0 ? a.kp[i2].octave : -1;
+            if (best_level == second_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) continue;  // projection.cc:69-72
+            if (lane == 0) {
+                a.curr_match_last[i1] = (int32_t)il;
+                const bool blocks = a.last_obs ? a.last_obs[il] != 0 : true;  // projection.cc:41-43 re-tests has_observation()
+                if (blocks) s_taken[i1 >> 5] |= 1u << (i1 & 31);
+            }
+            ++num;
+            __syncwarp();
+        }
+    }
+    if (lane == 0) *a.n_events = num;
+}
+
 }  // namespace
 }  // namespace lps
 
@@ -382,7 +492,7 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
         UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
 #undef UP
         if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
-        ProjArgs a;
+        ProjArgs a = {};
         a.cam = *cam;
         for (int i = 0; i < 16; ++i) {
             a.Tc[i] = pose_cw_curr[i];
@@ -437,5 +547,93 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
             --*n_matches;
         }
     }
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                                      const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                                      const uint8_t* lm_has_observation, uint32_t n_kp, const lpslam_keypoint* kp_undist,
+                                      const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
+                                      const float* scale_factors, float margin, float lowe_ratio, int32_t* kp_match_lm,
+                                      uint32_t* n_matches) {
+    LPS_ARG(cam && n_matches && scale_factors, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n_kp == 0 || (kp_undist && kp_desc && kp_x_right && kp_has_observed_lm && kp_match_lm), "null frame argument");
+    LPS_ARG(n_lm == 0 || (lm_active && lm_reproj && lm_x_right && lm_scale_level && lm_desc), "null landmark argument");
+    LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1 && cam->num_scale_levels >= 1 && cam->num_scale_levels <= (uint32_t)kMaxLevels,
+            "bad camera grid / level count");
+    LPS_ARG(n_kp < (1u << 20), "too many keypoints");
+    for (uint32_t i = 0; i < n_kp; ++i) kp_match_lm[i] = -1;
+    if (n_kp == 0 || n_lm == 0) return LPSLAM_OK;
+    for (uint32_t i = 0; i < n_lm; ++i)
+        LPS_ARG(!lm_active[i] || (lm_scale_level[i] >= 0 && (uint32_t)lm_scale_level[i] < cam->num_scale_levels),
+                "landmark scale level out of range");
+
+    const uint32_t ncell = cam->grid_cols * cam->grid_rows;
+    ArenaBump ar;
+    const size_t o_act = ar.take(n_lm), o_rp = ar.take(16 * (size_t)n_lm), o_lxr = ar.take(4 * (size_t)n_lm), o_lvl = ar.take(4 * (size_t)n_lm);
+    const size_t o_ld = ar.take(32 * (size_t)n_lm), o_obs = ar.take(n_lm), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_kp);
+    const size_t o_desc = ar.take(32 * (size_t)n_kp), o_xr = ar.take(4 * (size_t)n_kp), o_tk = ar.take(n_kp);
+    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
+    const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_m = ar.take(4 * (size_t)n_kp), o_ne = ar.take(4);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    cudaError_t e = cudaSuccess;
+    uint32_t n_ev = 0;
+    do {
+#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
+        UP(o_act, lm_active, n_lm);
+        UP(o_rp, lm_reproj, 16 * (size_t)n_lm);
+        UP(o_lxr, lm_x_right, 4 * (size_t)n_lm);
+        UP(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
+        UP(o_ld, lm_desc, 32 * (size_t)n_lm);
+        if (lm_has_observation) UP(o_obs, lm_has_observation, n_lm);
+        UP(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
+        UP(o_desc, kp_desc, 32 * (size_t)n_kp);
+        UP(o_xr, kp_x_right, 4 * (size_t)n_kp);
+        UP(o_tk, kp_has_observed_lm, n_kp);
+        UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+#undef UP
+        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        ProjArgs a = {};
+        a.cam = *cam;
+        a.mode = 1;
+        a.n_last = n_lm;
+        a.n_curr = n_kp;
+        a.last_has_lm = dev + o_act;
+        a.last_desc = dev + o_ld;
+        a.last_octave = (const int32_t*)(dev + o_lvl);
+        a.last_obs = lm_has_observation ? dev + o_obs : nullptr;
+        a.lm_reproj = (const double*)(dev + o_rp);
+        a.lm_x_right = (const float*)(dev + o_lxr);
+        a.lowe_ratio = lowe_ratio;
+        a.kp = (const lpslam_keypoint*)(dev + o_kp);
+        a.desc = dev + o_desc;
+        a.x_right = (const float*)(dev + o_xr);
+        a.curr_taken = dev + o_tk;
+        a.scale = (const float*)(dev + o_sc);
+        a.margin = margin;
+        a.cell_count = (uint32_t*)(dev + o_cc);
+        a.cell_start = (uint32_t*)(dev + o_cs);
+        a.cell_fill = (uint32_t*)(dev + o_cf);
+        a.cell_items = (uint32_t*)(dev + o_ci);
+        a.top_key = (uint4*)(dev + o_tkey);
+        a.top_idx = (int4*)(dev + o_tidx);
+        a.curr_match_last = (int32_t*)(dev + o_m);
+        a.n_events = (uint32_t*)(dev + o_ne);
+        k_grid_count<<<(n_kp + 255) / 256, 256>>>(a);
+        k_grid_scan<<<1, 1024>>>(a);
+        k_grid_fill<<<(n_kp + 255) / 256, 256>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
+        k_proj_topk<<<(n_lm + 127) / 128, 128>>>(a);
+        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(kp_match_lm, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+    } while (false);
+    cudaFree(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_landmarks", __FILE__, __LINE__);
+    *n_matches = n_ev;
     return LPSLAM_OK;
 }

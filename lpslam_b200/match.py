@@ -86,6 +86,9 @@ register("lpslam_match_projection", C.c_int, [C.POINTER(_lib.Camera), C.c_void_p
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p,
                                               _lib.u32p])
+register("lpslam_match_landmarks", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_float, C.c_float, C.c_void_p, _lib.u32p])
 
 
 def compute_descriptor_distance_32(desc_1, desc_2):
@@ -156,6 +159,30 @@ class projection:
                                             _lib.ptr(obs), len(kp), kp.ctypes.data, cd.ctypes.data, xr.ctypes.data,
                                             tk.ctypes.data, sf.ctypes.data, float(margin), int(self.check_orientation_),
                                             out.ctypes.data, C.byref(n)))
+        return out, int(n.value)
+
+    def match_frame_and_landmarks(self, cam, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_descs, undist_keypts, descs,
+                                  stereo_x_right, has_observed_lm, scale_factors, margin=5.0, lm_has_observation=None):
+        """match/projection.cc:11-83 over flat arrays: returns (kp_match_lm, num_matches). lm_active is
+        is_observable_in_tracking_ && !will_be_erased(); lm_reproj / lm_x_right / lm_scale_level are the values cached on the
+        landmarks by the tracker (data/landmark.h:112-115)."""
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64).reshape(-1, 2)
+        lxr = np.ascontiguousarray(lm_x_right, np.float32)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_descs, np.uint8).reshape(-1, 32)
+        obs = None if lm_has_observation is None else np.ascontiguousarray(lm_has_observation, np.uint8)
+        kp = np.ascontiguousarray(undist_keypts, KP_DTYPE)
+        cd = np.ascontiguousarray(descs, np.uint8)
+        xr = np.ascontiguousarray(stereo_x_right, np.float32)
+        tk = np.ascontiguousarray(has_observed_lm, np.uint8)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        out = np.full(len(kp), -1, np.int32)
+        n = C.c_uint32(0)
+        check(lib().lpslam_match_landmarks(C.byref(cam), len(act), act.ctypes.data, rp.ctypes.data, lxr.ctypes.data, lvl.ctypes.data,
+                                           ld.ctypes.data, _lib.ptr(obs), len(kp), kp.ctypes.data, cd.ctypes.data, xr.ctypes.data,
+                                           tk.ctypes.data, sf.ctypes.data, float(margin), self.lowe_ratio_, out.ctypes.data,
+                                           C.byref(n)))
         return out, int(n.value)
 
 

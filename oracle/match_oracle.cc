@@ -242,6 +242,95 @@ int orc_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r, c
     return kept;
 }
 
+// data/common.cc:97-118: cell (x, y) -> keypoint indices in insertion order
+static std::vector<std::vector<unsigned>> assign_grid(const orc_camera* cam, uint32_t n, const orc_keypoint* kp) {
+    const int gc = static_cast<int>(cam->grid_cols), gr = static_cast<int>(cam->grid_rows);
+    std::vector<std::vector<unsigned>> grid(static_cast<size_t>(gc) * gr);
+    for (unsigned i = 0; i < n; ++i) {
+        const int cx = cvprim::round_half_even((kp[i].x - cam->min_x) * cam->inv_cell_width);
+        const int cy = cvprim::round_half_even((kp[i].y - cam->min_y) * cam->inv_cell_height);
+        if (0 <= cx && cx < gc && 0 <= cy && cy < gr) grid[static_cast<size_t>(cx) * gr + cy].push_back(i);
+    }
+    return grid;
+}
+
+// data/common.cc:127-186 get_keypoints_in_cell
+static void keypoints_in_cell(const orc_camera* cam, const std::vector<std::vector<unsigned>>& grid, const orc_keypoint* kp,
+                              float ref_x, float ref_y, float m, int min_level, int max_level, std::vector<unsigned>& idx) {
+    idx.clear();
+    const int gc = static_cast<int>(cam->grid_cols), gr = static_cast<int>(cam->grid_rows);
+    const int min_cx = std::max(0, cvprim::floor_int((ref_x - cam->min_x - m) * cam->inv_cell_width));
+    if (gc <= min_cx) return;
+    const int max_cx = std::min(gc - 1, cvprim::ceil_int((ref_x - cam->min_x + m) * cam->inv_cell_width));
+    if (max_cx < 0) return;
+    const int min_cy = std::max(0, cvprim::floor_int((ref_y - cam->min_y - m) * cam->inv_cell_height));
+    if (gr <= min_cy) return;
+    const int max_cy = std::min(gr - 1, cvprim::ceil_int((ref_y - cam->min_y + m) * cam->inv_cell_height));
+    if (max_cy < 0) return;
+    const bool check_level = (0 < min_level) || (0 <= max_level);
+    for (int cx = min_cx; cx <= max_cx; ++cx)
+        for (int cy = min_cy; cy <= max_cy; ++cy)
+            for (unsigned i : grid[static_cast<size_t>(cx) * gr + cy]) {
+                if (check_level) {
+                    if (kp[i].octave < min_level) continue;
+                    if (0 <= max_level && max_level < kp[i].octave) continue;
+                }
+                const float ddx = kp[i].x - ref_x, ddy = kp[i].y - ref_y;
+                if (std::abs(ddx) < m && std::abs(ddy) < m) idx.push_back(i);
+            }
+}
+
+// match/projection.cc:11-83 match_frame_and_landmarks (the local-map search of every tracked frame): the landmarks come
+// with the reprojection the tracker cached on them (data/landmark.h:112-115)
+int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj /*n_lm x 2*/,
+                        const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                        const uint8_t* lm_has_observation /* nullable = all 1 */, uint32_t n_kp, const orc_keypoint* kp,
+                        const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
+                        const float* scale_factors, float margin, float lowe_ratio, int32_t* kp_match_lm) {
+    unsigned num = 0;
+    const auto grid = assign_grid(cam, n_kp, kp);
+    std::vector<uint8_t> taken(kp_has_observed_lm, kp_has_observed_lm + n_kp);
+    std::fill(kp_match_lm, kp_match_lm + n_kp, -1);
+    std::vector<unsigned> idx;
+    for (unsigned j = 0; j < n_lm; ++j) {
+        if (!lm_active[j]) continue;  // !is_observable_in_tracking_ || will_be_erased()  (:16-21)
+        const int level = lm_scale_level[j];
+        const float m = margin * scale_factors[level];
+        keypoints_in_cell(cam, grid, kp, static_cast<float>(lm_reproj[2 * j]), static_cast<float>(lm_reproj[2 * j + 1]), m, level - 1,
+                          level, idx);
+        if (idx.empty()) continue;
+        const uint8_t* ld = lm_desc + static_cast<size_t>(j) * 32;
+        unsigned best = MAX_HAMMING_DIST, second = MAX_HAMMING_DIST;
+        int best_level = -1, second_level = -1, best_i = -1;
+        for (unsigned i : idx) {
+            if (taken[i]) continue;  // :41-43, sees the assignments of earlier landmarks
+            if (0 < kp_x_right[i]) {
+                const float err = std::abs(lm_x_right[j] - kp_x_right[i]);
+                if (m < err) continue;
+            }
+            const unsigned d = hamming_32(ld, kp_desc + static_cast<size_t>(i) * 32);
+            if (d < best) {
+                second = best;
+                best = d;
+                second_level = best_level;
+                best_level = kp[i].octave;
+                best_i = static_cast<int>(i);
+            }
+            else if (d < second) {
+                second_level = kp[i].octave;
+                second = d;
+            }
+        }
+        if (best <= HAMMING_DIST_THR_HIGH) {
+            if (best_level == second_level && best > lowe_ratio * second) continue;  // :69-72
+            kp_match_lm[best_i] = static_cast<int32_t>(j);
+            taken[best_i] = lm_has_observation ? lm_has_observation[j] : 1;
+            ++num;
+        }
+    }
+    return static_cast<int>(num);
+}
+
 // match/projection.cc:85-208 with data/common.cc:97-186 and camera/perspective.cc:151-169
 int orc_match_projection(const orc_camera* cam, const double* Tc, const double* Tl, uint32_t n_last,
                          const uint8_t* last_has_lm, const uint8_t* last_outlier, const double* last_pos_w,

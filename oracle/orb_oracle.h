@@ -93,6 +93,15 @@ int orc_match_projection(const orc_camera* cam, const double* pose_cw_curr /*4x4
                          const uint8_t* last_lm_has_observation /* n_last, NULL = all landmarks have observations */,
                          int32_t* curr_match_last /* n_curr: index of the last-frame landmark or -1 */);
 
+/* match/projection.cc:11-83 match_frame_and_landmarks over flat arrays. lm_active = is_observable_in_tracking_ &&
+ * !will_be_erased(); kp_match_lm[i] = index of the landmark assigned to keypoint i by this call, or -1. Returns num_matches. */
+int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj /*n_lm x 2*/,
+                        const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc /*n_lm x 32*/,
+                        const uint8_t* lm_has_observation /* nullable = all 1 */, uint32_t n_kp,
+                        const orc_keypoint* kp_undist, const uint8_t* kp_desc, const float* kp_x_right,
+                        const uint8_t* kp_has_observed_lm, const float* scale_factors, float margin, float lowe_ratio,
+                        int32_t* kp_match_lm);
+
 /* exact brute-force top-2 (reference semantics of a sequential strict-< scan): per query best index, best and second distance */
 void orc_knn_top2(const uint8_t* q, uint32_t nq, const uint8_t* db, uint64_t ndb, int64_t* best_idx, uint32_t* best_d,
                   uint32_t* second_d);

@@ -103,6 +103,8 @@ class Oracle:
             L.orc_match_projection.argtypes = [C.POINTER(_CameraStruct), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                                C.c_uint32, u8p, u8p, C.POINTER(C.c_double), u8p, i32p, f32p,
                                                C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, C.c_float, C.c_int, u8p, i32p]
+            L.orc_match_landmarks.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, u8p, C.POINTER(C.c_double), f32p, i32p, u8p, u8p,
+                                              C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, C.c_float, C.c_float, i32p]
             L.orc_knn_top2.argtypes = [u8p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_int64), C.POINTER(C.c_uint32),
                                        C.POINTER(C.c_uint32)]
 
@@ -210,6 +212,26 @@ class Oracle:
                                           margin, int(check_orientation),
                                           None if last_lm_has_observation is None else _ptr(np.ascontiguousarray(last_lm_has_observation, np.uint8), u8p),
                                           _ptr(out, i32p))
+        return out, n
+
+    def match_landmarks(self, cam, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_desc, kp, kp_desc, kp_x_right,
+                        kp_has_observed_lm, scale, margin, lowe_ratio, lm_has_observation=None):
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64)
+        lxr = np.ascontiguousarray(lm_x_right, np.float32)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_desc, np.uint8)
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        kd = np.ascontiguousarray(kp_desc, np.uint8)
+        xr = np.ascontiguousarray(kp_x_right, np.float32)
+        tk = np.ascontiguousarray(kp_has_observed_lm, np.uint8)
+        scale = np.ascontiguousarray(scale, np.float32)
+        out = np.empty(len(kp), np.int32)
+        n = self.lib.orc_match_landmarks(C.byref(cam), len(act), _ptr(act, u8p), _ptr(rp, C.POINTER(C.c_double)), _ptr(lxr, f32p),
+                                         _ptr(lvl, i32p), _ptr(ld, u8p),
+                                         None if lm_has_observation is None else _ptr(np.ascontiguousarray(lm_has_observation, np.uint8), u8p),
+                                         len(kp), kp.ctypes.data, _ptr(kd, u8p), _ptr(xr, f32p), _ptr(tk, u8p), _ptr(scale, f32p),
+                                         margin, lowe_ratio, _ptr(out, i32p))
         return out, n
 
     def knn_top2(self, q, db):

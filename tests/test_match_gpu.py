@@ -115,3 +115,72 @@ def test_projection(oracle, seed, stereo, temps):
                                                                               obs)
             assert np.array_equal(got, want) and ng == nw
     assert nw > 50
+
+
+def landmarks_case(oracle, seed, stereo, with_temporaries):
+    """local map for match_frame_and_landmarks: up to three landmarks per frame keypoint (so that landmarks fight for
+    keypoints and the ratio test sees near-duplicates), reprojections jittered around the keypoints, levels at or above
+    the keypoint octave, plus unrelated landmarks anywhere in the image"""
+    rng = np.random.default_rng(seed)
+    img = synth_image(480, 640, 80 + seed)
+    o = oracle.extractor(max_kpts=1000)
+    kp, desc = o.extract(img)
+    n = len(kp)
+    args = dict(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480, focal_x_baseline=50.0 if stereo else 0.0,
+                true_baseline=0.1, is_monocular=not stereo)
+    src = np.concatenate([np.arange(n), rng.integers(0, n, n), rng.integers(0, n // 10, n // 2)])
+    rng.shuffle(src)
+    m = len(src)
+    reproj = np.stack([kp["x"][src], kp["y"][src]], axis=1).astype(np.float64) + rng.normal(0, 2.0, (m, 2))
+    level = np.clip(kp["octave"][src] + rng.integers(0, 2, m), 0, 7).astype(np.int32)
+    ldesc = desc[src] ^ np.packbits(rng.random((m, 256)) < 0.06, axis=1, bitorder="little")
+    extra = 200
+    reproj = np.concatenate([reproj, rng.uniform([-20, -20], [660, 500], (extra, 2))])
+    level = np.concatenate([level, rng.integers(0, 8, extra).astype(np.int32)])
+    ldesc = np.concatenate([ldesc, rng.integers(0, 256, (extra, 32), dtype=np.uint8)])
+    m += extra
+    active = (rng.random(m) < 0.9).astype(np.uint8)
+    depth = rng.uniform(2.0, 8.0, n)
+    xr = np.where(rng.random(n) < 0.5, kp["x"] - 50.0 / depth, -1.0).astype(np.float32) if stereo else np.full(n, -1.0, np.float32)
+    lxr = (reproj[:, 0] - rng.uniform(3.0, 30.0, m)).astype(np.float32)
+    lxr[: len(src)] = np.where(xr[src] > 0, xr[src] + rng.normal(0, 3.0, len(src)), lxr[: len(src)]).astype(np.float32)
+    taken = (rng.random(n) < 0.1).astype(np.uint8)
+    obs = (rng.random(m) < 0.5).astype(np.uint8) if with_temporaries else None
+    return args, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, o.table(0), obs
+
+
+@pytest.mark.parametrize("seed,stereo,temps", [(1, False, False), (2, True, False), (3, True, True), (4, False, True)])
+def test_frame_and_landmarks(oracle, seed, stereo, temps):
+    # match/projection.cc:11-83; margins as the tracker uses them (module/tracking_module.cc search_local_landmarks: 5 / 20)
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    args, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs = landmarks_case(oracle, seed, stereo, temps)
+    total = 0
+    for margin in (5.0, 20.0):
+        for ratio in (0.8, 0.6):
+            want, nw = oracle.match_landmarks(pyoracle.make_camera(**args), active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf,
+                                              margin, ratio, obs)
+            got, ng = match.projection(ratio, True).match_frame_and_landmarks(match.make_camera(**args), active, reproj, lxr, level,
+                                                                              ldesc, kp, desc, xr, taken, sf, margin, obs)
+            assert np.array_equal(got, want) and ng == nw
+            total += nw
+    assert total > 400
+
+
+def test_frame_and_landmarks_edges():
+    from lpslam_b200 import match
+    cam = match.make_camera(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    sf = (1.2 ** np.arange(8)).astype(np.float32)
+    kp = np.zeros(0, match.KP_DTYPE)
+    out, n = match.projection(0.8, True).match_frame_and_landmarks(cam, np.ones(3, np.uint8), np.zeros((3, 2)), np.zeros(3, np.float32),
+                                                                   np.zeros(3, np.int32), np.zeros((3, 32), np.uint8), kp,
+                                                                   np.zeros((0, 32), np.uint8), np.zeros(0, np.float32),
+                                                                   np.zeros(0, np.uint8), sf, 5.0)
+    assert n == 0 and len(out) == 0
+    kp = np.zeros(2, match.KP_DTYPE)
+    kp["x"], kp["y"] = [100.0, 300.0], [100.0, 200.0]
+    out, n = match.projection(0.8, True).match_frame_and_landmarks(cam, np.zeros(0, np.uint8), np.zeros((0, 2)), np.zeros(0, np.float32),
+                                                                   np.zeros(0, np.int32), np.zeros((0, 32), np.uint8), kp,
+                                                                   np.zeros((2, 32), np.uint8), np.full(2, -1, np.float32),
+                                                                   np.zeros(2, np.uint8), sf, 5.0)
+    assert n == 0 and (out == -1).all()

@@ -106,3 +106,54 @@ def test_angle_checker_top3(oracle):
     ids = [35] * 5 + [324] * 4 + [127] * 3 + [0, 60, 180, 270]
     inv = oracle.angle_invalid(deltas, ids)
     assert sorted(inv.tolist()) == [0, 60, 180, 270]
+
+
+def test_landmark_matcher_semantics(oracle):
+    """match/projection.cc:11-83 hand-built cases for the port: strict '<' updates, the ratio test only between
+    candidates of the same scale level, keypoints claimed by earlier landmarks, the x_right gate."""
+    from oracle import pyoracle
+    cam = pyoracle.make_camera(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    kp = np.zeros(3, pyoracle.KP_DTYPE)
+    kp["x"], kp["y"], kp["octave"] = [100.0, 102.0, 300.0], [100.0, 101.0, 200.0], [1, 1, 0]
+    d = np.zeros((3, 32), np.uint8)
+    d[1, 0] = 0x03          # keypoint 1 is 2 bits from keypoint 0
+    d[2] = 0xFF
+    none = np.full(3, -1.0, np.float32)
+    free = np.zeros(3, np.uint8)
+
+    def run(lm_desc, reproj, level, ratio=0.8, taken=free, xr=none, lxr=None, active=None, obs=None):
+        m = len(level)
+        return oracle.match_landmarks(cam, np.ones(m, np.uint8) if active is None else active, reproj, np.zeros(m, np.float32) if lxr is None else lxr,
+                                      level, lm_desc, kp, d, xr, taken, sf, 5.0, ratio, obs)
+
+    one = np.zeros((1, 32), np.uint8)
+    # best = keypoint 0 (distance 0), second = keypoint 1 (distance 2) on the same level: 0 > 0.8 * 2 is false -> match
+    out, n = run(one, [[100.0, 100.0]], [1])
+    assert n == 1 and list(out) == [0, -1, -1]
+    # landmark 1 bit from keypoint 0 and 1 bit from keypoint 1 -> tie, first visited wins, ratio 1 > 0.8 * 1 rejects
+    tie = one.copy()
+    tie[0, 0] = 0x01
+    out, n = run(tie, [[100.0, 100.0]], [1])
+    assert n == 0
+    # same, but the second best sits on another level: no ratio test
+    kp["octave"][1] = 0
+    out, n = run(tie, [[100.0, 100.0]], [1])
+    assert n == 1 and out[0] == 0
+    kp["octave"][1] = 1
+    # two identical landmarks: the first claims keypoint 0, the second falls to keypoint 1
+    out, n = run(np.zeros((2, 32), np.uint8), [[100.0, 100.0], [100.0, 100.0]], [1, 1])
+    assert n == 2 and list(out) == [0, 1, -1]
+    # ... unless the first landmark has no observation: then the second one overwrites keypoint 0
+    out, n = run(np.zeros((2, 32), np.uint8), [[100.0, 100.0], [100.0, 100.0]], [1, 1], obs=np.array([0, 1], np.uint8))
+    assert n == 2 and list(out) == [1, -1, -1]
+    # level window is [level - 1, level]: a level-3 landmark does not see octave-1 keypoints
+    out, n = run(one, [[100.0, 100.0]], [3])
+    assert n == 0
+    # x_right gate: |x_right_lm - x_right_kp| > margin * scale drops keypoint 0, keypoint 1 (no stereo) stays
+    xr = np.array([90.0, -1.0, -1.0], np.float32)
+    out, n = run(one, [[100.0, 100.0]], [1], xr=xr, lxr=np.array([70.0], np.float32))
+    assert n == 1 and out[1] == 0
+    # inactive landmarks are skipped
+    out, n = run(one, [[100.0, 100.0]], [1], active=np.zeros(1, np.uint8))
+    assert n == 0
