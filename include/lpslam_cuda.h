@@ -204,6 +204,19 @@ int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, const uint8_
                            const uint8_t* kp_has_observed_lm, const float* scale_factors, float margin, float lowe_ratio,
                            int32_t* kp_match_lm, uint32_t* n_matches);
 
+/* Per-frame post-processing that follows extraction in data::frame's constructors (data/frame.cc:37-51,75-92) for the
+ * perspective camera model: undistort_keypoints (camera/perspective.cc:98-130, cv::undistortPoints with K, (k1 k2 p1 p2
+ * k3), P = K, 20 iterations / 1e-6), convert_keypoints_to_bearings (:132-141) and assign_keypoints_to_grid
+ * (data/common.cc:97-118). The grid comes back as CSR over cell = cx * grid_rows + cy (cell_start has grid_cols *
+ * grid_rows + 1 entries), keypoint indices ascending inside a cell = the reference's push_back order. */
+typedef struct {
+    double fx, fy, cx, cy;
+    double dist[5]; /* k1 k2 p1 p2 k3, camera/perspective.h */
+} lpslam_perspective;
+int lpslam_frame_postprocess(const lpslam_perspective* model, const lpslam_camera* cam, uint32_t n,
+                             const lpslam_keypoint* keypts, lpslam_keypoint* undist_keypts, double* bearings /*n x 3*/,
+                             uint32_t* cell_start, uint32_t* cell_items /*n*/, uint32_t* n_in_grid);
+
 /* ---------------------------------------------------------------- kNN database (relocalisation / loop query) ----- */
 /* Brute-force Hamming top-2 of query descriptors against a device-resident descriptor database (generalises the
  * best / second-best scan of match/robust.cc:252-274 and the BoW-candidate search of module/relocalizer.cc:31-46).

@@ -437,6 +437,61 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
     if (lane == 0) *a.n_events = num;
 }
 
+// ---- frame post-processing that follows extraction (data/frame.cc:37-51,75-92), perspective model --------------------
+// camera/perspective.cc:98-141. cv::undistortPoints(K, (k1 k2 p1 p2 k3), R = I, P = K, TermCriteria(EPS | MAX_ITER, 20,
+// 1e-6)): iterative inversion of the Brown-Conrady model in double, evaluated in OpenCV's operation order with explicit
+// round-to-nearest multiplies and adds (no FMA contraction), result rounded to float. The zero rational / thin-prism
+// coefficients of the 5-parameter model contribute exact zeros and are dropped.
+__device__ __forceinline__ double dm(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double da(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double ds(double a, double b) { return __dsub_rn(a, b); }
+
+__global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lpslam_keypoint* __restrict__ in,
+                                     lpslam_keypoint* __restrict__ out, double* __restrict__ bearings) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    lpslam_keypoint k = in[i];
+    const double k0 = m.dist[0], k1 = m.dist[1], p1 = m.dist[2], p2 = m.dist[3], k4 = m.dist[4];
+    const double ifx = __ddiv_rn(1.0, m.fx), ify = __ddiv_rn(1.0, m.fy);
+    const double u = (double)k.x, v = (double)k.y;
+    double x = dm(ds(u, m.cx), ifx), y = dm(ds(v, m.cy), ify);
+    const double x0 = x, y0 = y;
+    double error = 1.7976931348623157e308;
+    for (int j = 0; j < 20; ++j) {
+        if (error < 1e-6) break;
+        double r2 = da(dm(x, x), dm(y, y));
+        const double icdist = __ddiv_rn(1.0, da(1.0, dm(da(dm(da(dm(k4, r2), k1), r2), k0), r2)));
+        if (icdist < 0) {  // calib3d regression 14583: fall back to the un-iterated point
+            x = dm(ds(u, m.cx), ifx);
+            y = dm(ds(v, m.cy), ify);
+            break;
+        }
+        const double dX = da(dm(dm(dm(2.0, p1), x), y), dm(p2, da(r2, dm(dm(2.0, x), x))));
+        const double dY = da(dm(p1, da(r2, dm(dm(2.0, y), y))), dm(dm(dm(2.0, p2), x), y));
+        x = dm(ds(x0, dX), icdist);
+        y = dm(ds(y0, dY), icdist);
+        r2 = da(dm(x, x), dm(y, y));
+        const double r4 = dm(r2, r2), r6 = dm(r4, r2);
+        const double a1 = dm(dm(2.0, x), y), a2 = da(r2, dm(dm(2.0, x), x)), a3 = da(r2, dm(dm(2.0, y), y));
+        const double cdist = da(da(da(1.0, dm(k0, r2)), dm(k1, r4)), dm(k4, r6));
+        const double xd0 = da(da(dm(dm(x, cdist), 1.0), dm(p1, a1)), dm(p2, a2));
+        const double yd0 = da(da(dm(dm(y, cdist), 1.0), dm(p1, a3)), dm(p2, a1));
+        const double ex = ds(da(dm(xd0, m.fx), m.cx), u), ey = ds(da(dm(yd0, m.fy), m.cy), v);
+        error = __dsqrt_rn(da(dm(ex, ex), dm(ey, ey)));
+    }
+    k.x = (float)da(dm(m.fx, x), m.cx);
+    k.y = (float)da(dm(m.fy, y), m.cy);
+    k.response = 0.f;   // cv::KeyPoint defaults: undistort_keypoints copies pt, angle, size, octave only
+    k.class_id = -1;
+    out[i] = k;
+    // camera/perspective.cc:132-141
+    const double xn = __ddiv_rn(ds((double)k.x, m.cx), m.fx), yn = __ddiv_rn(ds((double)k.y, m.cy), m.fy);
+    const double l2 = __dsqrt_rn(da(da(dm(xn, xn), dm(yn, yn)), 1.0));
+    bearings[3 * (size_t)i] = __ddiv_rn(xn, l2);
+    bearings[3 * (size_t)i + 1] = __ddiv_rn(yn, l2);
+    bearings[3 * (size_t)i + 2] = __ddiv_rn(1.0, l2);
+}
+
 }  // namespace
 }  // namespace lps
 
@@ -635,5 +690,53 @@ extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, c
     cudaFree(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_landmarks", __FILE__, __LINE__);
     *n_matches = n_ev;
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const lpslam_camera* cam, uint32_t n,
+                                        const lpslam_keypoint* keypts, lpslam_keypoint* undist_keypts, double* bearings,
+                                        uint32_t* cell_start, uint32_t* cell_items, uint32_t* n_in_grid) {
+    LPS_ARG(model && cam && cell_start && n_in_grid, "null argument");
+    LPS_ARG(n == 0 || (keypts && undist_keypts && bearings && cell_items), "null keypoint argument");
+    LPS_ARG(model->fx != 0.0 && model->fy != 0.0, "focal length must be non-zero");
+    LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1, "bad camera grid");
+    const uint32_t ncell = cam->grid_cols * cam->grid_rows;
+    *n_in_grid = 0;
+    for (uint32_t c = 0; c <= ncell; ++c) cell_start[c] = 0;
+    if (n == 0) return LPSLAM_OK;  // perspective.cc:100-103: empty input is passed through
+    ArenaBump ar;
+    const size_t o_in = ar.take(sizeof(lpslam_keypoint) * (size_t)n), o_out = ar.take(sizeof(lpslam_keypoint) * (size_t)n);
+    const size_t o_b = ar.take(24 * (size_t)n), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    cudaError_t e = cudaSuccess;
+    do {
+        if ((e = cudaMemcpy(dev + o_in, keypts, sizeof(lpslam_keypoint) * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        k_undistort_bearings<<<(n + 127) / 128, 128>>>(*model, n, (const lpslam_keypoint*)(dev + o_in), (lpslam_keypoint*)(dev + o_out),
+                                                      (double*)(dev + o_b));
+        ProjArgs a = {};
+        a.cam = *cam;
+        a.n_curr = n;
+        a.kp = (const lpslam_keypoint*)(dev + o_out);
+        a.cell_count = (uint32_t*)(dev + o_cc);
+        a.cell_start = (uint32_t*)(dev + o_cs);
+        a.cell_fill = (uint32_t*)(dev + o_cf);
+        a.cell_items = (uint32_t*)(dev + o_ci);
+        k_grid_count<<<(n + 255) / 256, 256>>>(a);
+        k_grid_scan<<<1, 1024>>>(a);
+        k_grid_fill<<<(n + 255) / 256, 256>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(undist_keypts, dev + o_out, sizeof(lpslam_keypoint) * (size_t)n, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(bearings, dev + o_b, 24 * (size_t)n, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(cell_start, dev + o_cs, 4 * (size_t)(ncell + 1), cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (cell_start[ncell] > 0)
+            if ((e = cudaMemcpy(cell_items, dev + o_ci, 4 * (size_t)cell_start[ncell], cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+    } while (false);
+    cudaFree(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_frame_postprocess", __FILE__, __LINE__);
+    *n_in_grid = cell_start[ncell];
     return LPSLAM_OK;
 }

@@ -91,6 +91,29 @@ register("lpslam_match_landmarks", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32,
                                              C.c_void_p, C.c_float, C.c_float, C.c_void_p, _lib.u32p])
 
 
+class Perspective(C.Structure):
+    """camera::perspective intrinsics + distortion (camera/perspective.h), lpslam_perspective in the C ABI"""
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("dist", C.c_double * 5)]
+
+
+register("lpslam_frame_postprocess", C.c_int, [C.POINTER(Perspective), C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, _lib.u32p])
+
+
+def frame_postprocess(model, cam, keypts):
+    """data/frame.cc:37-51: (undist_keypts, bearings, cell_start, cell_items) of a frame's keypoints on the device."""
+    kp = np.ascontiguousarray(keypts, KP_DTYPE)
+    und = np.empty_like(kp)
+    bearings = np.empty((len(kp), 3), np.float64)
+    ncell = cam.grid_cols * cam.grid_rows
+    start = np.zeros(ncell + 1, np.uint32)
+    items = np.empty(max(len(kp), 1), np.uint32)
+    n = C.c_uint32(0)
+    check(lib().lpslam_frame_postprocess(C.byref(model), C.byref(cam), len(kp), kp.ctypes.data, und.ctypes.data, bearings.ctypes.data,
+                                         start.ctypes.data, items.ctypes.data, C.byref(n)))
+    return und, bearings, start, items[: n.value]
+
+
 def compute_descriptor_distance_32(desc_1, desc_2):
     """match/base.h:18-40 on the device, row-wise over (N, 32) uint8 arrays (or a single pair)."""
     a = np.ascontiguousarray(np.atleast_2d(desc_1), np.uint8)

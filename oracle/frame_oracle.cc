@@ -1,0 +1,96 @@
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE. See orb_oracle.h.
+// Restatement of the per-frame post-processing that follows extraction in data::frame's constructors
+// (/root/reference/external/openvslam/src/openvslam/data/frame.cc:37-51,75-92): keypoint undistortion, bearing
+// conversion and grid assignment for the perspective camera model (camera/perspective.cc:98-141, data/common.cc:97-118).
+// The undistortion arithmetic lives in OpenCV (cv::undistortPoints, not vendored): it is restated here from the published
+// algorithm (iterative inversion of the Brown-Conrady model, calib3d undistort: cvUndistortPointsInternal) and PINNED
+// bit-for-bit against cv2 4.13 in tests/test_oracle_vs_cv2.py.
+#include "orb_oracle.h"
+#include "cvprim.h"
+
+#include <cmath>
+#include <limits>
+#include <vector>
+
+extern "C" {
+
+// camera/perspective.cc:98-130: cv::undistortPoints(mat, mat, K, dist(k1,k2,p1,p2,k3), Mat(), K,
+// TermCriteria(EPS | MAX_ITER, 20, 1e-6)); pt replaced, angle / size / octave copied, response / class_id left at the
+// cv::KeyPoint defaults (0, -1).
+void orc_undistort_keypoints(double fx, double fy, double cx, double cy, const double* dist5, uint32_t n, const orc_keypoint* in,
+                             orc_keypoint* out) {
+    const double k0 = dist5[0], k1 = dist5[1], p1 = dist5[2], p2 = dist5[3], k4 = dist5[4];
+    const double ifx = 1.0 / fx, ify = 1.0 / fy;
+    const int max_count = 20;
+    const double eps = 1e-6;
+    for (uint32_t i = 0; i < n; ++i) {
+        const double u = in[i].x, v = in[i].y;
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        double error = std::numeric_limits<double>::max();
+        for (int j = 0;; ++j) {
+            if (j >= max_count) break;
+            if (error < eps) break;
+            double r2 = x * x + y * y;
+            // rational terms k[5..7] are zero for a 5-coefficient model
+            const double icdist = (1 + ((0.0 * r2 + 0.0) * r2 + 0.0) * r2) / (1 + ((k4 * r2 + k1) * r2 + k0) * r2);
+            if (icdist < 0) {
+                x = (u - cx) * ifx;
+                y = (v - cy) * ify;
+                break;
+            }
+            const double deltaX = 2 * p1 * x * y + p2 * (r2 + 2 * x * x) + 0.0 * r2 + 0.0 * r2 * r2;
+            const double deltaY = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y + 0.0 * r2 + 0.0 * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+            {
+                r2 = x * x + y * y;
+                const double r4 = r2 * r2, r6 = r4 * r2;
+                const double a1 = 2 * x * y, a2 = r2 + 2 * x * x, a3 = r2 + 2 * y * y;
+                const double cdist = 1 + k0 * r2 + k1 * r4 + k4 * r6;
+                const double icdist2 = 1. / (1 + 0.0 * r2 + 0.0 * r4 + 0.0 * r6);
+                const double xd0 = x * cdist * icdist2 + p1 * a1 + p2 * a2 + 0.0 * r2 + 0.0 * r4;
+                const double yd0 = y * cdist * icdist2 + p1 * a3 + p2 * a1 + 0.0 * r2 + 0.0 * r4;
+                const double x_proj = xd0 * fx + cx, y_proj = yd0 * fy + cy;
+                error = std::sqrt((x_proj - u) * (x_proj - u) + (y_proj - v) * (y_proj - v));
+            }
+        }
+        // new camera matrix P = K, R = identity: RR = P * I
+        const double xx = fx * x + 0.0 * y + cx, yy = 0.0 * x + fy * y + cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        out[i] = in[i];
+        out[i].x = static_cast<float>(xx * ww);
+        out[i].y = static_cast<float>(yy * ww);
+        out[i].response = 0.0f;
+        out[i].class_id = -1;
+    }
+}
+
+// camera/perspective.cc:132-141
+void orc_keypoints_to_bearings(double fx, double fy, double cx, double cy, uint32_t n, const orc_keypoint* kp, double* bearings) {
+    for (uint32_t i = 0; i < n; ++i) {
+        const double xn = (kp[i].x - cx) / fx, yn = (kp[i].y - cy) / fy;
+        const double l2 = std::sqrt(xn * xn + yn * yn + 1.0);
+        bearings[3 * i] = xn / l2;
+        bearings[3 * i + 1] = yn / l2;
+        bearings[3 * i + 2] = 1.0 / l2;
+    }
+}
+
+// data/common.cc:97-118 as CSR over cell = cx * grid_rows + cy, indices in insertion (ascending) order
+void orc_assign_grid(const orc_camera* cam, uint32_t n, const orc_keypoint* kp, uint32_t* cell_start, uint32_t* items) {
+    const int gc = static_cast<int>(cam->grid_cols), gr = static_cast<int>(cam->grid_rows);
+    std::vector<std::vector<uint32_t>> grid(static_cast<size_t>(gc) * gr);
+    for (uint32_t i = 0; i < n; ++i) {
+        const int cx = cvprim::round_half_even((kp[i].x - cam->min_x) * cam->inv_cell_width);
+        const int cy = cvprim::round_half_even((kp[i].y - cam->min_y) * cam->inv_cell_height);
+        if (0 <= cx && cx < gc && 0 <= cy && cy < gr) grid[static_cast<size_t>(cx) * gr + cy].push_back(i);
+    }
+    uint32_t pos = 0;
+    for (size_t c = 0; c < grid.size(); ++c) {
+        cell_start[c] = pos;
+        for (uint32_t i : grid[c]) items[pos++] = i;
+    }
+    cell_start[grid.size()] = pos;
+}
+
+}  // extern "C"

@@ -102,6 +102,12 @@ int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_
                         const uint8_t* kp_has_observed_lm, const float* scale_factors, float margin, float lowe_ratio,
                         int32_t* kp_match_lm);
 
+/* data/frame.cc:37-51,75-92 post-processing for the perspective model (camera/perspective.cc:98-141, data/common.cc:97-118) */
+void orc_undistort_keypoints(double fx, double fy, double cx, double cy, const double* dist5 /*k1 k2 p1 p2 k3*/, uint32_t n,
+                             const orc_keypoint* in, orc_keypoint* out);
+void orc_keypoints_to_bearings(double fx, double fy, double cx, double cy, uint32_t n, const orc_keypoint* kp, double* bearings);
+void orc_assign_grid(const orc_camera* cam, uint32_t n, const orc_keypoint* kp, uint32_t* cell_start /*cells + 1*/, uint32_t* items /*n*/);
+
 /* exact brute-force top-2 (reference semantics of a sequential strict-< scan): per query best index, best and second distance */
 void orc_knn_top2(const uint8_t* q, uint32_t nq, const uint8_t* db, uint64_t ndb, int64_t* best_idx, uint32_t* best_d,
                   uint32_t* second_d);

@@ -105,6 +105,12 @@ class Oracle:
                                                C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, C.c_float, C.c_int, u8p, i32p]
             L.orc_match_landmarks.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, u8p, C.POINTER(C.c_double), f32p, i32p, u8p, u8p,
                                               C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, C.c_float, C.c_float, i32p]
+            L.orc_undistort_keypoints.argtypes = [C.c_double] * 4 + [C.POINTER(C.c_double), C.c_uint32, C.c_void_p, C.c_void_p]
+            L.orc_undistort_keypoints.restype = None
+            L.orc_keypoints_to_bearings.argtypes = [C.c_double] * 4 + [C.c_uint32, C.c_void_p, C.POINTER(C.c_double)]
+            L.orc_keypoints_to_bearings.restype = None
+            L.orc_assign_grid.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+            L.orc_assign_grid.restype = None
             L.orc_knn_top2.argtypes = [u8p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_int64), C.POINTER(C.c_uint32),
                                        C.POINTER(C.c_uint32)]
 
@@ -233,6 +239,27 @@ class Oracle:
                                          len(kp), kp.ctypes.data, _ptr(kd, u8p), _ptr(xr, f32p), _ptr(tk, u8p), _ptr(scale, f32p),
                                          margin, lowe_ratio, _ptr(out, i32p))
         return out, n
+
+    def undistort_keypoints(self, fx, fy, cx, cy, dist5, kp):
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        d = np.ascontiguousarray(dist5, np.float64)
+        out = np.empty_like(kp)
+        self.lib.orc_undistort_keypoints(fx, fy, cx, cy, _ptr(d, C.POINTER(C.c_double)), len(kp), kp.ctypes.data, out.ctypes.data)
+        return out
+
+    def keypoints_to_bearings(self, fx, fy, cx, cy, kp):
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        out = np.empty((len(kp), 3), np.float64)
+        self.lib.orc_keypoints_to_bearings(fx, fy, cx, cy, len(kp), kp.ctypes.data, _ptr(out, C.POINTER(C.c_double)))
+        return out
+
+    def assign_grid(self, cam, kp):
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        ncell = cam.grid_cols * cam.grid_rows
+        start = np.empty(ncell + 1, np.uint32)
+        items = np.empty(len(kp), np.uint32)
+        self.lib.orc_assign_grid(C.byref(cam), len(kp), kp.ctypes.data, _ptr(start, C.POINTER(C.c_uint32)), _ptr(items, C.POINTER(C.c_uint32)))
+        return start, items[: start[-1]]
 
     def knn_top2(self, q, db):
         q = np.ascontiguousarray(q, np.uint8)

@@ -184,3 +184,32 @@ def test_frame_and_landmarks_edges():
                                                                    np.zeros((2, 32), np.uint8), np.full(2, -1, np.float32),
                                                                    np.zeros(2, np.uint8), sf, 5.0)
     assert n == 0 and (out == -1).all()
+
+
+@pytest.mark.parametrize("dist", [(-0.17, 0.027, 0.0005, -0.0003, 0.0), (0.05, -0.01, 0.0, 0.0, 0.002), (0.0, 0.0, 0.0, 0.0, 0.0)])
+def test_frame_postprocess(oracle, dist):
+    # data/frame.cc:37-51: undistort (cv::undistortPoints arithmetic, oracle pinned against cv2), bearings, grid
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    o = oracle.extractor(max_kpts=2000)
+    kp, _ = o.extract(synth_image(720, 1280, 91))
+    fx, fy, cx, cy = 700.0, 705.0, 640.0, 360.0
+    want_u = oracle.undistort_keypoints(fx, fy, cx, cy, dist, kp)
+    bounds = dict(min_x=float(want_u["x"].min()) + 5.0, max_x=float(want_u["x"].max()) - 5.0, min_y=-3.0, max_y=723.0)  # some keypoints fall off the grid
+    args = dict(fx=fx, fy=fy, cx=cx, cy=cy, cols=1280, rows=720)
+    ocam, cam = pyoracle.make_camera(**args), match.make_camera(**args)
+    for c in (ocam, cam):
+        c.min_x, c.max_x, c.min_y, c.max_y = bounds["min_x"], bounds["max_x"], bounds["min_y"], bounds["max_y"]
+        c.inv_cell_width = c.grid_cols / (c.max_x - c.min_x)
+        c.inv_cell_height = c.grid_rows / (c.max_y - c.min_y)
+    want_b = oracle.keypoints_to_bearings(fx, fy, cx, cy, want_u)
+    want_s, want_i = oracle.assign_grid(ocam, want_u)
+    model = match.Perspective(fx, fy, cx, cy, (match.C.c_double * 5)(*dist))
+    und, bearings, start, items = match.frame_postprocess(model, cam, kp)
+    for f in ("x", "y", "size", "angle", "response", "octave", "class_id"):
+        assert np.array_equal(und[f], want_u[f]), f
+    assert np.array_equal(bearings, want_b)          # double, bit-exact
+    assert np.array_equal(start, want_s) and np.array_equal(items, want_i)
+    assert 0 < len(items) < len(kp)
+    und0, b0, s0, i0 = match.frame_postprocess(model, cam, kp[:0])
+    assert len(und0) == 0 and s0[-1] == 0 and len(i0) == 0

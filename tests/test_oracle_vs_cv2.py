@@ -75,3 +75,25 @@ def test_rect_fill_matches_line_aa(oracle):
     want = np.zeros((100, 120), bool)
     want[20:72, 12:61] = True
     assert np.array_equal(m == 0, want)
+
+
+def test_undistort_points_vs_cv2():
+    """camera/perspective.cc:98-130 -> cv::undistortPoints(K, dist, P = K, (EPS | MAX_ITER, 20, 1e-6)): the restatement in
+    oracle/frame_oracle.cc is bit-identical to cv2 on lens models whose iteration converges inside the image. (Outside of
+    that, e.g. k1 = -0.3 at the image corners, OpenCV releases differ among themselves; the port keeps the loop of the 4.2
+    series the reference builds against.)"""
+    from oracle import pyoracle
+    o = pyoracle.port()
+    rng = np.random.default_rng(3)
+    K = np.array([[700.0, 0, 640.0], [0, 705.0, 360.0], [0, 0, 1]])
+    crit = (cv2.TERM_CRITERIA_EPS | cv2.TERM_CRITERIA_MAX_ITER, 20, 1e-6)
+    for dist in ([-0.17, 0.027, 0.0005, -0.0003, 0.0], [0.05, -0.01, 0, 0, 0.002], [0.1, 0.0, -0.002, 0.001, 0.0], [0, 0, 0, 0, 0]):
+        kp = np.zeros(20000, pyoracle.KP_DTYPE)
+        kp["x"], kp["y"] = rng.uniform(0, 1280, 20000), rng.uniform(0, 720, 20000)
+        kp["octave"], kp["angle"], kp["size"] = rng.integers(0, 8, 20000), rng.uniform(0, 360, 20000), 31.0
+        got = o.undistort_keypoints(700.0, 705.0, 640.0, 360.0, dist, kp)
+        src = np.stack([kp["x"], kp["y"]], 1).astype(np.float32).reshape(-1, 1, 2)
+        want = cv2.undistortPointsIter(src, K, np.array(dist, np.float64), None, K, crit).reshape(-1, 2)
+        assert np.array_equal(got["x"], want[:, 0]) and np.array_equal(got["y"], want[:, 1]), dist
+        assert np.array_equal(got["octave"], kp["octave"]) and np.array_equal(got["angle"], kp["angle"])
+        assert (got["response"] == 0).all() and (got["class_id"] == -1).all()
