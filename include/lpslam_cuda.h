@@ -109,6 +109,9 @@ typedef struct {
     uint32_t capacity;          /* rows available in kp / desc */
 } lpslam_orb_result_dev;
 int lpslam_orb_get_result_dev(lpslam_orb_ctx* ctx, lpslam_orb_result_dev* out);
+/* blocking copy of the packed results of the last *_dev call to the host (same layout as lpslam_orb_extract_batch;
+ * offsets has n_frames + 1 entries) */
+int lpslam_orb_fetch_result(lpslam_orb_ctx* ctx, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets);
 /* the context's own level-0 batch buffer (max_batch frames, row pitch *pitch, frame stride *frame_stride) for the
  * given image size: a producer that writes frames straight into it (decoder, undistortion kernel) and then passes the
  * same pointer to lpslam_orb_extract_batch_dev avoids the ingest copy. */
@@ -216,6 +219,32 @@ typedef struct {
 int lpslam_frame_postprocess(const lpslam_perspective* model, const lpslam_camera* cam, uint32_t n,
                              const lpslam_keypoint* keypts, lpslam_keypoint* undist_keypts, double* bearings /*n x 3*/,
                              uint32_t* cell_start, uint32_t* cell_items /*n*/, uint32_t* n_in_grid);
+
+/* ------------------------------------------------- image pre-processing ahead of the extractor (device kernels) ----- */
+/* util::convert_to_grayscale (util/image_converter.cc:8-39): cv::cvtColor(RGB | BGR | RGBA | BGRA -> GRAY) on 8-bit images.
+ * order: 0 = RGB(A), 1 = BGR(A). The *_dev forms take device pointers, work on n_images frames frame_stride bytes apart and
+ * only enqueue on `stream` (a cudaStream_t, NULL = default stream): their output can be the extractor's own level-0
+ * buffer (lpslam_orb_input_dev), so that a colour frame never returns to the host between decode and extraction. */
+int lpslam_gray(const uint8_t* src, int width, int height, size_t pitch, int channels, int order, uint8_t* dst, size_t dst_pitch);
+int lpslam_gray_dev(const uint8_t* src_dev, int width, int height, size_t pitch, size_t frame_stride, int channels, int order,
+                    uint32_t n_images, uint8_t* dst_dev, size_t dst_pitch, size_t dst_frame_stride, void* stream);
+/* LpSlam::ImageProcessing::imadjust with stretchlim (src/Utils/ImageProcessing.h:258-370), the body of the "AdjustIntensity"
+ * processor (src/Processor/AdjustIntensityProcessor.h:17-40, low_out -0.3, high_out 1.4) for 8UC1 images. auto_limits != 0
+ * = the std::nullopt form (1 % / 99 % histogram limits); limits_out (nullable) receives the low / high input limits. */
+int lpslam_imadjust(const uint8_t* src, int width, int height, size_t pitch, int auto_limits, double low_in, double high_in,
+                    double low_out, double high_out, uint8_t* dst, size_t dst_pitch, double* limits_out);
+size_t lpslam_imadjust_scratch_bytes(uint32_t n_images);
+int lpslam_imadjust_dev(const uint8_t* src_dev, int width, int height, size_t pitch, size_t frame_stride, uint32_t n_images,
+                        int auto_limits, double low_in, double high_in, double low_out, double high_out, uint8_t* dst_dev,
+                        size_t dst_pitch, size_t dst_frame_stride, void* scratch_dev, void* stream);
+/* LpSlam::ImageProcessing::Undistort::undistort (src/Utils/ImageProcessing.h:245-249): cv::remap(INTER_LINEAR,
+ * BORDER_CONSTANT 0) with the cached CV_32FC1 maps of cv::initUndistortRectifyMap (map_pitch in floats; the maps have the
+ * destination size and are shared by all n_images frames). */
+int lpslam_remap_linear(const uint8_t* src, int src_width, int src_height, size_t src_pitch, const float* map_x, const float* map_y,
+                        size_t map_pitch, uint8_t* dst, int dst_width, int dst_height, size_t dst_pitch);
+int lpslam_remap_linear_dev(const uint8_t* src_dev, int src_width, int src_height, size_t src_pitch, size_t src_frame_stride,
+                            const float* map_x_dev, const float* map_y_dev, size_t map_pitch, uint8_t* dst_dev, int dst_width,
+                            int dst_height, size_t dst_pitch, size_t dst_frame_stride, uint32_t n_images, void* stream);
 
 /* ---------------------------------------------------------------- kNN database (relocalisation / loop query) ----- */
 /* Brute-force Hamming top-2 of query descriptors against a device-resident descriptor database (generalises the

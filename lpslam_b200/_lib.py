@@ -69,6 +69,7 @@ SIGNATURES = {
                                            C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "lpslam_orb_extract_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_size_t]),
     "lpslam_orb_get_result_dev": (C.c_int, [C.c_void_p, C.POINTER(ResultDev)]),
+    "lpslam_orb_fetch_result": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "lpslam_orb_input_dev": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), szp, szp]),
     "lpslam_orb_sync": (C.c_int, [C.c_void_p]),
     "lpslam_orb_stream": (C.c_void_p, [C.c_void_p]),

@@ -286,6 +286,16 @@ int lpslam_orb_extract_batch_dev(lpslam_orb_ctx* c, const uint8_t* imgs_dev, uin
     return c->run_pipeline(n_frames, m, mp);
 }
 
+int lpslam_orb_fetch_result(lpslam_orb_ctx* c, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets) {
+    LPS_ARG(c && kp_out && desc_out && offsets, "null argument");
+    if (!c->has_result) {
+        set_error("no extraction has run on this context");
+        return LPSLAM_ERR_STATE;
+    }
+    LPS_CUDA(cudaSetDevice(c->device));
+    return fetch_results(c, c->last_batch, kp_out, desc_out, cap, offsets);
+}
+
 int lpslam_orb_get_result_dev(lpslam_orb_ctx* c, lpslam_orb_result_dev* out) {
     LPS_ARG(c && out, "null argument");
     if (!c->has_result) {

@@ -96,6 +96,23 @@ class orb_extractor:
                                              offs.ctypes.data))
         return [(kp[offs[f]:offs[f + 1]].copy(), desc[offs[f]:offs[f + 1]].copy()) for f in range(n)]
 
+    def input_dev(self, width, height):
+        """(ptr, pitch, frame_stride) of the context's own level-0 batch buffer: producers on the device write frames here"""
+        ptr, pitch, stride = C.c_void_p(), C.c_size_t(), C.c_size_t()
+        check(lib().lpslam_orb_input_dev(self._h, width, height, C.byref(ptr), C.byref(pitch), C.byref(stride)))
+        return ptr.value, pitch.value, stride.value
+
+    def extract_batch_dev(self, n, width, height, cap_per_frame=None):
+        """extraction of the n frames a device producer left in input_dev(); returns a list of (keypts, descriptors)"""
+        ptr, pitch, _ = self.input_dev(width, height)
+        check(lib().lpslam_orb_extract_batch_dev(self._h, ptr, n, width, height, pitch))
+        cap = n * (int(cap_per_frame) if cap_per_frame else 8 * self.orb_params_.max_num_keypts_ + 256)
+        kp = np.empty(cap, KP_DTYPE)
+        desc = np.empty((cap, 32), np.uint8)
+        offs = np.zeros(n + 1, np.uint32)
+        check(lib().lpslam_orb_fetch_result(self._h, kp.ctypes.data, desc.ctypes.data, cap, offs.ctypes.data))
+        return [(kp[offs[f]:offs[f + 1]].copy(), desc[offs[f]:offs[f + 1]].copy()) for f in range(n)]
+
     # ---- getters / setters (feature/orb_extractor.cc:149-206) ----
     def _get(self, which):
         v = C.c_double()

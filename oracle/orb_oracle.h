@@ -108,6 +108,15 @@ void orc_undistort_keypoints(double fx, double fy, double cx, double cy, const d
 void orc_keypoints_to_bearings(double fx, double fy, double cx, double cy, uint32_t n, const orc_keypoint* kp, double* bearings);
 void orc_assign_grid(const orc_camera* cam, uint32_t n, const orc_keypoint* kp, uint32_t* cell_start /*cells + 1*/, uint32_t* items /*n*/);
 
+/* image pre-processing ahead of extraction (image_oracle.cc): cvtColor -> GRAY, imadjust / stretchlim, remap INTER_LINEAR */
+void orc_gray_u8(const uint8_t* src, int w, int h, size_t pitch, int channels /*3|4*/, int order /*0 RGB, 1 BGR*/, uint8_t* dst,
+                 size_t dpitch);
+void orc_imadjust_u8(const uint8_t* src, int w, int h, size_t pitch, int auto_limits, double low_in, double high_in,
+                     double low_out, double high_out, uint8_t* dst, size_t dpitch, uint8_t* lut_out /*256, nullable*/,
+                     double* limits_out /*2, nullable*/);
+void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, size_t spitch, const float* map_x, const float* map_y,
+                         size_t map_pitch /*floats*/, uint8_t* dst, int dw, int dh, size_t dpitch);
+
 /* exact brute-force top-2 (reference semantics of a sequential strict-< scan): per query best index, best and second distance */
 void orc_knn_top2(const uint8_t* q, uint32_t nq, const uint8_t* db, uint64_t ndb, int64_t* best_idx, uint32_t* best_d,
                   uint32_t* second_d);

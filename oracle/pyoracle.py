@@ -111,6 +111,13 @@ class Oracle:
             L.orc_keypoints_to_bearings.restype = None
             L.orc_assign_grid.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
             L.orc_assign_grid.restype = None
+            L.orc_gray_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, u8p, C.c_size_t]
+            L.orc_gray_u8.restype = None
+            L.orc_imadjust_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
+                                          u8p, C.c_size_t, u8p, C.POINTER(C.c_double)]
+            L.orc_imadjust_u8.restype = None
+            L.orc_remap_linear_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, f32p, f32p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_size_t]
+            L.orc_remap_linear_u8.restype = None
             L.orc_knn_top2.argtypes = [u8p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_int64), C.POINTER(C.c_uint32),
                                        C.POINTER(C.c_uint32)]
 
@@ -260,6 +267,34 @@ class Oracle:
         items = np.empty(len(kp), np.uint32)
         self.lib.orc_assign_grid(C.byref(cam), len(kp), kp.ctypes.data, _ptr(start, C.POINTER(C.c_uint32)), _ptr(items, C.POINTER(C.c_uint32)))
         return start, items[: start[-1]]
+
+    def gray(self, img, order="BGR"):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w, ch = img.shape
+        dst = np.empty((h, w), np.uint8)
+        self.lib.orc_gray_u8(_ptr(img, u8p), w, h, img.strides[0], ch, 0 if order == "RGB" else 1, _ptr(dst, u8p), w)
+        return dst
+
+    def imadjust(self, img, low_in=None, high_in=None, low_out=0.0, high_out=1.0):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        dst = np.empty_like(img)
+        lut = np.empty(256, np.uint8)
+        lim = np.empty(2, np.float64)
+        auto = low_in is None or high_in is None
+        self.lib.orc_imadjust_u8(_ptr(img, u8p), w, h, img.strides[0], int(auto), 0.0 if auto else low_in, 1.0 if auto else high_in,
+                                 low_out, high_out, _ptr(dst, u8p), w, _ptr(lut, u8p), _ptr(lim, C.POINTER(C.c_double)))
+        return dst, lut, lim
+
+    def remap(self, img, map_x, map_y):
+        img = np.ascontiguousarray(img, np.uint8)
+        mx = np.ascontiguousarray(map_x, np.float32)
+        my = np.ascontiguousarray(map_y, np.float32)
+        dh, dw = mx.shape
+        dst = np.empty((dh, dw), np.uint8)
+        self.lib.orc_remap_linear_u8(_ptr(img, u8p), img.shape[1], img.shape[0], img.strides[0], _ptr(mx, f32p), _ptr(my, f32p), dw,
+                                     _ptr(dst, u8p), dw, dh, dw)
+        return dst
 
     def knn_top2(self, q, db):
         q = np.ascontiguousarray(q, np.uint8)

@@ -97,3 +97,62 @@ def test_undistort_points_vs_cv2():
         assert np.array_equal(got["x"], want[:, 0]) and np.array_equal(got["y"], want[:, 1]), dist
         assert np.array_equal(got["octave"], kp["octave"]) and np.array_equal(got["angle"], kp["angle"])
         assert (got["response"] == 0).all() and (got["class_id"] == -1).all()
+
+
+def _undistort_maps(h, w):
+    K = np.array([[0.9 * w, 0, w / 2.0], [0, 0.9 * w, h / 2.0], [0, 0, 1]])
+    dist = np.array([-0.25, 0.08, 0.001, -0.002, 0.0])
+    R = cv2.Rodrigues(np.array([0.01, -0.02, 0.005]))[0]
+    P = np.array([[0.85 * w, 0, w / 2.0 - 8, 0], [0, 0.85 * w, h / 2.0 + 5, 0], [0, 0, 1, 0]])
+    return cv2.initUndistortRectifyMap(K, dist, R, P, (w, h), cv2.CV_32FC1)
+
+
+def test_preprocessing_vs_cv2():
+    """util/image_converter.cc:8-39 (cvtColor), LpSlam ImageProcessing.h:258-370 (calcHist + convertTo) and :245-249
+    (remap INTER_LINEAR, CV_32FC1 maps) against cv2."""
+    from oracle import pyoracle
+    o = pyoracle.port()
+    rng = np.random.default_rng(11)
+    for h, w in ((480, 640), (97, 131)):
+        c3 = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        c4 = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        assert np.array_equal(o.gray(c3, "BGR"), cv2.cvtColor(c3, cv2.COLOR_BGR2GRAY))
+        assert np.array_equal(o.gray(c3, "RGB"), cv2.cvtColor(c3, cv2.COLOR_RGB2GRAY))
+        assert np.array_equal(o.gray(c4, "BGR"), cv2.cvtColor(c4, cv2.COLOR_BGRA2GRAY))
+        assert np.array_equal(o.gray(c4, "RGB"), cv2.cvtColor(c4, cv2.COLOR_RGBA2GRAY))
+        img = synth_image(h, w, 5)
+        mx, my = _undistort_maps(h, w)
+        mx[0, :10], my[5, :7], mx[7, 3], my[9, 9], mx[10, 10], mx[11, 11] = -5.3, h + 3.2, w - 0.6, -0.4, -0.97, -1.0
+        assert np.array_equal(o.remap(img, mx, my), cv2.remap(img, mx, my, cv2.INTER_LINEAR))
+        assert np.array_equal(o.remap(noise_image(h, w, 6), mx, my), cv2.remap(noise_image(h, w, 6), mx, my, cv2.INTER_LINEAR))
+    # imadjust: histogram limits against cv2.calcHist + the reference's loops, value map against convertScaleAbs on the
+    # non-negative side (Python has no Mat::convertTo; convertScaleAbs shares its float kernel) with dispatch off
+    was = cv2.useOptimized()
+    cv2.setUseOptimized(False)
+    try:
+        for seed in range(6):
+            img = np.clip(synth_image(240, 320, 20 + seed).astype(np.int32) // (1 + seed % 3) + 10 * seed, 0, 255).astype(np.uint8)
+            dst, lut, lim = o.imadjust(img, None, None, -0.3, 1.4)
+            hist = cv2.calcHist([img], [0], None, [256], [0, 256]).ravel()
+            total, s, lo, hi = img.size, 0, 0.0, 1.0
+            for i in range(256):
+                if s >= int(0.01 * total):
+                    lo = i
+                    break
+                s += int(hist[i])
+            s = 0
+            for i in range(255, -1, -1):
+                if s >= int((1 - 0.99) * total):
+                    hi = i
+                    break
+                s += int(hist[i])
+            assert lim[0] == lo / 255 and lim[1] == hi / 255
+            alpha = (1.4 + 0.3) / (lim[1] - lim[0])
+            beta = (1.4 - lim[1] * alpha) * 255
+            ramp = np.arange(256, dtype=np.uint8).reshape(1, 256).repeat(16, 0)
+            ref = cv2.convertScaleAbs(ramp, alpha=alpha, beta=beta)[0]
+            pos = (np.arange(256, dtype=np.float32) * np.float32(alpha) + np.float32(beta)) >= 0
+            assert np.array_equal(lut[pos], ref[pos]) and (lut[~pos] == 0).all()
+            assert np.array_equal(dst, lut[img])
+    finally:
+        cv2.setUseOptimized(was)
