@@ -19,36 +19,48 @@ namespace {
 
 __global__ void __launch_bounds__(256) k_gray(const uint8_t* __restrict__ src, int w, int h, size_t pitch, size_t stride, int ch,
                                               int order, uint8_t* __restrict__ dst, size_t dpitch, size_t dstride, int vec) {
-    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    // a thread converts 16 consecutive pixels: 3 (or 4) 128-bit loads, one 128-bit store
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 16;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
     if (x0 >= w || y >= h) return;
     const uint8_t* s = src + blockIdx.z * stride + (size_t)y * pitch + (size_t)x0 * ch;
     uint8_t* d = dst + blockIdx.z * dstride + (size_t)y * dpitch + x0;
     const int ir = order == 0 ? 0 : 2, ib = 2 - ir;
-    if (vec && x0 + 4 <= w) {
-        uint32_t wd[4];
+    if (vec && x0 + 16 <= w) {
+        uint32_t px[16];  // one pixel per word, channels in bytes 0..2
         if (ch == 4) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(s));
-            wd[0] = v.x; wd[1] = v.y; wd[2] = v.z; wd[3] = v.w;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(s) + q);
+                px[4 * q] = v.x; px[4 * q + 1] = v.y; px[4 * q + 2] = v.z; px[4 * q + 3] = v.w;
+            }
         }
         else {
-            const uint32_t a = __ldg(reinterpret_cast<const uint32_t*>(s)), b = __ldg(reinterpret_cast<const uint32_t*>(s) + 1),
-                           c = __ldg(reinterpret_cast<const uint32_t*>(s) + 2);
-            wd[0] = a;                          // p0 = bytes 0..2
-            wd[1] = __byte_perm(a, b, 0x6543);  // p1 = bytes 3..5
-            wd[2] = __byte_perm(b, c, 0x5432);  // p2 = bytes 6..8
-            wd[3] = c >> 8;                     // p3 = bytes 9..11
-        }
-        uint32_t out = 0;
+            uint32_t wd[12];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t r = (wd[k] >> (8 * ir)) & 255u, g = (wd[k] >> 8) & 255u, b = (wd[k] >> (8 * ib)) & 255u;
-            out |= ((b * 3735u + g * 19235u + r * 9798u + (1u << 14)) >> 15) << (8 * k);
+            for (int q = 0; q < 3; ++q) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(s) + q);
+                wd[4 * q] = v.x; wd[4 * q + 1] = v.y; wd[4 * q + 2] = v.z; wd[4 * q + 3] = v.w;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {  // 4 pixels = 3 words
+                const uint32_t a = wd[3 * q], b = wd[3 * q + 1], c = wd[3 * q + 2];
+                px[4 * q] = a;                              // bytes 0..2
+                px[4 * q + 1] = __byte_perm(a, b, 0x6543);  // bytes 3..5
+                px[4 * q + 2] = __byte_perm(b, c, 0x5432);  // bytes 6..8
+                px[4 * q + 3] = c >> 8;                     // bytes 9..11
+            }
         }
-        *reinterpret_cast<uint32_t*>(d) = out;
+        uint32_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const uint32_t r = (px[k] >> (8 * ir)) & 255u, g = (px[k] >> 8) & 255u, b = (px[k] >> (8 * ib)) & 255u;
+            o[k >> 2] |= ((b * 3735u + g * 19235u + r * 9798u + (1u << 14)) >> 15) << (8 * (k & 3));
+        }
+        *reinterpret_cast<uint4*>(d) = make_uint4(o[0], o[1], o[2], o[3]);
     }
     else {
-        for (int k = 0; k < 4 && x0 + k < w; ++k) {
+        for (int k = 0; k < 16 && x0 + k < w; ++k) {
             const uint8_t* p = s + k * ch;
             d[k] = (uint8_t)((p[ib] * 3735u + p[1] * 19235u + p[ir] * 9798u + (1u << 14)) >> 15);
         }
@@ -198,20 +210,21 @@ __global__ void __launch_bounds__(256) k_remap(const uint8_t* __restrict__ src, 
         const int sx = __float2int_rn(__fmul_rn(fxs[k], 32.0f)), sy = __float2int_rn(__fmul_rn(fys[k], 32.0f));
         const int ix = min(max(sx >> 5, -32768), 32767), iy = min(max(sy >> 5, -32768), 32767);
         const int fx = sx & 31, fy = sy & 31;
-        uint32_t p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+        // taps outside of the image read as 0 (BORDER_CONSTANT): predicated loads from one running address per row
+        // (no clamping, no branch between the map fetch and the 16 pixel loads of a thread: all are in flight together)
         const bool x0ok = (unsigned)ix < (unsigned)sw, x1ok = (unsigned)(ix + 1) < (unsigned)sw;
-        if ((unsigned)iy < (unsigned)sh) {
-            const uint8_t* r = s + (size_t)iy * spitch;
-            if (x0ok) p00 = __ldg(r + ix);
-            if (x1ok) p01 = __ldg(r + ix + 1);
-        }
-        if ((unsigned)(iy + 1) < (unsigned)sh) {
-            const uint8_t* r = s + (size_t)(iy + 1) * spitch;
-            if (x0ok) p10 = __ldg(r + ix);
-            if (x1ok) p11 = __ldg(r + ix + 1);
-        }
-        const uint32_t w0 = (32 - fy) * (32 - fx) * 32, w1 = (32 - fy) * fx * 32, w2 = fy * (32 - fx) * 32, w3 = fy * fx * 32;
-        out |= ((p00 * w0 + p01 * w1 + p10 * w2 + p11 * w3 + (1u << 14)) >> 15) << (8 * k);
+        const bool y0ok = (unsigned)iy < (unsigned)sh, y1ok = (unsigned)(iy + 1) < (unsigned)sh;
+        const uint8_t* r0 = s + (ptrdiff_t)(iy * (int)spitch + ix);
+        const uint8_t* r1 = r0 + spitch;
+        uint32_t p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+        if (x0ok && y0ok) p00 = __ldg(r0);
+        if (x1ok && y0ok) p01 = __ldg(r0 + 1);
+        if (x0ok && y1ok) p10 = __ldg(r1);
+        if (x1ok && y1ok) p11 = __ldg(r1 + 1);
+        // weights (32-fy)(32-fx)*32 ... and (sum + 2^14) >> 15 == ((top (32-fy) + bottom fy) + 2^9) >> 10 with
+        // top = p00 (32-fx) + p01 fx: all integers, the common factor 32 cancels exactly
+        const uint32_t ax = 32 - fx, top = p00 * ax + p01 * fx, bot = p10 * ax + p11 * fx;
+        out |= ((top * (32 - fy) + bot * fy + (1u << 9)) >> 10) << (8 * k);
     }
     if (vec && full)
         *reinterpret_cast<uint32_t*>(d) = out;
@@ -233,10 +246,9 @@ int lpslam_gray_dev(const uint8_t* src_dev, int width, int height, size_t pitch,
     LPS_ARG(src_dev && dst_dev, "null image pointer");
     LPS_ARG(width > 0 && height > 0 && (channels == 3 || channels == 4) && (order == 0 || order == 1), "bad image geometry / channel order");
     LPS_ARG(pitch >= (size_t)width * channels && dst_pitch >= (size_t)width && n_images >= 1, "bad pitch / image count");
-    const size_t al = channels == 4 ? 16 : 4;
-    const int vec = aligned(src_dev, al) && pitch % al == 0 && frame_stride % al == 0 && aligned(dst_dev, 4) && dst_pitch % 4 == 0
-                    && dst_frame_stride % 4 == 0;
-    dim3 blk(64, 4), grd((width + 255) / 256, (height + 3) / 4, n_images);
+    const int vec = aligned(src_dev, 16) && pitch % 16 == 0 && frame_stride % 16 == 0 && aligned(dst_dev, 16) && dst_pitch % 16 == 0
+                    && dst_frame_stride % 16 == 0;
+    dim3 blk(32, 8), grd((width + 32 * 16 - 1) / (32 * 16), (height + 7) / 8, n_images);
     k_gray<<<grd, blk, 0, (cudaStream_t)stream>>>(src_dev, width, height, pitch, frame_stride, channels, order, dst_dev, dst_pitch,
                                                   dst_frame_stride, vec);
     LPS_CUDA(cudaGetLastError());
