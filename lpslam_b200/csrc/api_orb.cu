@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace lps {
@@ -67,6 +68,12 @@ int lpslam_orb_create(lpslam_orb_ctx** out, const lpslam_orb_params* p, int devi
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) {
+        e = cudaStreamCreateWithFlags(&c->chain[i], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_join[i], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_fork, cudaEventDisableTiming);
+    if (const char* env = getenv("LPSLAM_PYR_CHAINS")) c->pyr_chains = std::min(std::max(atoi(env), 1), 4);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_frame_off, sizeof(uint32_t) * (max_batch + 2), cudaHostAllocDefault);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
     if (e != cudaSuccess) {
@@ -82,6 +89,12 @@ void lpslam_orb_destroy(lpslam_orb_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->side) cudaStreamSynchronize(c->side);
+    for (int i = 0; i < 3; ++i) {
+        if (c->chain[i]) cudaStreamSynchronize(c->chain[i]);
+        if (c->chain[i]) cudaStreamDestroy(c->chain[i]);
+        if (c->ev_chain_join[i]) cudaEventDestroy(c->ev_chain_join[i]);
+    }
+    if (c->ev_chain_fork) cudaEventDestroy(c->ev_chain_fork);
     c->release_geometry();
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);

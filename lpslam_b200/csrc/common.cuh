@@ -70,6 +70,10 @@ struct LevelGeom {
     // schedule of the column-walk resize, indexed by SOURCE row r = 0 .. src.h (r = src.h stands for the clamped row
     // src.h - 1): x = destination row completed by the source rows (r - 1, r), or -1; y = its row coefficients b0 | b1 << 16
     const int2* srctab;
+    // per 2-pixel window of the column-walk resize (window i covers destination columns 2 i - 2 kApron, + 1; apron and
+    // overhang columns included): two uint4 = (source byte offset of the window's first word, PRMT selector of pixel 0,
+    // of pixel 1, coefficient pair of pixel 0 | coefficient pair of pixel 1, live flag, -, -)
+    const uint4* wintab;
     int walk_ok;         // the column-walk kernel applies (down-scaling by less than 3 in x, monotonic rows)
     int mode;            // 0 = general bilinear, 1 = exact 2x2 decimation (OpenCV routes it to INTER_AREA), 2 = same size copy
     // FAST cell grid of the level

@@ -120,7 +120,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
     cells.clear();
     memset(lv, 0, sizeof lv);
     ArenaPlan plan;
-    std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L), off_rt(L);
+    std::vector<size_t> off_img(L), off_blur(L), off_xo(L), off_xc(L), off_yo(L), off_yc(L), off_rt(L), off_wt(L);
+    std::vector<std::vector<uint4>> wintab(L);
     std::vector<std::vector<int2>> rowtab(L);
     std::vector<std::vector<uint16_t>> qix(L), qiy(L);
     std::vector<std::vector<int>> qbx(L), qby(L);
@@ -170,6 +171,27 @@ int lpslam_orb_ctx::configure(int width, int height) {
                 rowtab[l][r] = make_int2(y, (int)((uint32_t)(uint16_t)yc[l][y].x | ((uint32_t)(uint16_t)yc[l][y].y << 16)));
             }
             off_rt[l] = plan.take(rowtab[l].size() * sizeof(int2));
+            if (g.walk_ok) {
+                // loop-invariant window description of the column-walk kernel, one entry per destination column pair
+                auto refl = [](int p, int len) {
+                    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+                    return p;
+                };
+                const int n_win = (g.w + 2 * kApron + 2560) / 2;
+                wintab[l].resize(2 * (size_t)n_win);
+                for (int i = 0; i < n_win; ++i) {
+                    const int xg = 2 * i - 2 * kApron;
+                    const int xa = refl(xg, g.w), xb = refl(xg + 1, g.w);
+                    const int sa = xofs[l][xa], sb = xofs[l][xb];
+                    const int base = std::min(sa, sb) & ~3;
+                    const uint32_t oa = (uint32_t)std::min(sa - base, 6), ob = (uint32_t)std::min(sb - base, 6);
+                    const short2 ca = xc[l][xa], cb = xc[l][xb];
+                    wintab[l][2 * i] = make_uint4((uint32_t)base, oa | ((oa + 1) << 4), ob | ((ob + 1) << 4),
+                                                  (uint32_t)(uint16_t)ca.x | ((uint32_t)(uint16_t)ca.y << 16));
+                    wintab[l][2 * i + 1] = make_uint4((uint32_t)(uint16_t)cb.x | ((uint32_t)(uint16_t)cb.y << 16), xg < g.w + kApron ? 1u : 0u, 0u, 0u);
+                }
+                off_wt[l] = plan.take(wintab[l].size() * sizeof(uint4));
+            }
         }
         // ---- FAST cell grid, feature/orb_extractor.cc:293-332 ----
         g.cell_begin = (int)cells.size();
@@ -317,6 +339,10 @@ int lpslam_orb_ctx::configure(int width, int height) {
             lv[l].yofs = (const int*)(arena + off_yo[l]);
             lv[l].ycoef = (const short2*)(arena + off_yc[l]);
             lv[l].srctab = (const int2*)(arena + off_rt[l]);
+            if (lv[l].walk_ok) {
+                lv[l].wintab = (const uint4*)(arena + off_wt[l]);
+                LPS_CUDA(cudaMemcpyAsync(arena + off_wt[l], wintab[l].data(), wintab[l].size() * sizeof(uint4), cudaMemcpyHostToDevice, stream));
+            }
             LPS_CUDA(cudaMemcpyAsync(arena + off_rt[l], rowtab[l].data(), rowtab[l].size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_xo[l], xofs[l].data(), xofs[l].size() * 4, cudaMemcpyHostToDevice, stream));
             LPS_CUDA(cudaMemcpyAsync(arena + off_xc[l], xc[l].data(), xc[l].size() * 4, cudaMemcpyHostToDevice, stream));
@@ -403,7 +429,25 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     uint32_t pad_mask = 1u;  // level 0 arrives without its apron; so do levels made by the exact-half / copy / wide-ratio paths
     for (int l = 1; l < L; ++l)
         if (!resize_writes_apron(lv[l - 1], lv[l])) pad_mask |= 1u << l;
-    for (int l = 1; l < L; ++l) launch_resize(lv[l - 1], lv[l], B, stream);
+    {
+        const int chains = std::min(pyr_chains, B);
+        auto run_chain = [&](int f0, int f1, cudaStream_t st) {
+            for (int l = 1; l < L; ++l) {
+                LevelGeom s = lv[l - 1], d = lv[l];
+                s.img += (size_t)f0 * s.frame_stride;
+                d.img += (size_t)f0 * d.frame_stride;
+                launch_resize(s, d, f1 - f0, st);
+            }
+        };
+        if (chains > 1) LPS_CUDA(cudaEventRecord(ev_chain_fork, stream));
+        for (int c = 1; c < chains; ++c) {
+            LPS_CUDA(cudaStreamWaitEvent(chain[c - 1], ev_chain_fork, 0));
+            run_chain(B * c / chains, B * (c + 1) / chains, chain[c - 1]);
+            LPS_CUDA(cudaEventRecord(ev_chain_join[c - 1], chain[c - 1]));
+        }
+        run_chain(0, B / chains, stream);
+        for (int c = 1; c < chains; ++c) LPS_CUDA(cudaStreamWaitEvent(stream, ev_chain_join[c - 1], 0));
+    }
     // The blur and the apron of level 0 depend on the pyramid only: outside of stage timing they run on the side stream,
     // next to FAST and the quadtree (memory-bound work beside compare-pipe-bound and latency-bound work), and are joined
     // before the descriptors. With stage timing on, everything stays on one stream so that each stage is timed alone.

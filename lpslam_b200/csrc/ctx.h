@@ -11,6 +11,11 @@ struct lpslam_orb_ctx {
     // side stream: level-0 apron + blur run beside FAST and the quadtree (they only depend on the pyramid)
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // the pyramid of a batch is built as up to 4 independent chains of frames on their own streams, so that the small
+    // levels of one chain run beside the large levels of another (each level launch alone leaves most SMs idle at its tail)
+    cudaStream_t chain[3] = {};
+    cudaEvent_t ev_chain_fork = nullptr, ev_chain_join[3] = {};
+    int pyr_chains = 1;  // measured on B200: 2 chains 0.132 ms vs 0.135 ms, 3-4 chains slower (LPSLAM_PYR_CHAINS)
     uint32_t max_batch = 1;
 
     // feature/orb_params.h

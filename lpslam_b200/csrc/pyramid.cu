@@ -166,18 +166,16 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
     Window wd[RW_NW];
 #pragma unroll
     for (int g = 0; g < RW_NW; ++g) {
-        const int xg = warp_x0 + 64 * g + lane2;
-        live[g] = xg < dst.w + kApron;
-        const int xa = reflect101(xg, dst.w), xb = reflect101(xg + 1, dst.w);
-        const int sa = dst.xofs[xa], sb = dst.xofs[xb];
-        const short2 ca = dst.xcoef[xa], cb = dst.xcoef[xb];
-        const int base = min(sa, sb) & ~3;
-        wd[g].ptr = s + base + (ptrdiff_t)r_first * spitch;
-        const uint32_t oa = (uint32_t)min(sa - base, 6), ob = (uint32_t)min(sb - base, 6);  // the launcher guarantees <= 6
-        wd[g].sel0 = oa | ((oa + 1) << 4);
-        wd[g].sel1 = ob | ((ob + 1) << 4);
-        wd[g].c0 = (uint32_t)(uint16_t)ca.x | ((uint32_t)(uint16_t)ca.y << 16);
-        wd[g].c1 = (uint32_t)(uint16_t)cb.x | ((uint32_t)(uint16_t)cb.y << 16);
+        // host-built window table (ctx.cu): what used to be two reflections, four dependent table reads and the selector
+        // arithmetic per window is two 128-bit loads
+        const int wi = (warp_x0 + 64 * g + lane2 + 2 * kApron) >> 1;
+        const uint4 t0 = __ldg(dst.wintab + 2 * wi), t1 = __ldg(dst.wintab + 2 * wi + 1);
+        wd[g].ptr = s + t0.x + (ptrdiff_t)r_first * spitch;
+        wd[g].sel0 = t0.y;
+        wd[g].sel1 = t0.z;
+        wd[g].c0 = t0.w;
+        wd[g].c1 = t1.x;
+        live[g] = t1.y != 0;
     }
     uint8_t* d = dst.img + blockIdx.z * dst.frame_stride + warp_x0 + lane2;  // window g stores at d + 64 g
     asm volatile("" : "+l"(d));  // not to be rematerialised from the kernel parameters at every emitted row
