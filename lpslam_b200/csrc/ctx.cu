@@ -146,7 +146,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
         g.inv_scale = inv_scale[l];
         g.kp_size = (float)(unsigned)(kPatch * scale[l]);  // orb_extractor.cc:383
         g.quota = quota[l];
-        off_img[l] = plan.take(g.frame_stride * max_batch);
+        off_img[l] = plan.take(g.frame_stride * max_batch + 8 * (size_t)g.pitch);  // slack: the resize prefetches rows past a frame
         off_blur[l] = plan.take(g.frame_stride * max_batch);
         if (l > 0) {
             const LevelGeom& p = lv[l - 1];

@@ -225,22 +225,31 @@ __global__ void __launch_bounds__(256) k_resize_walk(LevelGeom src, LevelGeom ds
         }
     };
 
+    // Rows are fetched four source rows ahead of their use (a band is a short dependent chain of row loads otherwise: at
+    // the small levels a block lives for a dozen rows and the loads' latency was most of its life). The reads run up to
+    // four rows past the band's last source row: inside the apron, or inside the slack ctx.cu leaves behind every level.
     uint32_t A[RW_PX], B[RW_PX];
-    RowW w0, w1;
+    RowW w0, w1, w2, w3;
     {
         RowW wa;
         fetch(wa);
         fetch(w0);
         fetch(w1);
+        fetch(w2);
+        fetch(w3);
         hsum(wa, A);
     }
     const int n = r_last - r_first;  // source rows r_first + 1 .. r_last are walked
     int i = 1;
-    for (; i + 1 <= n; i += 2) {
+    for (; i + 3 <= n; i += 4) {
         step(i, A, B, w0);
         step(i + 1, B, A, w1);
+        step(i + 2, A, B, w2);
+        step(i + 3, B, A, w3);
     }
     if (i <= n) step(i, A, B, w0);
+    if (i + 1 <= n) step(i + 1, B, A, w1);
+    if (i + 2 <= n) step(i + 2, A, B, w2);
 }
 
 // exact 2x decimation: OpenCV's INTER_LINEAR takes the INTER_AREA fast path, (a + b + c + d + 2) >> 2
