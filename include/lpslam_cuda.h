@@ -246,6 +246,14 @@ int lpslam_remap_linear_dev(const uint8_t* src_dev, int src_width, int src_heigh
                             const float* map_x_dev, const float* map_y_dev, size_t map_pitch, uint8_t* dst_dev, int dst_width,
                             int dst_height, size_t dst_pitch, size_t dst_frame_stride, uint32_t n_images, void* stream);
 
+/* data::landmark::compute_descriptor (data/landmark.cc:127-183), batched: the observations' descriptors of landmark l
+ * are rows [offsets[l], offsets[l + 1]) of obs_desc (keyframes that will be erased already left out, :147-149).
+ * best_idx[l] = index inside the landmark's own list of the observation whose median Hamming distance to the others is
+ * smallest (first one on ties; 0 for an empty list); desc_out (nullable, n_landmarks x 32) receives that descriptor
+ * (zeros for an empty list). Feeds the kNN database from a map (lpslam_knn_add). */
+int lpslam_landmark_descriptors(const uint8_t* obs_desc, const uint32_t* offsets /*n_landmarks + 1*/, uint32_t n_landmarks,
+                                uint32_t* best_idx, uint8_t* desc_out);
+
 /* ---------------------------------------------------------------- kNN database (relocalisation / loop query) ----- */
 /* Brute-force Hamming top-2 of query descriptors against a device-resident descriptor database (generalises the
  * best / second-best scan of match/robust.cc:252-274 and the BoW-candidate search of module/relocalizer.cc:31-46).

@@ -112,6 +112,19 @@ def frame_postprocess(model, cam, keypts):
     check(lib().lpslam_frame_postprocess(C.byref(model), C.byref(cam), len(kp), kp.ctypes.data, und.ctypes.data, bearings.ctypes.data,
                                          start.ctypes.data, items.ctypes.data, C.byref(n)))
     return und, bearings, start, items[: n.value]
+register("lpslam_landmark_descriptors", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p])
+
+
+def compute_landmark_descriptors(obs_descs, offsets):
+    """data::landmark::compute_descriptor (data/landmark.cc:127-183) for a batch of landmarks: obs_descs[offsets[l]:offsets[l+1]]
+    are the descriptors of landmark l's observations. Returns (best_idx, descriptors)."""
+    d = np.ascontiguousarray(obs_descs, np.uint8).reshape(-1, 32)
+    off = np.ascontiguousarray(offsets, np.uint32)
+    n = len(off) - 1
+    best = np.zeros(n, np.uint32)
+    out = np.zeros((n, 32), np.uint8)
+    check(lib().lpslam_landmark_descriptors(d.ctypes.data, off.ctypes.data, n, best.ctypes.data, out.ctypes.data))
+    return best, out
 
 
 def compute_descriptor_distance_32(desc_1, desc_2):

@@ -331,6 +331,30 @@ int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_
     return static_cast<int>(num);
 }
 
+// data/landmark.cc:151-177 for one landmark: index of the representative descriptor among its n observations
+uint32_t orc_landmark_descriptor(const uint8_t* descs, uint32_t n) {
+    std::vector<std::vector<unsigned>> hamm(n, std::vector<unsigned>(n));
+    for (unsigned i = 0; i < n; ++i) {
+        hamm[i][i] = 0;
+        for (unsigned j = i + 1; j < n; ++j) {
+            const unsigned d = hamming_32(descs + static_cast<size_t>(i) * 32, descs + static_cast<size_t>(j) * 32);
+            hamm[i][j] = d;
+            hamm[j][i] = d;
+        }
+    }
+    unsigned best_median = MAX_HAMMING_DIST, best = 0;
+    for (unsigned idx = 0; idx < n; ++idx) {
+        std::vector<unsigned> part(hamm[idx].begin(), hamm[idx].begin() + n);
+        std::sort(part.begin(), part.end());
+        const unsigned median = part.at(static_cast<unsigned>(0.5 * (n - 1)));
+        if (median < best_median) {
+            best_median = median;
+            best = idx;
+        }
+    }
+    return best;
+}
+
 // match/projection.cc:85-208 with data/common.cc:97-186 and camera/perspective.cc:151-169
 int orc_match_projection(const orc_camera* cam, const double* Tc, const double* Tl, uint32_t n_last,
                          const uint8_t* last_has_lm, const uint8_t* last_outlier, const double* last_pos_w,

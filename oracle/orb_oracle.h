@@ -117,6 +117,9 @@ void orc_imadjust_u8(const uint8_t* src, int w, int h, size_t pitch, int auto_li
 void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, size_t spitch, const float* map_x, const float* map_y,
                          size_t map_pitch /*floats*/, uint8_t* dst, int dw, int dh, size_t dpitch);
 
+/* data/landmark.cc:151-177: representative descriptor (index) among n observation descriptors */
+uint32_t orc_landmark_descriptor(const uint8_t* descs, uint32_t n);
+
 /* exact brute-force top-2 (reference semantics of a sequential strict-< scan): per query best index, best and second distance */
 void orc_knn_top2(const uint8_t* q, uint32_t nq, const uint8_t* db, uint64_t ndb, int64_t* best_idx, uint32_t* best_d,
                   uint32_t* second_d);

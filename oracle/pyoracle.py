@@ -118,6 +118,8 @@ class Oracle:
             L.orc_imadjust_u8.restype = None
             L.orc_remap_linear_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, f32p, f32p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_size_t]
             L.orc_remap_linear_u8.restype = None
+            L.orc_landmark_descriptor.argtypes = [u8p, C.c_uint32]
+            L.orc_landmark_descriptor.restype = C.c_uint32
             L.orc_knn_top2.argtypes = [u8p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_int64), C.POINTER(C.c_uint32),
                                        C.POINTER(C.c_uint32)]
 
@@ -295,6 +297,10 @@ class Oracle:
         self.lib.orc_remap_linear_u8(_ptr(img, u8p), img.shape[1], img.shape[0], img.strides[0], _ptr(mx, f32p), _ptr(my, f32p), dw,
                                      _ptr(dst, u8p), dw, dh, dw)
         return dst
+
+    def landmark_descriptor(self, descs):
+        d = np.ascontiguousarray(descs, np.uint8).reshape(-1, 32)
+        return int(self.lib.orc_landmark_descriptor(_ptr(d, u8p), len(d)))
 
     def knn_top2(self, q, db):
         q = np.ascontiguousarray(q, np.uint8)

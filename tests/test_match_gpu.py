@@ -213,3 +213,25 @@ def test_frame_postprocess(oracle, dist):
     assert 0 < len(items) < len(kp)
     und0, b0, s0, i0 = match.frame_postprocess(model, cam, kp[:0])
     assert len(und0) == 0 and s0[-1] == 0 and len(i0) == 0
+
+
+def test_landmark_descriptors(oracle):
+    # data/landmark.cc:127-183: observation lists of 0..300 descriptors, clustered so that medians tie often
+    from lpslam_b200 import match
+    rng = np.random.default_rng(12)
+    sizes = list(rng.integers(1, 12, 300)) + [0, 1, 2, 3, 32, 33, 64, 65, 100, 300, 0]
+    chunks = []
+    for n in sizes:
+        base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+        flips = rng.random((n, 256)) < rng.choice([0.0, 0.02, 0.1])
+        chunks.append(base.repeat(n, 0) ^ np.packbits(flips, axis=1, bitorder="little"))
+    descs = np.concatenate(chunks)
+    offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+    best, out = match.compute_landmark_descriptors(descs, offsets)
+    for l, n in enumerate(sizes):
+        if n == 0:
+            assert best[l] == 0 and not out[l].any()
+            continue
+        want = oracle.landmark_descriptor(descs[offsets[l]:offsets[l + 1]])
+        assert best[l] == want, (l, n)
+        assert np.array_equal(out[l], descs[offsets[l] + want])
