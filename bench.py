@@ -283,6 +283,8 @@ def gpu_arm(args):
     roofline = {"bound": "hbm", "kernel": per_stage[rk]["kernel"], "achieved": per_stage[rk]["achieved_gbs"], "peak": peak,
                 "peak_source": peak_src, "unit": "GB/s", "frac": per_stage[rk]["frac"], "traffic": per_stage[rk]["traffic"],
                 "dominant_stage": dom, "stage_ms": {k: round(v, 4) for k, v in stage.items()}, "stages": per_stage,
+                "stage_timing": "stage_ms: a separate pass with every stage alone on one stream (CUDA events inside the library); in "
+                                "the timed region of 'value' the level-0 apron and the blur run on a side stream beside FAST / quadtree",
                 "note": "k_fast_cells reads each level once (algorithmic bytes = sum of level pixels) but is bound by the "
                         "integer compare pipe, not by HBM; the HBM-bound kernels are k_resize_walk and k_gauss7 (stages)"}
 
