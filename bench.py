@@ -176,10 +176,10 @@ def gpu_arm(args):
     # of the step's pairs through the blocking host-buffer entry point, so one context's PCIe copies overlap the other's
     # kernels (the reference also extracts on two threads, data/frame.cc:65-66).
     halves = []
-    Bh = max(B // 2, 1)
-    for hx in range(2):
-        lo = hx * Bh
-        n = Bh if hx == 0 else B - Bh
+    n_ctx = max(1, min(int(os.environ.get("LPSLAM_E2E_CONTEXTS", "4")), B))
+    for hx in range(n_ctx):
+        lo = B * hx // n_ctx
+        n = B * (hx + 1) // n_ctx - lo
         if n <= 0:
             continue
         e = orb.orb_extractor(max_num_keypts=KPTS, device=local, max_batch=2 * n)
@@ -196,7 +196,7 @@ def gpu_arm(args):
                                      bufs["xr"], bufs["dep"]))
         return int(offs[2 * n])
 
-    pool = cf.ThreadPoolExecutor(max_workers=2)
+    pool = cf.ThreadPoolExecutor(max_workers=len(halves))
 
     def e2e_step():
         return sum(pool.map(run_half, halves))
@@ -322,7 +322,7 @@ def gpu_arm(args):
                       "parallelism": "frame-parallel x%d" % world},
            "e2e": {"value": pairs_total / (e2e_ms * 1e-3), "unit": "stereo frames/s", "ms_per_step": e2e_ms / args.steps,
                    "h2d_bytes_per_step": 2 * B * W * H, "d2h_bytes_per_step": n_kp * (28 + 32 + 8) + 4 * (2 * B + 2),
-                   "timing": "wall clock around the blocking host-buffer C-ABI calls (2 contexts x 1 host thread each per GPU), max over ranks"},
+                   "timing": "wall clock around the blocking host-buffer C-ABI calls (%d contexts x 1 host thread each per GPU), max over ranks" % len(halves)},
            "gpu_launches": args.steps * LAUNCHES_PER_STEP, "clocks": clk, "roofline": roofline, "knn": knn_out}
     pool.shutdown()
     if world > 1:

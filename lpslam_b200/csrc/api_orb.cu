@@ -73,6 +73,7 @@ int lpslam_orb_create(lpslam_orb_ctx** out, const lpslam_orb_params* p, int devi
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_join[i], cudaEventDisableTiming);
     }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_fork, cudaEventDisableTiming);
+    if (const char* env = getenv("LPSLAM_SUBBATCH")) c->sub_batches = std::min(std::max(atoi(env), 1), 4);
     if (const char* env = getenv("LPSLAM_PYR_CHAINS")) c->pyr_chains = std::min(std::max(atoi(env), 1), 4);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_frame_off, sizeof(uint32_t) * (max_batch + 2), cudaHostAllocDefault);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);

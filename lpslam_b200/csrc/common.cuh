@@ -126,6 +126,7 @@ struct FastArgs {
     const CellDesc* cells;    // device table
     int num_cells;            // per frame
     int batch;
+    int frame0;               // first frame of this launch (sub-batches of a step run on their own streams)
     uint32_t ini_thr, min_thr;
     uint32_t* cell_counts;    // [batch][num_cells]
     uint32_t* cell_slots;     // [batch][num_cells][kCellSlots] packed lx | ly<<8 | score<<16
@@ -137,6 +138,7 @@ void launch_fast(const FastArgs& a, cudaStream_t st);
 struct TreeArgs {
     const LevelGeom* lv;  // device table
     int num_levels, batch, num_cells;
+    int frame0;  // first frame of this launch
     const CellDesc* cells;
     const uint32_t* cell_counts;
     const uint32_t* cell_slots;

@@ -468,16 +468,41 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     fa.cells = cells_dev;
     fa.num_cells = num_cells;
     fa.batch = B;
+    fa.frame0 = 0;
     fa.ini_thr = ini_thr;
     fa.min_thr = min_thr;
     fa.cell_counts = cell_counts;
     fa.cell_slots = cell_slots;
     fa.mask = mask_ptr;
     fa.mask_pitch = mask_pitch;
-    launch_fast(fa, stream);
-    mark();  // 2
     tree.batch = B;
-    launch_quadtree(tree, lv, stream);
+    tree.frame0 = 0;
+    // Outside of stage timing FAST + quadtree run as sub-batches of frames on their own streams: the quadtree is a
+    // latency-bound kernel (block-serial list discipline, ~27 % issue utilisation) and FAST is bound by the compare pipe, so
+    // the quadtree of one sub-batch runs beside the FAST of the next instead of after it.
+    const int subs = timing ? 1 : std::min(std::min(sub_batches, B), 4);
+    if (subs > 1) {
+        LPS_CUDA(cudaEventRecord(ev_chain_fork, stream));
+        for (int sb = 0; sb < subs; ++sb) {
+            cudaStream_t st = sb == 0 ? stream : chain[sb - 1];
+            if (sb > 0) LPS_CUDA(cudaStreamWaitEvent(st, ev_chain_fork, 0));
+            FastArgs f2 = fa;
+            f2.frame0 = B * sb / subs;
+            f2.batch = B * (sb + 1) / subs - f2.frame0;
+            launch_fast(f2, st);
+            TreeArgs t2 = tree;
+            t2.frame0 = f2.frame0;
+            t2.batch = f2.batch;
+            launch_quadtree(t2, lv, st);
+            if (sb > 0) LPS_CUDA(cudaEventRecord(ev_chain_join[sb - 1], st));
+        }
+        for (int sb = 1; sb < subs; ++sb) LPS_CUDA(cudaStreamWaitEvent(stream, ev_chain_join[sb - 1], 0));
+    }
+    else {
+        launch_fast(fa, stream);
+        mark();  // 2
+        launch_quadtree(tree, lv, stream);
+    }
     mark();  // 3
     if (fork)
         LPS_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));

@@ -15,6 +15,7 @@ struct lpslam_orb_ctx {
     // levels of one chain run beside the large levels of another (each level launch alone leaves most SMs idle at its tail)
     cudaStream_t chain[3] = {};
     cudaEvent_t ev_chain_fork = nullptr, ev_chain_join[3] = {};
+    int sub_batches = 1;  // FAST + quadtree sub-batches on own streams (LPSLAM_SUBBATCH); measured on B200: 2 -> no gain, 3-4 -> 8-10 % slower
     int pyr_chains = 1;  // measured on B200: 2 chains 0.132 ms vs 0.135 ms, 3-4 chains slower (LPSLAM_PYR_CHAINS)
     uint32_t max_batch = 1;
 

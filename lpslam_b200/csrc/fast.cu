@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
     __shared__ uint16_t s_corner[kCell * kCell];
     __shared__ int s_ncorner;
 
-    const int cell_id = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
+    const int cell_id = blockIdx.x, frame = blockIdx.y + a.frame0, tid = threadIdx.x;
     const CellDesc c = a.cells[cell_id];
     const LevelGeom lv = a.lv[c.level];
     uint32_t* count_out = a.cell_counts + (size_t)frame * a.num_cells + cell_id;

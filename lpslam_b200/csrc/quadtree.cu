@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
     __shared__ int s_i[4];
 
     // grid = (frame, level): the blocks of the fullest level (0) are scheduled first, the light ones fill the tail
-    const int level = blockIdx.y, frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int level = blockIdx.y, frame = blockIdx.x + a.frame0, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LevelGeom lv = a.lv[level];
     Scan scan{s_scan};
 
