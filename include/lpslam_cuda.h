@@ -254,6 +254,15 @@ int lpslam_remap_linear_dev(const uint8_t* src_dev, int src_width, int src_heigh
 int lpslam_landmark_descriptors(const uint8_t* obs_desc, const uint32_t* offsets /*n_landmarks + 1*/, uint32_t n_landmarks,
                                 uint32_t* best_idx, uint8_t* desc_out);
 
+/* match::area::match_in_consistent_area (match/area.cc:8-112), the matcher of the monocular initializer
+ * (initialize/... via module/initializer.cc): frame-1 keypoints of scale level 0 search frame 2 inside a window of
+ * +-margin around prev_matched_pts (n1 x 2 floats, updated in place with the matched frame-2 positions, area.cc:104-108).
+ * matched_indices_2_in_frm_1[i] = frame-2 keypoint matched to frame-1 keypoint i, or -1. */
+int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lpslam_keypoint* kp1_undist, const uint8_t* desc1,
+                      float* prev_matched_pts, uint32_t n2, const lpslam_keypoint* kp2_undist, const uint8_t* desc2,
+                      int margin, float lowe_ratio, int check_orientation, int32_t* matched_indices_2_in_frm_1,
+                      uint32_t* n_matches);
+
 /* ---------------------------------------------------------------- kNN database (relocalisation / loop query) ----- */
 /* Brute-force Hamming top-2 of query descriptors against a device-resident descriptor database (generalises the
  * best / second-best scan of match/robust.cc:252-274 and the BoW-candidate search of module/relocalizer.cc:31-46).

@@ -52,7 +52,10 @@ struct ProjArgs {
     uint32_t* n_events;
     // mode 1 = match_frame_and_landmarks (projection.cc:11-83): the "last frame" arrays describe local landmarks that come
     // with their cached reprojection (data/landmark.h:112-115); last_has_lm = is_observable_in_tracking_ && !will_be_erased()
-    int mode;
+    int mode;  // 2 = area::match_in_consistent_area (area.cc:8-112): rows = frame-1 keypoints, window around prev_pts
+    const float* prev_pts;     // n_last x 2 (mode 2)
+    int32_t* match_2_of_1;     // n_last (mode 2)
+    int32_t* match_1_of_2;     // n_curr (mode 2)
     const double* lm_reproj;   // n_last x 2
     const float* lm_x_right;   // n_last
     float lowe_ratio;
@@ -155,6 +158,16 @@ __device__ Projected cell_window(const ProjArgs& a, Projected p);
 __device__ Projected project(const ProjArgs& a, uint32_t il, bool forward, bool backward) {
     Projected p;
     p.ok = false;
+    if (a.mode == 2) {
+        if (!a.last_has_lm[il]) return p;  // area.cc:23-26: only keypoints of scale level 0
+        p.min_level = 0;                   // area.cc:29-30: get_keypoints_in_cell(x, y, margin, level_1, level_1)
+        p.max_level = 0;
+        p.ref_x = a.prev_pts[2 * (size_t)il];
+        p.ref_y = a.prev_pts[2 * (size_t)il + 1];
+        p.x_right = 0.f;
+        p.m = a.margin;
+        return cell_window(a, p);
+    }
     if (a.mode == 1) {
         if (!a.last_has_lm[il]) return p;
         const int level = a.last_octave[il];
@@ -234,9 +247,11 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
                 if (!(fabsf(__fsub_rn(k.x, p.ref_x)) < p.m && fabsf(__fsub_rn(k.y, p.ref_y)) < p.m)) continue;
                 ++seq;
                 if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
-                const float xr = a.x_right[i];
-                if (xr > 0) {
-                    if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
+                if (a.mode != 2) {
+                    const float xr = a.x_right[i];
+                    if (xr > 0) {
+                        if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
+                    }
                 }
                 const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
                 f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)));
@@ -492,6 +507,100 @@ __global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lps
     bearings[3 * (size_t)i + 2] = __ddiv_rn(1.0, l2);
 }
 
+// area::match_in_consistent_area (area.cc:20-91): rows are replayed in order against the per-keypoint best distance of
+// frame 2 ("ignore if the already-matched point is closer in Hamming space", area.cc:47-50); a later row may take a
+// keypoint over, which deletes the earlier match. s_dist = matched_dists_in_frm_2.
+__global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
+    extern __shared__ uint32_t s_raw[];
+    uint16_t* s_dist = reinterpret_cast<uint16_t*>(s_raw);
+    const int lane = threadIdx.x;
+    for (uint32_t i = lane; i < a.n_curr; i += 32) {
+        s_dist[i] = (uint16_t)MAX_HAMMING_DIST;
+        a.match_1_of_2[i] = -1;
+    }
+    for (uint32_t i = lane; i < a.n_last; i += 32) a.match_2_of_1[i] = -1;
+    __syncwarp();
+    int num = 0;
+    uint32_t n_ev = 0;
+    constexpr unsigned HAMMING_DIST_THR_LOW = 50;  // match/base.h:13
+    for (uint32_t base = 0; base < a.n_last; base += 32) {
+        const uint32_t mine = base + lane;
+        const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
+        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_LOW);
+        while (todo) {
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t il = base + j;
+            const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
+                                   __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
+            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j), __shfl_sync(0xFFFFFFFFu, mi.y, j),
+                               __shfl_sync(0xFFFFFFFFu, mi.z, j), __shfl_sync(0xFFFFFFFFu, mi.w, j)};
+            uint32_t b1 = EMPTY, b2 = EMPTY;
+            int i1 = -1;
+            bool have2 = false;
+#pragma unroll
+            for (int q = 0; q < K; ++q) {
+                if (k[q] == EMPTY) continue;
+                if (s_dist[ix[q]] <= (k[q] >> 20)) continue;  // area.cc:48
+                if (i1 < 0) {
+                    b1 = k[q];
+                    i1 = ix[q];
+                }
+                else if (!have2) {
+                    b2 = k[q];
+                    have2 = true;
+                }
+            }
+            if (!have2 && k[K - 1] != EMPTY) {
+                // the kept four do not decide best and second: exact rescan in reference order by lane 0
+                uint32_t r1 = EMPTY, r2 = EMPTY;
+                int ri1 = -1;
+                if (lane == 0) {
+                    const Projected p = project(a, il, false, false);
+                    visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d) {
+                        if (s_dist[i] <= d) return;
+                        const uint32_t kk = (d << 20) | seq;
+                        if (kk < r1) {
+                            r2 = r1;
+                            r1 = kk;
+                            ri1 = (int)i;
+                        }
+                        else if (kk < r2) {
+                            r2 = kk;
+                        }
+                    });
+                }
+                b1 = __shfl_sync(0xFFFFFFFFu, r1, 0);
+                i1 = __shfl_sync(0xFFFFFFFFu, ri1, 0);
+                b2 = __shfl_sync(0xFFFFFFFFu, r2, 0);
+            }
+            if (i1 < 0) continue;
+            const unsigned best = b1 >> 20, second = b2 == EMPTY ? MAX_HAMMING_DIST : (b2 >> 20);
+            if (HAMMING_DIST_THR_LOW < best) continue;
+            if (__fmul_rn((float)second, a.lowe_ratio) < (float)best) continue;  // area.cc:67-69
+            if (lane == 0) {
+                const int prev = a.match_1_of_2[i1];  // area.cc:76-80: the earlier owner of the keypoint loses its match
+                if (0 <= prev) {
+                    a.match_2_of_1[prev] = -1;
+                    --num;
+                }
+                a.match_2_of_1[il] = i1;
+                a.match_1_of_2[i1] = (int32_t)il;
+                s_dist[i1] = (uint16_t)best;
+                ++num;
+                a.events[n_ev] = make_int2((int)il, i1);
+            }
+            ++n_ev;
+            __syncwarp();
+        }
+    }
+    if (lane == 0) {
+        a.n_events[0] = n_ev;
+        a.n_events[1] = (uint32_t)num;
+    }
+}
+
 }  // namespace
 }  // namespace lps
 
@@ -738,5 +847,102 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
     cudaFree(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_frame_postprocess", __FILE__, __LINE__);
     *n_in_grid = cell_start[ncell];
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lpslam_keypoint* kp1_undist, const uint8_t* desc1,
+                                 float* prev_matched_pts, uint32_t n2, const lpslam_keypoint* kp2_undist, const uint8_t* desc2,
+                                 int margin, float lowe_ratio, int check_orientation, int32_t* matched_indices_2_in_frm_1,
+                                 uint32_t* n_matches) {
+    LPS_ARG(cam && n_matches, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n1 == 0 || (kp1_undist && desc1 && prev_matched_pts && matched_indices_2_in_frm_1), "null frame-1 argument");
+    LPS_ARG(n2 == 0 || (kp2_undist && desc2), "null frame-2 argument");
+    LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1, "bad camera grid");
+    LPS_ARG(n2 < (1u << 20) && n2 <= 40000, "too many frame-2 keypoints");
+    for (uint32_t i = 0; i < n1; ++i) matched_indices_2_in_frm_1[i] = -1;
+    if (n1 == 0 || n2 == 0) return LPSLAM_OK;
+    std::vector<uint8_t> use(n1);
+    std::vector<int32_t> zero_level(n1, 0);
+    for (uint32_t i = 0; i < n1; ++i) use[i] = kp1_undist[i].octave <= 0;  // area.cc:23-26
+
+    const uint32_t ncell = cam->grid_cols * cam->grid_rows;
+    ArenaBump ar;
+    const size_t o_use = ar.take(n1), o_pp = ar.take(8 * (size_t)n1), o_d1 = ar.take(32 * (size_t)n1), o_lvl = ar.take(4 * (size_t)n1);
+    const size_t o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n2), o_d2 = ar.take(32 * (size_t)n2);
+    const size_t o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1)), o_cf = ar.take(4 * (size_t)ncell);
+    const size_t o_ci = ar.take(4 * (size_t)n2), o_tkey = ar.take(16 * (size_t)n1), o_tidx = ar.take(16 * (size_t)n1);
+    const size_t o_m21 = ar.take(4 * (size_t)n1), o_m12 = ar.take(4 * (size_t)n2), o_ev = ar.take(8 * (size_t)n1), o_ne = ar.take(8);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    cudaError_t e = cudaSuccess;
+    std::vector<int2> events;
+    uint32_t ne[2] = {0, 0};
+    do {
+#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
+        UP(o_use, use.data(), n1);
+        UP(o_pp, prev_matched_pts, 8 * (size_t)n1);
+        UP(o_d1, desc1, 32 * (size_t)n1);
+        UP(o_lvl, zero_level.data(), 4 * (size_t)n1);
+        UP(o_kp, kp2_undist, sizeof(lpslam_keypoint) * (size_t)n2);
+        UP(o_d2, desc2, 32 * (size_t)n2);
+#undef UP
+        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        ProjArgs a = {};
+        a.cam = *cam;
+        a.mode = 2;
+        a.n_last = n1;
+        a.n_curr = n2;
+        a.last_has_lm = dev + o_use;
+        a.last_desc = dev + o_d1;
+        a.last_octave = (const int32_t*)(dev + o_lvl);
+        a.prev_pts = (const float*)(dev + o_pp);
+        a.lowe_ratio = lowe_ratio;
+        a.kp = (const lpslam_keypoint*)(dev + o_kp);
+        a.desc = dev + o_d2;
+        a.margin = (float)margin;
+        a.cell_count = (uint32_t*)(dev + o_cc);
+        a.cell_start = (uint32_t*)(dev + o_cs);
+        a.cell_fill = (uint32_t*)(dev + o_cf);
+        a.cell_items = (uint32_t*)(dev + o_ci);
+        a.top_key = (uint4*)(dev + o_tkey);
+        a.top_idx = (int4*)(dev + o_tidx);
+        a.match_2_of_1 = (int32_t*)(dev + o_m21);
+        a.match_1_of_2 = (int32_t*)(dev + o_m12);
+        a.events = (int2*)(dev + o_ev);
+        a.n_events = (uint32_t*)(dev + o_ne);
+        k_grid_count<<<(n2 + 255) / 256, 256>>>(a);
+        k_grid_scan<<<1, 1024>>>(a);
+        k_grid_fill<<<(n2 + 255) / 256, 256>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
+        k_proj_topk<<<(n1 + 127) / 128, 128>>>(a);
+        k_area_resolve<<<1, 32, ((n2 + 1) / 2) * 4 + 4>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(matched_indices_2_in_frm_1, dev + o_m21, 4 * (size_t)n1, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(ne, dev + o_ne, 8, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (check_orientation && ne[0]) {
+            events.resize(ne[0]);
+            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)ne[0], cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        }
+    } while (false);
+    cudaFree(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_area", __FILE__, __LINE__);
+    int num = (int)ne[1];
+    if (check_orientation) {  // area.cc:87-101: every accepted row entered the histogram, also rows that lost their match later
+        std::vector<std::pair<float, int>> deltas;
+        for (const int2& ev : events) deltas.emplace_back(kp1_undist[ev.x].angle - kp2_undist[ev.y].angle, ev.x);
+        for (int id : angle_invalid_matches(deltas)) {
+            if (0 <= matched_indices_2_in_frm_1[id]) {
+                matched_indices_2_in_frm_1[id] = -1;
+                --num;
+            }
+        }
+    }
+    for (uint32_t i = 0; i < n1; ++i)  // area.cc:104-108
+        if (0 <= matched_indices_2_in_frm_1[i]) {
+            prev_matched_pts[2 * i] = kp2_undist[matched_indices_2_in_frm_1[i]].x;
+            prev_matched_pts[2 * i + 1] = kp2_undist[matched_indices_2_in_frm_1[i]].y;
+        }
+    *n_matches = (uint32_t)num;
     return LPSLAM_OK;
 }

@@ -112,6 +112,31 @@ def frame_postprocess(model, cam, keypts):
     check(lib().lpslam_frame_postprocess(C.byref(model), C.byref(cam), len(kp), kp.ctypes.data, und.ctypes.data, bearings.ctypes.data,
                                          start.ctypes.data, items.ctypes.data, C.byref(n)))
     return und, bearings, start, items[: n.value]
+register("lpslam_match_area", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                        C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, _lib.u32p])
+
+
+class area:
+    """match::area (match/area.h): the matcher of the monocular initializer"""
+
+    def __init__(self, lowe_ratio=0.9, check_orientation=True):
+        self.lowe_ratio_, self.check_orientation_ = float(lowe_ratio), bool(check_orientation)
+
+    def match_in_consistent_area(self, cam, undist_keypts_1, descs_1, undist_keypts_2, descs_2, prev_matched_pts, margin=100):
+        """match/area.cc:8-112 over flat arrays: returns (matched_indices_2_in_frm_1, num_matches, prev_matched_pts)."""
+        k1 = np.ascontiguousarray(undist_keypts_1, KP_DTYPE)
+        k2 = np.ascontiguousarray(undist_keypts_2, KP_DTYPE)
+        d1 = np.ascontiguousarray(descs_1, np.uint8)
+        d2 = np.ascontiguousarray(descs_2, np.uint8)
+        pp = np.array(prev_matched_pts, np.float32).reshape(-1, 2).copy()
+        out = np.full(len(k1), -1, np.int32)
+        n = C.c_uint32(0)
+        check(lib().lpslam_match_area(C.byref(cam), len(k1), k1.ctypes.data, d1.ctypes.data, pp.ctypes.data, len(k2), k2.ctypes.data,
+                                      d2.ctypes.data, int(margin), self.lowe_ratio_, int(self.check_orientation_), out.ctypes.data,
+                                      C.byref(n)))
+        return out, int(n.value), pp
+
+
 register("lpslam_landmark_descriptors", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p])
 
 

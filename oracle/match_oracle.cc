@@ -331,6 +331,66 @@ int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_
     return static_cast<int>(num);
 }
 
+// match/area.cc:8-112 match_in_consistent_area over flat arrays; prev_pts (n1 x 2) is updated in place
+int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
+                   const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,
+                   int32_t* matched_2_in_1) {
+    int num = 0;
+    AngleHistogram hist;
+    const auto grid = assign_grid(cam, n2, kp2);
+    std::fill(matched_2_in_1, matched_2_in_1 + n1, -1);
+    std::vector<unsigned> matched_dists_2(n2, MAX_HAMMING_DIST);
+    std::vector<int> matched_1_in_2(n2, -1);
+    std::vector<unsigned> idx;
+    for (unsigned i1 = 0; i1 < n1; ++i1) {
+        const int level = kp1[i1].octave;
+        if (0 < level) continue;
+        keypoints_in_cell(cam, grid, kp2, prev_pts[2 * i1], prev_pts[2 * i1 + 1], static_cast<float>(margin), level, level, idx);
+        if (idx.empty()) continue;
+        const uint8_t* d1 = desc1 + static_cast<size_t>(i1) * 32;
+        unsigned best = MAX_HAMMING_DIST, second = MAX_HAMMING_DIST;
+        int best_2 = -1;
+        for (unsigned i2 : idx) {
+            const unsigned d = hamming_32(d1, desc2 + static_cast<size_t>(i2) * 32);
+            if (matched_dists_2[i2] <= d) continue;
+            if (d < best) {
+                second = best;
+                best = d;
+                best_2 = static_cast<int>(i2);
+            }
+            else if (d < second) {
+                second = d;
+            }
+        }
+        if (HAMMING_DIST_THR_LOW < best) continue;
+        if (second * lowe_ratio < static_cast<float>(best)) continue;
+        const int prev_1 = matched_1_in_2[best_2];
+        if (0 <= prev_1) {
+            matched_2_in_1[prev_1] = -1;
+            --num;
+        }
+        matched_2_in_1[i1] = best_2;
+        matched_1_in_2[best_2] = static_cast<int>(i1);
+        matched_dists_2[best_2] = best;
+        ++num;
+        if (check_orientation) hist.append(kp1[i1].angle - kp2[best_2].angle, static_cast<int>(i1));
+    }
+    if (check_orientation) {
+        for (int id : hist.invalid()) {
+            if (0 <= matched_2_in_1[id]) {
+                matched_2_in_1[id] = -1;
+                --num;
+            }
+        }
+    }
+    for (unsigned i1 = 0; i1 < n1; ++i1)
+        if (0 <= matched_2_in_1[i1]) {
+            prev_pts[2 * i1] = kp2[matched_2_in_1[i1]].x;
+            prev_pts[2 * i1 + 1] = kp2[matched_2_in_1[i1]].y;
+        }
+    return num;
+}
+
 // data/landmark.cc:151-177 for one landmark: index of the representative descriptor among its n observations
 uint32_t orc_landmark_descriptor(const uint8_t* descs, uint32_t n) {
     std::vector<std::vector<unsigned>> hamm(n, std::vector<unsigned>(n));

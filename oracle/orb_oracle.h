@@ -117,6 +117,11 @@ void orc_imadjust_u8(const uint8_t* src, int w, int h, size_t pitch, int auto_li
 void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, size_t spitch, const float* map_x, const float* map_y,
                          size_t map_pitch /*floats*/, uint8_t* dst, int dw, int dh, size_t dpitch);
 
+/* match/area.cc:8-112 match_in_consistent_area over flat arrays (prev_pts n1 x 2 floats, in / out). Returns num_matches. */
+int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
+                   const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,
+                   int32_t* matched_2_in_1);
+
 /* data/landmark.cc:151-177: representative descriptor (index) among n observation descriptors */
 uint32_t orc_landmark_descriptor(const uint8_t* descs, uint32_t n);
 

@@ -118,6 +118,8 @@ class Oracle:
             L.orc_imadjust_u8.restype = None
             L.orc_remap_linear_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, f32p, f32p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_size_t]
             L.orc_remap_linear_u8.restype = None
+            L.orc_match_area.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, C.c_void_p, u8p, f32p, C.c_uint32, C.c_void_p, u8p, C.c_int,
+                                         C.c_float, C.c_int, i32p]
             L.orc_landmark_descriptor.argtypes = [u8p, C.c_uint32]
             L.orc_landmark_descriptor.restype = C.c_uint32
             L.orc_knn_top2.argtypes = [u8p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_int64), C.POINTER(C.c_uint32),
@@ -297,6 +299,17 @@ class Oracle:
         self.lib.orc_remap_linear_u8(_ptr(img, u8p), img.shape[1], img.shape[0], img.strides[0], _ptr(mx, f32p), _ptr(my, f32p), dw,
                                      _ptr(dst, u8p), dw, dh, dw)
         return dst
+
+    def match_area(self, cam, kp1, desc1, prev_pts, kp2, desc2, margin, lowe_ratio, check_orientation):
+        kp1 = np.ascontiguousarray(kp1, KP_DTYPE)
+        kp2 = np.ascontiguousarray(kp2, KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, np.uint8)
+        d2 = np.ascontiguousarray(desc2, np.uint8)
+        pp = np.array(prev_pts, np.float32).reshape(-1, 2).copy()
+        out = np.empty(len(kp1), np.int32)
+        n = self.lib.orc_match_area(C.byref(cam), len(kp1), kp1.ctypes.data, _ptr(d1, u8p), _ptr(pp, f32p), len(kp2), kp2.ctypes.data,
+                                    _ptr(d2, u8p), int(margin), lowe_ratio, int(check_orientation), _ptr(out, i32p))
+        return out, n, pp
 
     def landmark_descriptor(self, descs):
         d = np.ascontiguousarray(descs, np.uint8).reshape(-1, 32)

@@ -235,3 +235,36 @@ def test_landmark_descriptors(oracle):
         want = oracle.landmark_descriptor(descs[offsets[l]:offsets[l + 1]])
         assert best[l] == want, (l, n)
         assert np.array_equal(out[l], descs[offsets[l] + want])
+
+
+@pytest.mark.parametrize("seed,chk", [(1, True), (2, False), (3, True)])
+def test_area(oracle, seed, chk):
+    # match/area.cc:8-112 (monocular initializer): frame 2 = frame 1 shifted, plus decoys that fight for the same keypoints
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    rng = np.random.default_rng(seed)
+    a = synth_image(480, 640, 50 + seed)
+    b = np.roll(a, (3, 7), axis=(0, 1))
+    o = oracle.extractor(max_kpts=1000)
+    k1, d1 = o.extract(a)
+    k2, d2 = o.extract(b)
+    args = dict(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    prev = np.stack([k1["x"], k1["y"]], axis=1).astype(np.float32)   # initializer: previous match = own position
+    total = 0
+    for margin in (20, 100):
+        for ratio in (0.9, 0.7):
+            want, nw, pw = oracle.match_area(pyoracle.make_camera(**args), k1, d1, prev, k2, d2, margin, ratio, chk)
+            got, ng, pg = match.area(ratio, chk).match_in_consistent_area(match.make_camera(**args), k1, d1, k2, d2, prev, margin)
+            assert np.array_equal(got, want) and ng == nw and np.array_equal(pg, pw)
+            total += nw
+    assert total > 100
+    # second round from the updated positions, with near-duplicate descriptors in frame 1 (take-overs, area.cc:76-80)
+    d1b = d1.copy()
+    d1b[1::2] = d1b[::2][: len(d1b[1::2])] ^ np.packbits(rng.random((len(d1b[1::2]), 256)) < 0.01, axis=1, bitorder="little")
+    k1b = k1.copy()
+    k1b["x"][1::2], k1b["y"][1::2] = k1b["x"][::2][: len(k1b[1::2])], k1b["y"][::2][: len(k1b[1::2])]
+    k1b["octave"][1::2] = k1b["octave"][::2][: len(k1b[1::2])]
+    prevb = np.stack([k1b["x"], k1b["y"]], axis=1).astype(np.float32)
+    want, nw, pw = oracle.match_area(pyoracle.make_camera(**args), k1b, d1b, prevb, k2, d2, 50, 0.95, chk)
+    got, ng, pg = match.area(0.95, chk).match_in_consistent_area(match.make_camera(**args), k1b, d1b, k2, d2, prevb, 50)
+    assert np.array_equal(got, want) and ng == nw and np.array_equal(pg, pw) and nw > 20
