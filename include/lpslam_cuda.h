@@ -254,6 +254,30 @@ int lpslam_remap_linear_dev(const uint8_t* src_dev, int src_width, int src_heigh
 int lpslam_landmark_descriptors(const uint8_t* obs_desc, const uint32_t* offsets /*n_landmarks + 1*/, uint32_t n_landmarks,
                                 uint32_t* best_idx, uint8_t* desc_out);
 
+/* The reprojection matchers of match/projection.cc share one inner loop: every row (a landmark with its reprojection into
+ * the frame, its predicted scale level and its descriptor) searches the frame's grid inside margin * scale_factors[level]
+ * for the free keypoint with the smallest Hamming distance. lpslam_match_reprojected is that loop with the knobs in which
+ * the reference's functions differ; the geometry in front of it (reproject_to_image, the valid-distance gate,
+ * predict_scale_level: a few flops per landmark in Eigen) stays in the caller, so it is the reference's own code:
+ *   match_frame_and_landmarks  (projection.cc:11-83)    level window (-1, 0), thr 100, ratio on,  stereo gate on  = lpslam_match_landmarks
+ *   match_frame_and_keyframe   (projection.cc:210-312)  level window (-1,+1), thr = hamm_dist_thr, ratio off, gate off,
+ *                                                       orientation check against the keyframe keypoints' angles (lm_angle)
+ * lm_angle != NULL runs the angle_checker over (lm_angle[row] - keypoint angle) and clears the rejected keypoints. */
+typedef struct {
+    float margin;
+    float lowe_ratio;
+    uint32_t hamm_dist_thr;
+    int32_t level_lo, level_hi; /* octave window = [level + level_lo, level + level_hi] */
+    int32_t use_ratio;          /* Lowe ratio between best and second best on the same scale level (projection.cc:69-72) */
+    int32_t use_x_right;        /* stereo reprojection gate (projection.cc:45-50); off: lm_x_right / kp_x_right may be NULL */
+} lpslam_reproj_match_params;
+int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_reproj_match_params* params, uint32_t n_lm,
+                             const uint8_t* lm_active, const double* lm_reproj /*n_lm x 2*/, const float* lm_x_right,
+                             const int32_t* lm_scale_level, const uint8_t* lm_desc, const uint8_t* lm_has_observation,
+                             const float* lm_angle, uint32_t n_kp, const lpslam_keypoint* kp_undist, const uint8_t* kp_desc,
+                             const float* kp_x_right, const uint8_t* kp_has_landmark, const float* scale_factors,
+                             int32_t* kp_match_lm, uint32_t* n_matches);
+
 /* match::area::match_in_consistent_area (match/area.cc:8-112), the matcher of the monocular initializer
  * (initialize/... via module/initializer.cc): frame-1 keypoints of scale level 0 search frame 2 inside a window of
  * +-margin around prev_matched_pts (n1 x 2 floats, updated in place with the matched frame-2 positions, area.cc:104-108).

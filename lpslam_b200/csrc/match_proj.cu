@@ -59,6 +59,10 @@ struct ProjArgs {
     const double* lm_reproj;   // n_last x 2
     const float* lm_x_right;   // n_last
     float lowe_ratio;
+    // mode 1 knobs (lpslam_reproj_match_params): octave window relative to the predicted level, acceptance threshold,
+    // Lowe ratio on / off, stereo x_right gate on / off
+    int level_lo, level_hi, use_ratio, use_xr;
+    unsigned hamm_thr;
 };
 
 __device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
@@ -171,8 +175,8 @@ __device__ Projected project(const ProjArgs& a, uint32_t il, bool forward, bool 
     if (a.mode == 1) {
         if (!a.last_has_lm[il]) return p;
         const int level = a.last_octave[il];
-        p.min_level = level - 1;  // projection.cc:27-29
-        p.max_level = level;
+        p.min_level = level + a.level_lo;  // projection.cc:27-29: (level - 1, level)
+        p.max_level = level + a.level_hi;
         p.ref_x = (float)a.lm_reproj[2 * (size_t)il];
         p.ref_y = (float)a.lm_reproj[2 * (size_t)il + 1];
         p.x_right = a.lm_x_right[il];
@@ -247,7 +251,7 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
                 if (!(fabsf(__fsub_rn(k.x, p.ref_x)) < p.m && fabsf(__fsub_rn(k.y, p.ref_y)) < p.m)) continue;
                 ++seq;
                 if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
-                if (a.mode != 2) {
+                if (a.mode == 0 || (a.mode == 1 && a.use_xr)) {
                     const float xr = a.x_right[i];
                     if (xr > 0) {
                         if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
@@ -386,7 +390,7 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
         const uint32_t mine = base + lane;
         const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
         const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
-        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_HIGH);
+        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= a.hamm_thr);
         while (todo) {
             const int j = __ffs(todo) - 1;
             todo &= todo - 1;
@@ -410,8 +414,8 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
                     i2 = ix[q];
                 }
             }
-            if (i2 < 0 && k[K - 1] != EMPTY) {
-                // fewer than two free entries among the four kept and the list may be longer: exact rescan by lane 0
+            if ((a.use_ratio ? i2 < 0 : i1 < 0) && k[K - 1] != EMPTY) {
+                // too few free entries among the four kept and the list may be longer: exact rescan by lane 0
                 uint32_t r1 = EMPTY, r2 = EMPTY;
                 int ri1 = -1, ri2 = -1;
                 if (lane == 0) {
@@ -437,13 +441,16 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
             }
             if (i1 < 0) continue;
             const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
-            if (HAMMING_DIST_THR_HIGH < best) continue;
-            const int best_level = a.kp[i1].octave, second_level = i2 >= 0 ? a.kp[i2].octave : -1;
-            if (best_level == second_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) continue;  // projection.cc:69-72
+            if (a.hamm_thr < best) continue;
+            if (a.use_ratio) {
+                const int best_level = a.kp[i1].octave, second_level = i2 >= 0 ? a.kp[i2].octave : -1;
+                if (best_level == second_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) continue;  // projection.cc:69-72
+            }
             if (lane == 0) {
                 a.curr_match_last[i1] = (int32_t)il;
                 const bool blocks = a.last_obs ? a.last_obs[il] != 0 : true;  // projection.cc:41-43 re-tests has_observation()
                 if (blocks) s_taken[i1 >> 5] |= 1u << (i1 & 31);
+                if (a.events) a.events[num] = make_int2((int)il, i1);
             }
             ++num;
             __syncwarp();
@@ -714,16 +721,25 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
     return LPSLAM_OK;
 }
 
-extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
-                                      const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
-                                      const uint8_t* lm_has_observation, uint32_t n_kp, const lpslam_keypoint* kp_undist,
-                                      const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
-                                      const float* scale_factors, float margin, float lowe_ratio, int32_t* kp_match_lm,
-                                      uint32_t* n_matches) {
-    LPS_ARG(cam && n_matches && scale_factors, "null argument");
+extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_reproj_match_params* prm, uint32_t n_lm,
+                                        const uint8_t* lm_active, const double* lm_reproj, const float* lm_x_right,
+                                        const int32_t* lm_scale_level, const uint8_t* lm_desc, const uint8_t* lm_has_observation,
+                                        const float* lm_angle, uint32_t n_kp, const lpslam_keypoint* kp_undist,
+                                        const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
+                                        const float* scale_factors, int32_t* kp_match_lm, uint32_t* n_matches) {
+    LPS_ARG(cam && prm && n_matches && scale_factors, "null argument");
+    const float margin = prm->margin, lowe_ratio = prm->lowe_ratio;
+    std::vector<float> zeros_lm, neg_kp;
+    if (!prm->use_x_right) {  // the gate is off: the arrays are not looked at
+        zeros_lm.assign(n_lm, 0.f);
+        neg_kp.assign(n_kp, -1.f);
+        lm_x_right = zeros_lm.data();
+        kp_x_right = neg_kp.data();
+    }
     *n_matches = 0;
     LPS_ARG(n_kp == 0 || (kp_undist && kp_desc && kp_x_right && kp_has_observed_lm && kp_match_lm), "null frame argument");
     LPS_ARG(n_lm == 0 || (lm_active && lm_reproj && lm_x_right && lm_scale_level && lm_desc), "null landmark argument");
+    LPS_ARG(prm->hamm_dist_thr <= 256 && prm->level_lo <= prm->level_hi, "bad matcher parameters");
     LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1 && cam->num_scale_levels >= 1 && cam->num_scale_levels <= (uint32_t)kMaxLevels,
             "bad camera grid / level count");
     LPS_ARG(n_kp < (1u << 20), "too many keypoints");
@@ -740,11 +756,12 @@ extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, c
     const size_t o_desc = ar.take(32 * (size_t)n_kp), o_xr = ar.take(4 * (size_t)n_kp), o_tk = ar.take(n_kp);
     const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
-    const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_m = ar.take(4 * (size_t)n_kp), o_ne = ar.take(4);
+    const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_m = ar.take(4 * (size_t)n_kp), o_ne = ar.take(4), o_ev = ar.take(8 * (size_t)n_lm);
     uint8_t* dev = nullptr;
     LPS_CUDA(cudaMalloc(&dev, ar.off));
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
+    std::vector<int2> events;
     do {
 #define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
         UP(o_act, lm_active, n_lm);
@@ -772,6 +789,12 @@ extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, c
         a.lm_reproj = (const double*)(dev + o_rp);
         a.lm_x_right = (const float*)(dev + o_lxr);
         a.lowe_ratio = lowe_ratio;
+        a.level_lo = prm->level_lo;
+        a.level_hi = prm->level_hi;
+        a.use_ratio = prm->use_ratio;
+        a.use_xr = prm->use_x_right;
+        a.hamm_thr = prm->hamm_dist_thr;
+        a.events = lm_angle ? (int2*)(dev + o_ev) : nullptr;
         a.kp = (const lpslam_keypoint*)(dev + o_kp);
         a.desc = dev + o_desc;
         a.x_right = (const float*)(dev + o_xr);
@@ -795,11 +818,36 @@ extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, c
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(kp_match_lm, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (lm_angle && n_ev) {
+            events.resize(n_ev);
+            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        }
     } while (false);
     cudaFree(dev);
-    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_landmarks", __FILE__, __LINE__);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_reprojected", __FILE__, __LINE__);
     *n_matches = n_ev;
+    if (lm_angle) {  // angle_checker over (row angle - keypoint angle, keypoint), projection.cc:297-311
+        std::vector<std::pair<float, int>> deltas;
+        for (const int2& ev : events) deltas.emplace_back(lm_angle[ev.x] - kp_undist[ev.y].angle, ev.y);
+        for (int id : angle_invalid_matches(deltas)) {
+            kp_match_lm[id] = -1;
+            --*n_matches;
+        }
+    }
     return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_landmarks(const lpslam_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                                      const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                                      const uint8_t* lm_has_observation, uint32_t n_kp, const lpslam_keypoint* kp_undist,
+                                      const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
+                                      const float* scale_factors, float margin, float lowe_ratio, int32_t* kp_match_lm,
+                                      uint32_t* n_matches) {
+    // projection.cc:11-83: window (level - 1, level), threshold HAMMING_DIST_THR_HIGH, ratio test, stereo gate
+    const lpslam_reproj_match_params prm = {margin, lowe_ratio, HAMMING_DIST_THR_HIGH, -1, 0, 1, 1};
+    return lpslam_match_reprojected(cam, &prm, n_lm, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_desc, lm_has_observation,
+                                    nullptr, n_kp, kp_undist, kp_desc, kp_x_right, kp_has_observed_lm, scale_factors, kp_match_lm,
+                                    n_matches);
 }
 
 extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const lpslam_camera* cam, uint32_t n,

@@ -112,6 +112,40 @@ def frame_postprocess(model, cam, keypts):
     check(lib().lpslam_frame_postprocess(C.byref(model), C.byref(cam), len(kp), kp.ctypes.data, und.ctypes.data, bearings.ctypes.data,
                                          start.ctypes.data, items.ctypes.data, C.byref(n)))
     return und, bearings, start, items[: n.value]
+class ReprojMatchParams(C.Structure):
+    """lpslam_reproj_match_params"""
+    _fields_ = [("margin", C.c_float), ("lowe_ratio", C.c_float), ("hamm_dist_thr", C.c_uint32), ("level_lo", C.c_int32),
+                ("level_hi", C.c_int32), ("use_ratio", C.c_int32), ("use_x_right", C.c_int32)]
+
+
+register("lpslam_match_reprojected", C.c_int, [C.POINTER(_lib.Camera), C.POINTER(ReprojMatchParams), C.c_uint32, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _lib.u32p])
+
+
+def match_reprojected(cam, params, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_descs, undist_keypts, descs, stereo_x_right,
+                      has_landmark, scale_factors, lm_has_observation=None, lm_angle=None):
+    """lpslam_match_reprojected over numpy arrays: returns (kp_match_lm, num_matches)."""
+    act = np.ascontiguousarray(lm_active, np.uint8)
+    rp = np.ascontiguousarray(lm_reproj, np.float64).reshape(-1, 2)
+    lxr = None if lm_x_right is None else np.ascontiguousarray(lm_x_right, np.float32)
+    lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+    ld = np.ascontiguousarray(lm_descs, np.uint8).reshape(-1, 32)
+    obs = None if lm_has_observation is None else np.ascontiguousarray(lm_has_observation, np.uint8)
+    ang = None if lm_angle is None else np.ascontiguousarray(lm_angle, np.float32)
+    kp = np.ascontiguousarray(undist_keypts, KP_DTYPE)
+    cd = np.ascontiguousarray(descs, np.uint8)
+    xr = None if stereo_x_right is None else np.ascontiguousarray(stereo_x_right, np.float32)
+    tk = np.ascontiguousarray(has_landmark, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    out = np.full(len(kp), -1, np.int32)
+    n = C.c_uint32(0)
+    check(lib().lpslam_match_reprojected(C.byref(cam), C.byref(params), len(act), act.ctypes.data, rp.ctypes.data, _lib.ptr(lxr),
+                                         lvl.ctypes.data, ld.ctypes.data, _lib.ptr(obs), _lib.ptr(ang), len(kp), kp.ctypes.data,
+                                         cd.ctypes.data, _lib.ptr(xr), tk.ctypes.data, sf.ctypes.data, out.ctypes.data, C.byref(n)))
+    return out, int(n.value)
+
+
 register("lpslam_match_area", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                         C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, _lib.u32p])
 
@@ -221,6 +255,15 @@ class projection:
                                             tk.ctypes.data, sf.ctypes.data, float(margin), int(self.check_orientation_),
                                             out.ctypes.data, C.byref(n)))
         return out, int(n.value)
+
+    def match_frame_and_keyframe(self, cam, lm_active, lm_reproj, lm_scale_level, lm_descs, keyfrm_angles, undist_keypts, descs,
+                                 has_landmark, scale_factors, margin, hamm_dist_thr):
+        """match/projection.cc:210-312 after the caller's geometry (reproject_to_image, valid-distance gate, predict_scale_level):
+        lm_active = landmark exists, is not erased, is not in already_matched_lms, reprojects into the image and passes the
+        distance gate. Returns (kp_match_lm, num_matches)."""
+        prm = ReprojMatchParams(float(margin), 0.0, int(hamm_dist_thr), -1, 1, 0, 0)
+        return match_reprojected(cam, prm, lm_active, lm_reproj, None, lm_scale_level, lm_descs, undist_keypts, descs, None, has_landmark,
+                                 scale_factors, None, keyfrm_angles if self.check_orientation_ else None)
 
     def match_frame_and_landmarks(self, cam, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_descs, undist_keypts, descs,
                                   stereo_x_right, has_observed_lm, scale_factors, margin=5.0, lm_has_observation=None):

@@ -280,31 +280,37 @@ static void keypoints_in_cell(const orc_camera* cam, const std::vector<std::vect
             }
 }
 
-// match/projection.cc:11-83 match_frame_and_landmarks (the local-map search of every tracked frame): the landmarks come
-// with the reprojection the tracker cached on them (data/landmark.h:112-115)
-int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj /*n_lm x 2*/,
-                        const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
-                        const uint8_t* lm_has_observation /* nullable = all 1 */, uint32_t n_kp, const orc_keypoint* kp,
-                        const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
-                        const float* scale_factors, float margin, float lowe_ratio, int32_t* kp_match_lm) {
-    unsigned num = 0;
+// The inner loop shared by the reprojection matchers of match/projection.cc, with the knobs in which they differ:
+//   match_frame_and_landmarks (:11-83)   window (level - 1, level), thr HAMMING_DIST_THR_HIGH, ratio test, stereo gate
+//   match_frame_and_keyframe (:210-312)  window (level - 1, level + 1), thr = hamm_dist_thr, no ratio test, no stereo gate,
+//                                        'if (curr_frm.landmarks_.at(curr_idx)) continue', angle check
+// The rows come with the reprojection / predicted level the caller computed (data/landmark.h:112-115 caches them for the
+// local map; match_frame_and_keyframe computes them inline with camera/perspective.cc:151-169 and landmark.cc:239-256).
+int orc_match_reprojected(const orc_camera* cam, float margin, float lowe_ratio, uint32_t hamm_thr, int level_lo, int level_hi,
+                          int use_ratio, int use_x_right, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                          const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                          const uint8_t* lm_has_observation, const float* lm_angle, uint32_t n_kp, const orc_keypoint* kp,
+                          const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_taken, const float* scale_factors,
+                          int32_t* kp_match_lm) {
+    int num = 0;
+    AngleHistogram hist;
     const auto grid = assign_grid(cam, n_kp, kp);
-    std::vector<uint8_t> taken(kp_has_observed_lm, kp_has_observed_lm + n_kp);
+    std::vector<uint8_t> taken(kp_taken, kp_taken + n_kp);
     std::fill(kp_match_lm, kp_match_lm + n_kp, -1);
     std::vector<unsigned> idx;
     for (unsigned j = 0; j < n_lm; ++j) {
-        if (!lm_active[j]) continue;  // !is_observable_in_tracking_ || will_be_erased()  (:16-21)
+        if (!lm_active[j]) continue;
         const int level = lm_scale_level[j];
         const float m = margin * scale_factors[level];
-        keypoints_in_cell(cam, grid, kp, static_cast<float>(lm_reproj[2 * j]), static_cast<float>(lm_reproj[2 * j + 1]), m, level - 1,
-                          level, idx);
+        keypoints_in_cell(cam, grid, kp, static_cast<float>(lm_reproj[2 * j]), static_cast<float>(lm_reproj[2 * j + 1]), m,
+                          level + level_lo, level + level_hi, idx);
         if (idx.empty()) continue;
         const uint8_t* ld = lm_desc + static_cast<size_t>(j) * 32;
         unsigned best = MAX_HAMMING_DIST, second = MAX_HAMMING_DIST;
         int best_level = -1, second_level = -1, best_i = -1;
         for (unsigned i : idx) {
-            if (taken[i]) continue;  // :41-43, sees the assignments of earlier landmarks
-            if (0 < kp_x_right[i]) {
+            if (taken[i]) continue;  // sees the assignments of earlier rows
+            if (use_x_right && 0 < kp_x_right[i]) {
                 const float err = std::abs(lm_x_right[j] - kp_x_right[i]);
                 if (m < err) continue;
             }
@@ -321,14 +327,32 @@ int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_
                 second = d;
             }
         }
-        if (best <= HAMMING_DIST_THR_HIGH) {
-            if (best_level == second_level && best > lowe_ratio * second) continue;  // :69-72
+        if (best <= hamm_thr && best_i >= 0) {
+            if (use_ratio && best_level == second_level && best > lowe_ratio * second) continue;
             kp_match_lm[best_i] = static_cast<int32_t>(j);
             taken[best_i] = lm_has_observation ? lm_has_observation[j] : 1;
             ++num;
+            if (lm_angle) hist.append(lm_angle[j] - kp[best_i].angle, best_i);
         }
     }
-    return static_cast<int>(num);
+    if (lm_angle) {
+        for (int id : hist.invalid()) {
+            kp_match_lm[id] = -1;
+            --num;
+        }
+    }
+    return num;
+}
+
+// match/projection.cc:11-83 match_frame_and_landmarks (the local-map search of every tracked frame)
+int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj /*n_lm x 2*/,
+                        const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                        const uint8_t* lm_has_observation /* nullable = all 1 */, uint32_t n_kp, const orc_keypoint* kp,
+                        const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_has_observed_lm,
+                        const float* scale_factors, float margin, float lowe_ratio, int32_t* kp_match_lm) {
+    return orc_match_reprojected(cam, margin, lowe_ratio, HAMMING_DIST_THR_HIGH, -1, 0, 1, 1, n_lm, lm_active, lm_reproj, lm_x_right,
+                                 lm_scale_level, lm_desc, lm_has_observation, nullptr, n_kp, kp, kp_desc, kp_x_right,
+                                 kp_has_observed_lm, scale_factors, kp_match_lm);
 }
 
 // match/area.cc:8-112 match_in_consistent_area over flat arrays; prev_pts (n1 x 2) is updated in place

@@ -117,6 +117,14 @@ void orc_imadjust_u8(const uint8_t* src, int w, int h, size_t pitch, int auto_li
 void orc_remap_linear_u8(const uint8_t* src, int sw, int sh, size_t spitch, const float* map_x, const float* map_y,
                          size_t map_pitch /*floats*/, uint8_t* dst, int dw, int dh, size_t dpitch);
 
+/* shared inner loop of the reprojection matchers of match/projection.cc (match_oracle.cc) */
+int orc_match_reprojected(const orc_camera* cam, float margin, float lowe_ratio, uint32_t hamm_thr, int level_lo, int level_hi,
+                          int use_ratio, int use_x_right, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                          const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                          const uint8_t* lm_has_observation, const float* lm_angle, uint32_t n_kp, const orc_keypoint* kp,
+                          const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_taken, const float* scale_factors,
+                          int32_t* kp_match_lm);
+
 /* match/area.cc:8-112 match_in_consistent_area over flat arrays (prev_pts n1 x 2 floats, in / out). Returns num_matches. */
 int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
                    const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,

@@ -118,6 +118,9 @@ class Oracle:
             L.orc_imadjust_u8.restype = None
             L.orc_remap_linear_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, f32p, f32p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_size_t]
             L.orc_remap_linear_u8.restype = None
+            L.orc_match_reprojected.argtypes = [C.POINTER(_CameraStruct), C.c_float, C.c_float, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                C.c_uint32, u8p, C.POINTER(C.c_double), f32p, i32p, u8p, u8p, f32p,
+                                                C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, i32p]
             L.orc_match_area.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, C.c_void_p, u8p, f32p, C.c_uint32, C.c_void_p, u8p, C.c_int,
                                          C.c_float, C.c_int, i32p]
             L.orc_landmark_descriptor.argtypes = [u8p, C.c_uint32]
@@ -299,6 +302,29 @@ class Oracle:
         self.lib.orc_remap_linear_u8(_ptr(img, u8p), img.shape[1], img.shape[0], img.strides[0], _ptr(mx, f32p), _ptr(my, f32p), dw,
                                      _ptr(dst, u8p), dw, dh, dw)
         return dst
+
+    def match_reprojected(self, cam, margin, lowe_ratio, hamm_thr, level_lo, level_hi, use_ratio, use_x_right, lm_active, lm_reproj,
+                          lm_x_right, lm_scale_level, lm_desc, kp, kp_desc, kp_x_right, kp_taken, scale, lm_has_observation=None,
+                          lm_angle=None):
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64)
+        lxr = np.ascontiguousarray(lm_x_right, np.float32)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_desc, np.uint8)
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        kd = np.ascontiguousarray(kp_desc, np.uint8)
+        xr = np.ascontiguousarray(kp_x_right, np.float32)
+        tk = np.ascontiguousarray(kp_taken, np.uint8)
+        scale = np.ascontiguousarray(scale, np.float32)
+        out = np.empty(len(kp), np.int32)
+        n = self.lib.orc_match_reprojected(C.byref(cam), margin, lowe_ratio, hamm_thr, level_lo, level_hi, int(use_ratio), int(use_x_right),
+                                           len(act), _ptr(act, u8p), _ptr(rp, C.POINTER(C.c_double)), _ptr(lxr, f32p), _ptr(lvl, i32p),
+                                           _ptr(ld, u8p),
+                                           None if lm_has_observation is None else _ptr(np.ascontiguousarray(lm_has_observation, np.uint8), u8p),
+                                           None if lm_angle is None else _ptr(np.ascontiguousarray(lm_angle, np.float32), f32p),
+                                           len(kp), kp.ctypes.data, _ptr(kd, u8p), _ptr(xr, f32p), _ptr(tk, u8p), _ptr(scale, f32p),
+                                           _ptr(out, i32p))
+        return out, n
 
     def match_area(self, cam, kp1, desc1, prev_pts, kp2, desc2, margin, lowe_ratio, check_orientation):
         kp1 = np.ascontiguousarray(kp1, KP_DTYPE)

@@ -268,3 +268,34 @@ def test_area(oracle, seed, chk):
     want, nw, pw = oracle.match_area(pyoracle.make_camera(**args), k1b, d1b, prevb, k2, d2, 50, 0.95, chk)
     got, ng, pg = match.area(0.95, chk).match_in_consistent_area(match.make_camera(**args), k1b, d1b, k2, d2, prevb, 50)
     assert np.array_equal(got, want) and ng == nw and np.array_equal(pg, pw) and nw > 20
+
+
+@pytest.mark.parametrize("seed,stereo", [(5, False), (6, True)])
+def test_frame_and_keyframe_and_knobs(oracle, seed, stereo):
+    # match/projection.cc:210-312 (window level-1..level+1, caller's threshold, no ratio, angle check) and every other
+    # combination of the shared loop's knobs
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    args, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs = landmarks_case(oracle, seed, stereo, True)
+    rng = np.random.default_rng(seed)
+    lm_angle = rng.uniform(0, 360, len(active)).astype(np.float32)
+    near = rng.random(len(active)) < 0.7
+    src_angle = np.interp(np.arange(len(active)), np.arange(len(kp)), kp["angle"]).astype(np.float32)
+    lm_angle = np.where(near, src_angle, lm_angle).astype(np.float32)
+    ocam, cam = pyoracle.make_camera(**args), match.make_camera(**args)
+    total = 0
+    for margin, thr in ((10.0, 100), (15.0, 50)):
+        for chk in (True, False):
+            want, nw = oracle.match_reprojected(ocam, margin, 0.0, thr, -1, 1, 0, 0, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf,
+                                                None, lm_angle if chk else None)
+            got, ng = match.projection(0.6, chk).match_frame_and_keyframe(cam, active, reproj, level, ldesc, lm_angle, kp, desc, taken, sf,
+                                                                          margin, thr)
+            assert np.array_equal(got, want) and ng == nw
+            total += nw
+    assert total > 200
+    for lo, hi, use_ratio, use_xr, thr in ((0, 0, 1, 0, 80), (-2, 2, 0, 1, 100), (-1, 0, 1, 1, 30), (0, 1, 1, 1, 256)):
+        prm = match.ReprojMatchParams(8.0, 0.75, thr, lo, hi, use_ratio, use_xr)
+        want, nw = oracle.match_reprojected(ocam, 8.0, 0.75, thr, lo, hi, use_ratio, use_xr, active, reproj, lxr, level, ldesc, kp, desc, xr,
+                                            taken, sf, obs, lm_angle)
+        got, ng = match.match_reprojected(cam, prm, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs, lm_angle)
+        assert np.array_equal(got, want) and ng == nw
