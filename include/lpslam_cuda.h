@@ -278,6 +278,20 @@ int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_reproj_match
                              const float* kp_x_right, const uint8_t* kp_has_landmark, const float* scale_factors,
                              int32_t* kp_match_lm, uint32_t* n_matches);
 
+/* The search loop of match::bow_tree::match_frame_and_keyframe (match/bow_tree.cc:16-126), the matcher of BoW-based
+ * tracking and relocalisation: the caller walks the two BoW feature vectors (the vocabulary library's containers) and
+ * emits, in iteration order, one row per keyframe keypoint that holds a live landmark (bow_tree.cc:45-57) with its
+ * descriptor and the frame keypoints of the same vocabulary node as its candidate list (cand_items[begin .. end)). Every
+ * row takes the free candidate with the smallest distance (strict '<', first wins), accepted when best <= hamm_dist_thr
+ * (HAMMING_DIST_THR_LOW = 50 there) and, with use_ratio, lowe_ratio * second_best >= best; a matched keypoint is not
+ * available to later rows. row_angle != NULL runs the orientation check (bow_tree.cc:91-95,111-117).
+ * kp_match_row[i] = row matched to frame keypoint i, or -1; kp_taken (nullable) marks keypoints occupied beforehand. */
+int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc, const uint32_t* row_cand_begin,
+                            const uint32_t* row_cand_end, const uint32_t* cand_items, uint32_t n_items,
+                            const float* row_angle, uint32_t n_kp, const uint8_t* kp_desc, const float* kp_angle,
+                            const uint8_t* kp_taken, uint32_t hamm_dist_thr, float lowe_ratio, int use_ratio,
+                            int32_t* kp_match_row, uint32_t* n_matches);
+
 /* match::area::match_in_consistent_area (match/area.cc:8-112), the matcher of the monocular initializer
  * (initialize/... via module/initializer.cc): frame-1 keypoints of scale level 0 search frame 2 inside a window of
  * +-margin around prev_matched_pts (n1 x 2 floats, updated in place with the matched frame-2 positions, area.cc:104-108).

@@ -63,6 +63,11 @@ struct ProjArgs {
     // Lowe ratio on / off, stereo x_right gate on / off
     int level_lo, level_hi, use_ratio, use_xr;
     unsigned hamm_thr;
+    // mode 3 = candidate lists instead of the grid (bow_tree.cc:16-110: the frame keypoints of the row's vocabulary node):
+    // row il scans cand_items[cand_begin[il] .. cand_end[il]); the ratio test ignores scale levels
+    const uint32_t* cand_begin;
+    const uint32_t* cand_end;
+    const uint32_t* cand_items;
 };
 
 __device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
@@ -162,6 +167,10 @@ __device__ Projected cell_window(const ProjArgs& a, Projected p);
 __device__ Projected project(const ProjArgs& a, uint32_t il, bool forward, bool backward) {
     Projected p;
     p.ok = false;
+    if (a.mode == 3) {
+        p.ok = a.cand_begin[il] < a.cand_end[il];
+        return p;
+    }
     if (a.mode == 2) {
         if (!a.last_has_lm[il]) return p;  // area.cc:23-26: only keypoints of scale level 0
         p.min_level = 0;                   // area.cc:29-30: get_keypoints_in_cell(x, y, margin, level_1, level_1)
@@ -236,8 +245,18 @@ template <typename F>
 __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const uint32_t* taken_bits, F f) {
     const uint4* dl = reinterpret_cast<const uint4*>(a.last_desc + (size_t)il * 32);
     const uint4 l0 = __ldg(dl), l1 = __ldg(dl + 1);
-    const bool check_level = (0 < p.min_level) || (0 <= p.max_level);
     uint32_t seq = 0;
+    if (a.mode == 3) {
+        for (uint32_t q = a.cand_begin[il]; q < a.cand_end[il]; ++q) {
+            const uint32_t i = a.cand_items[q];
+            ++seq;
+            if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
+            const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
+            f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)));
+        }
+        return;
+    }
+    const bool check_level = (0 < p.min_level) || (0 <= p.max_level);
     for (int cx = p.min_cx; cx <= p.max_cx; ++cx)
         for (int cy = p.min_cy; cy <= p.max_cy; ++cy) {
             const uint32_t c = cx * a.cam.grid_rows + cy;
@@ -443,8 +462,8 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
             const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
             if (a.hamm_thr < best) continue;
             if (a.use_ratio) {
-                const int best_level = a.kp[i1].octave, second_level = i2 >= 0 ? a.kp[i2].octave : -1;
-                if (best_level == second_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) continue;  // projection.cc:69-72
+                const bool same_level = a.mode == 3 || a.kp[i1].octave == (i2 >= 0 ? a.kp[i2].octave : -1);
+                if (same_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) continue;  // projection.cc:69-72, bow_tree.cc:85-88
             }
             if (lane == 0) {
                 a.curr_match_last[i1] = (int32_t)il;
@@ -992,5 +1011,85 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
             prev_matched_pts[2 * i + 1] = kp2_undist[matched_indices_2_in_frm_1[i]].y;
         }
     *n_matches = (uint32_t)num;
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc, const uint32_t* row_cand_begin,
+                                       const uint32_t* row_cand_end, const uint32_t* cand_items, uint32_t n_items,
+                                       const float* row_angle, uint32_t n_kp, const uint8_t* kp_desc, const float* kp_angle,
+                                       const uint8_t* kp_taken, uint32_t hamm_dist_thr, float lowe_ratio, int use_ratio,
+                                       int32_t* kp_match_row, uint32_t* n_matches) {
+    LPS_ARG(n_matches, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n_kp == 0 || (kp_desc && kp_match_row), "null keypoint argument");
+    LPS_ARG(n_rows == 0 || (row_desc && row_cand_begin && row_cand_end), "null row argument");
+    LPS_ARG(n_items == 0 || cand_items, "null candidate list");
+    LPS_ARG(!row_angle || kp_angle, "keypoint angles required for the orientation check");
+    LPS_ARG(n_kp < (1u << 20) && hamm_dist_thr <= 256, "bad sizes / threshold");
+    for (uint32_t i = 0; i < n_kp; ++i) kp_match_row[i] = -1;
+    if (n_kp == 0 || n_rows == 0) return LPSLAM_OK;
+    for (uint32_t r = 0; r < n_rows; ++r)
+        LPS_ARG(row_cand_begin[r] <= row_cand_end[r] && row_cand_end[r] <= n_items, "candidate range out of bounds");
+    for (uint32_t q = 0; q < n_items; ++q) LPS_ARG(cand_items[q] < n_kp, "candidate index out of range");
+
+    ArenaBump ar;
+    const size_t o_rd = ar.take(32 * (size_t)n_rows), o_cb = ar.take(4 * (size_t)n_rows), o_ce = ar.take(4 * (size_t)n_rows);
+    const size_t o_it = ar.take(4 * (size_t)n_items), o_kd = ar.take(32 * (size_t)n_kp), o_tk = ar.take(n_kp);
+    const size_t o_tkey = ar.take(16 * (size_t)n_rows), o_tidx = ar.take(16 * (size_t)n_rows), o_m = ar.take(4 * (size_t)n_kp);
+    const size_t o_ev = ar.take(8 * (size_t)n_rows), o_ne = ar.take(4);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    cudaError_t e = cudaSuccess;
+    uint32_t n_ev = 0;
+    std::vector<int2> events;
+    do {
+#define UP(off, src, bytes) if ((bytes) && (e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
+        UP(o_rd, row_desc, 32 * (size_t)n_rows);
+        UP(o_cb, row_cand_begin, 4 * (size_t)n_rows);
+        UP(o_ce, row_cand_end, 4 * (size_t)n_rows);
+        UP(o_it, cand_items, 4 * (size_t)n_items);
+        UP(o_kd, kp_desc, 32 * (size_t)n_kp);
+        if (kp_taken) UP(o_tk, kp_taken, n_kp);
+#undef UP
+        if (!kp_taken && (e = cudaMemset(dev + o_tk, 0, n_kp)) != cudaSuccess) break;
+        ProjArgs a = {};
+        a.mode = 3;
+        a.n_last = n_rows;
+        a.n_curr = n_kp;
+        a.last_desc = dev + o_rd;
+        a.cand_begin = (const uint32_t*)(dev + o_cb);
+        a.cand_end = (const uint32_t*)(dev + o_ce);
+        a.cand_items = (const uint32_t*)(dev + o_it);
+        a.desc = dev + o_kd;
+        a.curr_taken = dev + o_tk;
+        a.lowe_ratio = lowe_ratio;
+        a.use_ratio = use_ratio;
+        a.hamm_thr = hamm_dist_thr;
+        a.top_key = (uint4*)(dev + o_tkey);
+        a.top_idx = (int4*)(dev + o_tidx);
+        a.curr_match_last = (int32_t*)(dev + o_m);
+        a.events = row_angle ? (int2*)(dev + o_ev) : nullptr;
+        a.n_events = (uint32_t*)(dev + o_ne);
+        k_proj_topk<<<(n_rows + 127) / 128, 128>>>(a);
+        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(kp_match_row, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (row_angle && n_ev) {
+            events.resize(n_ev);
+            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        }
+    } while (false);
+    cudaFree(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_candidates", __FILE__, __LINE__);
+    *n_matches = n_ev;
+    if (row_angle) {  // bow_tree.cc:91-95,111-117
+        std::vector<std::pair<float, int>> deltas;
+        for (const int2& ev : events) deltas.emplace_back(row_angle[ev.x] - kp_angle[ev.y], ev.y);
+        for (int id : angle_invalid_matches(deltas)) {
+            kp_match_row[id] = -1;
+            --*n_matches;
+        }
+    }
     return LPSLAM_OK;
 }

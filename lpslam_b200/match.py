@@ -146,6 +146,56 @@ def match_reprojected(cam, params, lm_active, lm_reproj, lm_x_right, lm_scale_le
     return out, int(n.value)
 
 
+register("lpslam_match_candidates", C.c_int, [C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_void_p, _lib.u32p])
+
+
+class bow_tree:
+    """match::bow_tree (match/bow_tree.h): BoW feature vectors are passed as (node_ids, node_start, items) uint32 arrays, node
+    ids ascending (the iteration order of DBoW2::FeatureVector / fbow::BoWFeatVector)."""
+
+    def __init__(self, lowe_ratio=0.6, check_orientation=True):
+        self.lowe_ratio_, self.check_orientation_ = float(lowe_ratio), bool(check_orientation)
+
+    def match_frame_and_keyframe(self, keyfrm_feat_vec, keyfrm_has_live_lm, keyfrm_descs, keyfrm_angles, frm_feat_vec, frm_descs,
+                                 frm_angles):
+        """match/bow_tree.cc:16-126: returns (frm_match_keyfrm, num_matches); frm_match_keyfrm[i] = keyframe keypoint whose
+        landmark frame keypoint i receives (matched_lms_in_frm.at(i) = keyfrm_lms.at(that)), or -1."""
+        kid, kst, kit = [np.ascontiguousarray(x, np.uint32) for x in keyfrm_feat_vec]
+        fid, fst, fit = [np.ascontiguousarray(x, np.uint32) for x in frm_feat_vec]
+        valid = np.ascontiguousarray(keyfrm_has_live_lm, np.uint8)
+        kd = np.ascontiguousarray(keyfrm_descs, np.uint8)
+        fd = np.ascontiguousarray(frm_descs, np.uint8)
+        # the merge walk of bow_tree.cc:36-109 over the two node lists: one row per keyframe keypoint with a live landmark
+        rows, begin, end = [], [], []
+        a = b = 0
+        while a < len(kid) and b < len(fid):
+            if kid[a] == fid[b]:
+                for ki in kit[kst[a]:kst[a + 1]]:
+                    if valid[ki]:
+                        rows.append(ki)
+                        begin.append(fst[b])
+                        end.append(fst[b + 1])
+                a += 1
+                b += 1
+            elif kid[a] < fid[b]:
+                a += 1
+            else:
+                b += 1
+        rows = np.asarray(rows, np.int64)
+        out = np.full(len(fd), -1, np.int32)
+        n = C.c_uint32(0)
+        rd = np.ascontiguousarray(kd[rows]) if len(rows) else np.zeros((0, 32), np.uint8)
+        rb, re_ = np.asarray(begin, np.uint32), np.asarray(end, np.uint32)
+        ra = np.ascontiguousarray(np.asarray(keyfrm_angles, np.float32)[rows]) if self.check_orientation_ else None
+        fa = np.ascontiguousarray(frm_angles, np.float32) if self.check_orientation_ else None
+        check(lib().lpslam_match_candidates(len(rows), rd.ctypes.data, rb.ctypes.data, re_.ctypes.data, fit.ctypes.data, len(fit),
+                                            _lib.ptr(ra), len(fd), fd.ctypes.data, _lib.ptr(fa), None, HAMMING_DIST_THR_LOW,
+                                            self.lowe_ratio_, 1, out.ctypes.data, C.byref(n)))
+        res = np.where(out >= 0, rows[np.clip(out, 0, max(len(rows) - 1, 0))] if len(rows) else -1, -1).astype(np.int32)
+        return res, int(n.value)
+
+
 register("lpslam_match_area", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                         C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, _lib.u32p])
 

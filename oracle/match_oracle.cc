@@ -355,6 +355,62 @@ int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_
                                  kp_has_observed_lm, scale_factors, kp_match_lm);
 }
 
+// match/bow_tree.cc:16-126 match_frame_and_keyframe with the feature vectors given as node -> index lists (sorted by
+// node id, the iteration order of both vocabulary libraries' containers). kf_valid = keyframe keypoint holds a live landmark.
+int orc_match_bow(uint32_t n_nodes_kf, const uint32_t* kf_node_id, const uint32_t* kf_node_start, const uint32_t* kf_items,
+                  uint32_t n_nodes_f, const uint32_t* f_node_id, const uint32_t* f_node_start, const uint32_t* f_items,
+                  const uint8_t* kf_valid, const uint8_t* kf_desc, const float* kf_angle, uint32_t n_f, const uint8_t* f_desc,
+                  const float* f_angle, float lowe_ratio, int check_orientation, int32_t* f_match_kf) {
+    int num = 0;
+    AngleHistogram hist;
+    std::fill(f_match_kf, f_match_kf + n_f, -1);
+    uint32_t a = 0, b = 0;
+    while (a < n_nodes_kf && b < n_nodes_f) {
+        if (kf_node_id[a] == f_node_id[b]) {
+            for (uint32_t qa = kf_node_start[a]; qa < kf_node_start[a + 1]; ++qa) {
+                const uint32_t ki = kf_items[qa];
+                if (!kf_valid[ki]) continue;
+                const uint8_t* kd = kf_desc + static_cast<size_t>(ki) * 32;
+                unsigned best = MAX_HAMMING_DIST, second = MAX_HAMMING_DIST;
+                int best_f = -1;
+                for (uint32_t qb = f_node_start[b]; qb < f_node_start[b + 1]; ++qb) {
+                    const uint32_t fi = f_items[qb];
+                    if (f_match_kf[fi] >= 0) continue;  // matched_lms_in_frm.at(frm_idx) != nullptr
+                    const unsigned d = hamming_32(kd, f_desc + static_cast<size_t>(fi) * 32);
+                    if (d < best) {
+                        second = best;
+                        best = d;
+                        best_f = static_cast<int>(fi);
+                    }
+                    else if (d < second) {
+                        second = d;
+                    }
+                }
+                if (HAMMING_DIST_THR_LOW < best) continue;
+                if (lowe_ratio * second < static_cast<float>(best)) continue;
+                f_match_kf[best_f] = static_cast<int32_t>(ki);
+                if (check_orientation) hist.append(kf_angle[ki] - f_angle[best_f], best_f);
+                ++num;
+            }
+            ++a;
+            ++b;
+        }
+        else if (kf_node_id[a] < f_node_id[b]) {
+            while (a < n_nodes_kf && kf_node_id[a] < f_node_id[b]) ++a;  // lower_bound
+        }
+        else {
+            while (b < n_nodes_f && f_node_id[b] < kf_node_id[a]) ++b;
+        }
+    }
+    if (check_orientation) {
+        for (int id : hist.invalid()) {
+            f_match_kf[id] = -1;
+            --num;
+        }
+    }
+    return num;
+}
+
 // match/area.cc:8-112 match_in_consistent_area over flat arrays; prev_pts (n1 x 2) is updated in place
 int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
                    const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,

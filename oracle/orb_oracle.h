@@ -125,6 +125,13 @@ int orc_match_reprojected(const orc_camera* cam, float margin, float lowe_ratio,
                           const uint8_t* kp_desc, const float* kp_x_right, const uint8_t* kp_taken, const float* scale_factors,
                           int32_t* kp_match_lm);
 
+/* match/bow_tree.cc:16-126 match_frame_and_keyframe; feature vectors as sorted node ids + CSR index lists.
+ * f_match_kf[i] = keyframe keypoint whose landmark frame keypoint i received, or -1. Returns num_matches. */
+int orc_match_bow(uint32_t n_nodes_kf, const uint32_t* kf_node_id, const uint32_t* kf_node_start, const uint32_t* kf_items,
+                  uint32_t n_nodes_f, const uint32_t* f_node_id, const uint32_t* f_node_start, const uint32_t* f_items,
+                  const uint8_t* kf_valid, const uint8_t* kf_desc, const float* kf_angle, uint32_t n_f, const uint8_t* f_desc,
+                  const float* f_angle, float lowe_ratio, int check_orientation, int32_t* f_match_kf);
+
 /* match/area.cc:8-112 match_in_consistent_area over flat arrays (prev_pts n1 x 2 floats, in / out). Returns num_matches. */
 int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
                    const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,

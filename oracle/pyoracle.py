@@ -121,6 +121,9 @@ class Oracle:
             L.orc_match_reprojected.argtypes = [C.POINTER(_CameraStruct), C.c_float, C.c_float, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int,
                                                 C.c_uint32, u8p, C.POINTER(C.c_double), f32p, i32p, u8p, u8p, f32p,
                                                 C.c_uint32, C.c_void_p, u8p, f32p, u8p, f32p, i32p]
+            u32p = C.POINTER(C.c_uint32)
+            L.orc_match_bow.argtypes = [C.c_uint32, u32p, u32p, u32p, C.c_uint32, u32p, u32p, u32p, u8p, u8p, f32p, C.c_uint32, u8p, f32p,
+                                        C.c_float, C.c_int, i32p]
             L.orc_match_area.argtypes = [C.POINTER(_CameraStruct), C.c_uint32, C.c_void_p, u8p, f32p, C.c_uint32, C.c_void_p, u8p, C.c_int,
                                          C.c_float, C.c_int, i32p]
             L.orc_landmark_descriptor.argtypes = [u8p, C.c_uint32]
@@ -324,6 +327,22 @@ class Oracle:
                                            None if lm_angle is None else _ptr(np.ascontiguousarray(lm_angle, np.float32), f32p),
                                            len(kp), kp.ctypes.data, _ptr(kd, u8p), _ptr(xr, f32p), _ptr(tk, u8p), _ptr(scale, f32p),
                                            _ptr(out, i32p))
+        return out, n
+
+    def match_bow(self, kf_vec, f_vec, kf_valid, kf_desc, kf_angle, f_desc, f_angle, lowe_ratio, check_orientation):
+        """kf_vec / f_vec: (node_ids, node_start, items) uint32 arrays"""
+        u32p = C.POINTER(C.c_uint32)
+        ka = [np.ascontiguousarray(x, np.uint32) for x in kf_vec]
+        fa = [np.ascontiguousarray(x, np.uint32) for x in f_vec]
+        kv = np.ascontiguousarray(kf_valid, np.uint8)
+        kd = np.ascontiguousarray(kf_desc, np.uint8)
+        kang = np.ascontiguousarray(kf_angle, np.float32)
+        fd = np.ascontiguousarray(f_desc, np.uint8)
+        fang = np.ascontiguousarray(f_angle, np.float32)
+        out = np.empty(len(fd), np.int32)
+        n = self.lib.orc_match_bow(len(ka[0]), _ptr(ka[0], u32p), _ptr(ka[1], u32p), _ptr(ka[2], u32p), len(fa[0]), _ptr(fa[0], u32p),
+                                   _ptr(fa[1], u32p), _ptr(fa[2], u32p), _ptr(kv, u8p), _ptr(kd, u8p), _ptr(kang, f32p), len(fd),
+                                   _ptr(fd, u8p), _ptr(fang, f32p), lowe_ratio, int(check_orientation), _ptr(out, i32p))
         return out, n
 
     def match_area(self, cam, kp1, desc1, prev_pts, kp2, desc2, margin, lowe_ratio, check_orientation):

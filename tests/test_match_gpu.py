@@ -299,3 +299,39 @@ def test_frame_and_keyframe_and_knobs(oracle, seed, stereo):
                                             taken, sf, obs, lm_angle)
         got, ng = match.match_reprojected(cam, prm, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs, lm_angle)
         assert np.array_equal(got, want) and ng == nw
+
+
+def bow_vector(rng, n, n_nodes):
+    """random vocabulary-node assignment of n keypoints as (node_ids ascending, node_start, items in ascending keypoint order)"""
+    node = rng.integers(0, n_nodes, n)
+    ids = np.unique(node)
+    items = np.concatenate([np.nonzero(node == v)[0] for v in ids]).astype(np.uint32)
+    start = np.concatenate([[0], np.cumsum([(node == v).sum() for v in ids])]).astype(np.uint32)
+    return (ids.astype(np.uint32), start, items), node
+
+
+@pytest.mark.parametrize("seed,chk", [(1, True), (2, False), (3, True)])
+def test_bow_tree(oracle, seed, chk):
+    # match/bow_tree.cc:16-126: keyframe = frame descriptors with noise, nodes mostly shared so that matches exist, few
+    # nodes so that rows fight for keypoints
+    from lpslam_b200 import match
+    rng = np.random.default_rng(seed)
+    o = oracle.extractor(max_kpts=1000)
+    kp, desc = o.extract(synth_image(480, 640, 70 + seed))
+    n = len(kp)
+    perm = rng.permutation(n)
+    kdesc = desc[perm] ^ np.packbits(rng.random((n, 256)) < 0.04, axis=1, bitorder="little")
+    kang = (kp["angle"][perm] + rng.normal(0, 3.0, n)).astype(np.float32) % 360
+    fvec, fnode = bow_vector(rng, n, 60)
+    knode = np.where(rng.random(n) < 0.85, fnode[perm], rng.integers(0, 80, n))
+    ids = np.unique(knode)
+    kvec = (ids.astype(np.uint32), np.concatenate([[0], np.cumsum([(knode == v).sum() for v in ids])]).astype(np.uint32),
+            np.concatenate([np.nonzero(knode == v)[0] for v in ids]).astype(np.uint32))
+    valid = (rng.random(n) < 0.8).astype(np.uint8)
+    total = 0
+    for ratio in (0.6, 0.75, 0.9):
+        want, nw = oracle.match_bow(kvec, fvec, valid, kdesc, kang, desc, kp["angle"], ratio, chk)
+        got, ng = match.bow_tree(ratio, chk).match_frame_and_keyframe(kvec, valid, kdesc, kang, fvec, desc, kp["angle"])
+        assert np.array_equal(got, want) and ng == nw
+        total += nw
+    assert total > 300
