@@ -110,7 +110,7 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
     size_t o_rec = o_off + 256, o_xr = o_rec + align_up(8 * (size_t)rows, 256), o_dep = o_xr + align_up(4 * (size_t)rows, 256);
     size_t o_corr = o_dep + align_up(4 * (size_t)rows, 256), o_perm = o_corr + align_up(4 * (size_t)rows, 256);
     size_t o_rows = o_perm + align_up(4 * (size_t)rows, 256), total = o_rows + align_up(4 * (size_t)(level_h[0] + 1), 256);
-    LPS_CUDA(cudaMalloc(&dev, total));
+    LPS_CUDA(scratch_alloc((void**)&dev, total));
     cudaStream_t st = nullptr;
     int rc = LPSLAM_OK;
     auto fail = [&](cudaError_t e, const char* what) {
@@ -169,7 +169,7 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
     }
 done:
 #undef TRY
-    cudaFree(dev);
+    scratch_free(dev);
     return rc;
 }
 

@@ -46,6 +46,10 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// per-thread, grow-only device scratch for the short entry points (scratch.cu); scratch_free must follow every scratch_alloc
+cudaError_t scratch_alloc(void** out, size_t bytes);
+void scratch_free(void* p);
+
 // bump planner for one-shot device scratch (offsets aligned to 256 bytes)
 struct ArenaBump {
     size_t off = 0;

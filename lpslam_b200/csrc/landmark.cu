@@ -84,7 +84,7 @@ extern "C" int lpslam_landmark_descriptors(const uint8_t* obs_desc, const uint32
     const size_t o_d = ar.take(32 * (size_t)total), o_o = ar.take(4 * (size_t)(n_landmarks + 1)), o_b = ar.take(4 * (size_t)n_landmarks);
     const size_t o_out = ar.take(32 * (size_t)n_landmarks);
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
     cudaError_t e = cudaSuccess;
     do {
         if (total && (e = cudaMemcpy(dev + o_d, obs_desc, 32 * (size_t)total, cudaMemcpyHostToDevice)) != cudaSuccess) break;
@@ -97,7 +97,7 @@ extern "C" int lpslam_landmark_descriptors(const uint8_t* obs_desc, const uint32
         if ((e = cudaMemcpy(best_idx, dev + o_b, 4 * (size_t)n_landmarks, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if (desc_out && (e = cudaMemcpy(desc_out, dev + o_out, 32 * (size_t)n_landmarks, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
     } while (false);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_landmark_descriptors", __FILE__, __LINE__);
     return LPSLAM_OK;
 }

@@ -216,7 +216,7 @@ int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* d
     uint8_t* dev = nullptr;
     const size_t o_d1 = 0, o_d2 = align_up(32 * (size_t)n1, 256), o_v = o_d2 + align_up(32 * (size_t)n2, 256);
     const size_t o_top = o_v + align_up(n2, 256), o_m = o_top + align_up(16 * (size_t)n2, 256), o_n = o_m + align_up(4 * (size_t)n1, 256);
-    LPS_CUDA(cudaMalloc(&dev, o_n + 256));
+    LPS_CUDA(scratch_alloc((void**)&dev, o_n + 256));
     int rc = LPSLAM_OK;
     cudaError_t e;
     do {
@@ -231,7 +231,7 @@ int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* d
         if ((e = cudaMemcpy(n_matches, dev + o_n, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
     } while (false);
     if (e != cudaSuccess) rc = cuda_fail(e, "lpslam_match_bruteforce", __FILE__, __LINE__);
-    cudaFree(dev);
+    scratch_free(dev);
     if (rc == LPSLAM_OK && check_orientation) {
         // appended in keyframe-row order, as the reference does while it scans (match/robust.cc:293-297)
         std::vector<std::pair<int, int>> by_row;
@@ -253,7 +253,7 @@ int lpslam_hamming_pairs(const uint8_t* a, const uint8_t* b, uint32_t n, uint32_
     if (n == 0) return LPSLAM_OK;
     uint8_t* dev = nullptr;
     const size_t sz = align_up(32 * (size_t)n, 256);
-    LPS_CUDA(cudaMalloc(&dev, 2 * sz + 4 * (size_t)n));
+    LPS_CUDA(scratch_alloc((void**)&dev, 2 * sz + 4 * (size_t)n));
     cudaError_t e;
     do {
         if ((e = cudaMemcpy(dev, a, 32 * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
@@ -262,7 +262,7 @@ int lpslam_hamming_pairs(const uint8_t* a, const uint8_t* b, uint32_t n, uint32_
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         e = cudaMemcpy(dist, dev + 2 * sz, 4 * (size_t)n, cudaMemcpyDeviceToHost);
     } while (false);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_hamming_pairs", __FILE__, __LINE__);
     return LPSLAM_OK;
 }

@@ -5,9 +5,10 @@
 //   k_grid_*        assign_keypoints_to_grid: CSR lists per cell, indices ascending inside a cell (= insertion order)
 //   k_proj_topk     one thread per last-frame landmark: reproject (double, no FMA), walk the cells x-outer / y-inner like
 //                   get_keypoints_in_cell, apply the octave / window / x_right gates and keep the 4 best (distance, visit order)
-//   k_proj_resolve  one warp replays the landmarks in order against the "already holds an observed landmark" bitmap; that
+//   k_lm_resolve    one warp replays the landmarks in order against the "already holds an observed landmark" bitmap; that
 //                   bitmap changes as matches are made (projection.cc:163-165,189), which is what makes the loop sequential.
-//                   A landmark whose 4 candidates are all taken is rescanned exactly.
+//                   32 rows are decided at a time and committed up to the first conflict; a landmark whose 4 candidates
+//                   do not settle its decision is rescanned exactly.
 #include "common.cuh"
 
 #include <algorithm>
@@ -68,6 +69,7 @@ struct ProjArgs {
     const uint32_t* cand_begin;
     const uint32_t* cand_end;
     const uint32_t* cand_items;
+    int claim_in_smem;  // k_lm_resolve: a per-keypoint claim table follows the bitmap in shared memory
 };
 
 __device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
@@ -252,7 +254,7 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
             ++seq;
             if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
             const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
-            f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)));
+            f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)), 0);
         }
         return;
     }
@@ -277,7 +279,7 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
                     }
                 }
                 const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
-                f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)));
+                f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)), k.octave);
             }
         }
 }
@@ -302,11 +304,11 @@ __global__ void k_proj_topk(ProjArgs a) {
     uint32_t key[K] = {EMPTY, EMPTY, EMPTY, EMPTY};
     int idx[K] = {-1, -1, -1, -1};
     if (p.ok) {
-        visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d) {
+        visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
             const uint32_t kk = (d << 20) | seq;
             if (kk < key[3]) {
                 key[3] = kk;
-                idx[3] = (int)i;
+                idx[3] = (int)(i | ((uint32_t)(oct & 0x7F) << 24));  // octave rides along: the resolve loop never touches a.kp
 #pragma unroll
                 for (int q = 3; q > 0; --q)
                     if (key[q] < key[q - 1]) {
@@ -320,79 +322,15 @@ __global__ void k_proj_topk(ProjArgs a) {
     a.top_idx[il] = make_int4(idx[0], idx[1], idx[2], idx[3]);
 }
 
-__global__ void __launch_bounds__(32) k_proj_resolve(ProjArgs a) {
-    extern __shared__ uint32_t s_taken[];
-    const int lane = threadIdx.x;
-    const uint32_t words = (a.n_curr + 31) / 32;
-    for (uint32_t w = lane; w < words; w += 32) {
-        uint32_t bits = 0;
-        for (uint32_t b = 0; b < 32 && w * 32 + b < a.n_curr; ++b) bits |= (a.curr_taken[w * 32 + b] ? 1u : 0u) << b;
-        s_taken[w] = bits;
-    }
-    for (uint32_t i = lane; i < a.n_curr; i += 32) a.curr_match_last[i] = -1;
-    __syncwarp();
-    bool fw, bw;
-    motion_flags(a, fw, bw);
-    uint32_t num = 0;
-    for (uint32_t base = 0; base < a.n_last; base += 32) {
-        const uint32_t mine = base + lane;
-        const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
-        const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
-        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_HIGH);
-        while (todo) {
-            const int j = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const uint32_t il = base + j;
-            const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
-                                   __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
-            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j), __shfl_sync(0xFFFFFFFFu, mi.y, j),
-                               __shfl_sync(0xFFFFFFFFu, mi.z, j), __shfl_sync(0xFFFFFFFFu, mi.w, j)};
-            uint32_t best = EMPTY;
-            int best_i = -1;
-#pragma unroll
-            for (int q = K - 1; q >= 0; --q) {
-                if (k[q] == EMPTY) continue;
-                if (!((s_taken[ix[q] >> 5] >> (ix[q] & 31)) & 1u)) {
-                    best = k[q];
-                    best_i = ix[q];
-                }
-            }
-            if (best_i < 0 && k[K - 1] != EMPTY) {
-                // all four taken and the list may be longer: exact rescan in reference order by lane 0
-                uint32_t b = EMPTY;
-                int bi = -1;
-                if (lane == 0) {
-                    const Projected p = project(a, il, fw, bw);
-                    visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d) {
-                        const uint32_t kk = (d << 20) | seq;
-                        if (kk < b) {
-                            b = kk;
-                            bi = (int)i;
-                        }
-                    });
-                }
-                best = __shfl_sync(0xFFFFFFFFu, b, 0);
-                best_i = __shfl_sync(0xFFFFFFFFu, bi, 0);
-            }
-            if (best_i < 0) continue;
-            if (HAMMING_DIST_THR_HIGH < (best >> 20)) continue;
-            if (lane == 0) {
-                a.curr_match_last[best_i] = (int32_t)il;
-                // projection.cc:163-165 re-tests has_observation() of the landmark the keypoint holds now
-                const bool blocks = a.last_obs ? a.last_obs[il] != 0 : true;
-                if (blocks) s_taken[best_i >> 5] |= 1u << (best_i & 31);
-                a.events[num] = make_int2((int)il, best_i);
-            }
-            ++num;
-            __syncwarp();
-        }
-    }
-    if (lane == 0) *a.n_events = num;
-}
-
-// match_frame_and_landmarks (projection.cc:31-79): like k_proj_resolve, but the decision needs the best AND the second
-// best candidate that is still free (Lowe ratio, applied only when both sit on the same scale level). In a list ordered by
-// (distance, visit order) those are the first two free entries (strict '<' updates, projection.cc:55-66).
+// Ordered resolve for the reprojection / candidate-list matchers (projection.cc:31-79, :145-190, :264-296,
+// bow_tree.cc:58-97). The reference loop is sequential because a matched keypoint is no longer available to later rows.
+// One warp replays it 32 rows at a time: every lane decides ITS row against the current "taken" bitmap (first and second
+// free entry of the row's four kept candidates, in (distance, visit order) = the strict '<' updates of the reference),
+// then the lanes are committed in row order up to the first lane whose candidates contain a keypoint that an earlier
+// lane of the batch just took; that lane and the ones behind it are decided again. Rows whose four kept candidates do
+// not settle the decision (too few free ones and the list was longer) are rescanned exactly by one lane.
+// A single warp running one row per iteration spent ~600 cycles per row on dependent shuffles and shared-memory reads;
+// the batch form needs a few hundred instructions per 32 rows when no conflict occurs.
 __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
     extern __shared__ uint32_t s_taken[];
     const int lane = threadIdx.x;
@@ -402,76 +340,123 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
         for (uint32_t b = 0; b < 32 && w * 32 + b < a.n_curr; ++b) bits |= (a.curr_taken[w * 32 + b] ? 1u : 0u) << b;
         s_taken[w] = bits;
     }
-    for (uint32_t i = lane; i < a.n_curr; i += 32) a.curr_match_last[i] = -1;
+    // optional claim table behind the bitmap (the launcher provides it while it fits: n_curr words)
+    uint32_t* s_claim = a.claim_in_smem ? s_taken + words : nullptr;
+    for (uint32_t i = lane; i < a.n_curr; i += 32) {
+        a.curr_match_last[i] = -1;
+        if (s_claim) s_claim[i] = 0xFFFFFFFFu;
+    }
     __syncwarp();
+    bool fw = false, bw = false;
+    if (a.mode == 0) motion_flags(a, fw, bw);
+    const bool need_second = a.use_ratio != 0;
     uint32_t num = 0;
     for (uint32_t base = 0; base < a.n_last; base += 32) {
-        const uint32_t mine = base + lane;
-        const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
-        const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
-        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= a.hamm_thr);
-        while (todo) {
-            const int j = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const uint32_t il = base + j;
-            const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
-                                   __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
-            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j), __shfl_sync(0xFFFFFFFFu, mi.y, j),
-                               __shfl_sync(0xFFFFFFFFu, mi.z, j), __shfl_sync(0xFFFFFFFFu, mi.w, j)};
+        const uint32_t il = base + lane;
+        const uint4 mk = il < a.n_last ? a.top_key[il] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const int4 mi = il < a.n_last ? a.top_idx[il] : make_int4(-1, -1, -1, -1);
+        const bool blocks = (a.last_obs && il < a.n_last) ? a.last_obs[il] != 0 : true;  // has_observation() of the row's landmark
+        const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
+        const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
+        uint32_t pending = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= a.hamm_thr);
+        while (pending) {
+            const bool mine = (pending >> lane) & 1u;
+            // ---- decide this lane's row against the current bitmap ----
             uint32_t b1 = EMPTY, b2 = EMPTY;
-            int i1 = -1, i2 = -1;
+            int i1 = -1, i2 = -1, o1 = -1, o2 = -1;
+            if (mine) {
 #pragma unroll
-            for (int q = 0; q < K; ++q) {
-                if (k[q] == EMPTY) continue;
-                if ((s_taken[ix[q] >> 5] >> (ix[q] & 31)) & 1u) continue;
-                if (i1 < 0) {
-                    b1 = k[q];
-                    i1 = ix[q];
-                }
-                else if (i2 < 0) {
-                    b2 = k[q];
-                    i2 = ix[q];
+                for (int q = 0; q < K; ++q) {
+                    if (k[q] == EMPTY) continue;
+                    const int ixq = raw[q] & 0x00FFFFFF;
+                    if ((s_taken[ixq >> 5] >> (ixq & 31)) & 1u) continue;
+                    if (i1 < 0) {
+                        b1 = k[q];
+                        i1 = ixq;
+                        o1 = raw[q] >> 24;
+                    }
+                    else if (i2 < 0) {
+                        b2 = k[q];
+                        i2 = ixq;
+                        o2 = raw[q] >> 24;
+                    }
                 }
             }
-            if ((a.use_ratio ? i2 < 0 : i1 < 0) && k[K - 1] != EMPTY) {
-                // too few free entries among the four kept and the list may be longer: exact rescan by lane 0
-                uint32_t r1 = EMPTY, r2 = EMPTY;
-                int ri1 = -1, ri2 = -1;
-                if (lane == 0) {
-                    const Projected p = project(a, il, false, false);
-                    visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d) {
+            const bool rescan = mine && (need_second ? i2 < 0 : i1 < 0) && k[K - 1] != EMPTY;
+            const int first = __ffs(pending) - 1;
+            if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first)) {
+                // the first pending row needs the exact list: its lane walks it in reference order, alone
+                if (lane == first) {
+                    b1 = b2 = EMPTY;
+                    i1 = i2 = o1 = o2 = -1;
+                    const Projected p = project(a, il, fw, bw);
+                    visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
                         const uint32_t kk = (d << 20) | seq;
-                        if (kk < r1) {
-                            r2 = r1;
-                            ri2 = ri1;
-                            r1 = kk;
-                            ri1 = (int)i;
+                        if (kk < b1) {
+                            b2 = b1;
+                            i2 = i1;
+                            o2 = o1;
+                            b1 = kk;
+                            i1 = (int)i;
+                            o1 = oct;
                         }
-                        else if (kk < r2) {
-                            r2 = kk;
-                            ri2 = (int)i;
+                        else if (kk < b2) {
+                            b2 = kk;
+                            i2 = (int)i;
+                            o2 = oct;
                         }
                     });
                 }
-                b1 = __shfl_sync(0xFFFFFFFFu, r1, 0);
-                i1 = __shfl_sync(0xFFFFFFFFu, ri1, 0);
-                b2 = __shfl_sync(0xFFFFFFFFu, r2, 0);
-                i2 = __shfl_sync(0xFFFFFFFFu, ri2, 0);
             }
-            if (i1 < 0) continue;
-            const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
-            if (a.hamm_thr < best) continue;
-            if (a.use_ratio) {
-                const bool same_level = a.mode == 3 || a.kp[i1].octave == (i2 >= 0 ? a.kp[i2].octave : -1);
-                if (same_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) continue;  // projection.cc:69-72, bow_tree.cc:85-88
+            // ---- accept? (projection.cc:68-79 / :184-190 / :287-296, bow_tree.cc:80-97) ----
+            bool accept = mine && i1 >= 0 && (lane == first || !rescan);
+            if (accept) {
+                const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
+                if (a.hamm_thr < best) accept = false;
+                else if (a.use_ratio) {
+                    const bool same_level = a.mode == 3 || o1 == (i2 >= 0 ? o2 : -1);
+                    if (same_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) accept = false;
+                }
             }
-            if (lane == 0) {
+            // ---- a lane waits when it is undecided, or when an earlier pending lane accepts one of its four candidates.
+            // Entries behind the ones a lane used cannot change its first / second free entry, so the kept four are all
+            // that matters for a lane that was decided from them; an undecided lane is only ever resolved as `first`.
+            bool wait = mine && rescan && lane != first;
+            if (s_claim) {
+                // claim table in shared memory: the lowest lane that accepts a keypoint in this round
+                if (mine && accept) atomicMin(&s_claim[i1], (uint32_t)lane);
+                __syncwarp();
+                if (mine) {
+#pragma unroll
+                    for (int q = 0; q < K; ++q)
+                        if (k[q] != EMPTY && s_claim[raw[q] & 0x00FFFFFF] < (uint32_t)lane) wait = true;
+                }
+                __syncwarp();
+                if (mine && accept) s_claim[i1] = 0xFFFFFFFFu;
+            }
+            else {
+                for (uint32_t mm = pending; mm; mm &= mm - 1) {
+                    const int M = __ffs(mm) - 1;
+                    const int accM = __shfl_sync(0xFFFFFFFFu, (int)accept, M);
+                    const int iM = __shfl_sync(0xFFFFFFFFu, i1, M);
+                    if (mine && lane > M && accM) {
+#pragma unroll
+                        for (int q = 0; q < K; ++q)
+                            if (k[q] != EMPTY && (raw[q] & 0x00FFFFFF) == iM) wait = true;
+                    }
+                }
+            }
+            const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, wait) & pending;
+            const uint32_t commit = waiting ? (pending & ((1u << (__ffs(waiting) - 1)) - 1u)) : pending;  // rows before the first waiter
+            const bool go = (commit >> lane) & 1u;
+            const uint32_t acc_mask = __ballot_sync(0xFFFFFFFFu, go && accept);
+            if (go && accept) {
                 a.curr_match_last[i1] = (int32_t)il;
-                const bool blocks = a.last_obs ? a.last_obs[il] != 0 : true;  // projection.cc:41-43 re-tests has_observation()
-                if (blocks) s_taken[i1 >> 5] |= 1u << (i1 & 31);
-                if (a.events) a.events[num] = make_int2((int)il, i1);
+                if (blocks) atomicOr(&s_taken[i1 >> 5], 1u << (i1 & 31));
+                if (a.events) a.events[num + __popc(acc_mask & ((1u << lane) - 1u))] = make_int2((int)il, i1);
             }
-            ++num;
+            num += __popc(acc_mask);
+            pending &= ~commit;
             __syncwarp();
         }
     }
@@ -538,11 +523,13 @@ __global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lps
 // keypoint over, which deletes the earlier match. s_dist = matched_dists_in_frm_2.
 __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
     extern __shared__ uint32_t s_raw[];
-    uint16_t* s_dist = reinterpret_cast<uint16_t*>(s_raw);
+    // [owner int32 x n2 | dist uint16 x n2]: matched_indices_1_in_frm_2 and matched_dists_in_frm_2 stay in shared memory
+    int32_t* s_owner = reinterpret_cast<int32_t*>(s_raw);
+    uint16_t* s_dist = reinterpret_cast<uint16_t*>(s_raw + a.n_curr);
     const int lane = threadIdx.x;
     for (uint32_t i = lane; i < a.n_curr; i += 32) {
         s_dist[i] = (uint16_t)MAX_HAMMING_DIST;
-        a.match_1_of_2[i] = -1;
+        s_owner[i] = -1;
     }
     for (uint32_t i = lane; i < a.n_last; i += 32) a.match_2_of_1[i] = -1;
     __syncwarp();
@@ -553,6 +540,7 @@ __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
         const uint32_t mine = base + lane;
         const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
         const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
+        const int my_obs = (a.last_obs && mine < a.n_last) ? a.last_obs[mine] : 1;  // has_observation() of the row's landmark
         uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_LOW);
         while (todo) {
             const int j = __ffs(todo) - 1;
@@ -560,8 +548,8 @@ __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
             const uint32_t il = base + j;
             const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
                                    __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
-            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j), __shfl_sync(0xFFFFFFFFu, mi.y, j),
-                               __shfl_sync(0xFFFFFFFFu, mi.z, j), __shfl_sync(0xFFFFFFFFu, mi.w, j)};
+            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j) & 0x00FFFFFF, __shfl_sync(0xFFFFFFFFu, mi.y, j) & 0x00FFFFFF,
+                               __shfl_sync(0xFFFFFFFFu, mi.z, j) & 0x00FFFFFF, __shfl_sync(0xFFFFFFFFu, mi.w, j) & 0x00FFFFFF};
             uint32_t b1 = EMPTY, b2 = EMPTY;
             int i1 = -1;
             bool have2 = false;
@@ -584,7 +572,7 @@ __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
                 int ri1 = -1;
                 if (lane == 0) {
                     const Projected p = project(a, il, false, false);
-                    visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d) {
+                    visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
                         if (s_dist[i] <= d) return;
                         const uint32_t kk = (d << 20) | seq;
                         if (kk < r1) {
@@ -606,13 +594,13 @@ __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
             if (HAMMING_DIST_THR_LOW < best) continue;
             if (__fmul_rn((float)second, a.lowe_ratio) < (float)best) continue;  // area.cc:67-69
             if (lane == 0) {
-                const int prev = a.match_1_of_2[i1];  // area.cc:76-80: the earlier owner of the keypoint loses its match
+                const int prev = s_owner[i1];  // area.cc:76-80: the earlier owner of the keypoint loses its match
                 if (0 <= prev) {
                     a.match_2_of_1[prev] = -1;
                     --num;
                 }
                 a.match_2_of_1[il] = i1;
-                a.match_1_of_2[i1] = (int32_t)il;
+                s_owner[i1] = (int32_t)il;
                 s_dist[i1] = (uint16_t)best;
                 ++num;
                 a.events[n_ev] = make_int2((int)il, i1);
@@ -662,7 +650,7 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
     const size_t o_tidx = ar.take(16 * (size_t)n_last), o_m = ar.take(4 * (size_t)n_curr), o_ev = ar.take(8 * (size_t)n_last);
     const size_t o_ne = ar.take(4);
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
     int rc = LPSLAM_OK;
     cudaError_t e = cudaSuccess;
     std::vector<int2> events;
@@ -716,7 +704,10 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
         k_grid_fill<<<(n_curr + 255) / 256, 256>>>(a);
         k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
         k_proj_topk<<<(n_last + 127) / 128, 128>>>(a);
-        k_proj_resolve<<<1, 32, ((n_curr + 31) / 32) * 4>>>(a);
+        a.hamm_thr = HAMMING_DIST_THR_HIGH;
+        a.use_ratio = 0;
+        a.claim_in_smem = n_curr <= 10000;
+        k_lm_resolve<<<1, 32, ((n_curr + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_curr : 0)>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(curr_match_last, dev + o_m, 4 * (size_t)n_curr, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
@@ -726,7 +717,7 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
         }
     } while (false);
     if (e != cudaSuccess) rc = cuda_fail(e, "lpslam_match_projection", __FILE__, __LINE__);
-    cudaFree(dev);
+    scratch_free(dev);
     if (rc) return rc;
     *n_matches = n_ev;
     if (check_orientation) {
@@ -777,7 +768,7 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
     const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_m = ar.take(4 * (size_t)n_kp), o_ne = ar.take(4), o_ev = ar.take(8 * (size_t)n_lm);
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
     std::vector<int2> events;
@@ -833,7 +824,8 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
         k_grid_fill<<<(n_kp + 255) / 256, 256>>>(a);
         k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
         k_proj_topk<<<(n_lm + 127) / 128, 128>>>(a);
-        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4>>>(a);
+        a.claim_in_smem = n_kp <= 10000;
+        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_kp : 0)>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(kp_match_lm, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
@@ -842,7 +834,7 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
             if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         }
     } while (false);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_reprojected", __FILE__, __LINE__);
     *n_matches = n_ev;
     if (lm_angle) {  // angle_checker over (row angle - keypoint angle, keypoint), projection.cc:297-311
@@ -885,7 +877,7 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
     const size_t o_b = ar.take(24 * (size_t)n), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n);
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
     cudaError_t e = cudaSuccess;
     do {
         if ((e = cudaMemcpy(dev + o_in, keypts, sizeof(lpslam_keypoint) * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
@@ -911,7 +903,7 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
         if (cell_start[ncell] > 0)
             if ((e = cudaMemcpy(cell_items, dev + o_ci, 4 * (size_t)cell_start[ncell], cudaMemcpyDeviceToHost)) != cudaSuccess) break;
     } while (false);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_frame_postprocess", __FILE__, __LINE__);
     *n_in_grid = cell_start[ncell];
     return LPSLAM_OK;
@@ -926,7 +918,7 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
     LPS_ARG(n1 == 0 || (kp1_undist && desc1 && prev_matched_pts && matched_indices_2_in_frm_1), "null frame-1 argument");
     LPS_ARG(n2 == 0 || (kp2_undist && desc2), "null frame-2 argument");
     LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1, "bad camera grid");
-    LPS_ARG(n2 < (1u << 20) && n2 <= 40000, "too many frame-2 keypoints");
+    LPS_ARG(n2 <= 8000, "too many frame-2 keypoints (the per-keypoint state lives in 48 KB of shared memory)");
     for (uint32_t i = 0; i < n1; ++i) matched_indices_2_in_frm_1[i] = -1;
     if (n1 == 0 || n2 == 0) return LPSLAM_OK;
     std::vector<uint8_t> use(n1);
@@ -941,7 +933,7 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
     const size_t o_ci = ar.take(4 * (size_t)n2), o_tkey = ar.take(16 * (size_t)n1), o_tidx = ar.take(16 * (size_t)n1);
     const size_t o_m21 = ar.take(4 * (size_t)n1), o_m12 = ar.take(4 * (size_t)n2), o_ev = ar.take(8 * (size_t)n1), o_ne = ar.take(8);
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
     cudaError_t e = cudaSuccess;
     std::vector<int2> events;
     uint32_t ne[2] = {0, 0};
@@ -983,7 +975,7 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
         k_grid_fill<<<(n2 + 255) / 256, 256>>>(a);
         k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
         k_proj_topk<<<(n1 + 127) / 128, 128>>>(a);
-        k_area_resolve<<<1, 32, ((n2 + 1) / 2) * 4 + 4>>>(a);
+        k_area_resolve<<<1, 32, (size_t)n2 * 4 + ((n2 + 1) / 2) * 4 + 4>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(matched_indices_2_in_frm_1, dev + o_m21, 4 * (size_t)n1, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(ne, dev + o_ne, 8, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
@@ -992,7 +984,7 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
             if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)ne[0], cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         }
     } while (false);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_area", __FILE__, __LINE__);
     int num = (int)ne[1];
     if (check_orientation) {  // area.cc:87-101: every accepted row entered the histogram, also rows that lost their match later
@@ -1038,7 +1030,7 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
     const size_t o_tkey = ar.take(16 * (size_t)n_rows), o_tidx = ar.take(16 * (size_t)n_rows), o_m = ar.take(4 * (size_t)n_kp);
     const size_t o_ev = ar.take(8 * (size_t)n_rows), o_ne = ar.take(4);
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, ar.off));
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
     std::vector<int2> events;
@@ -1071,7 +1063,8 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
         a.events = row_angle ? (int2*)(dev + o_ev) : nullptr;
         a.n_events = (uint32_t*)(dev + o_ne);
         k_proj_topk<<<(n_rows + 127) / 128, 128>>>(a);
-        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4>>>(a);
+        a.claim_in_smem = n_kp <= 10000;
+        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_kp : 0)>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(kp_match_row, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
@@ -1080,7 +1073,7 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
             if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         }
     } while (false);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_candidates", __FILE__, __LINE__);
     *n_matches = n_ev;
     if (row_angle) {  // bow_tree.cc:91-95,111-117

@@ -303,7 +303,7 @@ int lpslam_remap_linear_dev(const uint8_t* src_dev, int src_width, int src_heigh
 namespace {
 struct DevBuf {
     uint8_t* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
+    ~DevBuf() { scratch_free(p); }
 };
 }
 
@@ -312,7 +312,7 @@ int lpslam_gray(const uint8_t* src, int width, int height, size_t pitch, int cha
     LPS_ARG(pitch >= (size_t)width * channels && dst_pitch >= (size_t)width, "bad pitch");
     const size_t sp = align_up((size_t)width * channels, 16), dp = align_up((size_t)width, 16);
     DevBuf b;
-    LPS_CUDA(cudaMalloc(&b.p, (sp + dp) * height));
+    LPS_CUDA(scratch_alloc((void**)&b.p, (sp + dp) * height));
     LPS_CUDA(cudaMemcpy2D(b.p, sp, src, pitch, (size_t)width * channels, height, cudaMemcpyHostToDevice));
     int rc = lpslam_gray_dev(b.p, width, height, sp, sp * height, channels, order, 1, b.p + sp * height, dp, dp * height, nullptr);
     if (rc) return rc;
@@ -326,7 +326,7 @@ int lpslam_imadjust(const uint8_t* src, int width, int height, size_t pitch, int
     const size_t sp = align_up((size_t)width, 16);
     const size_t scratch = align_up(lpslam_imadjust_scratch_bytes(1), 16);
     DevBuf b;
-    LPS_CUDA(cudaMalloc(&b.p, scratch + 2 * sp * height));
+    LPS_CUDA(scratch_alloc((void**)&b.p, scratch + 2 * sp * height));
     uint8_t* s = b.p + scratch;
     uint8_t* d = s + sp * height;
     LPS_CUDA(cudaMemcpy2D(s, sp, src, pitch, width, height, cudaMemcpyHostToDevice));
@@ -345,7 +345,7 @@ int lpslam_remap_linear(const uint8_t* src, int src_width, int src_height, size_
     const size_t sp = align_up((size_t)src_width, 16), dp = align_up((size_t)dst_width, 16), mp = align_up((size_t)dst_width, 4);
     DevBuf b;
     const size_t o_d = sp * src_height, o_mx = align_up(o_d + dp * dst_height, 16), o_my = o_mx + 4 * mp * dst_height;
-    LPS_CUDA(cudaMalloc(&b.p, o_my + 4 * mp * dst_height));
+    LPS_CUDA(scratch_alloc((void**)&b.p, o_my + 4 * mp * dst_height));
     LPS_CUDA(cudaMemcpy2D(b.p, sp, src, src_pitch, src_width, src_height, cudaMemcpyHostToDevice));
     LPS_CUDA(cudaMemcpy2D(b.p + o_mx, 4 * mp, map_x, 4 * map_pitch, 4 * (size_t)dst_width, dst_height, cudaMemcpyHostToDevice));
     LPS_CUDA(cudaMemcpy2D(b.p + o_my, 4 * mp, map_y, 4 * map_pitch, 4 * (size_t)dst_width, dst_height, cudaMemcpyHostToDevice));
