@@ -6,8 +6,9 @@
 // and claims its best. The claim makes the loop order-dependent, so the work is split:
 //   k_bf_topk     all rows in parallel: the 4 smallest keys (distance << 16 | index) of every row ignoring claims.
 //                 In key order, "best / second among unclaimed" is simply the first two unclaimed keys.
-//   k_bf_resolve  one warp replays the rows in order against a shared-memory claim bitmap. A row whose top-4 list runs
-//                 out of unclaimed entries before the decision is certain is rescanned exactly by the warp.
+//   k_bf_resolve  one warp replays the rows in order against a shared-memory claim bitmap, 32 rows per round (commit up to the
+//                 first conflict). A row whose top-4 list runs out of unclaimed entries before the decision is certain is
+//                 rescanned exactly by the warp.
 #include "common.cuh"
 
 #include <algorithm>
@@ -72,39 +73,42 @@ __global__ void __launch_bounds__(256) k_bf_topk(const uint8_t* __restrict__ des
     if (lane == 0) topk[row] = make_uint4(out[0], out[1], out[2], out[3]);
 }
 
-// one warp, rows in reference order
+// One warp, rows in reference order, 32 rows per round: every lane decides its own row from its four kept keys against the
+// claim bitmap; rows are committed in order up to the first one whose kept keys contain a keypoint that an earlier row of
+// the round just claimed; that row and the ones behind it are decided again. A row whose four keys do not settle the
+// decision is rescanned exactly by the whole warp when it is the first pending row.
+// s_first (optional, n1 words behind the bitmap): lowest lane claiming a keypoint in the current round.
 __global__ void __launch_bounds__(32) k_bf_resolve(const uint8_t* __restrict__ desc_1, uint32_t n1, const uint8_t* __restrict__ desc_2,
-                                                   uint32_t n2, const uint4* __restrict__ topk, float lowe_ratio,
+                                                   uint32_t n2, const uint4* __restrict__ topk, float lowe_ratio, int first_in_smem,
                                                    int32_t* __restrict__ match_2_in_1, uint32_t* __restrict__ n_matches) {
     extern __shared__ uint32_t s_claim[];  // bitmap over frame keypoints
     const int lane = threadIdx.x;
     const uint32_t words = (n1 + 31) / 32;
+    uint32_t* s_first = first_in_smem ? s_claim + words : nullptr;
     for (uint32_t i = lane; i < words; i += 32) s_claim[i] = 0;
-    for (uint32_t i = lane; i < n1; i += 32) match_2_in_1[i] = -1;
+    for (uint32_t i = lane; i < n1; i += 32) {
+        match_2_in_1[i] = -1;
+        if (s_first) s_first[i] = 0xFFFFFFFFu;
+    }
     __syncwarp();
     uint32_t num = 0;
     for (uint32_t base = 0; base < n2; base += 32) {
-        const uint32_t mine = base + lane;
-        const uint4 mk = mine < n2 ? topk[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
-        const uint32_t active = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 16) <= HAMMING_DIST_THR_LOW);
-        uint32_t todo = active;
-        while (todo) {  // rows whose unconditional best is already > 50 can never match and claim nothing
-            const int j = __ffs(todo) - 1;
-            todo &= todo - 1;
-            uint32_t k[K];
-            k[0] = __shfl_sync(0xFFFFFFFFu, mk.x, j);
-            k[1] = __shfl_sync(0xFFFFFFFFu, mk.y, j);
-            k[2] = __shfl_sync(0xFFFFFFFFu, mk.z, j);
-            k[3] = __shfl_sync(0xFFFFFFFFu, mk.w, j);
-            // first two unclaimed keys of the list (every lane computes the same thing)
+        const uint32_t row = base + lane;
+        const uint4 mk = row < n2 ? topk[row] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
+        // rows whose unconditional best is already > 50 can never match and claim nothing
+        uint32_t pending = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 16) <= HAMMING_DIST_THR_LOW);
+        while (pending) {
+            const bool mine = (pending >> lane) & 1u;
+            // first two unclaimed keys of the list
             uint32_t best = EMPTY, second = EMPTY;
             int seen = 0;
+            if (mine) {
 #pragma unroll
-            for (int q = 0; q < K; ++q) {
-                if (k[q] == EMPTY) continue;
-                const uint32_t i1 = k[q] & 0xFFFFu;
-                const bool claimed = (s_claim[i1 >> 5] >> (i1 & 31)) & 1u;
-                if (!claimed) {
+                for (int q = 0; q < K; ++q) {
+                    if (k[q] == EMPTY) continue;
+                    const uint32_t i1 = k[q] & 0xFFFFu;
+                    if ((s_claim[i1 >> 5] >> (i1 & 31)) & 1u) continue;
                     if (seen == 0) best = k[q];
                     else if (seen == 1) second = k[q];
                     ++seen;
@@ -112,7 +116,7 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const uint8_t* __restrict__ d
             }
             const bool list_complete = (k[K - 1] == EMPTY);  // fewer than K frame keypoints exist: nothing beyond the list
             bool exact = (seen >= 2) || list_complete;
-            if (!exact && seen == 1) {
+            if (mine && !exact && seen == 1) {
                 // second >= the list's last distance; if the ratio test passes with that bound it passes with the truth
                 const unsigned lb = k[K - 1] >> 16, bd = best >> 16;
                 if (bd > HAMMING_DIST_THR_LOW) exact = true;  // rejected whatever the second is
@@ -121,10 +125,11 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const uint8_t* __restrict__ d
                     second = lb << 16;
                 }
             }
-            if (!exact) {
-                // exact rescan of this row over the unclaimed frame keypoints (reference inner loop, match/robust.cc:252-274)
-                const uint32_t row = base + j;
-                const uint4* d2 = reinterpret_cast<const uint4*>(desc_2 + (size_t)row * 32);
+            const bool rescan = mine && !exact;
+            const int first = __ffs(pending) - 1;
+            if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first)) {
+                // exact rescan of the first pending row over the unclaimed frame keypoints (match/robust.cc:252-274), whole warp
+                const uint4* d2 = reinterpret_cast<const uint4*>(desc_2 + (size_t)(base + first) * 32);
                 const uint4 a0 = __ldg(d2), a1 = __ldg(d2 + 1);
                 uint32_t b = EMPTY, s = EMPTY;
                 for (uint32_t i = lane; i < n1; i += 32) {
@@ -142,20 +147,52 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const uint8_t* __restrict__ d
                     b = nb;
                     s = ns;
                 }
-                best = b;
-                second = s;
+                if (lane == first) {
+                    best = b;
+                    second = s;
+                }
             }
-            if (best == EMPTY) continue;  // best_idx_1 < 0
-            const unsigned bd = best >> 16;
-            const unsigned sd = second == EMPTY ? MAX_HAMMING_DIST : (second >> 16);
-            if (HAMMING_DIST_THR_LOW < bd) continue;
-            if (__fmul_rn(lowe_ratio, (float)sd) < (float)bd) continue;  // match/robust.cc:285
+            bool accept = mine && best != EMPTY && (lane == first || !rescan);
+            if (accept) {
+                const unsigned bd = best >> 16;
+                const unsigned sd = second == EMPTY ? MAX_HAMMING_DIST : (second >> 16);
+                if (HAMMING_DIST_THR_LOW < bd) accept = false;
+                else if (__fmul_rn(lowe_ratio, (float)sd) < (float)bd) accept = false;  // match/robust.cc:285
+            }
             const uint32_t i1 = best & 0xFFFFu;
-            if (lane == 0) {
-                s_claim[i1 >> 5] |= 1u << (i1 & 31);
-                match_2_in_1[i1] = (int32_t)(base + j);
+            bool wait = mine && rescan && lane != first;
+            if (s_first) {
+                if (accept) atomicMin(&s_first[i1], (uint32_t)lane);
+                __syncwarp();
+                if (mine) {
+#pragma unroll
+                    for (int q = 0; q < K; ++q)
+                        if (k[q] != EMPTY && s_first[k[q] & 0xFFFFu] < (uint32_t)lane) wait = true;
+                }
+                __syncwarp();
+                if (accept) s_first[i1] = 0xFFFFFFFFu;
             }
-            ++num;
+            else {
+                for (uint32_t mm = pending; mm; mm &= mm - 1) {
+                    const int M = __ffs(mm) - 1;
+                    const int accM = __shfl_sync(0xFFFFFFFFu, (int)accept, M);
+                    const uint32_t iM = __shfl_sync(0xFFFFFFFFu, i1, M);
+                    if (mine && lane > M && accM) {
+#pragma unroll
+                        for (int q = 0; q < K; ++q)
+                            if (k[q] != EMPTY && (k[q] & 0xFFFFu) == iM) wait = true;
+                    }
+                }
+            }
+            const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, wait) & pending;
+            const uint32_t commit = waiting ? (pending & ((1u << (__ffs(waiting) - 1)) - 1u)) : pending;
+            const bool go = ((commit >> lane) & 1u) && accept;
+            if (go) {
+                atomicOr(&s_claim[i1 >> 5], 1u << (i1 & 31));
+                match_2_in_1[i1] = (int32_t)row;
+            }
+            num += __popc(__ballot_sync(0xFFFFFFFFu, go));
+            pending &= ~commit;
             __syncwarp();
         }
     }
@@ -224,8 +261,10 @@ int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* d
         if ((e = cudaMemcpy(dev + o_d2, desc_2, 32 * (size_t)n2, cudaMemcpyHostToDevice)) != cudaSuccess) break;
         if (valid_2 && (e = cudaMemcpy(dev + o_v, valid_2, n2, cudaMemcpyHostToDevice)) != cudaSuccess) break;
         k_bf_topk<<<(n2 + 7) / 8, 256>>>(dev + o_d1, n1, dev + o_d2, n2, valid_2 ? dev + o_v : nullptr, (uint4*)(dev + o_top));
-        k_bf_resolve<<<1, 32, ((n1 + 31) / 32) * 4>>>(dev + o_d1, n1, dev + o_d2, n2, (const uint4*)(dev + o_top), lowe_ratio,
-                                                      (int32_t*)(dev + o_m), (uint32_t*)(dev + o_n));
+        const int first_in_smem = n1 <= 10000;
+        k_bf_resolve<<<1, 32, ((n1 + 31) / 32) * 4 + (first_in_smem ? 4 * (size_t)n1 : 0)>>>(
+            dev + o_d1, n1, dev + o_d2, n2, (const uint4*)(dev + o_top), lowe_ratio, first_in_smem, (int32_t*)(dev + o_m),
+            (uint32_t*)(dev + o_n));
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(match_2_in_1, dev + o_m, 4 * (size_t)n1, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(n_matches, dev + o_n, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;

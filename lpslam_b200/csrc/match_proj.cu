@@ -382,7 +382,18 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
                     }
                 }
             }
-            const bool rescan = mine && (need_second ? i2 < 0 : i1 < 0) && k[K - 1] != EMPTY;
+            bool settled = (need_second ? i2 >= 0 : i1 >= 0) || k[K - 1] == EMPTY;
+            if (mine && !settled) {
+                // everything behind the kept four is at least as far as the fourth: that bound often settles the row
+                const unsigned lb = k[K - 1] >> 20;
+                if (i1 >= 0) {  // the second is missing
+                    const unsigned bd = b1 >> 20;
+                    if (a.hamm_thr < bd) settled = true;                                     // rejected whatever the second is
+                    else if (!((float)bd > __fmul_rn(a.lowe_ratio, (float)lb))) settled = true;  // passes the ratio test for any second >= lb
+                }
+                else if (a.hamm_thr < lb) settled = true;  // no free candidate can be close enough
+            }
+            const bool rescan = mine && !settled;
             const int first = __ffs(pending) - 1;
             if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first)) {
                 // the first pending row needs the exact list: its lane walks it in reference order, alone
@@ -520,16 +531,17 @@ __global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lps
 
 // area::match_in_consistent_area (area.cc:20-91): rows are replayed in order against the per-keypoint best distance of
 // frame 2 ("ignore if the already-matched point is closer in Hamming space", area.cc:47-50); a later row may take a
-// keypoint over, which deletes the earlier match. s_dist = matched_dists_in_frm_2.
+// keypoint over, which deletes the earlier match. Same batch form as k_lm_resolve: 32 rows are decided per round against
+// the current per-keypoint state, rows are committed in order up to the first one whose kept candidates contain a keypoint
+// that an earlier row of the round just matched (its distance gate moved), the rest are decided again.
+// s_state[i] = matched_dists_in_frm_2[i] << 20 | (matched_indices_1_in_frm_2[i] + 1); s_claim as in k_lm_resolve.
 __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
-    extern __shared__ uint32_t s_raw[];
-    // [owner int32 x n2 | dist uint16 x n2]: matched_indices_1_in_frm_2 and matched_dists_in_frm_2 stay in shared memory
-    int32_t* s_owner = reinterpret_cast<int32_t*>(s_raw);
-    uint16_t* s_dist = reinterpret_cast<uint16_t*>(s_raw + a.n_curr);
+    extern __shared__ uint32_t s_state[];
+    uint32_t* s_claim = s_state + a.n_curr;
     const int lane = threadIdx.x;
     for (uint32_t i = lane; i < a.n_curr; i += 32) {
-        s_dist[i] = (uint16_t)MAX_HAMMING_DIST;
-        s_owner[i] = -1;
+        s_state[i] = (uint32_t)MAX_HAMMING_DIST << 20;
+        s_claim[i] = 0xFFFFFFFFu;
     }
     for (uint32_t i = lane; i < a.n_last; i += 32) a.match_2_of_1[i] = -1;
     __syncwarp();
@@ -537,75 +549,101 @@ __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
     uint32_t n_ev = 0;
     constexpr unsigned HAMMING_DIST_THR_LOW = 50;  // match/base.h:13
     for (uint32_t base = 0; base < a.n_last; base += 32) {
-        const uint32_t mine = base + lane;
-        const uint4 mk = mine < a.n_last ? a.top_key[mine] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
-        const int4 mi = mine < a.n_last ? a.top_idx[mine] : make_int4(-1, -1, -1, -1);
-        const int my_obs = (a.last_obs && mine < a.n_last) ? a.last_obs[mine] : 1;  // has_observation() of the row's landmark
-        uint32_t todo = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_LOW);
-        while (todo) {
-            const int j = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const uint32_t il = base + j;
-            const uint32_t k[K] = {__shfl_sync(0xFFFFFFFFu, mk.x, j), __shfl_sync(0xFFFFFFFFu, mk.y, j),
-                                   __shfl_sync(0xFFFFFFFFu, mk.z, j), __shfl_sync(0xFFFFFFFFu, mk.w, j)};
-            const int ix[K] = {__shfl_sync(0xFFFFFFFFu, mi.x, j) & 0x00FFFFFF, __shfl_sync(0xFFFFFFFFu, mi.y, j) & 0x00FFFFFF,
-                               __shfl_sync(0xFFFFFFFFu, mi.z, j) & 0x00FFFFFF, __shfl_sync(0xFFFFFFFFu, mi.w, j) & 0x00FFFFFF};
+        const uint32_t il = base + lane;
+        const uint4 mk = il < a.n_last ? a.top_key[il] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
+        const int4 mi = il < a.n_last ? a.top_idx[il] : make_int4(-1, -1, -1, -1);
+        const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
+        const int ix[K] = {mi.x & 0x00FFFFFF, mi.y & 0x00FFFFFF, mi.z & 0x00FFFFFF, mi.w & 0x00FFFFFF};
+        uint32_t pending = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= HAMMING_DIST_THR_LOW);
+        while (pending) {
+            const bool mine = (pending >> lane) & 1u;
             uint32_t b1 = EMPTY, b2 = EMPTY;
             int i1 = -1;
             bool have2 = false;
+            if (mine) {
 #pragma unroll
-            for (int q = 0; q < K; ++q) {
-                if (k[q] == EMPTY) continue;
-                if (s_dist[ix[q]] <= (k[q] >> 20)) continue;  // area.cc:48
-                if (i1 < 0) {
-                    b1 = k[q];
-                    i1 = ix[q];
-                }
-                else if (!have2) {
-                    b2 = k[q];
-                    have2 = true;
+                for (int q = 0; q < K; ++q) {
+                    if (k[q] == EMPTY) continue;
+                    if ((s_state[ix[q]] >> 20) <= (k[q] >> 20)) continue;  // area.cc:48
+                    if (i1 < 0) {
+                        b1 = k[q];
+                        i1 = ix[q];
+                    }
+                    else if (!have2) {
+                        b2 = k[q];
+                        have2 = true;
+                    }
                 }
             }
-            if (!have2 && k[K - 1] != EMPTY) {
-                // the kept four do not decide best and second: exact rescan in reference order by lane 0
-                uint32_t r1 = EMPTY, r2 = EMPTY;
-                int ri1 = -1;
-                if (lane == 0) {
+            bool settled = have2 || k[K - 1] == EMPTY;
+            if (mine && !settled) {
+                // everything behind the kept four is at least as far as the fourth: that bound often settles the row
+                const unsigned lb = k[K - 1] >> 20;
+                if (i1 >= 0) {
+                    const unsigned bd = b1 >> 20;
+                    if (HAMMING_DIST_THR_LOW < bd) settled = true;
+                    else if (!(__fmul_rn((float)lb, a.lowe_ratio) < (float)bd)) settled = true;  // passes for any second >= lb
+                }
+                else if (HAMMING_DIST_THR_LOW < lb) settled = true;
+            }
+            const bool rescan = mine && !settled;
+            const int first = __ffs(pending) - 1;
+            if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first)) {
+                // the kept four do not decide best and second: exact rescan in reference order by the row's lane
+                if (lane == first) {
+                    b1 = b2 = EMPTY;
+                    i1 = -1;
                     const Projected p = project(a, il, false, false);
-                    visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
-                        if (s_dist[i] <= d) return;
+                    visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int) {
+                        if ((s_state[i] >> 20) <= d) return;
                         const uint32_t kk = (d << 20) | seq;
-                        if (kk < r1) {
-                            r2 = r1;
-                            r1 = kk;
-                            ri1 = (int)i;
+                        if (kk < b1) {
+                            b2 = b1;
+                            b1 = kk;
+                            i1 = (int)i;
                         }
-                        else if (kk < r2) {
-                            r2 = kk;
+                        else if (kk < b2) {
+                            b2 = kk;
                         }
                     });
                 }
-                b1 = __shfl_sync(0xFFFFFFFFu, r1, 0);
-                i1 = __shfl_sync(0xFFFFFFFFu, ri1, 0);
-                b2 = __shfl_sync(0xFFFFFFFFu, r2, 0);
             }
-            if (i1 < 0) continue;
-            const unsigned best = b1 >> 20, second = b2 == EMPTY ? MAX_HAMMING_DIST : (b2 >> 20);
-            if (HAMMING_DIST_THR_LOW < best) continue;
-            if (__fmul_rn((float)second, a.lowe_ratio) < (float)best) continue;  // area.cc:67-69
-            if (lane == 0) {
-                const int prev = s_owner[i1];  // area.cc:76-80: the earlier owner of the keypoint loses its match
+            bool accept = mine && i1 >= 0 && (lane == first || !rescan);
+            const unsigned best = b1 >> 20;
+            if (accept) {
+                const unsigned second = b2 == EMPTY ? MAX_HAMMING_DIST : (b2 >> 20);
+                if (HAMMING_DIST_THR_LOW < best) accept = false;
+                else if (__fmul_rn((float)second, a.lowe_ratio) < (float)best) accept = false;  // area.cc:67-69
+            }
+            bool wait = mine && rescan && lane != first;
+            if (mine && accept) atomicMin(&s_claim[i1], (uint32_t)lane);
+            __syncwarp();
+            if (mine) {
+#pragma unroll
+                for (int q = 0; q < K; ++q)
+                    if (k[q] != EMPTY && s_claim[ix[q]] < (uint32_t)lane) wait = true;
+            }
+            __syncwarp();
+            if (mine && accept) s_claim[i1] = 0xFFFFFFFFu;
+            const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, wait) & pending;
+            const uint32_t commit = waiting ? (pending & ((1u << (__ffs(waiting) - 1)) - 1u)) : pending;
+            const bool go = ((commit >> lane) & 1u) && accept;
+            const uint32_t acc_mask = __ballot_sync(0xFFFFFFFFu, go);
+            bool took_over = false;
+            if (go) {
+                // distinct keypoints within a round (a later lane holding the same one waited), earlier owners are earlier rows
+                const int prev = (int)(s_state[i1] & 0xFFFFFu) - 1;  // area.cc:76-80: the earlier owner loses its match
                 if (0 <= prev) {
                     a.match_2_of_1[prev] = -1;
-                    --num;
+                    took_over = true;
                 }
                 a.match_2_of_1[il] = i1;
-                s_owner[i1] = (int32_t)il;
-                s_dist[i1] = (uint16_t)best;
-                ++num;
-                a.events[n_ev] = make_int2((int)il, i1);
+                s_state[i1] = (best << 20) | (il + 1);
+                a.events[n_ev + __popc(acc_mask & ((1u << lane) - 1u))] = make_int2((int)il, i1);
             }
-            ++n_ev;
+            n_ev += __popc(acc_mask);
+            num += __popc(acc_mask) - __popc(__ballot_sync(0xFFFFFFFFu, took_over));
+            pending &= ~commit;
             __syncwarp();
         }
     }
@@ -918,7 +956,7 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
     LPS_ARG(n1 == 0 || (kp1_undist && desc1 && prev_matched_pts && matched_indices_2_in_frm_1), "null frame-1 argument");
     LPS_ARG(n2 == 0 || (kp2_undist && desc2), "null frame-2 argument");
     LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1, "bad camera grid");
-    LPS_ARG(n2 <= 8000, "too many frame-2 keypoints (the per-keypoint state lives in 48 KB of shared memory)");
+    LPS_ARG(n2 <= 24000 && n1 < (1u << 20) - 1, "too many keypoints (the per-keypoint state of frame 2 lives in shared memory)");
     for (uint32_t i = 0; i < n1; ++i) matched_indices_2_in_frm_1[i] = -1;
     if (n1 == 0 || n2 == 0) return LPSLAM_OK;
     std::vector<uint8_t> use(n1);
@@ -975,7 +1013,11 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
         k_grid_fill<<<(n2 + 255) / 256, 256>>>(a);
         k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
         k_proj_topk<<<(n1 + 127) / 128, 128>>>(a);
-        k_area_resolve<<<1, 32, (size_t)n2 * 4 + ((n2 + 1) / 2) * 4 + 4>>>(a);
+        const size_t smem = 8 * (size_t)n2;
+        if (smem > 48 * 1024 &&
+            (e = cudaFuncSetAttribute(k_area_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+            break;
+        k_area_resolve<<<1, 32, smem>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cudaMemcpy(matched_indices_2_in_frm_1, dev + o_m21, 4 * (size_t)n1, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
         if ((e = cudaMemcpy(ne, dev + o_ne, 8, cudaMemcpyDeviceToHost)) != cudaSuccess) break;

@@ -335,3 +335,67 @@ def test_bow_tree(oracle, seed, chk):
         assert np.array_equal(got, want) and ng == nw
         total += nw
     assert total > 300
+
+
+def clustered(rng, n, protos, flip):
+    """descriptors drawn from a few prototypes with a handful of flipped bits: small distances everywhere, ties and near
+    ties, so that the kept four candidates run dry, the lower bounds do not settle rows and the exact rescans run"""
+    return protos[rng.integers(0, len(protos), n)] ^ np.packbits(rng.random((n, 256)) < flip, axis=1, bitorder="little")
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_frame_and_landmarks_clustered(oracle, seed):
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    args, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs = landmarks_case(oracle, seed, False, seed == 12)
+    rng = np.random.default_rng(seed)
+    protos = rng.integers(0, 256, (5, 32), dtype=np.uint8)
+    desc = clustered(rng, len(kp), protos, 0.03)
+    ldesc = clustered(rng, len(ldesc), protos, 0.03)
+    level = np.clip(kp["octave"][rng.integers(0, len(kp), len(level))], 0, 7).astype(np.int32)
+    total = 0
+    for margin in (5.0, 30.0):
+        for ratio in (0.8, 1.0, 2.0):
+            want, nw = oracle.match_landmarks(pyoracle.make_camera(**args), active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf,
+                                              margin, ratio, obs)
+            got, ng = match.projection(ratio, True).match_frame_and_landmarks(match.make_camera(**args), active, reproj, lxr, level,
+                                                                              ldesc, kp, desc, xr, taken, sf, margin, obs)
+            assert np.array_equal(got, want) and ng == nw
+            total += nw
+    assert total > 400
+
+
+@pytest.mark.parametrize("seed", [21, 22])
+def test_area_clustered(oracle, seed):
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    rng = np.random.default_rng(seed)
+    o = oracle.extractor(max_kpts=1500)
+    k1, _ = o.extract(synth_image(480, 640, seed))
+    k2, _ = o.extract(synth_image(480, 640, seed + 1))
+    k1["octave"][rng.random(len(k1)) < 0.7] = 0
+    k2["octave"][rng.random(len(k2)) < 0.7] = 0
+    protos = rng.integers(0, 256, (4, 32), dtype=np.uint8)
+    d1, d2 = clustered(rng, len(k1), protos, 0.03), clustered(rng, len(k2), protos, 0.03)
+    args = dict(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    prev = np.stack([k1["x"], k1["y"]], axis=1).astype(np.float32)
+    total = 0
+    for margin in (30, 120):
+        for ratio in (0.9, 1.0, 1.5):
+            want, nw, pw = oracle.match_area(pyoracle.make_camera(**args), k1, d1, prev, k2, d2, margin, ratio, True)
+            got, ng, pg = match.area(ratio, True).match_in_consistent_area(match.make_camera(**args), k1, d1, k2, d2, prev, margin)
+            assert np.array_equal(got, want) and ng == nw and np.array_equal(pg, pw)
+            total += nw
+    assert total > 200
+
+
+def test_bruteforce_clustered(oracle):
+    from lpslam_b200 import match
+    rng = np.random.default_rng(31)
+    protos = rng.integers(0, 256, (6, 32), dtype=np.uint8)
+    d1, d2 = clustered(rng, 1500, protos, 0.03), clustered(rng, 1700, protos, 0.03)
+    for ratio in (0.8, 1.0, 1.6):
+        want, nw = oracle.match_bruteforce(d1, d2, None, None, None, ratio, False)
+        _, got = match.robust(ratio, False).brute_force_match(d1, d2)
+        assert np.array_equal(got, want)
+    assert nw > 100
