@@ -105,11 +105,46 @@ __global__ void __launch_bounds__(1024) k_offsets(DescribeArgs a) {
     }
 }
 
-__global__ void __launch_bounds__(256) k_describe(DescribeArgs a) {
+__device__ __forceinline__ int dp4a_us(uint32_t pix, uint32_t w, int acc) {  // unsigned pixels x signed weights
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pix), "r"(w), "r"(acc));
+    return d;
+}
+
+constexpr int kDescribeBlocksPerSM = 2;
+constexpr unsigned kRun = 8;  // consecutive packed rows per warp before it strides on
+
+// Software pipeline over a warp's keypoints, three deep: the position of keypoint k + 2 is being read while the patch
+// rows of k + 1 are in flight and k is computed. Warps take runs of kRun consecutive packed rows, strided by the grid, so
+// that the warps resident at one time cover a few frames (their level images stay in L2).
+__global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(DescribeArgs a) {
     const int lane = threadIdx.x & 31;
-    const int warps_total = gridDim.x * (blockDim.x >> 5);
+    const unsigned warps_total = gridDim.x * (blockDim.x >> 5);
     const int n_seg = a.batch * a.num_levels;
     const unsigned total = min(a.level_off[n_seg], a.out_cap);
+    // Orientation patch rows are read as 16-byte pieces, three lanes per row and ten rows per load: a load then touches ten
+    // lines instead of one line per lane (the L1 wavefront rate is what bounds this kernel). Rows start 16-byte aligned,
+    // so a row's 31 pixels sit at bytes sh .. sh + 30 of a 48-byte span, sh = (x - 15) & 15 the same for every row.
+    // s_mask[|v|][sh][piece] keeps the bytes inside the disc (|u| <= u_max[|v|], feature/orb_extractor.cc:228-241); with the
+    // byte position p as IDP.4A weight, m10 = sum p I - (sh + 15) sum I and m01 = v sum I.
+    __shared__ uint4 s_mask[16 * 16 * 3];
+    for (int e = threadIdx.x; e < 16 * 16 * 3; e += blockDim.x) {
+        const int piece = e % 3, sh = (e / 3) % 16, um = c_umax[e / 48];
+        uint32_t m[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            m[w] = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int u = 16 * piece + 4 * w + b - sh - kHalfPatch;
+                if ((u < 0 ? -u : u) <= um) m[w] |= 0xFFu << (8 * b);
+            }
+        }
+        s_mask[e] = make_uint4(m[0], m[1], m[2], m[3]);
+    }
+    __syncthreads();
+    const unsigned k_first = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * kRun;
+    if (k_first >= total) return;
     float pat[32];  // this lane's 8 point pairs: x0, y0, x1, y1 each
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -119,56 +154,116 @@ __global__ void __launch_bounds__(256) k_describe(DescribeArgs a) {
         pat[4 * i + 2] = (float)q.z;
         pat[4 * i + 3] = (float)q.w;
     }
-    for (unsigned k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < total; k += warps_total) {
-        // segment (frame, level) holding packed row k
-        int lo = 0, hi = n_seg;
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (a.level_off[mid] <= k) lo = mid;
-            else hi = mid;
-        }
-        const int frame = lo / a.num_levels, level = lo % a.num_levels;
-        const unsigned idx = k - a.level_off[lo];
-        const LevelGeom& lv = a.lv[level];
-        const uint32_t xy = a.sel_xys[(size_t)frame * a.sel_stride + lv.sel_begin + idx];
-        const int score = a.sel_sc[(size_t)frame * a.sel_stride + lv.sel_begin + idx];
-        const int px = (int)(xy & 0xFFFFu) + kBorder, py = (int)(xy >> 16) + kBorder;
-        const int pitch = lv.pitch;
+    const int piece = lane % 3, row_in_load = lane / 3;  // lanes 30, 31 idle
+    const uint32_t pos0 = 0x03020100u + 0x01010101u * (uint32_t)(16 * piece);
 
-        // ---- orientation: lane = column offset u + 15 (lane 31 idles), rows v = -15..15 ----
-        const uint8_t* __restrict__ c0 = lv.img + frame * lv.frame_stride + (size_t)py * pitch + px;
-        int m10 = 0, m01 = 0;
-        const int u = lane - kHalfPatch;
-        const int au = abs(u);
-        if (lane < kPatch) {
-            // 31 independent predicated byte loads in flight (rows v = -15..15 of this lane's column)
-            int val[kPatch];
-#pragma unroll
-            for (int i = 0; i < kPatch; ++i) {
-                const int v = i - kHalfPatch;
-                val[i] = (au <= c_umax[v < 0 ? -v : v]) ? (int)__ldg(c0 + v * pitch + u) : 0;
+    struct Loc {   // stage 1: where the keypoint is
+        unsigned k;
+        int frame, level, score;
+        uint32_t xy;
+        bool ok;
+    };
+    struct Rows {  // stage 2: its patch rows on the way
+        unsigned k;
+        int frame, level, score, px, py;
+        unsigned sh;
+        uint4 d[4];
+        bool ok;
+    };
+    int lo = 0;
+    unsigned seg_begin = 0, seg_end = 0;
+    auto locate = [&](unsigned k) {
+        Loc L;
+        L.k = k;
+        L.ok = k < total;
+        L.frame = L.level = L.score = 0;
+        L.xy = 0;
+        if (L.ok) {
+            if (k >= seg_end) {  // (frame, level) segment holding packed row k; rows are visited in ascending order
+                int hi = n_seg;
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (a.level_off[mid] <= k) lo = mid;
+                    else hi = mid;
+                }
+                seg_begin = a.level_off[lo];
+                seg_end = a.level_off[lo + 1];
             }
-            int colsum = 0;
+            L.frame = lo / a.num_levels;
+            L.level = lo % a.num_levels;
+            const size_t at = (size_t)L.frame * a.sel_stride + a.lv[L.level].sel_begin + (k - seg_begin);
+            L.xy = a.sel_xys[at];
+            L.score = a.sel_sc[at];
+        }
+        return L;
+    };
+    auto fetch = [&](const Loc& L) {
+        Rows R;
+        R.k = L.k;
+        R.ok = L.ok;
+        R.frame = L.frame;
+        R.level = L.level;
+        R.score = L.score;
+        R.px = (int)(L.xy & 0xFFFFu) + kBorder;
+        R.py = (int)(L.xy >> 16) + kBorder;
+        R.sh = 0;
 #pragma unroll
-            for (int i = 0; i < kPatch; ++i) {
-                colsum += val[i];
-                m01 += (i - kHalfPatch) * val[i];
+        for (int i = 0; i < 4; ++i) R.d[i] = make_uint4(0, 0, 0, 0);
+        if (L.ok) {
+            const LevelGeom& lv = a.lv[L.level];
+            const uint8_t* row0 = lv.img + L.frame * lv.frame_stride + (size_t)R.py * lv.pitch + (R.px - kHalfPatch);
+            R.sh = (unsigned)(reinterpret_cast<uintptr_t>(row0) & 15);
+            const uint8_t* mine = row0 - R.sh + 16 * piece;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = 10 * i + row_in_load;
+                R.d[i] = (lane < 30 && r < kPatch) ? __ldg(reinterpret_cast<const uint4*>(mine + (ptrdiff_t)(r - kHalfPatch) * lv.pitch))
+                                                   : make_uint4(0, 0, 0, 0);
             }
-            m10 = u * colsum;
         }
+        return R;
+    };
+    auto next_k = [&](unsigned k) { return ((k + 1) % kRun) ? k + 1 : k + 1 + (warps_total - 1) * kRun; };
+
+    Loc A = locate(k_first);
+    Rows B = fetch(A);
+    A = locate(next_k(k_first));
+    while (B.ok) {
+        const Loc A2 = locate(next_k(A.k));
+        const LevelGeom& lv = a.lv[B.level];
+        const int pitch = lv.pitch;
+        // ---- orientation: masked bytes, IDP.4A with the byte positions and with ones ----
+        unsigned sum_p = 0;
+        int m01 = 0;
+        unsigned sum_1 = 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
-            m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
+        for (int i = 0; i < 4; ++i) {
+            const int r = 10 * i + row_in_load;
+            const int vv = r - kHalfPatch;
+            const int av = min(vv < 0 ? -vv : vv, 15);
+            const uint4 mk = s_mask[av * 48 + B.sh * 3 + piece];
+            const uint32_t d0 = B.d[i].x & mk.x, d1 = B.d[i].y & mk.y, d2 = B.d[i].z & mk.z, d3 = B.d[i].w & mk.w;
+            sum_p = __dp4a(d0, pos0, sum_p);
+            sum_p = __dp4a(d1, pos0 + 0x04040404u, sum_p);
+            sum_p = __dp4a(d2, pos0 + 0x08080808u, sum_p);
+            sum_p = __dp4a(d3, pos0 + 0x0C0C0C0Cu, sum_p);
+            unsigned rs = __dp4a(d0, 0x01010101u, 0u);
+            rs = __dp4a(d1, 0x01010101u, rs);
+            rs = __dp4a(d2, 0x01010101u, rs);
+            rs = __dp4a(d3, 0x01010101u, rs);
+            sum_1 += rs;
+            m01 += vv * (int)rs;
         }
+        const int m10 = __reduce_add_sync(0xFFFFFFFFu, (int)sum_p - (int)(B.sh + kHalfPatch) * (int)sum_1);
+        m01 = __reduce_add_sync(0xFFFFFFFFu, m01);
         const float angle = fast_atan2_deg((float)m01, (float)m10);
 
         // ---- descriptor: lane = output byte, 8 point pairs each ----
         const float arad = (float)((double)angle * 3.14159265358979323846 / 180.0);
         const float ca = ref_cos(arad);
         const float sa = ref_cos(__fsub_rn(3.14159265358979f / 2.0f, arad));
-        const uint8_t* __restrict__ cb = lv.blur + frame * lv.frame_stride + (size_t)py * pitch + px;
-        unsigned byte = 0;
+        const uint8_t* __restrict__ cb = lv.blur + B.frame * lv.frame_stride + (size_t)B.py * pitch + B.px;
+        int v0[8], v1[8];
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
             const float x0 = pat[4 * b], y0 = pat[4 * b + 1], x1 = pat[4 * b + 2], y1 = pat[4 * b + 3];
@@ -176,10 +271,17 @@ __global__ void __launch_bounds__(256) k_describe(DescribeArgs a) {
             const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
             const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
             const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
-            const int v0 = __ldg(cb + r0 * pitch + q0);
-            const int v1 = __ldg(cb + r1 * pitch + q1);
-            byte |= (unsigned)(v0 < v1) << b;
+            v0[b] = __ldg(cb + r0 * pitch + q0);
+            v1[b] = __ldg(cb + r1 * pitch + q1);
         }
+        // the next keypoint's rows leave now, behind this one's descriptor taps
+        const unsigned k = B.k;
+        const int level = B.level, px = B.px, py = B.py, score = B.score;
+        B = fetch(A);
+        A = A2;
+        unsigned byte = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) byte |= (unsigned)(v0[b] < v1[b]) << b;
         a.desc[(size_t)k * 32 + lane] = (uint8_t)byte;
 
         if (lane == 0) {
@@ -208,7 +310,7 @@ void launch_describe(const DescribeArgs& a, cudaStream_t st) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    k_describe<<<sms * 8, 256, 0, st>>>(a);
+    k_describe<<<sms * kDescribeBlocksPerSM, 256, 0, st>>>(a);
 }
 
 }  // namespace lps
