@@ -94,6 +94,9 @@ struct LevelGeom {
     const uint16_t* qiy;
     const int* qbx;     // nx + 1 entries
     const int* qby;     // ny + 1 entries
+    // path key of a candidate = qxk[x] + qyk[y] (initial node index above 2 bits per depth, host-built)
+    const uint32_t* qxk;
+    const uint32_t* qyk;
     int cand_begin;     // first candidate slot of the level in the per-frame candidate scratch
     int cand_cap;       // cell_count * kCellSlots
     int node_begin, node_cap;

@@ -125,7 +125,8 @@ int lpslam_orb_ctx::configure(int width, int height) {
     std::vector<std::vector<int2>> rowtab(L);
     std::vector<std::vector<uint16_t>> qix(L), qiy(L);
     std::vector<std::vector<int>> qbx(L), qby(L);
-    std::vector<size_t> off_qix(L), off_qiy(L), off_qbx(L), off_qby(L);
+    std::vector<std::vector<uint32_t>> qxk(L), qyk(L);
+    std::vector<size_t> off_qix(L), off_qiy(L), off_qbx(L), off_qby(L), off_qxk(L), off_qyk(L);
     int cand_total = 0, node_total = 0, sel_total = 0;
     for (int l = 0; l < L; ++l) {
         LevelGeom& g = lv[l];
@@ -267,6 +268,27 @@ int lpslam_orb_ctx::configure(int width, int height) {
             qby[l].resize(std::max(g.ny, maxiy + 1) + 1);
             for (size_t i = 0; i < qbx[l].size(); ++i) qbx[l][i] = (int)(g.dx * (unsigned)i);
             for (size_t i = 0; i < qby[l].size(); ++i) qby[l][i] = (int)(g.dy * (unsigned)i);
+            // Path-key halves. Whether a keypoint goes right at a depth depends on its x and its initial column only, whether it
+            // goes down on its y and its initial row only (orb_extractor_node.cc:6-50: half extents round up), so the key
+            // (initial node, then 2 bits per depth: bit 0 = right, bit 1 = bottom) is qxk[x] + qyk[y].
+            auto half_key = [&](int v, const std::vector<uint16_t>& qi, const std::vector<int>& qb, int shift) {
+                const unsigned i = qi[v];
+                int b = qb[i], e = qb[i + 1];
+                uint32_t path = 0;
+                for (int d = 0; d < g.depth; ++d) {
+                    const int hv = (e - b + 1) >> 1;  // cvCeil(extent / 2.0)
+                    uint32_t bit = 0;
+                    if (b + hv <= v) { bit = 1; b += hv; } else { e = b + hv; }
+                    path = (path << 2) | (bit << shift);
+                }
+                return path;
+            };
+            qxk[l].resize(ext_x + 1);
+            qyk[l].resize(ext_y + 1);
+            for (int x = 0; x <= ext_x; ++x) qxk[l][x] = ((uint32_t)qix[l][x] << (2 * g.depth)) + half_key(x, qix[l], qbx[l], 0);
+            for (int y = 0; y <= ext_y; ++y) qyk[l][y] = ((uint32_t)(qiy[l][y] * g.nx) << (2 * g.depth)) + half_key(y, qiy[l], qby[l], 1);
+            off_qxk[l] = plan.take(qxk[l].size() * 4);
+            off_qyk[l] = plan.take(qyk[l].size() * 4);
             off_qix[l] = plan.take(qix[l].size() * 2);
             off_qiy[l] = plan.take(qiy[l].size() * 2);
             off_qbx[l] = plan.take(qbx[l].size() * 4);
@@ -329,6 +351,10 @@ int lpslam_orb_ctx::configure(int width, int height) {
         lv[l].qiy = (const uint16_t*)(arena + off_qiy[l]);
         lv[l].qbx = (const int*)(arena + off_qbx[l]);
         lv[l].qby = (const int*)(arena + off_qby[l]);
+        lv[l].qxk = (const uint32_t*)(arena + off_qxk[l]);
+        lv[l].qyk = (const uint32_t*)(arena + off_qyk[l]);
+        LPS_CUDA(cudaMemcpyAsync(arena + off_qxk[l], qxk[l].data(), qxk[l].size() * 4, cudaMemcpyHostToDevice, stream));
+        LPS_CUDA(cudaMemcpyAsync(arena + off_qyk[l], qyk[l].data(), qyk[l].size() * 4, cudaMemcpyHostToDevice, stream));
         LPS_CUDA(cudaMemcpyAsync(arena + off_qix[l], qix[l].data(), qix[l].size() * 2, cudaMemcpyHostToDevice, stream));
         LPS_CUDA(cudaMemcpyAsync(arena + off_qiy[l], qiy[l].data(), qiy[l].size() * 2, cudaMemcpyHostToDevice, stream));
         LPS_CUDA(cudaMemcpyAsync(arena + off_qbx[l], qbx[l].data(), qbx[l].size() * 4, cudaMemcpyHostToDevice, stream));

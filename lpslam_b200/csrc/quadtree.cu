@@ -26,6 +26,8 @@ namespace {
 constexpr int QT = LPS_QT_THREADS;  // threads per block (two resident blocks per SM at 512)
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int PART_BITS = 14;  // leading key bits of the one-pass ordering (2^14 shared-memory bins)
+constexpr int SORT_CH = 8;  // sort rounds whose loads are issued together
 constexpr int POOL_CACHE = 16 * 1024;  // pool counts cached in shared memory (words)
 constexpr int F_LEAF = 1 << 8, F_POOL = 1 << 9, DEPTH_MASK = 0xFF;
 
@@ -71,36 +73,44 @@ __device__ __forceinline__ int lower_digit(const uint32_t* __restrict__ keys, in
     return lo;
 }
 
-__device__ __forceinline__ void split_node(const uint32_t* __restrict__ keys, int lo, int hi, int d, int D, int (&b)[5]) {
+// Dsorted = number of leading digits the key array is ordered by (D after the full sort); a split below that depth cannot
+// be answered from a prefix-sorted array: *deeper is raised and the block redoes the level with the full sort
+__device__ __forceinline__ void split_node(const uint32_t* __restrict__ keys, int lo, int hi, int d, int D, int Dsorted, int* deeper,
+                                           int (&b)[5]) {
     b[0] = lo;
     b[4] = hi;
     if (hi - lo <= 1 || d >= D) {  // a single keypoint always yields exactly one non-empty child
         b[1] = b[2] = b[3] = hi;
         return;
     }
+    if (d >= Dsorted) *deeper = 1;
     const int shift = 2 * (D - d - 1);
     b[2] = lower_digit(keys, lo, hi, shift, 2);
     b[1] = lower_digit(keys, lo, b[2], shift, 1);
     b[3] = lower_digit(keys, b[2], hi, shift, 3);
 }
 
-__device__ __forceinline__ uint32_t path_key(int x, int y, const LevelGeom& lv) {
-    // initial node: orb_extractor.cc:532-539 (float coordinate / double extent, truncated) through the host-built tables
-    const unsigned ix = lv.qix[x], iy = lv.qiy[y];
-    int bx = lv.qbx[ix], ex = lv.qbx[ix + 1];
-    int by = lv.qby[iy], ey = lv.qby[iy + 1];
-    uint32_t key = ix + iy * lv.nx;
-    for (int d = 0; d < lv.depth; ++d) {
-        const int hx = (ex - bx + 1) >> 1, hy = (ey - by + 1) >> 1;  // cvCeil(extent / 2.0)
-        uint32_t q = 0;
-        if (bx + hx <= x) { q |= 1; bx += hx; } else { ex = bx + hx; }
-        if (by + hy <= y) { q |= 2; by += hy; } else { ey = by + hy; }
-        key = (key << 2) | q;
+__device__ __forceinline__ int pad_idx(int lin) { return lin + (lin >> 5); }
+
+// lanes holding the same 9-bit value (8 digit bits + the "inactive" bit), by votes: MATCH.ANY costs over a thousand
+// cycles per call here (measured through the phase clocks), nine VOTEs and nine LOP3s do not
+__device__ __forceinline__ unsigned match_digit(unsigned d) {
+    unsigned peers = 0xFFFFFFFFu;
+#pragma unroll
+    for (int b = 0; b <= RADIX_BITS; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned v = __ballot_sync(0xFFFFFFFFu, bit);
+        peers &= bit ? v : ~v;
     }
-    return key;
+    return peers;
 }
 
-__device__ __forceinline__ int pad_idx(int lin) { return lin + (lin >> 5); }
+#ifdef LPS_QT_PROFILE  // phase clocks of block (frame 0, level 0): -DLPS_QT_PROFILE, read with lpslam_debug_qt_profile
+__device__ unsigned long long g_qt_prof[16];
+#define QT_MARK(i) do { if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_qt_prof[i] = clock64(); } while (0)
+#else
+#define QT_MARK(i) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(TreeArgs a) {
     extern __shared__ uint32_t s_dyn[];  // RADIX * QT counters (padded) during the sort, pool counts afterwards
@@ -138,6 +148,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
     uint32_t* sel_count = a.sel_count + (size_t)frame * a.num_levels + level;
     uint32_t* cand_count = a.cand_count + (size_t)frame * a.num_levels + level;
 
+    QT_MARK(0);
     // ------------------------------------------------------------------ A. candidate list in reference order
     const int ncl = lv.cell_cols * lv.cell_rows;
     int N = 0;
@@ -154,34 +165,111 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         if (tid == 0) *sel_count = 0;
         return;
     }
+    // the one-pass ordering of phase B counts its bins while the keys are made
+    const int keybits = 2 * lv.depth + lv.rbits;
+    const int D = lv.depth;
+    const int Dpart = min(D, max(0, (PART_BITS - lv.rbits) >> 1));  // digits covered by the one-pass ordering
+    const int tbits = lv.rbits + 2 * Dpart, drop = keybits - tbits, nbins = 1 << tbits;
+    bool full = lv.rbits > PART_BITS;
+#ifdef LPS_QT_FORCE_FULL
+    full = true;
+#endif
+    uint32_t* s_bin = s_dyn;  // <= 2^PART_BITS words
+    if (!full)
+        for (int i = tid; i < nbins; i += QT) s_bin[i] = 0;
     __syncthreads();
-    for (int ci = warp; ci < ncl; ci += QT / 32) {
-        const CellDesc c = a.cells[lv.cell_begin + ci];
-        const int cnt = (int)cell_counts[ci], base = (int)cell_base[ci];
-        const uint32_t* slots = cell_slots + (size_t)ci * kCellSlots;
-        for (int k = lane; k < cnt; k += 32) {
-            const uint32_t s = slots[k];
-            // window-local + 3 (ring margin) + 64 * cell index, relative to the 19-px border (orb_extractor.cc:362-363)
-            const int x = (int)(s & 255u) + 3 + kCell * c.j;
-            const int y = (int)((s >> 8) & 255u) + 3 + kCell * c.i;
-            cand_xy[base + k] = (uint32_t)x | ((uint32_t)y << 16);
-            cand_sc[base + k] = (uint8_t)(s >> 16);
-            keys[0][base + k] = path_key(x, y, lv);
-            vals[0][base + k] = (uint32_t)(base + k);
+    {
+        int ci = warp;
+        CellDesc c = a.cells[lv.cell_begin + min(ci, ncl - 1)];
+        int cnt = ci < ncl ? (int)cell_counts[ci] : 0, cbase = ci < ncl ? (int)cell_base[ci] : 0;
+        while (ci < ncl) {
+            // the next cell's header is on its way while this cell's slots are read
+            const int cn = ci + QT / 32;
+            const CellDesc c_next = a.cells[lv.cell_begin + min(cn, ncl - 1)];
+            const int cnt_next = cn < ncl ? (int)cell_counts[cn] : 0, cbase_next = cn < ncl ? (int)cell_base[cn] : 0;
+            const uint32_t* slots = cell_slots + (size_t)ci * kCellSlots;
+            for (int k0 = lane; k0 < cnt; k0 += 32 * 4) {
+                uint32_t sl[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) sl[j] = k0 + 32 * j < cnt ? slots[k0 + 32 * j] : 0u;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int k = k0 + 32 * j;
+                    if (k < cnt) {
+                        // window-local + 3 (ring margin) + 64 * cell index, relative to the 19-px border (orb_extractor.cc:362-363)
+                        const int x = (int)(sl[j] & 255u) + 3 + kCell * c.j;
+                        const int y = (int)((sl[j] >> 8) & 255u) + 3 + kCell * c.i;
+                        const uint32_t key = __ldg(lv.qxk + x) + __ldg(lv.qyk + y);
+                        cand_xy[cbase + k] = (uint32_t)x | ((uint32_t)y << 16);
+                        cand_sc[cbase + k] = (uint8_t)(sl[j] >> 16);
+                        keys[0][cbase + k] = key;
+                        if (!full) atomicAdd(&s_bin[key >> drop], 1u);
+                    }
+                }
+            }
+            ci = cn;
+            c = c_next;
+            cnt = cnt_next;
+            cbase = cbase_next;
         }
     }
     __syncthreads();
+    QT_MARK(1);
 
-    // ------------------------------------------------------------------ B. LSD radix sort by path key (stable)
-    // 8 bits per pass. Warp w owns the contiguous segment [w * seg, (w + 1) * seg) and walks it 32 keys at a time with
-    // coalesced loads; inside a round the rank of a key among the equal digits of its warp comes from __match_any_sync,
-    // so order is preserved: earlier segments, earlier rounds, lower lanes first. Counters live in shared memory as
+    // ------------------------------------------------------------------ B. order the candidates by path key
+    // First attempt: ONE counting pass over the leading PART_BITS of the key (shared-memory histogram, prefix, scatter by
+    // atomics). The tree only ever asks for the digit of a node's depth, the winner of a node does not depend on the order
+    // inside it, and with a few hundred nodes wanted out of thousands of candidates the tree stays far above the depth
+    // those bits cover. If a split below that depth is asked for after all, the level is redone with the complete sort:
+    // LSD radix, 8 bits per pass, stable. There warp w owns the contiguous segment [w * seg, (w + 1) * seg) and walks it 32
+    // keys at a time with coalesced loads; inside a round the rank of a key among the equal digits of its warp comes from
+    // votes, so order is preserved: earlier segments, earlier rounds, lower lanes first. Counters live in shared memory as
     // [digit][warp] (pitch 33: leaders of one warp hit different banks).
-    const int keybits = 2 * lv.depth + lv.rbits;
+    int m = 0;   // list length, identical in every thread
+    int nb = 0;  // node buffer holding the current list
+    bool filled = false;
+    const int quota = (int)lv.quota;
+    const uint32_t* __restrict__ skey;
+    const uint32_t* __restrict__ sval;
+    int Dsorted;
+  while (true) {  // at most twice: prefix ordering, then (rarely) the complete sort
+    int cur = 0;
+    if (!full) {
+        {   // exclusive prefix over the bins: thread t owns a contiguous run
+            const int per = (nbins + QT - 1) / QT, b0 = min(nbins, tid * per), b1 = min(nbins, b0 + per);
+            unsigned sum = 0;
+            for (int i = b0; i < b1; ++i) sum += s_bin[i];
+            unsigned long long tot;
+            unsigned run = (unsigned)scan.excl(sum, tot);
+            for (int i = b0; i < b1; ++i) {
+                const unsigned c = s_bin[i];
+                s_bin[i] = run;
+                run += c;
+            }
+        }
+        __syncthreads();
+        for (int k0 = tid; k0 < N; k0 += QT * SORT_CH) {
+            uint32_t kk[SORT_CH];
+#pragma unroll
+            for (int j = 0; j < SORT_CH; ++j) kk[j] = k0 + j * QT < N ? keys[0][k0 + j * QT] : 0u;
+#pragma unroll
+            for (int j = 0; j < SORT_CH; ++j)
+                if (k0 + j * QT < N) {
+                    const unsigned pos = atomicAdd(&s_bin[kk[j] >> drop], 1u);
+                    keys[1][pos] = kk[j];
+                    vals[1][pos] = (uint32_t)(k0 + j * QT);  // vals[0] is the identity
+                }
+        }
+        __syncthreads();
+        cur = 1;
+        Dsorted = Dpart;
+    }
+    else {
     const int seg = ((N + QT - 1) / QT) * 32;
     const int seg_lo = min(N, warp * seg), seg_hi = min(N, (warp + 1) * seg);
     uint32_t* s_cntr = s_dyn;  // RADIX * 33 words
-    int cur = 0;
+    for (int k = tid; k < N; k += QT) vals[0][k] = (uint32_t)k;
+    __syncthreads();
     for (int shift = 0; shift < keybits; shift += RADIX_BITS) {
         const uint32_t* __restrict__ kin = keys[cur];
         const uint32_t* __restrict__ vin = vals[cur];
@@ -189,13 +277,22 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         uint32_t* __restrict__ vout = vals[cur ^ 1];
         for (int i = tid; i < RADIX * 33; i += QT) s_cntr[i] = 0;
         __syncthreads();
-        for (int base = seg_lo; base < seg_hi; base += 32) {
-            const int k = base + lane;
-            const bool ok = k < seg_hi;
-            const unsigned d = ok ? ((kin[k] >> shift) & (RADIX - 1)) : RADIX;  // inactive lanes form their own group
-            const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
-            if (ok && (peers & ((1u << lane) - 1)) == 0) s_cntr[d * 33 + warp] += __popc(peers);
-            __syncwarp();
+        for (int base = seg_lo; base < seg_hi; base += 32 * SORT_CH) {
+            uint32_t kk[SORT_CH];  // SORT_CH rounds of loads in flight, then ranked from registers
+#pragma unroll
+            for (int j = 0; j < SORT_CH; ++j) {
+                const int k = base + 32 * j + lane;
+                kk[j] = k < seg_hi ? kin[k] : 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < SORT_CH; ++j) {
+                if (base + 32 * j >= seg_hi) break;  // warp-uniform
+                const bool ok = base + 32 * j + lane < seg_hi;
+                const unsigned d = ok ? ((kk[j] >> shift) & (RADIX - 1)) : RADIX;  // inactive lanes form their own group
+                const unsigned peers = match_digit(d);
+                if (ok && (peers & ((1u << lane) - 1)) == 0) s_cntr[d * 33 + warp] += __popc(peers);
+                __syncwarp();
+            }
         }
         __syncthreads();
         // exclusive scan in (digit major, warp minor) order: thread t owns digit t / 4, warps 8 (t % 4) .. + 8
@@ -216,34 +313,46 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
             }
         }
         __syncthreads();
-        for (int base = seg_lo; base < seg_hi; base += 32) {
-            const int k = base + lane;
-            const bool ok = k < seg_hi;
-            const uint32_t key = ok ? kin[k] : 0u;
-            const uint32_t val = ok ? vin[k] : 0u;
-            const unsigned d = ok ? ((key >> shift) & (RADIX - 1)) : RADIX;
-            const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
-            const unsigned before = __popc(peers & ((1u << lane) - 1));
-            unsigned pos = 0;
-            if (ok) pos = s_cntr[d * 33 + warp] + before;
-            __syncwarp();
-            if (ok) {
-                if (before == 0) s_cntr[d * 33 + warp] += __popc(peers);
-                kout[pos] = key;
-                vout[pos] = val;
+        for (int base = seg_lo; base < seg_hi; base += 32 * SORT_CH) {
+            uint32_t kk[SORT_CH], vv[SORT_CH];
+#pragma unroll
+            for (int j = 0; j < SORT_CH; ++j) {
+                const int k = base + 32 * j + lane;
+                kk[j] = k < seg_hi ? kin[k] : 0u;
+                vv[j] = k < seg_hi ? vin[k] : 0u;
             }
-            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < SORT_CH; ++j) {
+                if (base + 32 * j >= seg_hi) break;  // warp-uniform
+                const bool ok = base + 32 * j + lane < seg_hi;
+                const unsigned d = ok ? ((kk[j] >> shift) & (RADIX - 1)) : RADIX;
+                const unsigned peers = match_digit(d);
+                const unsigned before = __popc(peers & ((1u << lane) - 1));
+                unsigned pos = 0;
+                if (ok) pos = s_cntr[d * 33 + warp] + before;
+                __syncwarp();
+                if (ok) {
+                    if (before == 0) s_cntr[d * 33 + warp] += __popc(peers);
+                    kout[pos] = kk[j];
+                    vout[pos] = vv[j];
+                }
+                __syncwarp();
+            }
         }
         __syncthreads();
         cur ^= 1;
     }
-    const uint32_t* __restrict__ skey = keys[cur];
-    const uint32_t* __restrict__ sval = vals[cur];
-    const int D = lv.depth;
+    Dsorted = D;
+    }
+    skey = keys[cur];
+    sval = vals[cur];
+    if (tid == 0) s_i[2] = 0;
+    m = 0;
+    nb = 0;
+    filled = false;
+    QT_MARK(2);
 
     // ------------------------------------------------------------------ C. initial nodes (orb_extractor.cc:480-553)
-    int m = 0;  // list length, identical in every thread
-    int nb = 0; // node buffer holding the current list
     {
         const int ninit = lv.nx * lv.ny;
         for (int base = 0; base < ninit; base += QT) {
@@ -270,8 +379,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         __syncthreads();
     }
 
-    const int quota = (int)lv.quota;
-    bool filled = false;
+    QT_MARK(3);
 
     // ------------------------------------------------------------------ D. breadth passes (orb_extractor.cc:414-445)
     while (true) {
@@ -287,7 +395,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
                 }
                 else {
                     int b[5];
-                    split_node(skey, n_lo[nb][i], n_hi[nb][i], meta & DEPTH_MASK, D, b);
+                    split_node(skey, n_lo[nb][i], n_hi[nb][i], meta & DEPTH_MASK, D, Dsorted, &s_i[2], b);
                     t_b1[i] = b[1];
                     t_b2[i] = b[2];
                     t_b3[i] = b[3];
@@ -347,6 +455,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         if (quota < m + POOL) break;
     }
 
+    QT_MARK(4);
     // ------------------------------------------------------------------ E. fullest-first splitting (orb_extractor.cc:447-475)
     int* s_cnt = reinterpret_cast<int*>(s_dyn);  // pool counts cached in shared memory when they fit
     const int s_cnt_cap = POOL_CACHE;
@@ -392,7 +501,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
             if (s < np) {
                 const int i = t_srt[s];
                 int b[5];
-                split_node(skey, n_lo[nb][i], n_hi[nb][i], n_meta[nb][i] & DEPTH_MASK, D, b);
+                split_node(skey, n_lo[nb][i], n_hi[nb][i], n_meta[nb][i] & DEPTH_MASK, D, Dsorted, &s_i[2], b);
                 t_b1[s] = b[1];
                 t_b2[s] = b[2];
                 t_b3[s] = b[3];
@@ -463,6 +572,15 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         if (filled || quota <= m || m == prev) break;
     }
 
+    __syncthreads();
+    if (full || !s_i[2]) break;
+    __syncthreads();
+    full = true;  // a split below the ordered prefix was asked for: redo the level with the complete sort
+  }
+    QT_MARK(5);
+#ifdef LPS_QT_PROFILE
+    if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) { g_qt_prof[8] = N; g_qt_prof[9] = m; g_qt_prof[10] = keybits; g_qt_prof[11] = quota; }
+#endif
     // ------------------------------------------------------------------ F. winner per node, list order
     for (int i = warp; i < m; i += QT / 32) {
         const int lo = n_lo[nb][i], hi = n_hi[nb][i];
@@ -484,6 +602,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         }
     }
     if (tid == 0) *sel_count = (uint32_t)m;
+    QT_MARK(6);
 }
 
 }  // namespace
@@ -496,3 +615,9 @@ void launch_quadtree(const TreeArgs& a, const LevelGeom* lv_host, cudaStream_t s
 }
 
 }  // namespace lps
+
+#ifdef LPS_QT_PROFILE
+extern "C" int lpslam_debug_qt_profile(unsigned long long* out16) {
+    return (int)cudaMemcpyFromSymbol(out16, lps::g_qt_prof, sizeof(unsigned long long) * 16);
+}
+#endif
