@@ -297,6 +297,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
         const int ncl = g.cell_cols * g.cell_rows;
         g.cand_begin = cand_total;
         g.cand_cap = ncl * kCellSlots;
+        LPS_ARG(g.cand_cap < (1 << 24), "level too large: the quadtree packs a candidate index into 24 bits");
         cand_total += g.cand_cap;
         g.node_begin = node_total;
         g.node_cap = 4 * std::max<int>((int)g.quota, g.nx * g.ny) + 8;

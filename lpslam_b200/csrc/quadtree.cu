@@ -27,8 +27,9 @@ constexpr int QT = LPS_QT_THREADS;  // threads per block (two resident blocks pe
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int PART_BITS = 14;  // leading key bits of the one-pass ordering (2^14 shared-memory bins)
+constexpr int BIN_WORDS = (1 << PART_BITS) + (1 << (PART_BITS - 5));  // padded: index i lives at i + i / 32
 constexpr int SORT_CH = 8;  // sort rounds whose loads are issued together
-constexpr int POOL_CACHE = 16 * 1024;  // pool counts cached in shared memory (words)
+constexpr int POOL_CACHE = 4 * 1024;  // pool counts cached in shared memory (words), behind the bins
 constexpr int F_LEAF = 1 << 8, F_POOL = 1 << 9, DEPTH_MASK = 0xFF;
 
 struct Scan {
@@ -73,24 +74,38 @@ __device__ __forceinline__ int lower_digit(const uint32_t* __restrict__ keys, in
     return lo;
 }
 
-// Dsorted = number of leading digits the key array is ordered by (D after the full sort); a split below that depth cannot
-// be answered from a prefix-sorted array: *deeper is raised and the block redoes the level with the full sort
-__device__ __forceinline__ void split_node(const uint32_t* __restrict__ keys, int lo, int hi, int d, int D, int Dsorted, int* deeper,
-                                           int (&b)[5]) {
+__device__ __forceinline__ int pad_idx(int lin) { return lin + (lin >> 5); }
+
+// Dsorted = number of leading digits the key array is ordered by (D after the complete sort); a split below that depth
+// cannot be answered from a prefix-ordered array: *deeper is raised and the block redoes the level with the complete sort.
+// bins != nullptr (prefix ordering): bins[pad_idx(i)] = end of bin i = start of bin i + 1, so the three inner boundaries
+// of a node are three shared-memory reads at its children's first bins instead of three binary searches.
+__device__ __forceinline__ void split_node(const uint32_t* __restrict__ keys, int lo, int hi, int d, int D, int Dsorted,
+                                           const uint32_t* bins, int* deeper, int (&b)[5]) {
     b[0] = lo;
     b[4] = hi;
     if (hi - lo <= 1 || d >= D) {  // a single keypoint always yields exactly one non-empty child
         b[1] = b[2] = b[3] = hi;
         return;
     }
-    if (d >= Dsorted) *deeper = 1;
+    if (d >= Dsorted) {
+        *deeper = 1;
+        b[1] = b[2] = b[3] = hi;
+        return;
+    }
+    if (bins) {
+        const int sh = 2 * (Dsorted - d - 1);
+        const uint32_t child0 = ((keys[lo] >> (2 * (D - d))) << 2) << sh;  // first bin of child 0
+        b[1] = (int)bins[pad_idx((int)(child0 + (1u << sh)) - 1)];
+        b[2] = (int)bins[pad_idx((int)(child0 + (2u << sh)) - 1)];
+        b[3] = (int)bins[pad_idx((int)(child0 + (3u << sh)) - 1)];
+        return;
+    }
     const int shift = 2 * (D - d - 1);
     b[2] = lower_digit(keys, lo, hi, shift, 2);
     b[1] = lower_digit(keys, lo, b[2], shift, 1);
     b[3] = lower_digit(keys, b[2], hi, shift, 3);
 }
-
-__device__ __forceinline__ int pad_idx(int lin) { return lin + (lin >> 5); }
 
 // lanes holding the same 9-bit value (8 digit bits + the "inactive" bit), by votes: MATCH.ANY costs over a thousand
 // cycles per call here (measured through the phase clocks), nine VOTEs and nine LOP3s do not
@@ -176,7 +191,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
 #endif
     uint32_t* s_bin = s_dyn;  // <= 2^PART_BITS words
     if (!full)
-        for (int i = tid; i < nbins; i += QT) s_bin[i] = 0;
+        for (int i = tid; i < nbins + (nbins >> 5) + 1; i += QT) s_bin[i] = 0;
     __syncthreads();
     {
         int ci = warp;
@@ -203,7 +218,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
                         cand_xy[cbase + k] = (uint32_t)x | ((uint32_t)y << 16);
                         cand_sc[cbase + k] = (uint8_t)(sl[j] >> 16);
                         keys[0][cbase + k] = key;
-                        if (!full) atomicAdd(&s_bin[key >> drop], 1u);
+                        if (!full) atomicAdd(&s_bin[pad_idx((int)(key >> drop))], 1u);
                     }
                 }
             }
@@ -238,26 +253,29 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         {   // exclusive prefix over the bins: thread t owns a contiguous run
             const int per = (nbins + QT - 1) / QT, b0 = min(nbins, tid * per), b1 = min(nbins, b0 + per);
             unsigned sum = 0;
-            for (int i = b0; i < b1; ++i) sum += s_bin[i];
+            for (int i = b0; i < b1; ++i) sum += s_bin[pad_idx(i)];
             unsigned long long tot;
             unsigned run = (unsigned)scan.excl(sum, tot);
             for (int i = b0; i < b1; ++i) {
-                const unsigned c = s_bin[i];
-                s_bin[i] = run;
+                const unsigned c = s_bin[pad_idx(i)];
+                s_bin[pad_idx(i)] = run;
                 run += c;
             }
         }
         __syncthreads();
         for (int k0 = tid; k0 < N; k0 += QT * SORT_CH) {
-            uint32_t kk[SORT_CH];
+            uint32_t kk[SORT_CH], sc[SORT_CH];
 #pragma unroll
-            for (int j = 0; j < SORT_CH; ++j) kk[j] = k0 + j * QT < N ? keys[0][k0 + j * QT] : 0u;
+            for (int j = 0; j < SORT_CH; ++j) {
+                kk[j] = k0 + j * QT < N ? keys[0][k0 + j * QT] : 0u;
+                sc[j] = k0 + j * QT < N ? cand_sc[k0 + j * QT] : 0u;
+            }
 #pragma unroll
             for (int j = 0; j < SORT_CH; ++j)
                 if (k0 + j * QT < N) {
-                    const unsigned pos = atomicAdd(&s_bin[kk[j] >> drop], 1u);
+                    const unsigned pos = atomicAdd(&s_bin[pad_idx((int)(kk[j] >> drop))], 1u);
                     keys[1][pos] = kk[j];
-                    vals[1][pos] = (uint32_t)(k0 + j * QT);  // vals[0] is the identity
+                    vals[1][pos] = (sc[j] << 24) | (0xFFFFFFu - (uint32_t)(k0 + j * QT));  // what phase F compares
                 }
         }
         __syncthreads();
@@ -342,6 +360,11 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         __syncthreads();
         cur ^= 1;
     }
+    for (int k = tid; k < N; k += QT) {  // candidate index -> the word phase F compares
+        const uint32_t o = vals[cur][k];
+        vals[cur][k] = ((uint32_t)cand_sc[o] << 24) | (0xFFFFFFu - o);
+    }
+    __syncthreads();
     Dsorted = D;
     }
     skey = keys[cur];
@@ -358,7 +381,12 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
         for (int base = 0; base < ninit; base += QT) {
             const int r = base + tid;
             int lo = 0, hi = 0;
-            if (r < ninit) {
+            if (r < ninit && !full) {  // first and last bin of the initial node
+                const int first = r << (2 * Dpart), last = ((r + 1) << (2 * Dpart)) - 1;
+                lo = first ? (int)s_bin[pad_idx(first - 1)] : 0;
+                hi = (int)s_bin[pad_idx(last)];
+            }
+            else if (r < ninit) {
                 int l = 0, h = N;
                 const int sh = 2 * D;
                 while (l < h) { const int mid = (l + h) >> 1; if ((skey[mid] >> sh) < (unsigned)r) l = mid + 1; else h = mid; }
@@ -395,7 +423,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
                 }
                 else {
                     int b[5];
-                    split_node(skey, n_lo[nb][i], n_hi[nb][i], meta & DEPTH_MASK, D, Dsorted, &s_i[2], b);
+                    split_node(skey, n_lo[nb][i], n_hi[nb][i], meta & DEPTH_MASK, D, Dsorted, full ? nullptr : s_bin, &s_i[2], b);
                     t_b1[i] = b[1];
                     t_b2[i] = b[2];
                     t_b3[i] = b[3];
@@ -457,7 +485,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
 
     QT_MARK(4);
     // ------------------------------------------------------------------ E. fullest-first splitting (orb_extractor.cc:447-475)
-    int* s_cnt = reinterpret_cast<int*>(s_dyn);  // pool counts cached in shared memory when they fit
+    int* s_cnt = reinterpret_cast<int*>(s_dyn) + BIN_WORDS;  // pool counts cached in shared memory when they fit
     const int s_cnt_cap = POOL_CACHE;
     while (!filled) {
         const int prev = m;
@@ -501,7 +529,7 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
             if (s < np) {
                 const int i = t_srt[s];
                 int b[5];
-                split_node(skey, n_lo[nb][i], n_hi[nb][i], n_meta[nb][i] & DEPTH_MASK, D, Dsorted, &s_i[2], b);
+                split_node(skey, n_lo[nb][i], n_hi[nb][i], n_meta[nb][i] & DEPTH_MASK, D, Dsorted, full ? nullptr : s_bin, &s_i[2], b);
                 t_b1[s] = b[1];
                 t_b2[s] = b[2];
                 t_b3[s] = b[3];
@@ -576,29 +604,42 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
     if (full || !s_i[2]) break;
     __syncthreads();
     full = true;  // a split below the ordered prefix was asked for: redo the level with the complete sort
+#ifdef LPS_QT_PROFILE
+    if (tid == 0) atomicAdd(&g_qt_prof[12], 1ull);
+#endif
   }
     QT_MARK(5);
 #ifdef LPS_QT_PROFILE
     if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) { g_qt_prof[8] = N; g_qt_prof[9] = m; g_qt_prof[10] = keybits; g_qt_prof[11] = quota; }
 #endif
     // ------------------------------------------------------------------ F. winner per node, list order
-    for (int i = warp; i < m; i += QT / 32) {
-        const int lo = n_lo[nb][i], hi = n_hi[nb][i];
-        unsigned long long best = 0;
-        for (int k = lo + lane; k < hi; k += 32) {
-            const uint32_t o = sval[k];
-            const unsigned long long cand = ((unsigned long long)cand_sc[o] << 32) | (0xFFFFFFFFu - o);
-            best = cand > best ? cand : best;
-        }
+    // sval holds (score << 24) | (2^24 - 1 - candidate index): the greatest word of a node's range is its first keypoint
+    // with the strictly greatest response. A warp takes 32 consecutive nodes (bounds read by one load, handed round by
+    // shuffles), four nodes' first rounds in flight at a time; the 32 winners' coordinates are fetched together.
+    for (int g0 = 0; g0 < m; g0 += QT) {
+        const int mine = g0 + warp * 32 + lane;
+        const int my_lo = mine < m ? n_lo[nb][mine] : 0, my_hi = mine < m ? n_hi[nb][mine] : 0;
+        const int cntn = min(32, m - (g0 + warp * 32));  // warp-uniform, may be <= 0
+        uint32_t my_best = 0;
+        for (int j = 0; j < cntn; j += 4) {
+            uint32_t v[4];
+            int lo4[4], hi4[4];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const unsigned long long t = __shfl_xor_sync(0xFFFFFFFFu, best, o);
-            best = t > best ? t : best;
+            for (int u = 0; u < 4; ++u) {
+                lo4[u] = __shfl_sync(0xFFFFFFFFu, my_lo, (j + u) & 31);
+                hi4[u] = __shfl_sync(0xFFFFFFFFu, my_hi, (j + u) & 31);
+                v[u] = lo4[u] + lane < hi4[u] ? sval[lo4[u] + lane] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                for (int k = lo4[u] + 32 + lane; k < hi4[u]; k += 32) v[u] = max(v[u], sval[k]);
+                v[u] = __reduce_max_sync(0xFFFFFFFFu, v[u]);
+                if (lane == j + u) my_best = v[u];
+            }
         }
-        if (lane == 0) {
-            const uint32_t o = 0xFFFFFFFFu - (uint32_t)(best & 0xFFFFFFFFu);
-            sel_xy[i] = cand_xy[o];
-            sel_sc[i] = (uint8_t)(best >> 32);
+        if (mine < m) {
+            sel_xy[mine] = cand_xy[0xFFFFFFu - (my_best & 0xFFFFFFu)];
+            sel_sc[mine] = (uint8_t)(my_best >> 24);
         }
     }
     if (tid == 0) *sel_count = (uint32_t)m;
@@ -609,7 +650,8 @@ __global__ void __launch_bounds__(QT, 2048 / QT > 2 ? 2 : 2048 / QT) k_quadtree(
 
 void launch_quadtree(const TreeArgs& a, const LevelGeom* lv_host, cudaStream_t st) {
     (void)lv_host;
-    const size_t smem = (size_t)(POOL_CACHE > RADIX * 33 ? POOL_CACHE : RADIX * 33) * sizeof(uint32_t);
+    static_assert(BIN_WORDS >= RADIX * 33, "the LSD counters reuse the bin area");
+    const size_t smem = (size_t)(BIN_WORDS + POOL_CACHE) * sizeof(uint32_t);
     cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_quadtree<<<dim3(a.batch, a.num_levels), QT, smem, st>>>(a);
 }

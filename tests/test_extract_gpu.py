@@ -99,3 +99,16 @@ def test_batch_matches_single(orb, oracle):
         assert len(kp) == len(okp)
         assert np.array_equal(kp["x"], okp["x"]) and np.array_equal(kp["y"], okp["y"])
         assert (desc == odesc).all(axis=1).mean() >= 0.999
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_clustered_corners_deep_tree(orb, oracle, seed):
+    """all corners sit in a few small patches of noise on a flat canvas: the quadtree has to split far below the depth the
+    one-pass prefix ordering of k_quadtree covers, so levels are redone with the complete sort (orb_extractor.cc:401-475)"""
+    rng = np.random.default_rng(seed)
+    img = np.full((480, 640), 120, np.uint8)
+    for _ in range(3):
+        y0, x0 = int(rng.integers(40, 380)), int(rng.integers(40, 540))
+        img[y0:y0 + 48, x0:x0 + 56] = rng.integers(0, 256, (48, 56), dtype=np.uint8)
+    for n in (300, 1000, 3000):
+        assert compare(orb, oracle, img, n) > 50

@@ -23,3 +23,15 @@ names = ["A list+keys", "B radix sort", "C initial nodes", "(quota)", "D breadth
 for i in range(6):
     print(f"{names[i]:18s} {t[i + 1] - t[i]:9d} clk")
 print("total", t[6] - t[0], "clk; N =", t[8], "m =", t[9], "keybits =", t[10], "quota =", t[11])
+# deep trees: clustered corners force splits below the prefix-ordered depth (fallback counter, profile build only)
+import numpy as np  # noqa: E402
+rng = np.random.default_rng(1)
+img = np.full((480, 640), 120, np.uint8)
+for _ in range(3):
+    y0, x0 = int(rng.integers(40, 380)), int(rng.integers(40, 540))
+    img[y0:y0 + 48, x0:x0 + 56] = rng.integers(0, 256, (48, 56), dtype=np.uint8)
+L.lpslam_debug_qt_profile(out)
+before = out[12]
+orb.orb_extractor(max_num_keypts=3000).extract(img)
+L.lpslam_debug_qt_profile(out)
+print("complete-sort fallbacks on the clustered image:", out[12] - before, "(of 8 levels); during the stereo batches:", before)
