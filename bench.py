@@ -217,8 +217,24 @@ def gpu_arm(args):
     dptr, dpitch, dstride = C.c_void_p(), C.c_size_t(), C.c_size_t()
     check(L.lpslam_orb_input_dev(ext._h, W, H, C.byref(dptr), C.byref(dpitch), C.byref(dstride)))
 
+    # consecutive steps alternate between LPSLAM_DEV_CONTEXTS extractor contexts (own stream, own resident batch): a step's
+    # latency-bound tail (quadtree, descriptors, stereo) then runs beside the next step's FAST instead of before it
+    n_dev = max(1, int(os.environ.get("LPSLAM_DEV_CONTEXTS", "2")))
+    dev_ctx = [(ext, dptr, dpitch)]
+    for _ in range(n_dev - 1):
+        e2 = orb.orb_extractor(max_num_keypts=KPTS, device=local, max_batch=2 * B)
+        check(L.lpslam_stereo_frames(e2._h, pl_all, pr_all, B, W, H, W, FX_B, BASELINE, okp, odesc, 2 * B * 4096, offs_all.ctypes.data,
+                                     oxr, odep))
+        p2, pitch2, stride2 = C.c_void_p(), C.c_size_t(), C.c_size_t()
+        check(L.lpslam_orb_input_dev(e2._h, W, H, C.byref(p2), C.byref(pitch2), C.byref(stride2)))
+        dev_ctx.append((e2, p2, pitch2))
+    dev_streams = [torch.cuda.ExternalStream(L.lpslam_orb_stream(e._h), device=local) for e, _, _ in dev_ctx]
+    turn = [0]
+
     def dev_step():
-        check(L.lpslam_stereo_frames_dev(ext._h, dptr, B, W, H, dpitch.value, FX_B, BASELINE))
+        e, p_in, pitch_in = dev_ctx[turn[0] % len(dev_ctx)]
+        turn[0] += 1
+        check(L.lpslam_stereo_frames_dev(e._h, p_in, B, W, H, pitch_in.value, FX_B, BASELINE))
 
     def barrier():
         torch.cuda.synchronize()
@@ -226,19 +242,21 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup, on_stream):
+    def timed(fn, steps, warmup, on_streams):
         for _ in range(warmup):
             fn()
         barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = [torch.cuda.Event(enable_timing=True) for _ in on_streams]
         t0 = time.perf_counter()
-        ev0.record(on_stream)
+        ev0.record(on_streams[0])  # everything is idle after the barrier: the first stream's mark is the start of all
         for _ in range(steps):
             fn()
-        ev1.record(on_stream)
+        for ev, st in zip(ev1, on_streams):
+            ev.record(st)
         torch.cuda.synchronize()
         wall = (time.perf_counter() - t0) * 1e3
-        ms = ev0.elapsed_time(ev1)
+        ms = max(ev0.elapsed_time(ev) for ev in ev1)
         t = torch.tensor([ms, wall], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -247,7 +265,8 @@ def gpu_arm(args):
 
     clocks = ClockSampler(local)
     clocks.start()
-    dev_ms, _ = timed(dev_step, args.steps, args.warmup, stream)
+    dev_ms, _ = timed(dev_step, args.steps, args.warmup, dev_streams)
+    turn[0] = 0  # the stage pass below uses the first context
     clk = clocks.stop()
     # end to end: every context's host thread replays its share of each step back to back (a replay thread per context,
     # no join between steps), so one context's PCIe copies run beside the others' kernels; wall clock, the calls block
@@ -274,7 +293,7 @@ def gpu_arm(args):
     stage = {k: 0.0 for k in ("pyramid", "fast", "quadtree", "blur", "describe")}
     reps = 5
     for _ in range(reps):
-        dev_step()
+        check(L.lpslam_stereo_frames_dev(ext._h, dptr, B, W, H, dpitch.value, FX_B, BASELINE))
         st = ext.stage_times()
         for k in stage:
             stage[k] += st[k] / reps
@@ -318,7 +337,7 @@ def gpu_arm(args):
     def knn_step():
         knn.sharded_query(db, queries, KNN_QUERIES, cur.cuda_stream)
 
-    knn_ms, _ = timed(knn_step, max(args.steps, 5), 3, cur)
+    knn_ms, _ = timed(knn_step, max(args.steps, 5), 3, [cur])
     knn_steps = max(args.steps, 5)
     cmp_per_step = KNN_QUERIES * KNN_ROWS_PER_GPU * world
     knn_out = {"metric": "Gdesc-cmp/s kNN", "value": cmp_per_step * knn_steps / (knn_ms * 1e-3) / 1e9, "unit": "1e9 256-bit comparisons/s",
@@ -337,7 +356,9 @@ def gpu_arm(args):
                                   "matching (BASELINE configs[1])", "pairs_per_step_per_gpu": B, "images_per_step_per_gpu": 2 * B,
                       "keypoints_per_step": n_kp, "stereo_matches_per_step": n_match,
                       "l2": "inputs + pyramids of one step (%.0f MB) exceed the 126 MB L2" % (2 * B * 2 * 2.85),
-                      "parallelism": "frame-parallel x%d" % world},
+                      "parallelism": "frame-parallel x%d" % world,
+                      "contexts": "value: consecutive steps alternate between %d extractor contexts per GPU (own stream, own "
+                                  "resident batch); e2e: %d contexts per GPU" % (len(dev_ctx), len(halves))},
            "e2e": {"value": pairs_total / (e2e_ms * 1e-3), "unit": "stereo frames/s", "ms_per_step": e2e_ms / args.steps,
                    "h2d_bytes_per_step": 2 * B * W * H, "d2h_bytes_per_step": n_kp * (28 + 32 + 8) + 4 * (2 * B + 2),
                    "timing": "wall clock around the blocking host-buffer C-ABI calls: %d contexts per GPU, each replayed by its own host thread (its share of every step, back to back), max over ranks" % len(halves)},
