@@ -208,8 +208,9 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
             // halves hold d + 256: best = max(A - 256, 256 - Bm)
             const int ba = max((int)(A & 0xFFFFu) - 256, 256 - (int)(Bm & 0xFFFFu));
             const int bb = max((int)(A >> 16) - 256, 256 - (int)(Bm >> 16));
-            s_best[(ida >> 6) + 1][(ida & 63) + 1] = (uint8_t)max(ba, 0);
-            s_best[(idb >> 6) + 1][(idb & 63) + 1] = (uint8_t)max(bb, 0);
+            // strengths at or below the threshold are stored as 0: a corner beats such a neighbour anyway (its score is 0)
+            s_best[(ida >> 6) + 1][(ida & 63) + 1] = (uint8_t)(ba > thr ? ba : 0);
+            s_best[(idb >> 6) + 1][(idb & 63) + 1] = (uint8_t)(bb > thr ? bb : 0);
             // corners go into a second list: only they are looked at by the suppression
             if (ba > thr) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)ida;
             if (bb > thr && 2 * i + 1 < n) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)idb;
@@ -220,10 +221,10 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
         for (int i = tid; i < nc; i += 256) {
             const int id = s_corner[i], lx = id & 63, ly = id >> 6;
             const uint8_t* b = &s_best[ly + 1][lx + 1];
-            const int s = b[0] - 1;
-            auto sc = [thr](int v) { return v > thr ? v - 1 : 0; };
-            const bool keep = s > sc(b[-1]) && s > sc(b[1]) && s > sc(b[-BP - 1]) && s > sc(b[-BP]) && s > sc(b[-BP + 1])
-                              && s > sc(b[BP - 1]) && s > sc(b[BP]) && s > sc(b[BP + 1]);
+            // score = best - 1 for corners, 0 otherwise: strictly greater than all eight neighbours' scores
+            const int nb = max(max(max((int)b[-1], (int)b[1]), max((int)b[-BP - 1], (int)b[-BP])),
+                               max(max((int)b[-BP + 1], (int)b[BP - 1]), max((int)b[BP], (int)b[BP + 1])));
+            const bool keep = (int)b[0] > max(nb, 1);  // a strength of 1 (threshold 0) scores 0 and is never kept
             if (keep) atomicOr(&s_bits[ly][lx >> 5], 1u << (lx & 31));
         }
         __syncthreads();
