@@ -105,14 +105,14 @@ __global__ void __launch_bounds__(1024) k_offsets(DescribeArgs a) {
     }
 }
 
-__device__ __forceinline__ int dp4a_us(uint32_t pix, uint32_t w, int acc) {  // unsigned pixels x signed weights
-    int d;
-    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pix), "r"(w), "r"(acc));
-    return d;
-}
-
 constexpr int kDescribeBlocksPerSM = 2;
 constexpr unsigned kRun = 8;  // consecutive packed rows per warp before it strides on
+// The blurred patch a descriptor taps (|row|, |col| <= 18: the pattern's points lie within 13 of the centre, rotated) is
+// staged in shared memory by cp.async while the orientation is computed: rows of kTapPitch bytes starting at the 16-byte
+// boundary at or below column -18, four lanes per row and eight rows per copy. The 512 taps of a keypoint then are
+// shared-memory byte reads instead of 16 fully divergent global loads per lane.
+constexpr int kTapReach = 18, kTapRows = 2 * kTapReach + 1, kTapPitch = 80, kTapBuf = 40 * kTapPitch;
+constexpr int kDescribeSmem = 8 * 2 * kTapBuf;  // 8 warps, double buffered
 
 // Software pipeline over a warp's keypoints, three deep: the position of keypoint k + 2 is being read while the patch
 // rows of k + 1 are in flight and k is computed. Warps take runs of kRun consecutive packed rows, strided by the grid, so
@@ -128,6 +128,8 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
     // s_mask[|v|][sh][piece] keeps the bytes inside the disc (|u| <= u_max[|v|], feature/orb_extractor.cc:228-241); with the
     // byte position p as IDP.4A weight, m10 = sum p I - (sh + 15) sum I and m01 = v sum I.
     __shared__ uint4 s_mask[16 * 16 * 3];
+    extern __shared__ __align__(16) uint8_t s_tap[];
+    uint8_t* my_tap = s_tap + (threadIdx.x >> 5) * 2 * kTapBuf;
     for (int e = threadIdx.x; e < 16 * 16 * 3; e += blockDim.x) {
         const int piece = e % 3, sh = (e / 3) % 16, um = c_umax[e / 48];
         uint32_t m[4];
@@ -166,7 +168,7 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
     struct Rows {  // stage 2: its patch rows on the way
         unsigned k;
         int frame, level, score, px, py;
-        unsigned sh;
+        unsigned sh, tsh;
         uint4 d[4];
         bool ok;
     };
@@ -197,6 +199,7 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
         }
         return L;
     };
+    int tap_turn = 0;  // buffer the next staged patch goes to
     auto fetch = [&](const Loc& L) {
         Rows R;
         R.k = L.k;
@@ -206,7 +209,7 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
         R.score = L.score;
         R.px = (int)(L.xy & 0xFFFFu) + kBorder;
         R.py = (int)(L.xy >> 16) + kBorder;
-        R.sh = 0;
+        R.sh = R.tsh = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) R.d[i] = make_uint4(0, 0, 0, 0);
         if (L.ok) {
@@ -220,7 +223,21 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
                 R.d[i] = (lane < 30 && r < kPatch) ? __ldg(reinterpret_cast<const uint4*>(mine + (ptrdiff_t)(r - kHalfPatch) * lv.pitch))
                                                    : make_uint4(0, 0, 0, 0);
             }
+            // blurred patch -> this warp's buffer `tap_turn`
+            const uint8_t* t0 = lv.blur + L.frame * lv.frame_stride + (size_t)R.py * lv.pitch + (R.px - kTapReach);
+            R.tsh = (unsigned)(reinterpret_cast<uintptr_t>(t0) & 15);
+            const uint8_t* src = t0 - R.tsh + 16 * (lane & 3);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(my_tap + tap_turn * kTapBuf + 16 * (lane & 3));
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+                const int r = 8 * i + (lane >> 2);
+                if (r < kTapRows)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + r * kTapPitch),
+                                 "l"(src + (ptrdiff_t)(r - kTapReach) * lv.pitch));
+            }
         }
+        asm volatile("cp.async.commit_group;");
+        tap_turn ^= 1;
         return R;
     };
     auto next_k = [&](unsigned k) { return ((k + 1) % kRun) ? k + 1 : k + 1 + (warps_total - 1) * kRun; };
@@ -231,7 +248,6 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
     while (B.ok) {
         const Loc A2 = locate(next_k(A.k));
         const LevelGeom& lv = a.lv[B.level];
-        const int pitch = lv.pitch;
         // ---- orientation: masked bytes, IDP.4A with the byte positions and with ones ----
         unsigned sum_p = 0;
         int m01 = 0;
@@ -262,7 +278,10 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
         const float arad = (float)((double)angle * 3.14159265358979323846 / 180.0);
         const float ca = ref_cos(arad);
         const float sa = ref_cos(__fsub_rn(3.14159265358979f / 2.0f, arad));
-        const uint8_t* __restrict__ cb = lv.blur + B.frame * lv.frame_stride + (size_t)B.py * pitch + B.px;
+        // the patch of this keypoint was sent off one iteration ago, into the buffer the next fetch does not use
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        const uint8_t* cb = my_tap + (tap_turn ^ 1) * kTapBuf + kTapReach * kTapPitch + kTapReach + B.tsh;
         int v0[8], v1[8];
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
@@ -271,8 +290,8 @@ __global__ void __launch_bounds__(256, kDescribeBlocksPerSM) k_describe(Describe
             const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
             const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
             const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
-            v0[b] = __ldg(cb + r0 * pitch + q0);
-            v1[b] = __ldg(cb + r1 * pitch + q1);
+            v0[b] = cb[r0 * kTapPitch + q0];
+            v1[b] = cb[r1 * kTapPitch + q1];
         }
         // the next keypoint's rows leave now, behind this one's descriptor taps
         const unsigned k = B.k;
@@ -310,7 +329,12 @@ void launch_describe(const DescribeArgs& a, cudaStream_t st) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    k_describe<<<sms * kDescribeBlocksPerSM, 256, 0, st>>>(a);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, kDescribeSmem);
+        attr_set = true;
+    }
+    k_describe<<<sms * kDescribeBlocksPerSM, 256, kDescribeSmem, st>>>(a);
 }
 
 }  // namespace lps
