@@ -109,7 +109,7 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
     size_t o_desc = o_kp + align_up(sizeof(lpslam_keypoint) * (size_t)rows, 256), o_off = o_desc + align_up(32 * (size_t)rows, 256);
     size_t o_rec = o_off + 256, o_xr = o_rec + align_up(8 * (size_t)rows, 256), o_dep = o_xr + align_up(4 * (size_t)rows, 256);
     size_t o_corr = o_dep + align_up(4 * (size_t)rows, 256), o_perm = o_corr + align_up(4 * (size_t)rows, 256);
-    size_t o_rows = o_perm + align_up(4 * (size_t)rows, 256), total = o_rows + align_up(4 * (size_t)(level_h[0] + 1), 256);
+    size_t o_rows = o_perm + align_up(16 * (size_t)rows, 256), total = o_rows + align_up(4 * (size_t)(level_h[0] + 1), 256);
     LPS_CUDA(scratch_alloc((void**)&dev, total));
     cudaStream_t st = nullptr;
     int rc = LPSLAM_OK;
@@ -152,7 +152,7 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
         a.x_right = (float*)(dev + o_xr);
         a.depth = (float*)(dev + o_dep);
         a.corr = (int*)(dev + o_corr);
-        a.perm = (uint32_t*)(dev + o_perm);
+        a.perm = (uint4*)(dev + o_perm);
         a.row_start = (uint32_t*)(dev + o_rows);
         a.focal_x_baseline = focal_x_baseline;
         a.true_baseline = true_baseline;

@@ -191,7 +191,7 @@ struct StereoArgs {
     float* x_right;              // per packed row (left-eye rows are meaningful), -1 = no match
     float* depth;
     int* corr;                   // best SAD as int, -1 = no match
-    uint32_t* perm;              // per packed row: right-eye keypoints of a pair ordered by image row (counting sort)
+    uint4* perm;                 // right-eye keypoints of a pair in row order: (row interval, octave, x bits, packed row)
     uint32_t* row_start;         // [n_pairs][rows0 + 1] first perm slot (relative to the right eye's first row) of every image row
     float focal_x_baseline, true_baseline;
     int rows0;                   // level-0 image rows

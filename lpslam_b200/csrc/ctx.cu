@@ -340,7 +340,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
     const size_t off_sxr = plan.take(4 * (size_t)out_cap);
     const size_t off_sdep = plan.take(4 * (size_t)out_cap);
     const size_t off_scorr = plan.take(4 * (size_t)out_cap);
-    const size_t off_sperm = plan.take(4 * (size_t)out_cap);
+    const size_t off_sperm = plan.take(16 * (size_t)out_cap);
     const size_t off_srows = plan.take(4 * (size_t)(height + 1) * ((max_batch + 1) / 2));
 
     LPS_CUDA(cudaMalloc(&arena, plan.off));
@@ -436,7 +436,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
     stereo.x_right = (float*)(arena + off_sxr);
     stereo.depth = (float*)(arena + off_sdep);
     stereo.corr = (int*)(arena + off_scorr);
-    stereo.perm = (uint32_t*)(arena + off_sperm);
+    stereo.perm = (uint4*)(arena + off_sperm);
     stereo.row_start = (uint32_t*)(arena + off_srows);
     stereo.rows0 = height;
     LPS_CUDA(cudaStreamSynchronize(stream));  // the host-side tables go out of scope

@@ -88,8 +88,11 @@ __global__ void __launch_bounds__(1024) k_stereo_rows(StereoArgs a) {
     }
     __syncthreads();
     for (uint32_t k = rbeg + tid; k < rend; k += 1024) {
-        const uint32_t pos = atomicAdd(&s_rows[min(max((int)a.kp[k].y, 0), rows - 1)], 1u);
-        a.perm[rbeg + pos] = k;
+        const lpslam_keypoint kp = a.kp[k];
+        const uint32_t pos = atomicAdd(&s_rows[min(max((int)kp.y, 0), rows - 1)], 1u);
+        const uint2 rec = a.rec[k];
+        // everything the candidate scan tests, in scan order: (row interval, octave, x, packed row of the keypoint)
+        a.perm[rbeg + pos] = make_uint4(rec.x, rec.y, __float_as_uint(kp.x), k);
     }
 }
 
@@ -122,12 +125,12 @@ __global__ void __launch_bounds__(256) k_stereo_match(StereoArgs a) {
         const uint32_t* __restrict__ rs = a.row_start + (size_t)pair * (a.rows0 + 1);
         const uint32_t s_lo = rs[max(row - reach, 0)], s_hi = rs[min(row + reach + 1, a.rows0)];
         for (uint32_t s = s_lo + lane; s < s_hi; s += 32) {
-            const uint32_t ir = a.perm[rbeg + s];
-            const uint2 rec = a.rec[ir];
+            const uint4 rec = a.perm[rbeg + s];
+            const uint32_t ir = rec.w;
             const int min_r = (int)(rec.x & 0xFFFFu), max_r = (int)(rec.x >> 16), oct = (int)rec.y;
             if (row < min_r || row > max_r) continue;
             if (oct < kl.octave - 1 || oct > kl.octave + 1) continue;
-            const float xr = a.kp[ir].x;
+            const float xr = __uint_as_float(rec.z);
             if (xr < min_xr || max_xr < xr) continue;
             const uint4* dr = reinterpret_cast<const uint4*>(a.desc + (size_t)ir * 32);
             const unsigned d = hamming256(l0, l1, __ldg(dr), __ldg(dr + 1));
