@@ -278,6 +278,25 @@ int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_reproj_match
                              const float* kp_x_right, const uint8_t* kp_has_landmark, const float* scale_factors,
                              int32_t* kp_match_lm, uint32_t* n_matches);
 
+/* The search loop shared by match::fuse::detect_duplication (match/fuse.cc:12-120, loop closing: landmarks of the loop
+ * candidate's covisibilities into a keyframe under a Sim3) and fuse::replace_duplication (match/fuse.cc:122-266, local
+ * mapping: fusing a keyframe's landmarks into its neighbours). The caller keeps the per-landmark geometry (will_be_erased,
+ * reproject_to_image, the valid-distance and viewing-angle gates, predict_scale_level: fuse.cc:28-66 / :134-172) and
+ * passes every surviving landmark as a row; every row independently takes the keypoint with the smallest Hamming distance
+ * (strict '<', first wins) inside margin * scale_factors[level] whose octave is level - 1 or level. best_idx[row] = that
+ * keypoint when its distance is <= HAMMING_DIST_THR_LOW (50), else -1; best_dist (nullable) = the distance (256 when the
+ * row had no candidate). The association step behind it (duplicate / add_observation, fuse.cc:103-116 / :240-261) walks
+ * best_idx in row order on the caller's landmark objects.
+ *   chi_square_gate != 0  replace_duplication's reprojection-error gate (fuse.cc:199-222: 3 degrees of freedom for
+ *                         keypoints with kp_x_right >= 0, 2 otherwise, against inv_level_sigma_sq[octave])
+ *   unsigned_levels != 0  replace_duplication compares unsigned levels, so `octave < level - 1` wraps for level 0 and such
+ *                         rows never match (fuse.cc:193); detect_duplication uses int (fuse.cc:60,84) */
+int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi_square_gate, int unsigned_levels, uint32_t n_lm,
+                      const uint8_t* lm_active, const double* lm_reproj /*n_lm x 2*/, const float* lm_x_right,
+                      const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp, const lpslam_keypoint* kp_undist,
+                      const uint8_t* kp_desc, const float* kp_x_right, const float* scale_factors,
+                      const float* inv_level_sigma_sq, int32_t* best_idx, uint32_t* best_dist, uint32_t* n_fused);
+
 /* The search loop of match::bow_tree::match_frame_and_keyframe (match/bow_tree.cc:16-126), the matcher of BoW-based
  * tracking and relocalisation: the caller walks the two BoW feature vectors (the vocabulary library's containers) and
  * emits, in iteration order, one row per keyframe keypoint that holds a live landmark (bow_tree.cc:45-57) with its

@@ -70,6 +70,11 @@ struct ProjArgs {
     const uint32_t* cand_end;
     const uint32_t* cand_items;
     int claim_in_smem;  // k_lm_resolve: a per-keypoint claim table follows the bitmap in shared memory
+    // fuse::replace_duplication's reprojection-error gate (fuse.cc:199-222)
+    int chi_gate;
+    const float* inv_sigma_sq;
+    int32_t* row_best;   // k_rows_best: keypoint of every row or -1
+    uint32_t* row_dist;  // its Hamming distance (256 when the row saw no candidate)
 };
 
 __device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
@@ -278,6 +283,21 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
                         if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
                     }
                 }
+                if (a.chi_gate) {
+                    // double (reprojection) - float (keypoint) differences, float x_right difference, summed in the
+                    // reference's order; 3 degrees of freedom when the keypoint has a stereo match, 2 otherwise
+                    const double ex = __dsub_rn(a.lm_reproj[2 * (size_t)il], (double)k.x);
+                    const double ey = __dsub_rn(a.lm_reproj[2 * (size_t)il + 1], (double)k.y);
+                    double sq = __dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey));
+                    const float kxr = a.x_right[i];
+                    double chi = (double)5.99146f;
+                    if (kxr >= 0) {
+                        const float exr = __fsub_rn(a.lm_x_right[il], kxr);
+                        sq = __dadd_rn(sq, (double)__fmul_rn(exr, exr));
+                        chi = (double)7.81473f;
+                    }
+                    if (chi < __dmul_rn(sq, (double)a.inv_sigma_sq[k.octave])) continue;
+                }
                 const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
                 f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)), k.octave);
             }
@@ -320,6 +340,16 @@ __global__ void k_proj_topk(ProjArgs a) {
     }
     a.top_key[il] = make_uint4(key[0], key[1], key[2], key[3]);
     a.top_idx[il] = make_int4(idx[0], idx[1], idx[2], idx[3]);
+}
+
+// rows that do not compete for keypoints (match/fuse.cc): the first kept candidate is the answer
+__global__ void k_rows_best(ProjArgs a) {
+    const uint32_t il = blockIdx.x * blockDim.x + threadIdx.x;
+    if (il >= a.n_last) return;
+    const uint32_t key = a.top_key[il].x;
+    const unsigned d = key == EMPTY ? MAX_HAMMING_DIST : (key >> 20);
+    a.row_dist[il] = d;
+    a.row_best[il] = (key != EMPTY && d <= a.hamm_thr) ? (a.top_idx[il].x & 0x00FFFFFF) : -1;
 }
 
 // Ordered resolve for the reprojection / candidate-list matchers (projection.cc:31-79, :145-190, :264-296,
@@ -1125,6 +1155,109 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
             kp_match_row[id] = -1;
             --*n_matches;
         }
+    }
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi_square_gate, int unsigned_levels, uint32_t n_lm,
+                                 const uint8_t* lm_active, const double* lm_reproj, const float* lm_x_right,
+                                 const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp,
+                                 const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const float* kp_x_right,
+                                 const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx,
+                                 uint32_t* best_dist, uint32_t* n_fused) {
+    LPS_ARG(cam && scale_factors && n_fused, "null argument");
+    *n_fused = 0;
+    LPS_ARG(n_lm == 0 || (lm_active && lm_reproj && lm_scale_level && lm_desc && best_idx), "null landmark argument");
+    LPS_ARG(n_kp == 0 || (kp_undist && kp_desc), "null keyframe argument");
+    LPS_ARG(!chi_square_gate || (inv_level_sigma_sq && (n_lm == 0 || lm_x_right) && (n_kp == 0 || kp_x_right)),
+            "the reprojection-error gate needs x_right of both sides and inv_level_sigma_sq");
+    LPS_ARG(cam->grid_cols >= 1 && cam->grid_rows >= 1 && cam->num_scale_levels >= 1 && cam->num_scale_levels <= (uint32_t)kMaxLevels,
+            "bad camera grid / level count");
+    LPS_ARG(n_kp < (1u << 20), "too many keypoints");
+    for (uint32_t i = 0; i < n_lm; ++i) {
+        best_idx[i] = -1;
+        if (best_dist) best_dist[i] = 256;
+    }
+    if (n_kp == 0 || n_lm == 0) return LPSLAM_OK;
+    std::vector<uint8_t> act(lm_active, lm_active + n_lm);
+    for (uint32_t i = 0; i < n_lm; ++i) {
+        LPS_ARG(!act[i] || (lm_scale_level[i] >= 0 && (uint32_t)lm_scale_level[i] < cam->num_scale_levels),
+                "landmark scale level out of range");
+        // fuse.cc:193 compares unsigned levels: `scale_level < pred_scale_level - 1` wraps for a predicted level of 0
+        if (unsigned_levels && lm_scale_level[i] == 0) act[i] = 0;
+    }
+    const uint32_t ncell = cam->grid_cols * cam->grid_rows;
+    ArenaBump ar;
+    const size_t o_act = ar.take(n_lm), o_rp = ar.take(16 * (size_t)n_lm), o_lxr = ar.take(4 * (size_t)n_lm), o_lvl = ar.take(4 * (size_t)n_lm);
+    const size_t o_ld = ar.take(32 * (size_t)n_lm), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_kp);
+    const size_t o_desc = ar.take(32 * (size_t)n_kp), o_xr = ar.take(4 * (size_t)n_kp), o_sc = ar.take(4 * kMaxLevels);
+    const size_t o_isq = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
+    const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_rb = ar.take(4 * (size_t)n_lm), o_rd = ar.take(4 * (size_t)n_lm);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    cudaError_t e = cudaSuccess;
+    std::vector<uint32_t> dist(n_lm);
+    do {
+#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
+        UP(o_act, act.data(), n_lm);
+        UP(o_rp, lm_reproj, 16 * (size_t)n_lm);
+        UP(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
+        UP(o_ld, lm_desc, 32 * (size_t)n_lm);
+        UP(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
+        UP(o_desc, kp_desc, 32 * (size_t)n_kp);
+        UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+        if (chi_square_gate) {
+            UP(o_lxr, lm_x_right, 4 * (size_t)n_lm);
+            UP(o_xr, kp_x_right, 4 * (size_t)n_kp);
+            UP(o_isq, inv_level_sigma_sq, 4 * (size_t)cam->num_scale_levels);
+        }
+#undef UP
+        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        ProjArgs a = {};
+        a.cam = *cam;
+        a.mode = 1;
+        a.n_last = n_lm;
+        a.n_curr = n_kp;
+        a.last_has_lm = dev + o_act;
+        a.last_desc = dev + o_ld;
+        a.last_octave = (const int32_t*)(dev + o_lvl);
+        a.lm_reproj = (const double*)(dev + o_rp);
+        a.lm_x_right = (const float*)(dev + o_lxr);
+        a.level_lo = -1;  // fuse.cc:84-87 / :193-195: octave in [pred - 1, pred]
+        a.level_hi = 0;
+        a.use_xr = 0;
+        a.hamm_thr = 50;  // HAMMING_DIST_THR_LOW, fuse.cc:99 / :236
+        a.chi_gate = chi_square_gate ? 1 : 0;
+        a.inv_sigma_sq = (const float*)(dev + o_isq);
+        a.kp = (const lpslam_keypoint*)(dev + o_kp);
+        a.desc = dev + o_desc;
+        a.x_right = (const float*)(dev + o_xr);
+        a.scale = (const float*)(dev + o_sc);
+        a.margin = margin;
+        a.cell_count = (uint32_t*)(dev + o_cc);
+        a.cell_start = (uint32_t*)(dev + o_cs);
+        a.cell_fill = (uint32_t*)(dev + o_cf);
+        a.cell_items = (uint32_t*)(dev + o_ci);
+        a.top_key = (uint4*)(dev + o_tkey);
+        a.top_idx = (int4*)(dev + o_tidx);
+        a.row_best = (int32_t*)(dev + o_rb);
+        a.row_dist = (uint32_t*)(dev + o_rd);
+        k_grid_count<<<(n_kp + 255) / 256, 256>>>(a);
+        k_grid_scan<<<1, 1024>>>(a);
+        k_grid_fill<<<(n_kp + 255) / 256, 256>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
+        k_proj_topk<<<(n_lm + 127) / 128, 128>>>(a);
+        k_rows_best<<<(n_lm + 255) / 256, 256>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(best_idx, dev + o_rb, 4 * (size_t)n_lm, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(dist.data(), dev + o_rd, 4 * (size_t)n_lm, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+    } while (false);
+    scratch_free(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_fuse", __FILE__, __LINE__);
+    for (uint32_t i = 0; i < n_lm; ++i) {
+        if (best_dist) best_dist[i] = dist[i];
+        *n_fused += best_idx[i] >= 0;
     }
     return LPSLAM_OK;
 }

@@ -146,6 +146,52 @@ def match_reprojected(cam, params, lm_active, lm_reproj, lm_x_right, lm_scale_le
     return out, int(n.value)
 
 
+register("lpslam_match_fuse", C.c_int, [C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, _lib.u32p])
+
+
+class fuse:
+    """match::fuse (match/fuse.h): the keypoint search of detect_duplication / replace_duplication. The caller keeps the
+    per-landmark geometry and the association step (they work on its landmark / keyframe objects); rows are the landmarks
+    that passed the visibility gates, with their reprojection, x_right and predicted scale level."""
+
+    def __init__(self, lowe_ratio=0.6):
+        self.lowe_ratio_ = float(lowe_ratio)  # the fuse matcher carries it (match/base.h) but never applies it
+
+    @staticmethod
+    def _search(cam, margin, chi, unsigned_levels, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_descs, undist_keypts, descs,
+                stereo_x_right, scale_factors, inv_level_sigma_sq):
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64).reshape(-1, 2)
+        lxr = None if lm_x_right is None else np.ascontiguousarray(lm_x_right, np.float32)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_descs, np.uint8).reshape(-1, 32)
+        kp = np.ascontiguousarray(undist_keypts, KP_DTYPE)
+        cd = np.ascontiguousarray(descs, np.uint8)
+        xr = None if stereo_x_right is None else np.ascontiguousarray(stereo_x_right, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        isq = None if inv_level_sigma_sq is None else np.ascontiguousarray(inv_level_sigma_sq, np.float32)
+        best = np.full(len(act), -1, np.int32)
+        dist = np.full(len(act), 256, np.uint32)
+        n = C.c_uint32(0)
+        check(lib().lpslam_match_fuse(C.byref(cam), float(margin), int(chi), int(unsigned_levels), len(act), act.ctypes.data, rp.ctypes.data,
+                                      _lib.ptr(lxr), lvl.ctypes.data, ld.ctypes.data, len(kp), kp.ctypes.data, cd.ctypes.data,
+                                      _lib.ptr(xr), sf.ctypes.data, _lib.ptr(isq), best.ctypes.data, dist.ctypes.data, C.byref(n)))
+        return best, dist, int(n.value)
+
+    def detect_duplication(self, cam, lm_active, lm_reproj, lm_scale_level, lm_descs, undist_keypts, descs, scale_factors, margin):
+        """match/fuse.cc:12-120 (search loop :69-101): returns (best_idx, best_dist, num_fused)"""
+        return self._search(cam, margin, False, False, lm_active, lm_reproj, None, lm_scale_level, lm_descs, undist_keypts, descs, None,
+                            scale_factors, None)
+
+    def replace_duplication(self, cam, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_descs, undist_keypts, descs, stereo_x_right,
+                            scale_factors, inv_level_sigma_sq, margin=3.0):
+        """match/fuse.cc:122-266 (search loop :176-238, with the reprojection-error gate and the unsigned level arithmetic)"""
+        return self._search(cam, margin, True, True, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_descs, undist_keypts, descs,
+                            stereo_x_right, scale_factors, inv_level_sigma_sq)
+
+
 register("lpslam_match_candidates", C.c_int, [C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_int, C.c_void_p, _lib.u32p])
 

@@ -355,6 +355,72 @@ int orc_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_
                                  kp_has_observed_lm, scale_factors, kp_match_lm);
 }
 
+// The search loop shared by fuse::detect_duplication (match/fuse.cc:69-101) and fuse::replace_duplication
+// (match/fuse.cc:176-238): every row (a landmark that passed the caller's visibility gates, with its reprojection, x_right
+// and predicted scale level) takes the keypoint with the smallest Hamming distance (strict '<', first wins) among the
+// keypoints inside margin * scale_factors[level] whose octave is level - 1 or level; rows are independent (nothing is
+// marked as taken). chi_gate != 0 adds replace_duplication's reprojection-error gate (3 degrees of freedom for keypoints
+// with a stereo match, 2 otherwise, fuse.cc:199-222). unsigned_levels != 0 reproduces replace_duplication's unsigned
+// arithmetic: `scale_level < pred_scale_level - 1` wraps for a predicted level of 0 and rejects every candidate (fuse.cc:193).
+// best_idx[j] = keypoint of row j or -1 (also when the best distance exceeds HAMMING_DIST_THR_LOW), best_dist[j] = its distance.
+int orc_match_fuse(const orc_camera* cam, float margin, int chi_gate, int unsigned_levels, uint32_t n_lm, const uint8_t* lm_active,
+                   const double* lm_reproj, const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                   uint32_t n_kp, const orc_keypoint* kp, const uint8_t* kp_desc, const float* kp_x_right,
+                   const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx, uint32_t* best_dist) {
+    int num = 0;
+    const auto grid = assign_grid(cam, n_kp, kp);
+    std::vector<unsigned> idx;
+    for (unsigned j = 0; j < n_lm; ++j) {
+        best_idx[j] = -1;
+        best_dist[j] = MAX_HAMMING_DIST;
+        if (!lm_active[j]) continue;
+        const int pred = lm_scale_level[j];
+        keypoints_in_cell(cam, grid, kp, static_cast<float>(lm_reproj[2 * j]), static_cast<float>(lm_reproj[2 * j + 1]),
+                          margin * scale_factors[pred], -1, -1, idx);
+        if (idx.empty()) continue;
+        const uint8_t* ld = lm_desc + static_cast<size_t>(j) * 32;
+        unsigned best = MAX_HAMMING_DIST;
+        int best_i = -1;
+        for (unsigned i : idx) {
+            if (unsigned_levels) {
+                const unsigned scale_level = static_cast<unsigned>(kp[i].octave), upred = static_cast<unsigned>(pred);
+                if (scale_level < upred - 1 || upred < scale_level) continue;
+            }
+            else {
+                const int scale_level = kp[i].octave;
+                if (scale_level < pred - 1 || pred < scale_level) continue;
+            }
+            if (chi_gate) {
+                if (kp_x_right[i] >= 0) {
+                    const auto e_x = lm_reproj[2 * j] - kp[i].x;
+                    const auto e_y = lm_reproj[2 * j + 1] - kp[i].y;
+                    const auto e_x_right = lm_x_right[j] - kp_x_right[i];
+                    const auto reproj_error_sq = e_x * e_x + e_y * e_y + e_x_right * e_x_right;
+                    constexpr float chi_sq_3D = 7.81473;
+                    if (chi_sq_3D < reproj_error_sq * inv_level_sigma_sq[kp[i].octave]) continue;
+                }
+                else {
+                    const auto e_x = lm_reproj[2 * j] - kp[i].x;
+                    const auto e_y = lm_reproj[2 * j + 1] - kp[i].y;
+                    const auto reproj_error_sq = e_x * e_x + e_y * e_y;
+                    constexpr float chi_sq_2D = 5.99146;
+                    if (chi_sq_2D < reproj_error_sq * inv_level_sigma_sq[kp[i].octave]) continue;
+                }
+            }
+            const unsigned d = hamming_32(ld, kp_desc + static_cast<size_t>(i) * 32);
+            if (d < best) {
+                best = d;
+                best_i = static_cast<int>(i);
+            }
+        }
+        best_dist[j] = best;
+        if (HAMMING_DIST_THR_LOW < best) continue;
+        best_idx[j] = best_i;
+        ++num;
+    }
+    return num;
+}
+
 // match/bow_tree.cc:16-126 match_frame_and_keyframe with the feature vectors given as node -> index lists (sorted by
 // node id, the iteration order of both vocabulary libraries' containers). kf_valid = keyframe keypoint holds a live landmark.
 int orc_match_bow(uint32_t n_nodes_kf, const uint32_t* kf_node_id, const uint32_t* kf_node_start, const uint32_t* kf_items,

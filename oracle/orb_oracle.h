@@ -127,6 +127,10 @@ int orc_match_reprojected(const orc_camera* cam, float margin, float lowe_ratio,
 
 /* match/bow_tree.cc:16-126 match_frame_and_keyframe; feature vectors as sorted node ids + CSR index lists.
  * f_match_kf[i] = keyframe keypoint whose landmark frame keypoint i received, or -1. Returns num_matches. */
+int orc_match_fuse(const orc_camera* cam, float margin, int chi_gate, int unsigned_levels, uint32_t n_lm, const uint8_t* lm_active,
+                   const double* lm_reproj, const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
+                   uint32_t n_kp, const orc_keypoint* kp, const uint8_t* kp_desc, const float* kp_x_right,
+                   const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx, uint32_t* best_dist);
 int orc_match_bow(uint32_t n_nodes_kf, const uint32_t* kf_node_id, const uint32_t* kf_node_start, const uint32_t* kf_items,
                   uint32_t n_nodes_f, const uint32_t* f_node_id, const uint32_t* f_node_start, const uint32_t* f_items,
                   const uint8_t* kf_valid, const uint8_t* kf_desc, const float* kf_angle, uint32_t n_f, const uint8_t* f_desc,

@@ -329,6 +329,30 @@ class Oracle:
                                            _ptr(out, i32p))
         return out, n
 
+    def match_fuse(self, cam, margin, chi_gate, unsigned_levels, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_desc, kp, kp_desc,
+                   kp_x_right, scale, inv_level_sigma_sq):
+        """search loop of fuse::detect_duplication / replace_duplication: (best_idx, best_dist, n_fused)"""
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64)
+        lxr = np.ascontiguousarray(lm_x_right, np.float32)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_desc, np.uint8)
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        kd = np.ascontiguousarray(kp_desc, np.uint8)
+        xr = np.ascontiguousarray(kp_x_right, np.float32)
+        scale = np.ascontiguousarray(scale, np.float32)
+        isq = np.ascontiguousarray(inv_level_sigma_sq, np.float32)
+        best = np.empty(len(act), np.int32)
+        dist = np.empty(len(act), np.uint32)
+        self.lib.orc_match_fuse.restype = C.c_int
+        self.lib.orc_match_fuse.argtypes = [C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_uint32, u8p, C.POINTER(C.c_double), f32p, i32p, u8p,
+                                            C.c_uint32, C.c_void_p, u8p, f32p, f32p, f32p, i32p, C.POINTER(C.c_uint32)]
+        n = self.lib.orc_match_fuse(C.cast(C.byref(cam), C.c_void_p), margin, int(chi_gate), int(unsigned_levels), len(act), _ptr(act, u8p),
+                                    _ptr(rp, C.POINTER(C.c_double)), _ptr(lxr, f32p), _ptr(lvl, i32p), _ptr(ld, u8p), len(kp),
+                                    kp.ctypes.data, _ptr(kd, u8p), _ptr(xr, f32p), _ptr(scale, f32p), _ptr(isq, f32p), _ptr(best, i32p),
+                                    _ptr(dist, C.POINTER(C.c_uint32)))
+        return best, dist, n
+
     def match_bow(self, kf_vec, f_vec, kf_valid, kf_desc, kf_angle, f_desc, f_angle, lowe_ratio, check_orientation):
         """kf_vec / f_vec: (node_ids, node_start, items) uint32 arrays"""
         u32p = C.POINTER(C.c_uint32)

@@ -399,3 +399,37 @@ def test_bruteforce_clustered(oracle):
         _, got = match.robust(ratio, False).brute_force_match(d1, d2)
         assert np.array_equal(got, want)
     assert nw > 100
+
+
+@pytest.mark.parametrize("seed,stereo", [(1, False), (2, True), (3, True)])
+def test_fuse(oracle, seed, stereo):
+    # match/fuse.cc:69-101 (detect_duplication) and :176-238 (replace_duplication: chi-square gate, unsigned level quirk)
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    args, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs = landmarks_case(oracle, seed, stereo, False)
+    isq = (1.0 / (np.asarray(sf, np.float32) ** 2)).astype(np.float32)
+    total = 0
+    for margin in (3.0, 4.0, 10.0):
+        want, wd, nw = oracle.match_fuse(pyoracle.make_camera(**args), margin, False, False, active, reproj, lxr, level, ldesc, kp, desc, xr,
+                                         sf, isq)
+        got, gd, ng = match.fuse().detect_duplication(match.make_camera(**args), active, reproj, level, ldesc, kp, desc, sf, margin)
+        assert np.array_equal(got, want) and np.array_equal(gd, wd) and ng == nw
+        total += nw
+        want, wd, nw = oracle.match_fuse(pyoracle.make_camera(**args), margin, True, True, active, reproj, lxr, level, ldesc, kp, desc, xr,
+                                         sf, isq)
+        got, gd, ng = match.fuse().replace_duplication(match.make_camera(**args), active, reproj, lxr, level, ldesc, kp, desc, xr, sf, isq,
+                                                       margin)
+        assert np.array_equal(got, want) and np.array_equal(gd, wd) and ng == nw
+        assert (got[np.asarray(level) == 0] == -1).all()  # fuse.cc:193 on unsigned levels
+        total += nw
+    assert total > 500
+
+
+def test_fuse_edges():
+    from lpslam_b200 import match
+    cam = match.make_camera(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    sf = np.array([1.2 ** i for i in range(8)], np.float32)
+    kp = np.zeros(0, match.KP_DTYPE)
+    best, dist, n = match.fuse().detect_duplication(cam, np.ones(3, np.uint8), np.zeros((3, 2)), np.zeros(3, np.int32),
+                                                    np.zeros((3, 32), np.uint8), kp, np.zeros((0, 32), np.uint8), sf, 3.0)
+    assert n == 0 and (best == -1).all() and (dist == 256).all()

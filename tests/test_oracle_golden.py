@@ -157,3 +157,46 @@ def test_landmark_matcher_semantics(oracle):
     # inactive landmarks are skipped
     out, n = run(one, [[100.0, 100.0]], [1], active=np.zeros(1, np.uint8))
     assert n == 0
+
+
+def test_fuse_search_semantics(oracle):
+    """match/fuse.cc:69-101 / :176-238 hand-built cases for the port: rows are independent (two landmarks may name the same
+    keypoint), octave window [level - 1, level], HAMMING_DIST_THR_LOW, replace_duplication's chi-square gate and its
+    unsigned level arithmetic."""
+    from oracle import pyoracle
+    cam = pyoracle.make_camera(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    isq = (1.0 / sf ** 2).astype(np.float32)
+    kp = np.zeros(3, pyoracle.KP_DTYPE)
+    kp["x"], kp["y"], kp["octave"] = [100.0, 102.0, 300.0], [100.0, 101.0, 200.0], [1, 0, 2]
+    d = np.zeros((3, 32), np.uint8)
+    d[1, 0] = 0x03
+    d[2] = 0xFF
+    xr = np.array([-1.0, 90.0, -1.0], np.float32)
+
+    def run(lm_desc, reproj, level, chi=False, uns=False, lxr=None):
+        m = len(level)
+        return oracle.match_fuse(cam, 3.0, chi, uns, np.ones(m, np.uint8), reproj, np.zeros(m, np.float32) if lxr is None else lxr, level,
+                                 lm_desc, kp, d, xr, sf, isq)
+
+    two = np.zeros((2, 32), np.uint8)
+    best, dist, n = run(two, [[100.0, 100.0], [100.5, 100.0]], [1, 1])
+    assert n == 2 and list(best) == [0, 0] and list(dist) == [0, 0]          # nothing is marked as taken
+    best, dist, n = run(two[:1], [[100.0, 100.0]], [3])
+    assert n == 0 and best[0] == -1 and dist[0] == 256                      # octaves 1 and 0 are outside [2, 3]
+    far = np.full((1, 32), 0x0F, np.uint8)                                   # 128 bits from keypoint 0, 126 from keypoint 1
+    best, dist, n = run(far, [[100.0, 100.0]], [1])
+    assert n == 0 and best[0] == -1 and dist[0] == 126                      # best_dist (keypoint 1) is reported, the match is not
+    # chi-square gate: keypoint 0 (mono, 2 dof) sits 2.9 px away: 8.41 / 1.44 = 5.84 < 5.99 passes, 3.0 px -> 6.25 rejects
+    best, _, _ = run(two[:1], [[102.9, 100.0]], [1], chi=True)
+    assert best[0] == 0
+    best, dist, _ = run(two[:1], [[103.0, 100.0]], [1], chi=True)
+    assert best[0] != 0
+    # keypoint 1 has a stereo match (3 dof, x_right 90): an x_right error of 2.5 px alone gives 6.25 < 7.81 at level 0
+    best, _, _ = run(two[:1], [[102.0, 101.0]], [0], chi=True, lxr=np.array([92.5], np.float32))
+    assert best[0] == 1
+    best, _, _ = run(two[:1], [[102.0, 101.0]], [0], chi=True, lxr=np.array([93.0], np.float32))
+    assert best[0] == -1
+    # replace_duplication compares unsigned levels: a predicted level of 0 rejects every candidate (fuse.cc:193)
+    best, _, n = run(two[:1], [[102.0, 101.0]], [0], chi=True, uns=True, lxr=np.array([90.0], np.float32))
+    assert n == 0 and best[0] == -1
