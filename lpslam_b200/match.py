@@ -241,6 +241,49 @@ class bow_tree:
         res = np.where(out >= 0, rows[np.clip(out, 0, max(len(rows) - 1, 0))] if len(rows) else -1, -1).astype(np.int32)
         return res, int(n.value)
 
+    def match_keyframes(self, keyfrm_1_feat_vec, keyfrm_1_has_live_lm, keyfrm_1_descs, keyfrm_1_angles, keyfrm_2_feat_vec,
+                        keyfrm_2_has_live_lm, keyfrm_2_descs, keyfrm_2_angles):
+        """match/bow_tree.cc:128-250 (loop detection, before the Sim3 solver): returns (match_2_of_1, num_matches);
+        match_2_of_1[i] = keyframe-2 keypoint whose landmark keyframe-1 keypoint i receives
+        (matched_lms_in_keyfrm_1.at(i) = keyfrm_2_lms.at(that)), or -1. Same search as match_frame_and_keyframe: a
+        keyframe-2 keypoint without a live landmark is never a candidate, which is what 'occupied beforehand' means."""
+        id1, st1, it1 = [np.ascontiguousarray(x, np.uint32) for x in keyfrm_1_feat_vec]
+        id2, st2, it2 = [np.ascontiguousarray(x, np.uint32) for x in keyfrm_2_feat_vec]
+        v1 = np.ascontiguousarray(keyfrm_1_has_live_lm, np.uint8)
+        v2 = np.ascontiguousarray(keyfrm_2_has_live_lm, np.uint8)
+        d1 = np.ascontiguousarray(keyfrm_1_descs, np.uint8)
+        d2 = np.ascontiguousarray(keyfrm_2_descs, np.uint8)
+        rows, begin, end = [], [], []
+        a = b = 0
+        while a < len(id1) and b < len(id2):  # the merge walk of bow_tree.cc:150-236
+            if id1[a] == id2[b]:
+                for i1 in it1[st1[a]:st1[a + 1]]:
+                    if v1[i1]:
+                        rows.append(i1)
+                        begin.append(st2[b])
+                        end.append(st2[b + 1])
+                a += 1
+                b += 1
+            elif id1[a] < id2[b]:
+                a += 1
+            else:
+                b += 1
+        rows = np.asarray(rows, np.int64)
+        out = np.full(len(d2), -1, np.int32)
+        n = C.c_uint32(0)
+        rd = np.ascontiguousarray(d1[rows]) if len(rows) else np.zeros((0, 32), np.uint8)
+        rb, re_ = np.asarray(begin, np.uint32), np.asarray(end, np.uint32)
+        ra = np.ascontiguousarray(np.asarray(keyfrm_1_angles, np.float32)[rows]) if self.check_orientation_ else None
+        a2 = np.ascontiguousarray(keyfrm_2_angles, np.float32) if self.check_orientation_ else None
+        taken = np.ascontiguousarray(1 - np.minimum(v2, 1), np.uint8)
+        check(lib().lpslam_match_candidates(len(rows), rd.ctypes.data, rb.ctypes.data, re_.ctypes.data, it2.ctypes.data, len(it2),
+                                            _lib.ptr(ra), len(d2), d2.ctypes.data, _lib.ptr(a2), taken.ctypes.data, HAMMING_DIST_THR_LOW,
+                                            self.lowe_ratio_, 1, out.ctypes.data, C.byref(n)))
+        res = np.full(len(d1), -1, np.int32)
+        hit = np.nonzero(out >= 0)[0]
+        res[rows[out[hit]]] = hit.astype(np.int32)
+        return res, int(n.value)
+
 
 register("lpslam_match_area", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                         C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, _lib.u32p])

@@ -477,6 +477,66 @@ int orc_match_bow(uint32_t n_nodes_kf, const uint32_t* kf_node_id, const uint32_
     return num;
 }
 
+// match/bow_tree.cc:128-250 match_keyframes (Sim3 estimation between loop candidates): both sides are keyframes, only
+// keypoints that hold a live landmark take part (valid_1 / valid_2), the result is indexed by keyframe-1 keypoint.
+int orc_match_bow_keyframes(uint32_t n_nodes_1, const uint32_t* node_id_1, const uint32_t* node_start_1, const uint32_t* items_1,
+                            uint32_t n_nodes_2, const uint32_t* node_id_2, const uint32_t* node_start_2, const uint32_t* items_2,
+                            uint32_t n1, const uint8_t* valid_1, const uint8_t* desc_1, const float* angle_1, uint32_t n2,
+                            const uint8_t* valid_2, const uint8_t* desc_2, const float* angle_2, float lowe_ratio,
+                            int check_orientation, int32_t* match_2_of_1) {
+    int num = 0;
+    AngleHistogram hist;
+    std::fill(match_2_of_1, match_2_of_1 + n1, -1);
+    std::vector<uint8_t> already_2(n2, 0);
+    uint32_t a = 0, b = 0;
+    while (a < n_nodes_1 && b < n_nodes_2) {
+        if (node_id_1[a] == node_id_2[b]) {
+            for (uint32_t qa = node_start_1[a]; qa < node_start_1[a + 1]; ++qa) {
+                const uint32_t i1 = items_1[qa];
+                if (!valid_1[i1]) continue;
+                const uint8_t* d1 = desc_1 + static_cast<size_t>(i1) * 32;
+                unsigned best = MAX_HAMMING_DIST, second = MAX_HAMMING_DIST;
+                int best_2 = -1;
+                for (uint32_t qb = node_start_2[b]; qb < node_start_2[b + 1]; ++qb) {
+                    const uint32_t i2 = items_2[qb];
+                    if (!valid_2[i2]) continue;
+                    if (already_2[i2]) continue;
+                    const unsigned d = hamming_32(d1, desc_2 + static_cast<size_t>(i2) * 32);
+                    if (d < best) {
+                        second = best;
+                        best = d;
+                        best_2 = static_cast<int>(i2);
+                    }
+                    else if (d < second) {
+                        second = d;
+                    }
+                }
+                if (HAMMING_DIST_THR_LOW < best) continue;
+                if (lowe_ratio * second < static_cast<float>(best)) continue;
+                match_2_of_1[i1] = best_2;
+                already_2[best_2] = 1;
+                ++num;
+                if (check_orientation) hist.append(angle_1[i1] - angle_2[best_2], static_cast<int>(i1));
+            }
+            ++a;
+            ++b;
+        }
+        else if (node_id_1[a] < node_id_2[b]) {
+            while (a < n_nodes_1 && node_id_1[a] < node_id_2[b]) ++a;  // lower_bound
+        }
+        else {
+            while (b < n_nodes_2 && node_id_2[b] < node_id_1[a]) ++b;
+        }
+    }
+    if (check_orientation) {
+        for (int id : hist.invalid()) {
+            match_2_of_1[id] = -1;
+            --num;
+        }
+    }
+    return num;
+}
+
 // match/area.cc:8-112 match_in_consistent_area over flat arrays; prev_pts (n1 x 2) is updated in place
 int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
                    const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,

@@ -131,6 +131,11 @@ int orc_match_fuse(const orc_camera* cam, float margin, int chi_gate, int unsign
                    const double* lm_reproj, const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
                    uint32_t n_kp, const orc_keypoint* kp, const uint8_t* kp_desc, const float* kp_x_right,
                    const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx, uint32_t* best_dist);
+int orc_match_bow_keyframes(uint32_t n_nodes_1, const uint32_t* node_id_1, const uint32_t* node_start_1, const uint32_t* items_1,
+                            uint32_t n_nodes_2, const uint32_t* node_id_2, const uint32_t* node_start_2, const uint32_t* items_2,
+                            uint32_t n1, const uint8_t* valid_1, const uint8_t* desc_1, const float* angle_1, uint32_t n2,
+                            const uint8_t* valid_2, const uint8_t* desc_2, const float* angle_2, float lowe_ratio,
+                            int check_orientation, int32_t* match_2_of_1);
 int orc_match_bow(uint32_t n_nodes_kf, const uint32_t* kf_node_id, const uint32_t* kf_node_start, const uint32_t* kf_items,
                   uint32_t n_nodes_f, const uint32_t* f_node_id, const uint32_t* f_node_start, const uint32_t* f_items,
                   const uint8_t* kf_valid, const uint8_t* kf_desc, const float* kf_angle, uint32_t n_f, const uint8_t* f_desc,

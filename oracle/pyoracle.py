@@ -369,6 +369,24 @@ class Oracle:
                                    _ptr(fd, u8p), _ptr(fang, f32p), lowe_ratio, int(check_orientation), _ptr(out, i32p))
         return out, n
 
+    def match_bow_keyframes(self, vec_1, vec_2, valid_1, desc_1, angle_1, valid_2, desc_2, angle_2, lowe_ratio, check_orientation):
+        """bow_tree::match_keyframes: (match_2_of_1, n)"""
+        u32p = C.POINTER(C.c_uint32)
+        a = [np.ascontiguousarray(x, np.uint32) for x in vec_1]
+        b = [np.ascontiguousarray(x, np.uint32) for x in vec_2]
+        v1, v2 = np.ascontiguousarray(valid_1, np.uint8), np.ascontiguousarray(valid_2, np.uint8)
+        d1, d2 = np.ascontiguousarray(desc_1, np.uint8), np.ascontiguousarray(desc_2, np.uint8)
+        a1, a2 = np.ascontiguousarray(angle_1, np.float32), np.ascontiguousarray(angle_2, np.float32)
+        out = np.empty(len(d1), np.int32)
+        f = self.lib.orc_match_bow_keyframes
+        f.restype = C.c_int
+        f.argtypes = [C.c_uint32, u32p, u32p, u32p, C.c_uint32, u32p, u32p, u32p, C.c_uint32, u8p, u8p, f32p, C.c_uint32, u8p, u8p, f32p,
+                      C.c_float, C.c_int, i32p]
+        n = f(len(a[0]), _ptr(a[0], u32p), _ptr(a[1], u32p), _ptr(a[2], u32p), len(b[0]), _ptr(b[0], u32p), _ptr(b[1], u32p),
+              _ptr(b[2], u32p), len(d1), _ptr(v1, u8p), _ptr(d1, u8p), _ptr(a1, f32p), len(d2), _ptr(v2, u8p), _ptr(d2, u8p),
+              _ptr(a2, f32p), lowe_ratio, int(check_orientation), _ptr(out, i32p))
+        return out, n
+
     def match_area(self, cam, kp1, desc1, prev_pts, kp2, desc2, margin, lowe_ratio, check_orientation):
         kp1 = np.ascontiguousarray(kp1, KP_DTYPE)
         kp2 = np.ascontiguousarray(kp2, KP_DTYPE)

@@ -433,3 +433,31 @@ def test_fuse_edges():
     best, dist, n = match.fuse().detect_duplication(cam, np.ones(3, np.uint8), np.zeros((3, 2)), np.zeros(3, np.int32),
                                                     np.zeros((3, 32), np.uint8), kp, np.zeros((0, 32), np.uint8), sf, 3.0)
     assert n == 0 and (best == -1).all() and (dist == 256).all()
+
+
+@pytest.mark.parametrize("seed,chk", [(1, True), (2, False), (3, True)])
+def test_bow_tree_match_keyframes(oracle, seed, chk):
+    # match/bow_tree.cc:128-250: both sides keyframes, only keypoints with live landmarks take part, result per keyframe-1 keypoint
+    from lpslam_b200 import match
+    rng = np.random.default_rng(seed)
+    o = oracle.extractor(max_kpts=1000)
+    kp, desc = o.extract(synth_image(480, 640, 90 + seed))
+    n = len(kp)
+    perm = rng.permutation(n)
+    d1 = desc[perm] ^ np.packbits(rng.random((n, 256)) < 0.04, axis=1, bitorder="little")
+    a1 = (kp["angle"][perm] + rng.normal(0, 3.0, n)).astype(np.float32) % 360
+    vec2, node2 = bow_vector(rng, n, 50)
+    node1 = np.where(rng.random(n) < 0.85, node2[perm], rng.integers(0, 70, n))
+    ids = np.unique(node1)
+    vec1 = (ids.astype(np.uint32), np.concatenate([[0], np.cumsum([(node1 == v).sum() for v in ids])]).astype(np.uint32),
+            np.concatenate([np.nonzero(node1 == v)[0] for v in ids]).astype(np.uint32))
+    v1 = (rng.random(n) < 0.8).astype(np.uint8)
+    v2 = (rng.random(n) < 0.7).astype(np.uint8)
+    total = 0
+    for ratio in (0.6, 0.75, 0.95):
+        want, nw = oracle.match_bow_keyframes(vec1, vec2, v1, d1, a1, v2, desc, kp["angle"], ratio, chk)
+        got, ng = match.bow_tree(ratio, chk).match_keyframes(vec1, v1, d1, a1, vec2, v2, desc, kp["angle"])
+        assert np.array_equal(got, want) and ng == nw
+        assert (got[v1 == 0] == -1).all() and v2[got[got >= 0]].all()
+        total += nw
+    assert total > 200
