@@ -297,6 +297,51 @@ int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi_square_gat
                       const uint8_t* kp_desc, const float* kp_x_right, const float* scale_factors,
                       const float* inv_level_sigma_sq, int32_t* best_idx, uint32_t* best_dist, uint32_t* n_fused);
 
+/* The search loop of match::projection::match_by_Sim3_transform (match/projection.cc:317-413; loop closing: the landmarks
+ * seen from the loop candidates reprojected into the current keyframe under the estimated Sim3). The caller keeps the
+ * per-landmark geometry (will_be_erased, already_matched, reproject_to_image, the valid-distance and viewing-angle gates,
+ * predict_scale_level: :333-370) and passes the surviving landmarks as rows, in the order of `landmarks`. Every row takes
+ * the keypoint without a matched landmark (kp_has_matched_lm = matched_lms_in_keyfrm.at(idx) != nullptr, updated as rows
+ * match, :381-383 / :409) with the smallest distance (strict '<') inside margin * scale_factors[level], octave in
+ * [level - 1, level] compared as UNSIGNED (:385-390: a predicted level of 0 rejects every candidate), accepted when
+ * best <= HAMMING_DIST_THR_LOW (:405). kp_match_lm[i] = row now matched to keypoint i, or -1. */
+int lpslam_match_sim3(const lpslam_camera* cam, float margin, uint32_t n_lm, const uint8_t* lm_active,
+                      const double* lm_reproj /*n_lm x 2*/, const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp,
+                      const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const uint8_t* kp_has_matched_lm,
+                      const float* scale_factors, int32_t* kp_match_lm, uint32_t* n_matches);
+
+/* The two search loops and the cross-check of match::projection::match_keyframes_mutually (match/projection.cc:415-636; loop
+ * closing, after the Sim3 solver). Rows of side 1 = keyframe 1's keypoints (n_1 = landmarks_1.size()): lm1_active[i] = the
+ * keypoint holds a live landmark that is not matched already and passed the caller's geometry (:462-495), lm1_reproj_in_2 /
+ * lm1_level_in_2 = its reprojection into keyframe 2 and predicted level there, lm1_desc = the landmark's descriptor;
+ * side 2 likewise into keyframe 1. Every row independently takes the closest keypoint of the other keyframe (strict '<',
+ * octave in [level - 1, level] as unsigned, best <= HAMMING_DIST_THR_HIGH); matched_idx_2_in_1[i] = the keyframe-2 keypoint
+ * when both directions agree (:618-631: matched_lms_in_keyfrm_1.at(i) = landmarks_2.at(that)), else -1. */
+int lpslam_match_mutual(const lpslam_camera* cam_1, const lpslam_camera* cam_2, float margin, uint32_t n_1,
+                        const uint8_t* lm1_active, const double* lm1_reproj_in_2, const int32_t* lm1_level_in_2,
+                        const uint8_t* lm1_desc, const lpslam_keypoint* kp1_undist, const uint8_t* kp1_desc,
+                        const float* scale_factors_1, uint32_t n_2, const uint8_t* lm2_active, const double* lm2_reproj_in_1,
+                        const int32_t* lm2_level_in_1, const uint8_t* lm2_desc, const lpslam_keypoint* kp2_undist,
+                        const uint8_t* kp2_desc, const float* scale_factors_2, int32_t* matched_idx_2_in_1, uint32_t* n_matches);
+
+/* The search loop of match::robust::match_for_triangulation (match/robust.cc:18-178; local mapping, before new landmarks
+ * are triangulated). The caller walks the two BoW feature vectors and emits, in iteration order, one row per keyframe-1
+ * keypoint WITHOUT a landmark (row_idx_1, :64-69) with the keyframe-2 keypoints of the same vocabulary node as its
+ * candidate list. A candidate counts when it holds no landmark (kp2_has_lm), is not matched yet, its distance is
+ * <= HAMMING_DIST_THR_LOW, it is not within 3 degrees of the epipole (only when neither keypoint has a stereo match,
+ * :112-123) and passes check_epipolar_constraint (:323-341, E_12 row-major, 0.2 degree x scale_factors_1[octave]); among
+ * those the smallest distance wins and an EQUAL distance replaces the best (:108 `best_hamm_dist < hamm_dist`).
+ * epiplane_in_keyfrm_2 = reproject_to_bearing of keyframe 1's centre (:26-30). check_orientation runs the angle_checker
+ * (:143-147, :164-170). matched_idx_2_in_1[i] (n_1) = keyframe-2 keypoint or -1 (the pairs of :172-180 in order of i). */
+int lpslam_match_triangulation(uint32_t n_rows, const uint32_t* row_idx_1, const uint32_t* row_cand_begin,
+                               const uint32_t* row_cand_end, const uint32_t* cand_items, uint32_t n_items, uint32_t n_1,
+                               const lpslam_keypoint* kp1_undist, const uint8_t* kp1_desc, const double* bearings_1 /*n_1 x 3*/,
+                               const float* x_right_1, const float* scale_factors_1, uint32_t n_2,
+                               const lpslam_keypoint* kp2_undist, const uint8_t* kp2_desc, const double* bearings_2,
+                               const float* x_right_2, const uint8_t* kp2_has_lm, const double* E_12 /*9*/,
+                               const double* epiplane_in_keyfrm_2 /*3*/, int check_orientation, int32_t* matched_idx_2_in_1,
+                               uint32_t* n_matches);
+
 /* The search loop of match::bow_tree::match_frame_and_keyframe (match/bow_tree.cc:16-126), the matcher of BoW-based
  * tracking and relocalisation: the caller walks the two BoW feature vectors (the vocabulary library's containers) and
  * emits, in iteration order, one row per keyframe keypoint that holds a live landmark (bow_tree.cc:45-57) with its

@@ -75,7 +75,31 @@ struct ProjArgs {
     const float* inv_sigma_sq;
     int32_t* row_best;   // k_rows_best: keypoint of every row or -1
     uint32_t* row_dist;  // its Hamming distance (256 when the row saw no candidate)
+    // robust::match_for_triangulation (robust.cc:18-178) on candidate lists (mode 3): `best_hamm_dist < hamm_dist` skips, so
+    // an equal distance REPLACES the best (the last one in visit order wins); candidates pass the epipole gate (:114-123)
+    // and check_epipolar_constraint (:126-127, :323-341) before they count
+    int last_wins, tri;
+    const double* row_bearing;  // n_last x 3
+    const double* kp_bearing;   // n_curr x 3
+    const uint8_t* row_stereo;  // 0 <= stereo_x_right of the row's keypoint
+    const uint8_t* kp_stereo;
+    const float* row_scale;     // scale_factors_.at(keypt_1.octave)
+    double E[9], epi[3];
 };
+
+// robust.cc:323-341 check_epipolar_constraint: double arithmetic in source order, no contraction
+__device__ __forceinline__ bool epipolar_inlier(const double* E, const double* b1, const double* b2, float scale_1) {
+    double n[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+        n[r] = __dadd_rn(__dadd_rn(__dmul_rn(E[3 * r], b2[0]), __dmul_rn(E[3 * r + 1], b2[1])), __dmul_rn(E[3 * r + 2], b2[2]));
+    const double dot = __dadd_rn(__dadd_rn(__dmul_rn(n[0], b1[0]), __dmul_rn(n[1], b1[1])), __dmul_rn(n[2], b1[2]));
+    const double nrm = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(n[0], n[0]), __dmul_rn(n[1], n[1])), __dmul_rn(n[2], n[2])));
+    const double cos_residual = __ddiv_rn(dot, nrm);
+    const double residual_rad = __dsub_rn(M_PI / 2.0, fabs(acos(cos_residual)));
+    constexpr double residual_rad_thr = 0.2 * M_PI / 180.0;
+    return residual_rad < __dmul_rn(residual_rad_thr, (double)scale_1);
+}
 
 __device__ __forceinline__ int cv_round(double v) { return __double2int_rn(v); }
 __device__ __forceinline__ int cv_floor(double v) { return __double2int_rd(v); }
@@ -259,7 +283,17 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
             ++seq;
             if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
             const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
-            f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)), 0);
+            const unsigned d = hamming256(l0, l1, __ldg(dc), __ldg(dc + 1));
+            if (a.tri) {
+                if (a.hamm_thr < d) continue;  // robust.cc:108
+                const double* b2 = a.kp_bearing + 3 * (size_t)i;
+                if (!a.row_stereo[il] && !a.kp_stereo[i]) {  // robust.cc:112-123: nothing within 3 degrees of the epipole
+                    const double cos_dist = __dadd_rn(__dadd_rn(__dmul_rn(a.epi[0], b2[0]), __dmul_rn(a.epi[1], b2[1])), __dmul_rn(a.epi[2], b2[2]));
+                    if (0.99862953475 < cos_dist) continue;
+                }
+                if (!epipolar_inlier(a.E, a.row_bearing + 3 * (size_t)il, b2, a.row_scale[il])) continue;
+            }
+            f(seq, i, d, 0);
         }
         return;
     }
@@ -325,7 +359,7 @@ __global__ void k_proj_topk(ProjArgs a) {
     int idx[K] = {-1, -1, -1, -1};
     if (p.ok) {
         visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
-            const uint32_t kk = (d << 20) | seq;
+            const uint32_t kk = (d << 20) | (a.last_wins ? 0xFFFFFu - seq : seq);
             if (kk < key[3]) {
                 key[3] = kk;
                 idx[3] = (int)(i | ((uint32_t)(oct & 0x7F) << 24));  // octave rides along: the resolve loop never touches a.kp
@@ -432,7 +466,7 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
                     i1 = i2 = o1 = o2 = -1;
                     const Projected p = project(a, il, fw, bw);
                     visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
-                        const uint32_t kk = (d << 20) | seq;
+                        const uint32_t kk = (d << 20) | (a.last_wins ? 0xFFFFFu - seq : seq);
                         if (kk < b1) {
                             b2 = b1;
                             i2 = i1;
@@ -1159,12 +1193,14 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
     return LPSLAM_OK;
 }
 
-extern "C" int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi_square_gate, int unsigned_levels, uint32_t n_lm,
-                                 const uint8_t* lm_active, const double* lm_reproj, const float* lm_x_right,
-                                 const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp,
-                                 const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const float* kp_x_right,
-                                 const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx,
-                                 uint32_t* best_dist, uint32_t* n_fused) {
+// rows that search independently of each other (fuse.cc:69-101 / :176-238, projection.cc:503-533 / :585-615): grid build,
+// k_proj_topk, k_rows_best; best_idx[row] = the closest keypoint when its distance is <= hamm_thr
+static int rows_best_search(const char* who, uint32_t hamm_thr, const lpslam_camera* cam, float margin, int chi_square_gate,
+                            int unsigned_levels, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                            const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp,
+                            const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const float* kp_x_right,
+                            const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx,
+                            uint32_t* best_dist, uint32_t* n_fused) {
     LPS_ARG(cam && scale_factors && n_fused, "null argument");
     *n_fused = 0;
     LPS_ARG(n_lm == 0 || (lm_active && lm_reproj && lm_scale_level && lm_desc && best_idx), "null landmark argument");
@@ -1227,7 +1263,7 @@ extern "C" int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi
         a.level_lo = -1;  // fuse.cc:84-87 / :193-195: octave in [pred - 1, pred]
         a.level_hi = 0;
         a.use_xr = 0;
-        a.hamm_thr = 50;  // HAMMING_DIST_THR_LOW, fuse.cc:99 / :236
+        a.hamm_thr = hamm_thr;
         a.chi_gate = chi_square_gate ? 1 : 0;
         a.inv_sigma_sq = (const float*)(dev + o_isq);
         a.kp = (const lpslam_keypoint*)(dev + o_kp);
@@ -1254,10 +1290,189 @@ extern "C" int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi
         if ((e = cudaMemcpy(dist.data(), dev + o_rd, 4 * (size_t)n_lm, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
     } while (false);
     scratch_free(dev);
-    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_fuse", __FILE__, __LINE__);
+    if (e != cudaSuccess) return cuda_fail(e, who, __FILE__, __LINE__);
     for (uint32_t i = 0; i < n_lm; ++i) {
         if (best_dist) best_dist[i] = dist[i];
         *n_fused += best_idx[i] >= 0;
     }
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_fuse(const lpslam_camera* cam, float margin, int chi_square_gate, int unsigned_levels, uint32_t n_lm,
+                                 const uint8_t* lm_active, const double* lm_reproj, const float* lm_x_right,
+                                 const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp,
+                                 const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const float* kp_x_right,
+                                 const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx,
+                                 uint32_t* best_dist, uint32_t* n_fused) {
+    // HAMMING_DIST_THR_LOW, fuse.cc:99 / :236
+    return rows_best_search("lpslam_match_fuse", 50, cam, margin, chi_square_gate, unsigned_levels, n_lm, lm_active, lm_reproj,
+                            lm_x_right, lm_scale_level, lm_desc, n_kp, kp_undist, kp_desc, kp_x_right, scale_factors,
+                            inv_level_sigma_sq, best_idx, best_dist, n_fused);
+}
+
+extern "C" int lpslam_match_sim3(const lpslam_camera* cam, float margin, uint32_t n_lm, const uint8_t* lm_active,
+                                 const double* lm_reproj, const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp,
+                                 const lpslam_keypoint* kp_undist, const uint8_t* kp_desc, const uint8_t* kp_has_matched_lm,
+                                 const float* scale_factors, int32_t* kp_match_lm, uint32_t* n_matches) {
+    LPS_ARG(n_matches, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n_lm == 0 || (lm_active && lm_scale_level), "null landmark argument");
+    // projection.cc:385-390 compares unsigned levels: `scale_level < pred_scale_level - 1` wraps for a predicted level of 0,
+    // every candidate of such a row is skipped
+    std::vector<uint8_t> act(lm_active, lm_active + n_lm);
+    for (uint32_t i = 0; i < n_lm; ++i)
+        if (lm_scale_level[i] == 0) act[i] = 0;
+    // octave in [pred - 1, pred], best <= HAMMING_DIST_THR_LOW (:405), no ratio test, no stereo gate; a matched keypoint
+    // holds a landmark from then on (:381-383, :409)
+    const lpslam_reproj_match_params prm = {margin, 0.f, 50, -1, 0, 0, 0};
+    return lpslam_match_reprojected(cam, &prm, n_lm, act.data(), lm_reproj, nullptr, lm_scale_level, lm_desc, nullptr, nullptr, n_kp,
+                                    kp_undist, kp_desc, nullptr, kp_has_matched_lm, scale_factors, kp_match_lm, n_matches);
+}
+
+extern "C" int lpslam_match_mutual(const lpslam_camera* cam_1, const lpslam_camera* cam_2, float margin, uint32_t n_1,
+                                   const uint8_t* lm1_active, const double* lm1_reproj_in_2, const int32_t* lm1_level_in_2,
+                                   const uint8_t* lm1_desc, const lpslam_keypoint* kp1_undist, const uint8_t* kp1_desc,
+                                   const float* scale_factors_1, uint32_t n_2, const uint8_t* lm2_active,
+                                   const double* lm2_reproj_in_1, const int32_t* lm2_level_in_1, const uint8_t* lm2_desc,
+                                   const lpslam_keypoint* kp2_undist, const uint8_t* kp2_desc, const float* scale_factors_2,
+                                   int32_t* matched_idx_2_in_1, uint32_t* n_matches) {
+    LPS_ARG(n_matches, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n_1 == 0 || matched_idx_2_in_1, "null result");
+    std::vector<int32_t> two_of_1(n_1, -1), one_of_2(n_2, -1);
+    uint32_t n = 0;
+    // landmarks of keyframe 1 into keyframe 2 (projection.cc:453-534), then the other way round (:536-616); both loops
+    // compare unsigned levels (:511-513, :593-595) and accept best <= HAMMING_DIST_THR_HIGH (:530, :612)
+    int rc = rows_best_search("lpslam_match_mutual", HAMMING_DIST_THR_HIGH, cam_2, margin, 0, 1, n_1, lm1_active, lm1_reproj_in_2,
+                              nullptr, lm1_level_in_2, lm1_desc, n_2, kp2_undist, kp2_desc, nullptr, scale_factors_2, nullptr,
+                              two_of_1.data(), nullptr, &n);
+    if (rc != LPSLAM_OK) return rc;
+    rc = rows_best_search("lpslam_match_mutual", HAMMING_DIST_THR_HIGH, cam_1, margin, 0, 1, n_2, lm2_active, lm2_reproj_in_1, nullptr,
+                          lm2_level_in_1, lm2_desc, n_1, kp1_undist, kp1_desc, nullptr, scale_factors_1, nullptr, one_of_2.data(),
+                          nullptr, &n);
+    if (rc != LPSLAM_OK) return rc;
+    // projection.cc:618-631: only the cross-matches are recorded
+    for (uint32_t i = 0; i < n_1; ++i) {
+        const int32_t i2 = two_of_1[i];
+        matched_idx_2_in_1[i] = (i2 >= 0 && one_of_2[i2] == (int32_t)i) ? i2 : -1;
+        *n_matches += matched_idx_2_in_1[i] >= 0;
+    }
+    return LPSLAM_OK;
+}
+
+extern "C" int lpslam_match_triangulation(uint32_t n_rows, const uint32_t* row_idx_1, const uint32_t* row_cand_begin,
+                                          const uint32_t* row_cand_end, const uint32_t* cand_items, uint32_t n_items, uint32_t n_1,
+                                          const lpslam_keypoint* kp1_undist, const uint8_t* kp1_desc, const double* bearings_1,
+                                          const float* x_right_1, const float* scale_factors_1, uint32_t n_2,
+                                          const lpslam_keypoint* kp2_undist, const uint8_t* kp2_desc, const double* bearings_2,
+                                          const float* x_right_2, const uint8_t* kp2_has_lm, const double* E_12,
+                                          const double* epiplane_in_keyfrm_2, int check_orientation,
+                                          int32_t* matched_idx_2_in_1, uint32_t* n_matches) {
+    LPS_ARG(n_matches, "null argument");
+    *n_matches = 0;
+    LPS_ARG(n_1 == 0 || (kp1_undist && kp1_desc && bearings_1 && x_right_1 && matched_idx_2_in_1), "null keyframe-1 argument");
+    LPS_ARG(n_2 == 0 || (kp2_undist && kp2_desc && bearings_2 && x_right_2 && kp2_has_lm), "null keyframe-2 argument");
+    LPS_ARG(n_rows == 0 || (row_idx_1 && row_cand_begin && row_cand_end), "null row argument");
+    LPS_ARG(n_items == 0 || cand_items, "null candidate list");
+    LPS_ARG(E_12 && epiplane_in_keyfrm_2 && scale_factors_1, "null geometry argument");
+    LPS_ARG(n_2 < (1u << 20) && n_items < (1u << 20), "too many keypoints / candidates");
+    for (uint32_t i = 0; i < n_1; ++i) matched_idx_2_in_1[i] = -1;
+    if (n_1 == 0 || n_2 == 0 || n_rows == 0) return LPSLAM_OK;
+    for (uint32_t r = 0; r < n_rows; ++r) {
+        LPS_ARG(row_idx_1[r] < n_1, "row keypoint out of range");
+        LPS_ARG(row_cand_begin[r] <= row_cand_end[r] && row_cand_end[r] <= n_items, "candidate range out of bounds");
+        LPS_ARG(kp1_undist[row_idx_1[r]].octave >= 0 && kp1_undist[row_idx_1[r]].octave < kMaxLevels, "octave out of range");
+    }
+    for (uint32_t q = 0; q < n_items; ++q) LPS_ARG(cand_items[q] < n_2, "candidate index out of range");
+
+    // per-row copies of the keyframe-1 fields (rows are keyframe-1 keypoints in feature-vector order)
+    std::vector<uint8_t> rdesc(32 * (size_t)n_rows), rstereo(n_rows), kstereo(n_2);
+    std::vector<double> rbear(3 * (size_t)n_rows);
+    std::vector<float> rscale(n_rows);
+    for (uint32_t r = 0; r < n_rows; ++r) {
+        const uint32_t i1 = row_idx_1[r];
+        std::copy(kp1_desc + 32 * (size_t)i1, kp1_desc + 32 * (size_t)i1 + 32, rdesc.begin() + 32 * (size_t)r);
+        std::copy(bearings_1 + 3 * (size_t)i1, bearings_1 + 3 * (size_t)i1 + 3, rbear.begin() + 3 * (size_t)r);
+        rstereo[r] = 0 <= x_right_1[i1];
+        rscale[r] = scale_factors_1[kp1_undist[i1].octave];
+    }
+    for (uint32_t i = 0; i < n_2; ++i) kstereo[i] = 0 <= x_right_2[i];
+
+    ArenaBump ar;
+    const size_t o_rd = ar.take(32 * (size_t)n_rows), o_cb = ar.take(4 * (size_t)n_rows), o_ce = ar.take(4 * (size_t)n_rows);
+    const size_t o_it = ar.take(4 * (size_t)n_items), o_kd = ar.take(32 * (size_t)n_2), o_tk = ar.take(n_2);
+    const size_t o_rb = ar.take(24 * (size_t)n_rows), o_kb = ar.take(24 * (size_t)n_2), o_rs = ar.take(n_rows), o_ks = ar.take(n_2);
+    const size_t o_rsc = ar.take(4 * (size_t)n_rows);
+    const size_t o_tkey = ar.take(16 * (size_t)n_rows), o_tidx = ar.take(16 * (size_t)n_rows), o_m = ar.take(4 * (size_t)n_2);
+    const size_t o_ev = ar.take(8 * (size_t)n_rows), o_ne = ar.take(4);
+    uint8_t* dev = nullptr;
+    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    cudaError_t e = cudaSuccess;
+    uint32_t n_ev = 0;
+    std::vector<int2> events;
+    do {
+#define UP(off, src, bytes) if ((bytes) && (e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
+        UP(o_rd, rdesc.data(), 32 * (size_t)n_rows);
+        UP(o_cb, row_cand_begin, 4 * (size_t)n_rows);
+        UP(o_ce, row_cand_end, 4 * (size_t)n_rows);
+        UP(o_it, cand_items, 4 * (size_t)n_items);
+        UP(o_kd, kp2_desc, 32 * (size_t)n_2);
+        UP(o_tk, kp2_has_lm, n_2);
+        UP(o_rb, rbear.data(), 24 * (size_t)n_rows);
+        UP(o_kb, bearings_2, 24 * (size_t)n_2);
+        UP(o_rs, rstereo.data(), n_rows);
+        UP(o_ks, kstereo.data(), n_2);
+        UP(o_rsc, rscale.data(), 4 * (size_t)n_rows);
+#undef UP
+        ProjArgs a = {};
+        a.mode = 3;
+        a.tri = 1;
+        a.last_wins = 1;  // robust.cc:108: an equal distance replaces the best
+        a.n_last = n_rows;
+        a.n_curr = n_2;
+        a.last_desc = dev + o_rd;
+        a.cand_begin = (const uint32_t*)(dev + o_cb);
+        a.cand_end = (const uint32_t*)(dev + o_ce);
+        a.cand_items = (const uint32_t*)(dev + o_it);
+        a.desc = dev + o_kd;
+        a.curr_taken = dev + o_tk;  // robust.cc:87-91: keypoints with a landmark are never candidates
+        a.row_bearing = (const double*)(dev + o_rb);
+        a.kp_bearing = (const double*)(dev + o_kb);
+        a.row_stereo = dev + o_rs;
+        a.kp_stereo = dev + o_ks;
+        a.row_scale = (const float*)(dev + o_rsc);
+        for (int i = 0; i < 9; ++i) a.E[i] = E_12[i];
+        for (int i = 0; i < 3; ++i) a.epi[i] = epiplane_in_keyfrm_2[i];
+        a.use_ratio = 0;
+        a.hamm_thr = 50;  // HAMMING_DIST_THR_LOW, robust.cc:78,108
+        a.top_key = (uint4*)(dev + o_tkey);
+        a.top_idx = (int4*)(dev + o_tidx);
+        a.curr_match_last = (int32_t*)(dev + o_m);
+        a.events = (int2*)(dev + o_ev);
+        a.n_events = (uint32_t*)(dev + o_ne);
+        k_proj_topk<<<(n_rows + 127) / 128, 128>>>(a);
+        a.claim_in_smem = n_2 <= 10000;
+        k_lm_resolve<<<1, 32, ((n_2 + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_2 : 0)>>>(a);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if (n_ev) {
+            events.resize(n_ev);
+            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        }
+    } while (false);
+    scratch_free(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_triangulation", __FILE__, __LINE__);
+    *n_matches = n_ev;
+    std::vector<std::pair<float, int>> deltas;
+    for (const int2& ev : events) {  // events are in row order = the order of robust.cc:133-141
+        const uint32_t i1 = row_idx_1[ev.x];
+        matched_idx_2_in_1[i1] = ev.y;
+        if (check_orientation) deltas.emplace_back(kp1_undist[i1].angle - kp2_undist[ev.y].angle, (int)i1);
+    }
+    if (check_orientation)
+        for (int id : angle_invalid_matches(deltas)) {
+            matched_idx_2_in_1[id] = -1;
+            --*n_matches;
+        }
     return LPSLAM_OK;
 }

@@ -285,6 +285,109 @@ class bow_tree:
         return res, int(n.value)
 
 
+register("lpslam_match_sim3", C.c_int, [C.POINTER(_lib.Camera), C.c_float, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _lib.u32p])
+_MUTUAL_SIDE = [C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+register("lpslam_match_mutual", C.c_int, [C.POINTER(_lib.Camera), C.POINTER(_lib.Camera), C.c_float] + _MUTUAL_SIDE + _MUTUAL_SIDE
+         + [C.c_void_p, _lib.u32p])
+
+
+class _projection_keyframes:
+    """The keyframe-to-keyframe members of match::projection (match/projection.h) used by loop closing. The per-landmark
+    geometry in front of the search loops (reprojection under the Sim3, valid-distance / viewing-angle gates,
+    predict_scale_level) stays the caller's; rows come with its results."""
+
+    def __init__(self, lowe_ratio=0.6, check_orientation=True):
+        self.lowe_ratio_, self.check_orientation_ = float(lowe_ratio), bool(check_orientation)  # carried, not used by these two
+
+    def match_by_Sim3_transform(self, cam, lm_active, lm_reproj, lm_scale_level, lm_descs, undist_keypts, descs,
+                                has_matched_lm, scale_factors, margin):
+        """match/projection.cc:317-413: returns (kp_match_lm, num_matches); kp_match_lm[i] = row (landmark) that keypoint i
+        of the keyframe received (matched_lms_in_keyfrm.at(i) = lm), or -1."""
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64).reshape(-1, 2)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_descs, np.uint8).reshape(-1, 32)
+        kp = np.ascontiguousarray(undist_keypts, KP_DTYPE)
+        cd = np.ascontiguousarray(descs, np.uint8)
+        tk = np.ascontiguousarray(has_matched_lm, np.uint8)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        out = np.full(len(kp), -1, np.int32)
+        n = C.c_uint32(0)
+        check(lib().lpslam_match_sim3(C.byref(cam), float(margin), len(act), act.ctypes.data, rp.ctypes.data, lvl.ctypes.data,
+                                      ld.ctypes.data, len(kp), kp.ctypes.data, cd.ctypes.data, tk.ctypes.data, sf.ctypes.data,
+                                      out.ctypes.data, C.byref(n)))
+        return out, int(n.value)
+
+    def match_keyframes_mutually(self, cam_1, cam_2, side_1, side_2, margin):
+        """match/projection.cc:415-636. side_k = (lm_active, lm_reproj_in_other, lm_level_in_other, lm_descs, undist_keypts,
+        descs, scale_factors) of keyframe k, one landmark slot per keypoint. Returns (matched_idx_2_in_1, num_matches)."""
+        def prep(side):
+            act, rp, lvl, ld, kp, kd, sc = side
+            return [np.ascontiguousarray(act, np.uint8), np.ascontiguousarray(rp, np.float64).reshape(-1, 2),
+                    np.ascontiguousarray(lvl, np.int32), np.ascontiguousarray(ld, np.uint8).reshape(-1, 32),
+                    np.ascontiguousarray(kp, KP_DTYPE), np.ascontiguousarray(kd, np.uint8), np.ascontiguousarray(sc, np.float32)]
+
+        a, b = prep(side_1), prep(side_2)
+        out = np.full(len(a[4]), -1, np.int32)
+        n = C.c_uint32(0)
+
+        def args(x):
+            return [len(x[4]), x[0].ctypes.data, x[1].ctypes.data, x[2].ctypes.data, x[3].ctypes.data, x[4].ctypes.data,
+                    x[5].ctypes.data, x[6].ctypes.data]
+
+        check(lib().lpslam_match_mutual(C.byref(cam_1), C.byref(cam_2), float(margin), *args(a), *args(b), out.ctypes.data, C.byref(n)))
+        return out, int(n.value)
+
+
+register("lpslam_match_triangulation", C.c_int, [C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                                 C.c_void_p, _lib.u32p])
+
+
+def match_for_triangulation(feat_vec_1, side_1, feat_vec_2, side_2, E_12, epiplane_in_keyfrm_2, check_orientation=True):
+    """match::robust::match_for_triangulation (match/robust.cc:18-178). feat_vec_k = (node_ids, node_start, items);
+    side_1 = (undist_keypts, descs, bearings, stereo_x_right, has_landmark, scale_factors), side_2 the same without the
+    scale factors. Returns (matched_idx_2_in_1, num_matches); the pairs of :172-180 are the entries >= 0 in index order."""
+    id1, st1, it1 = [np.ascontiguousarray(x, np.uint32) for x in feat_vec_1]
+    id2, st2, it2 = [np.ascontiguousarray(x, np.uint32) for x in feat_vec_2]
+    kp1, d1, b1, x1, h1, sc1 = side_1
+    kp2, d2, b2, x2, h2 = side_2[:5]
+    kp1, kp2 = np.ascontiguousarray(kp1, KP_DTYPE), np.ascontiguousarray(kp2, KP_DTYPE)
+    d1, d2 = np.ascontiguousarray(d1, np.uint8), np.ascontiguousarray(d2, np.uint8)
+    b1, b2 = np.ascontiguousarray(b1, np.float64).reshape(-1, 3), np.ascontiguousarray(b2, np.float64).reshape(-1, 3)
+    x1, x2 = np.ascontiguousarray(x1, np.float32), np.ascontiguousarray(x2, np.float32)
+    h1, h2 = np.ascontiguousarray(h1, np.uint8), np.ascontiguousarray(h2, np.uint8)
+    sc1 = np.ascontiguousarray(sc1, np.float32)
+    E = np.ascontiguousarray(E_12, np.float64).reshape(9)
+    epi = np.ascontiguousarray(epiplane_in_keyfrm_2, np.float64).reshape(3)
+    rows, begin, end = [], [], []
+    a = b = 0
+    while a < len(id1) and b < len(id2):  # the merge walk of robust.cc:55-161
+        if id1[a] == id2[b]:
+            for i1 in it1[st1[a]:st1[a + 1]]:
+                if not h1[i1]:
+                    rows.append(i1)
+                    begin.append(st2[b])
+                    end.append(st2[b + 1])
+            a += 1
+            b += 1
+        elif id1[a] < id2[b]:
+            a += 1
+        else:
+            b += 1
+    ri = np.asarray(rows, np.uint32)
+    rb, re_ = np.asarray(begin, np.uint32), np.asarray(end, np.uint32)
+    out = np.full(len(kp1), -1, np.int32)
+    n = C.c_uint32(0)
+    check(lib().lpslam_match_triangulation(len(ri), ri.ctypes.data, rb.ctypes.data, re_.ctypes.data, it2.ctypes.data, len(it2),
+                                           len(kp1), kp1.ctypes.data, d1.ctypes.data, b1.ctypes.data, x1.ctypes.data, sc1.ctypes.data,
+                                           len(kp2), kp2.ctypes.data, d2.ctypes.data, b2.ctypes.data, x2.ctypes.data, h2.ctypes.data,
+                                           E.ctypes.data, epi.ctypes.data, int(check_orientation), out.ctypes.data, C.byref(n)))
+    return out, int(n.value)
+
+
 register("lpslam_match_area", C.c_int, [C.POINTER(_lib.Camera), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                         C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, _lib.u32p])
 
@@ -361,9 +464,16 @@ class robust:
         assert len(matches) == n.value
         return matches, out
 
+    def match_for_triangulation(self, feat_vec_1, side_1, feat_vec_2, side_2, E_12, epiplane_in_keyfrm_2):
+        """match/robust.cc:18-178: returns the (idx_1, idx_2) pairs in order of idx_1 and matched_idx_2_in_1."""
+        out, n = match_for_triangulation(feat_vec_1, side_1, feat_vec_2, side_2, E_12, epiplane_in_keyfrm_2, self.check_orientation_)
+        idx_1 = np.nonzero(out >= 0)[0]
+        assert len(idx_1) == n
+        return np.stack([idx_1, out[idx_1]], axis=1).astype(np.int32), out
 
-class projection:
-    """match::projection (match/projection.h:21-30)."""
+
+class projection(_projection_keyframes):
+    """match::projection (match/projection.h:21-30); match_by_Sim3_transform / match_keyframes_mutually come from the base."""
 
     def __init__(self, lowe_ratio=0.6, check_orientation=True):
         self.lowe_ratio_, self.check_orientation_ = float(lowe_ratio), bool(check_orientation)

@@ -537,6 +537,174 @@ int orc_match_bow_keyframes(uint32_t n_nodes_1, const uint32_t* node_id_1, const
     return num;
 }
 
+// match/projection.cc:317-413 match_by_Sim3_transform, the search loop (:372-410). Rows = the landmarks that passed the
+// caller's gates (:333-370) with their reprojection into the keyframe and predicted scale level; kp_has_lm =
+// matched_lms_in_keyfrm.at(idx) != nullptr on entry. kp_match_lm[i] = row whose landmark keypoint i received, or -1.
+int orc_match_sim3(const orc_camera* cam, float margin, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                   const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp, const orc_keypoint* kp,
+                   const uint8_t* kp_desc, const uint8_t* kp_has_lm, const float* scale_factors, int32_t* kp_match_lm) {
+    int num = 0;
+    const auto grid = assign_grid(cam, n_kp, kp);
+    std::vector<uint8_t> matched(kp_has_lm, kp_has_lm + n_kp);
+    std::fill(kp_match_lm, kp_match_lm + n_kp, -1);
+    std::vector<unsigned> indices;
+    for (unsigned j = 0; j < n_lm; ++j) {
+        if (!lm_active[j]) continue;
+        const unsigned pred_scale_level = static_cast<unsigned>(lm_scale_level[j]);
+        keypoints_in_cell(cam, grid, kp, static_cast<float>(lm_reproj[2 * j]), static_cast<float>(lm_reproj[2 * j + 1]),
+                          margin * scale_factors[pred_scale_level], -1, -1, indices);
+        if (indices.empty()) continue;
+        const uint8_t* ld = lm_desc + static_cast<size_t>(j) * 32;
+        unsigned best_dist = MAX_HAMMING_DIST;
+        int best_idx = -1;
+        for (const auto idx : indices) {
+            if (matched[idx]) continue;
+            const unsigned scale_level = static_cast<unsigned>(kp[idx].octave);
+            if (scale_level < pred_scale_level - 1 || pred_scale_level < scale_level) continue;  // unsigned, :385-390
+            const unsigned d = hamming_32(ld, kp_desc + static_cast<size_t>(idx) * 32);
+            if (d < best_dist) {
+                best_dist = d;
+                best_idx = static_cast<int>(idx);
+            }
+        }
+        if (HAMMING_DIST_THR_LOW < best_dist) continue;
+        matched[best_idx] = 1;
+        kp_match_lm[best_idx] = static_cast<int32_t>(j);
+        ++num;
+    }
+    return num;
+}
+
+// one direction of match/projection.cc:453-534 / :536-616: rows of keyframe A against the keypoints of keyframe B
+static void mutual_one_way(const orc_camera* cam_b, float margin, uint32_t n_a, const uint8_t* active, const double* reproj,
+                           const int32_t* level, const uint8_t* lm_desc, uint32_t n_b, const orc_keypoint* kp_b,
+                           const uint8_t* desc_b, const float* scale_b, std::vector<int>& out) {
+    out.assign(n_a, -1);
+    const auto grid = assign_grid(cam_b, n_b, kp_b);
+    std::vector<unsigned> indices;
+    for (unsigned a = 0; a < n_a; ++a) {
+        if (!active[a]) continue;
+        const unsigned pred_scale_level = static_cast<unsigned>(level[a]);
+        keypoints_in_cell(cam_b, grid, kp_b, static_cast<float>(reproj[2 * a]), static_cast<float>(reproj[2 * a + 1]),
+                          margin * scale_b[pred_scale_level], -1, -1, indices);
+        if (indices.empty()) continue;
+        const uint8_t* ld = lm_desc + static_cast<size_t>(a) * 32;
+        unsigned best_hamm_dist = MAX_HAMMING_DIST;
+        int best_idx = -1;
+        for (const auto idx : indices) {
+            const unsigned scale_level = static_cast<unsigned>(kp_b[idx].octave);
+            if (scale_level < pred_scale_level - 1 || pred_scale_level < scale_level) continue;
+            const unsigned d = hamming_32(ld, desc_b + static_cast<size_t>(idx) * 32);
+            if (d < best_hamm_dist) {
+                best_hamm_dist = d;
+                best_idx = static_cast<int>(idx);
+            }
+        }
+        if (best_hamm_dist <= HAMMING_DIST_THR_HIGH) out[a] = best_idx;
+    }
+}
+
+// match/projection.cc:415-636 match_keyframes_mutually: both search loops and the cross-check (:618-631)
+int orc_match_mutual(const orc_camera* cam_1, const orc_camera* cam_2, float margin, uint32_t n_1, const uint8_t* lm1_active,
+                     const double* lm1_reproj_in_2, const int32_t* lm1_level_in_2, const uint8_t* lm1_desc, const orc_keypoint* kp1,
+                     const uint8_t* desc1, const float* scale_1, uint32_t n_2, const uint8_t* lm2_active,
+                     const double* lm2_reproj_in_1, const int32_t* lm2_level_in_1, const uint8_t* lm2_desc, const orc_keypoint* kp2,
+                     const uint8_t* desc2, const float* scale_2, int32_t* matched_2_in_1) {
+    std::vector<int> two_in_1, one_in_2;
+    mutual_one_way(cam_2, margin, n_1, lm1_active, lm1_reproj_in_2, lm1_level_in_2, lm1_desc, n_2, kp2, desc2, scale_2, two_in_1);
+    mutual_one_way(cam_1, margin, n_2, lm2_active, lm2_reproj_in_1, lm2_level_in_1, lm2_desc, n_1, kp1, desc1, scale_1, one_in_2);
+    int num = 0;
+    for (unsigned i = 0; i < n_1; ++i) {
+        matched_2_in_1[i] = -1;
+        const int idx_2 = two_in_1[i];
+        if (idx_2 < 0) continue;
+        if (one_in_2[idx_2] == static_cast<int>(i)) {
+            matched_2_in_1[i] = idx_2;
+            ++num;
+        }
+    }
+    return num;
+}
+
+// match/robust.cc:323-341 check_epipolar_constraint (E_12 row-major; products summed left to right)
+static bool check_epipolar_constraint(const double* b1, const double* b2, const double* E, float bearing_1_scale_factor) {
+    double epi[3];
+    for (int r = 0; r < 3; ++r) epi[r] = E[3 * r] * b2[0] + E[3 * r + 1] * b2[1] + E[3 * r + 2] * b2[2];
+    const double norm = std::sqrt(epi[0] * epi[0] + epi[1] * epi[1] + epi[2] * epi[2]);
+    const double cos_residual = (epi[0] * b1[0] + epi[1] * b1[1] + epi[2] * b1[2]) / norm;
+    const double residual_rad = M_PI / 2.0 - std::abs(std::acos(cos_residual));
+    constexpr double residual_deg_thr = 0.2;
+    constexpr double residual_rad_thr = residual_deg_thr * M_PI / 180.0;
+    return residual_rad < residual_rad_thr * bearing_1_scale_factor;
+}
+
+// match/robust.cc:18-178 match_for_triangulation; feature vectors as sorted node ids + CSR index lists
+int orc_match_triangulation(uint32_t n_nodes_1, const uint32_t* node_id_1, const uint32_t* node_start_1, const uint32_t* items_1,
+                            uint32_t n_nodes_2, const uint32_t* node_id_2, const uint32_t* node_start_2, const uint32_t* items_2,
+                            uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc_1, const double* bearings_1,
+                            const float* x_right_1, const uint8_t* has_lm_1, const float* scale_1, uint32_t n2,
+                            const orc_keypoint* kp2, const uint8_t* desc_2, const double* bearings_2, const float* x_right_2,
+                            const uint8_t* has_lm_2, const double* E_12, const double* epiplane_in_keyfrm_2, int check_orientation,
+                            int32_t* matched_2_in_1) {
+    int num = 0;
+    AngleHistogram hist;
+    std::vector<uint8_t> is_already_matched_in_keyfrm_2(n2, 0);
+    std::fill(matched_2_in_1, matched_2_in_1 + n1, -1);
+    uint32_t a = 0, b = 0;
+    while (a < n_nodes_1 && b < n_nodes_2) {
+        if (node_id_1[a] == node_id_2[b]) {
+            for (uint32_t qa = node_start_1[a]; qa < node_start_1[a + 1]; ++qa) {
+                const uint32_t idx_1 = items_1[qa];
+                if (has_lm_1[idx_1]) continue;
+                const bool is_stereo_keypt_1 = 0 <= x_right_1[idx_1];
+                const double* bearing_1 = bearings_1 + 3 * static_cast<size_t>(idx_1);
+                const uint8_t* d1 = desc_1 + static_cast<size_t>(idx_1) * 32;
+                unsigned best_hamm_dist = HAMMING_DIST_THR_LOW;
+                int best_idx_2 = -1;
+                for (uint32_t qb = node_start_2[b]; qb < node_start_2[b + 1]; ++qb) {
+                    const uint32_t idx_2 = items_2[qb];
+                    if (has_lm_2[idx_2]) continue;
+                    if (is_already_matched_in_keyfrm_2[idx_2]) continue;
+                    const bool is_stereo_keypt_2 = 0 <= x_right_2[idx_2];
+                    const double* bearing_2 = bearings_2 + 3 * static_cast<size_t>(idx_2);
+                    const unsigned hamm_dist = hamming_32(d1, desc_2 + static_cast<size_t>(idx_2) * 32);
+                    if (HAMMING_DIST_THR_LOW < hamm_dist || best_hamm_dist < hamm_dist) continue;
+                    if (!is_stereo_keypt_1 && !is_stereo_keypt_2) {
+                        const double cos_dist = epiplane_in_keyfrm_2[0] * bearing_2[0] + epiplane_in_keyfrm_2[1] * bearing_2[1]
+                                                + epiplane_in_keyfrm_2[2] * bearing_2[2];
+                        constexpr double cos_dist_thr = 0.99862953475;
+                        if (cos_dist_thr < cos_dist) continue;
+                    }
+                    if (check_epipolar_constraint(bearing_1, bearing_2, E_12, scale_1[kp1[idx_1].octave])) {
+                        best_idx_2 = static_cast<int>(idx_2);
+                        best_hamm_dist = hamm_dist;
+                    }
+                }
+                if (best_idx_2 < 0) continue;
+                is_already_matched_in_keyfrm_2[best_idx_2] = 1;
+                matched_2_in_1[idx_1] = best_idx_2;
+                ++num;
+                if (check_orientation) hist.append(kp1[idx_1].angle - kp2[best_idx_2].angle, static_cast<int>(idx_1));
+            }
+            ++a;
+            ++b;
+        }
+        else if (node_id_1[a] < node_id_2[b]) {
+            while (a < n_nodes_1 && node_id_1[a] < node_id_2[b]) ++a;  // lower_bound
+        }
+        else {
+            while (b < n_nodes_2 && node_id_2[b] < node_id_1[a]) ++b;
+        }
+    }
+    if (check_orientation) {
+        for (int id : hist.invalid()) {
+            matched_2_in_1[id] = -1;
+            --num;
+        }
+    }
+    return num;
+}
+
 // match/area.cc:8-112 match_in_consistent_area over flat arrays; prev_pts (n1 x 2) is updated in place
 int orc_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc1, float* prev_pts, uint32_t n2,
                    const orc_keypoint* kp2, const uint8_t* desc2, int margin, float lowe_ratio, int check_orientation,

@@ -131,6 +131,23 @@ int orc_match_fuse(const orc_camera* cam, float margin, int chi_gate, int unsign
                    const double* lm_reproj, const float* lm_x_right, const int32_t* lm_scale_level, const uint8_t* lm_desc,
                    uint32_t n_kp, const orc_keypoint* kp, const uint8_t* kp_desc, const float* kp_x_right,
                    const float* scale_factors, const float* inv_level_sigma_sq, int32_t* best_idx, uint32_t* best_dist);
+/* match/projection.cc:317-413 match_by_Sim3_transform search loop; :415-636 match_keyframes_mutually (both loops + cross-check);
+ * match/robust.cc:18-178 match_for_triangulation (E_12 row-major). Each returns num_matches. */
+int orc_match_sim3(const orc_camera* cam, float margin, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj,
+                   const int32_t* lm_scale_level, const uint8_t* lm_desc, uint32_t n_kp, const orc_keypoint* kp,
+                   const uint8_t* kp_desc, const uint8_t* kp_has_lm, const float* scale_factors, int32_t* kp_match_lm);
+int orc_match_mutual(const orc_camera* cam_1, const orc_camera* cam_2, float margin, uint32_t n_1, const uint8_t* lm1_active,
+                     const double* lm1_reproj_in_2, const int32_t* lm1_level_in_2, const uint8_t* lm1_desc, const orc_keypoint* kp1,
+                     const uint8_t* desc1, const float* scale_1, uint32_t n_2, const uint8_t* lm2_active,
+                     const double* lm2_reproj_in_1, const int32_t* lm2_level_in_1, const uint8_t* lm2_desc, const orc_keypoint* kp2,
+                     const uint8_t* desc2, const float* scale_2, int32_t* matched_2_in_1);
+int orc_match_triangulation(uint32_t n_nodes_1, const uint32_t* node_id_1, const uint32_t* node_start_1, const uint32_t* items_1,
+                            uint32_t n_nodes_2, const uint32_t* node_id_2, const uint32_t* node_start_2, const uint32_t* items_2,
+                            uint32_t n1, const orc_keypoint* kp1, const uint8_t* desc_1, const double* bearings_1,
+                            const float* x_right_1, const uint8_t* has_lm_1, const float* scale_1, uint32_t n2,
+                            const orc_keypoint* kp2, const uint8_t* desc_2, const double* bearings_2, const float* x_right_2,
+                            const uint8_t* has_lm_2, const double* E_12, const double* epiplane_in_keyfrm_2, int check_orientation,
+                            int32_t* matched_2_in_1);
 int orc_match_bow_keyframes(uint32_t n_nodes_1, const uint32_t* node_id_1, const uint32_t* node_start_1, const uint32_t* items_1,
                             uint32_t n_nodes_2, const uint32_t* node_id_2, const uint32_t* node_start_2, const uint32_t* items_2,
                             uint32_t n1, const uint8_t* valid_1, const uint8_t* desc_1, const float* angle_1, uint32_t n2,

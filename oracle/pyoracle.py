@@ -387,6 +387,78 @@ class Oracle:
               _ptr(a2, f32p), lowe_ratio, int(check_orientation), _ptr(out, i32p))
         return out, n
 
+    def match_sim3(self, cam, margin, lm_active, lm_reproj, lm_scale_level, lm_desc, kp, kp_desc, kp_has_lm, scale):
+        """search loop of projection::match_by_Sim3_transform: (kp_match_lm, num_matches)"""
+        f64p = C.POINTER(C.c_double)
+        act = np.ascontiguousarray(lm_active, np.uint8)
+        rp = np.ascontiguousarray(lm_reproj, np.float64)
+        lvl = np.ascontiguousarray(lm_scale_level, np.int32)
+        ld = np.ascontiguousarray(lm_desc, np.uint8)
+        kp = np.ascontiguousarray(kp, KP_DTYPE)
+        kd = np.ascontiguousarray(kp_desc, np.uint8)
+        tk = np.ascontiguousarray(kp_has_lm, np.uint8)
+        scale = np.ascontiguousarray(scale, np.float32)
+        out = np.empty(len(kp), np.int32)
+        f = self.lib.orc_match_sim3
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_float, C.c_uint32, u8p, f64p, i32p, u8p, C.c_uint32, C.c_void_p, u8p, u8p, f32p, i32p]
+        n = f(C.cast(C.byref(cam), C.c_void_p), margin, len(act), _ptr(act, u8p), _ptr(rp, f64p), _ptr(lvl, i32p), _ptr(ld, u8p),
+              len(kp), kp.ctypes.data, _ptr(kd, u8p), _ptr(tk, u8p), _ptr(scale, f32p), _ptr(out, i32p))
+        return out, n
+
+    def match_mutual(self, cam_1, cam_2, margin, side_1, side_2):
+        """projection::match_keyframes_mutually; side = (lm_active, lm_reproj_in_other, lm_level_in_other, lm_desc, kp, kp_desc,
+        scale_factors): (matched_idx_2_in_1, num_matches)"""
+        f64p = C.POINTER(C.c_double)
+
+        def prep(side):
+            act, rp, lvl, ld, kp, kd, sc = side
+            return [np.ascontiguousarray(act, np.uint8), np.ascontiguousarray(rp, np.float64), np.ascontiguousarray(lvl, np.int32),
+                    np.ascontiguousarray(ld, np.uint8), np.ascontiguousarray(kp, KP_DTYPE), np.ascontiguousarray(kd, np.uint8),
+                    np.ascontiguousarray(sc, np.float32)]
+
+        a, b = prep(side_1), prep(side_2)
+        out = np.empty(len(a[4]), np.int32)
+        f = self.lib.orc_match_mutual
+        f.restype = C.c_int
+        one = [C.c_uint32, u8p, f64p, i32p, u8p, C.c_void_p, u8p, f32p]
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_float] + one + one + [i32p]
+
+        def args(x):
+            return [len(x[4]), _ptr(x[0], u8p), _ptr(x[1], f64p), _ptr(x[2], i32p), _ptr(x[3], u8p), x[4].ctypes.data, _ptr(x[5], u8p),
+                    _ptr(x[6], f32p)]
+
+        n = f(C.cast(C.byref(cam_1), C.c_void_p), C.cast(C.byref(cam_2), C.c_void_p), margin, *args(a), *args(b), _ptr(out, i32p))
+        return out, n
+
+    def match_triangulation(self, vec_1, vec_2, side_1, side_2, E_12, epiplane_in_keyfrm_2, check_orientation):
+        """robust::match_for_triangulation; side = (kp, desc, bearings, x_right, has_lm[, scale_factors for side 1]):
+        (matched_idx_2_in_1, num_matches)"""
+        u32p = C.POINTER(C.c_uint32)
+        f64p = C.POINTER(C.c_double)
+        a = [np.ascontiguousarray(x, np.uint32) for x in vec_1]
+        b = [np.ascontiguousarray(x, np.uint32) for x in vec_2]
+        kp1, d1, b1, x1, h1, sc1 = side_1
+        kp2, d2, b2, x2, h2 = side_2[:5]
+        kp1, kp2 = np.ascontiguousarray(kp1, KP_DTYPE), np.ascontiguousarray(kp2, KP_DTYPE)
+        d1, d2 = np.ascontiguousarray(d1, np.uint8), np.ascontiguousarray(d2, np.uint8)
+        b1, b2 = np.ascontiguousarray(b1, np.float64), np.ascontiguousarray(b2, np.float64)
+        x1, x2 = np.ascontiguousarray(x1, np.float32), np.ascontiguousarray(x2, np.float32)
+        h1, h2 = np.ascontiguousarray(h1, np.uint8), np.ascontiguousarray(h2, np.uint8)
+        sc1 = np.ascontiguousarray(sc1, np.float32)
+        E = np.ascontiguousarray(E_12, np.float64).reshape(9)
+        epi = np.ascontiguousarray(epiplane_in_keyfrm_2, np.float64).reshape(3)
+        out = np.empty(len(kp1), np.int32)
+        f = self.lib.orc_match_triangulation
+        f.restype = C.c_int
+        f.argtypes = [C.c_uint32, u32p, u32p, u32p, C.c_uint32, u32p, u32p, u32p, C.c_uint32, C.c_void_p, u8p, f64p, f32p, u8p, f32p,
+                      C.c_uint32, C.c_void_p, u8p, f64p, f32p, u8p, f64p, f64p, C.c_int, i32p]
+        n = f(len(a[0]), _ptr(a[0], u32p), _ptr(a[1], u32p), _ptr(a[2], u32p), len(b[0]), _ptr(b[0], u32p), _ptr(b[1], u32p),
+              _ptr(b[2], u32p), len(kp1), kp1.ctypes.data, _ptr(d1, u8p), _ptr(b1, f64p), _ptr(x1, f32p), _ptr(h1, u8p), _ptr(sc1, f32p),
+              len(kp2), kp2.ctypes.data, _ptr(d2, u8p), _ptr(b2, f64p), _ptr(x2, f32p), _ptr(h2, u8p), _ptr(E, f64p), _ptr(epi, f64p),
+              int(check_orientation), _ptr(out, i32p))
+        return out, n
+
     def match_area(self, cam, kp1, desc1, prev_pts, kp2, desc2, margin, lowe_ratio, check_orientation):
         kp1 = np.ascontiguousarray(kp1, KP_DTYPE)
         kp2 = np.ascontiguousarray(kp2, KP_DTYPE)

@@ -461,3 +461,172 @@ def test_bow_tree_match_keyframes(oracle, seed, chk):
         assert (got[v1 == 0] == -1).all() and v2[got[got >= 0]].all()
         total += nw
     assert total > 200
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_match_by_sim3_transform(oracle, seed):
+    # match/projection.cc:317-413 (search loop :372-410): landmarks fight for keypoints, unsigned level comparison
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    args, active, reproj, lxr, level, ldesc, kp, desc, xr, taken, sf, obs = landmarks_case(oracle, seed, False, False)
+    total = 0
+    for margin in (3.0, 7.5, 10.0):
+        want, nw = oracle.match_sim3(pyoracle.make_camera(**args), margin, active, reproj, level, ldesc, kp, desc, taken, sf)
+        got, ng = match.projection().match_by_Sim3_transform(match.make_camera(**args), active, reproj, level, ldesc, kp, desc, taken,
+                                                             sf, margin)
+        assert np.array_equal(got, want) and ng == nw
+        assert (got[taken != 0] == -1).all()
+        hit = got[got >= 0]
+        assert (np.asarray(level)[hit] > 0).all()  # :385-390 on unsigned levels: a predicted level of 0 never matches
+        total += nw
+    assert total > 500
+
+
+def mutual_side(rng, kp_self, kp_other, desc_other, n_other_levels=8):
+    """landmarks of one keyframe (a slot per keypoint): reprojected near a random keypoint of the other keyframe, descriptor =
+    that keypoint's with noise, level at or above its octave"""
+    n = len(kp_self)
+    tgt = rng.integers(0, len(kp_other), n)
+    reproj = np.stack([kp_other["x"][tgt], kp_other["y"][tgt]], axis=1).astype(np.float64) + rng.normal(0, 1.5, (n, 2))
+    level = np.clip(kp_other["octave"][tgt] + rng.integers(0, 2, n), 0, n_other_levels - 1).astype(np.int32)
+    ldesc = desc_other[tgt] ^ np.packbits(rng.random((n, 256)) < 0.08, axis=1, bitorder="little")
+    active = (rng.random(n) < 0.8).astype(np.uint8)
+    return active, reproj, level, ldesc, tgt
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_match_keyframes_mutually(oracle, seed):
+    # match/projection.cc:415-636: both one-way searches (threshold HIGH, unsigned levels) and the cross-check
+    from lpslam_b200 import match
+    from oracle import pyoracle
+    rng = np.random.default_rng(seed)
+    o1, o2 = oracle.extractor(max_kpts=1000), oracle.extractor(max_kpts=800)
+    kp1, d1 = o1.extract(synth_image(480, 640, 90 + seed))
+    kp2, d2 = o2.extract(synth_image(480, 640, 95 + seed))
+    sf = o1.table(0)
+    a1, r1, l1, ld1, t1 = mutual_side(rng, kp1, kp2, d2)
+    a2, r2, l2, ld2, t2 = mutual_side(rng, kp2, kp1, d1)
+    # make a share of the pairs mutual: landmark of keypoint t1[i] in keyframe 2 points back at i
+    back = rng.random(len(kp1)) < 0.6
+    idx = np.nonzero(back)[0]
+    r2[t1[idx]] = np.stack([kp1["x"][idx], kp1["y"][idx]], axis=1) + rng.normal(0, 1.0, (len(idx), 2))
+    l2[t1[idx]] = np.clip(kp1["octave"][idx] + rng.integers(0, 2, len(idx)), 0, 7)
+    ld2[t1[idx]] = d1[idx] ^ np.packbits(rng.random((len(idx), 256)) < 0.05, axis=1, bitorder="little")
+    args = dict(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    total = 0
+    for margin in (4.0, 7.5):
+        want, nw = oracle.match_mutual(pyoracle.make_camera(**args), pyoracle.make_camera(**args), margin, (a1, r1, l1, ld1, kp1, d1, sf),
+                                       (a2, r2, l2, ld2, kp2, d2, sf))
+        got, ng = match.projection().match_keyframes_mutually(match.make_camera(**args), match.make_camera(**args),
+                                                              (a1, r1, l1, ld1, kp1, d1, sf), (a2, r2, l2, ld2, kp2, d2, sf), margin)
+        assert np.array_equal(got, want) and ng == nw
+        total += nw
+    assert total > 100
+
+
+def triangulation_case(oracle, seed, stereo):
+    """two keyframes related by a sideways translation: bearings of keyframe 2 = bearings of keyframe 1 pushed through the
+    relative pose with random depths (so that E_12 holds for the true pairs), descriptors with noise, shared BoW nodes"""
+    rng = np.random.default_rng(seed)
+    o = oracle.extractor(max_kpts=1000)
+    kp1, d1 = o.extract(synth_image(480, 640, 60 + seed))
+    n = len(kp1)
+    fx = fy = 500.0
+    cx, cy = 320.0, 240.0
+    b1 = np.stack([(kp1["x"] - cx) / fx, (kp1["y"] - cy) / fy, np.ones(n)], axis=1).astype(np.float64)
+    b1 /= np.linalg.norm(b1, axis=1, keepdims=True)
+    ang = 0.05
+    R21 = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    t21 = np.array([0.3, 0.02, 0.05])
+    depth = rng.uniform(2.0, 10.0, n)
+    p2 = (R21 @ (b1 * depth[:, None]).T).T + t21
+    perm = rng.permutation(n)
+    b2 = p2[perm] / np.linalg.norm(p2[perm], axis=1, keepdims=True)
+    b2 += rng.normal(0, 1.5e-3, b2.shape)  # some pairs fall outside the 0.2 degree x scale band
+    b2 /= np.linalg.norm(b2, axis=1, keepdims=True)
+    kp2 = kp1[perm].copy()
+    kp2["angle"] = (kp2["angle"] + rng.normal(0, 4.0, n)).astype(np.float32) % 360
+    d2 = d1[perm] ^ np.packbits(rng.random((n, 256)) < 0.05, axis=1, bitorder="little")
+    # E_12 = [t_12]x R_12 with x_1 = R_12 x_2 + t_12
+    R12, t12 = R21.T, -R21.T @ t21
+    tx = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    E12 = tx @ R12
+    c1_in_2 = t21 / np.linalg.norm(t21)  # centre of keyframe 1 seen from keyframe 2, as a bearing
+    vec1, node1 = bow_vector(rng, n, 50)
+    node2 = np.where(rng.random(n) < 0.9, node1[perm], rng.integers(0, 60, n))
+    ids = np.unique(node2)
+    vec2 = (ids.astype(np.uint32), np.concatenate([[0], np.cumsum([(node2 == v).sum() for v in ids])]).astype(np.uint32),
+            np.concatenate([np.nonzero(node2 == v)[0] for v in ids]).astype(np.uint32))
+    h1 = (rng.random(n) < 0.3).astype(np.uint8)
+    h2 = (rng.random(n) < 0.3).astype(np.uint8)
+    x1 = np.where(rng.random(n) < 0.5, kp1["x"] - 5.0, -1.0).astype(np.float32) if stereo else np.full(n, -1.0, np.float32)
+    x2 = np.where(rng.random(n) < 0.5, kp2["x"] - 5.0, -1.0).astype(np.float32) if stereo else np.full(n, -1.0, np.float32)
+    return vec1, (kp1, d1, b1, x1, h1, o.table(0)), vec2, (kp2, d2, b2, x2, h2), E12, c1_in_2
+
+
+@pytest.mark.parametrize("seed,stereo,chk", [(1, False, True), (2, True, False), (3, True, True)])
+def test_match_for_triangulation(oracle, seed, stereo, chk):
+    # match/robust.cc:18-178: epipole gate, epipolar constraint, `<=` replacement of the best, keypoints consumed in order
+    from lpslam_b200 import match
+    vec1, s1, vec2, s2, E12, epi = triangulation_case(oracle, seed, stereo)
+    want, nw = oracle.match_triangulation(vec1, vec2, s1, s2, E12, epi, chk)
+    pairs, got = match.robust(0.6, chk).match_for_triangulation(vec1, s1, vec2, s2, E12, epi)
+    assert np.array_equal(got, want) and len(pairs) == nw
+    assert nw > 150
+    assert (got[s1[4] != 0] == -1).all() and (s2[4][got[got >= 0]] == 0).all()  # only keypoints without landmarks
+    # the epipole itself as a bearing: nothing near it may match when neither side is a stereo keypoint
+    want2, nw2 = oracle.match_triangulation(vec1, vec2, s1, s2, E12, s2[2][0], chk)
+    _, got2 = match.robust(0.6, chk).match_for_triangulation(vec1, s1, vec2, s2, E12, s2[2][0])
+    assert np.array_equal(got2, want2)
+
+
+def test_match_for_triangulation_last_equal_wins(oracle):
+    # robust.cc:108: `best_hamm_dist < hamm_dist` lets a later candidate at the SAME distance replace the best
+    from lpslam_b200 import match
+    from lpslam_b200.orb import KP_DTYPE
+    rng = np.random.default_rng(5)
+    n2 = 12
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    d1 = base[None].copy()
+    d2 = np.repeat(base[None], n2, axis=0)
+    for i in range(n2):  # distances 3, 2, 2, 3, 2, ... : the LAST of the distance-2 candidates must win
+        flips = 2 if i % 3 else 3
+        d2[i, :flips] ^= 1
+    kp1 = np.zeros(1, KP_DTYPE)
+    kp2 = np.zeros(n2, KP_DTYPE)
+    b1 = np.array([[0.0, 0.0, 1.0]])
+    b2 = np.repeat(np.array([[0.0, 0.0, 1.0]]), n2, axis=0)
+    E = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])  # t = x: bearings along z satisfy it exactly
+    vec1 = (np.array([7], np.uint32), np.array([0, 1], np.uint32), np.array([0], np.uint32))
+    vec2 = (np.array([7], np.uint32), np.array([0, n2], np.uint32), np.arange(n2, dtype=np.uint32))
+    s1 = (kp1, d1, b1, np.array([-1.0], np.float32), np.zeros(1, np.uint8), np.ones(8, np.float32))
+    s2 = (kp2, d2, b2, np.full(n2, -1.0, np.float32), np.zeros(n2, np.uint8))
+    epi = np.array([1.0, 0.0, 0.0])
+    want, nw = oracle.match_triangulation(vec1, vec2, s1, s2, E, epi, False)
+    _, got = match.robust(0.6, False).match_for_triangulation(vec1, s1, vec2, s2, E, epi)
+    assert nw == 1 and want[0] == 11 and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("seed", [31, 32])
+def test_match_for_triangulation_clustered(oracle, seed):
+    """few prototypes and few vocabulary nodes: long candidate lists full of equal distances, so that the kept four
+    candidates run dry, the exact rescans run and the `<=` replacement order decides most rows"""
+    from lpslam_b200 import match
+    vec1, s1, vec2, s2, E12, epi = triangulation_case(oracle, seed, seed % 2 == 0)
+    rng = np.random.default_rng(seed)
+    n = len(s1[0])
+    protos = rng.integers(0, 256, (4, 32), dtype=np.uint8)
+    d1, d2 = clustered(rng, n, protos, 0.01), clustered(rng, n, protos, 0.01)
+    vec1, _ = bow_vector(rng, n, 6)
+    vec2, _ = bow_vector(rng, n, 6)
+    # bearings all close to the axis and E_12 of a pure x translation: most pairs are inliers, the descriptor order decides
+    b = np.stack([rng.normal(0, 0.2, n), rng.normal(0, 2e-3, n), np.ones(n)], axis=1)
+    b /= np.linalg.norm(b, axis=1, keepdims=True)
+    b2 = b[rng.permutation(n)]
+    E = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])
+    s1 = (s1[0], d1, b, s1[3], (rng.random(n) < 0.1).astype(np.uint8), s1[5])
+    s2 = (s2[0], d2, b2, s2[3], (rng.random(n) < 0.1).astype(np.uint8))
+    want, nw = oracle.match_triangulation(vec1, vec2, s1, s2, E, np.array([1.0, 0.0, 0.0]), True)
+    _, got = match.robust(0.6, True).match_for_triangulation(vec1, s1, vec2, s2, E, np.array([1.0, 0.0, 0.0]))
+    assert np.array_equal(got, want)
+    assert nw > 200

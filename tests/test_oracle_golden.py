@@ -200,3 +200,98 @@ def test_fuse_search_semantics(oracle):
     # replace_duplication compares unsigned levels: a predicted level of 0 rejects every candidate (fuse.cc:193)
     best, _, n = run(two[:1], [[102.0, 101.0]], [0], chi=True, uns=True, lxr=np.array([90.0], np.float32))
     assert n == 0 and best[0] == -1
+
+
+def test_loop_closing_search_semantics(oracle):
+    """match/projection.cc:317-413 (match_by_Sim3_transform) and :415-636 (match_keyframes_mutually), hand-built cases for the
+    port: keypoints are consumed in row order, HAMMING_DIST_THR_LOW vs _HIGH, the unsigned level comparison, the cross-check."""
+    from oracle import pyoracle
+    cam = pyoracle.make_camera(fx=500.0, fy=500.0, cx=320.0, cy=240.0, cols=640, rows=480)
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    kp = np.zeros(3, pyoracle.KP_DTYPE)
+    kp["x"], kp["y"], kp["octave"] = [100.0, 101.0, 300.0], [100.0, 100.0, 200.0], [1, 1, 0]
+    d = np.zeros((3, 32), np.uint8)
+    d[1, 0] = 0x01
+    free = np.zeros(3, np.uint8)
+    two = np.zeros((2, 32), np.uint8)
+    # both rows prefer keypoint 0; the second finds it matched and falls back to keypoint 1 (distance 1)
+    out, n = oracle.match_sim3(cam, 5.0, np.ones(2, np.uint8), [[100.0, 100.0], [100.0, 100.0]], [1, 1], two, kp, d, free, sf)
+    assert n == 2 and list(out) == [0, 1, -1]
+    # a keypoint that already holds a matched landmark is never a candidate
+    out, n = oracle.match_sim3(cam, 5.0, np.ones(1, np.uint8), [[100.0, 100.0]], [1], two[:1], kp, d, np.array([1, 0, 0], np.uint8), sf)
+    assert n == 1 and list(out) == [-1, 0, -1]
+    # threshold LOW = 50: 51 differing bits are rejected
+    far = np.zeros((1, 32), np.uint8)
+    far[0, :6] = 0xFF
+    far[0, 6] = 0x07
+    out, n = oracle.match_sim3(cam, 5.0, np.ones(1, np.uint8), [[100.0, 100.0]], [1], far, kp, d, np.array([0, 1, 0], np.uint8), sf)
+    assert n == 0
+    # predicted level 0: `scale_level < 0u - 1` holds for every keypoint, nothing matches (keypoint 2 has octave 0)
+    out, n = oracle.match_sim3(cam, 5.0, np.ones(1, np.uint8), [[300.0, 200.0]], [0], two[:1], kp, d, free, sf)
+    assert n == 0
+    out, n = oracle.match_sim3(cam, 5.0, np.ones(1, np.uint8), [[300.0, 200.0]], [1], two[:1], kp, d, free, sf)
+    assert n == 1 and out[2] == 0
+
+    # mutual: keyframe 1 has 2 keypoints, keyframe 2 has 2; 1/0 <-> 2/1 agree, 1/1 -> 2/1 is one-sided
+    kp1 = np.zeros(2, pyoracle.KP_DTYPE)
+    kp1["x"], kp1["y"], kp1["octave"] = [50.0, 400.0], [60.0, 300.0], [1, 1]
+    kp2 = np.zeros(2, pyoracle.KP_DTYPE)
+    kp2["x"], kp2["y"], kp2["octave"] = [500.0, 200.0], [100.0, 150.0], [1, 1]
+    d1 = np.zeros((2, 32), np.uint8)
+    d2 = np.zeros((2, 32), np.uint8)
+    side_1 = (np.ones(2, np.uint8), [[200.0, 150.0], [200.5, 150.0]], [1, 1], np.zeros((2, 32), np.uint8), kp1, d1, sf)
+    side_2 = (np.ones(2, np.uint8), [[0.0, 0.0], [50.0, 60.0]], [1, 1], np.zeros((2, 32), np.uint8), kp2, d2, sf)
+    out, n = oracle.match_mutual(cam, cam, 5.0, side_1, side_2)
+    assert n == 1 and list(out) == [1, -1]
+    # threshold HIGH = 100: a landmark descriptor 100 bits away still matches, 101 does not
+    lm = np.zeros((2, 32), np.uint8)
+    lm[0, :12] = 0xFF
+    lm[0, 12] = 0x0F
+    out, n = oracle.match_mutual(cam, cam, 5.0, (side_1[0], side_1[1], side_1[2], lm, kp1, d1, sf), side_2)
+    assert n == 1
+    lm[0, 12] = 0x1F
+    out, n = oracle.match_mutual(cam, cam, 5.0, (side_1[0], side_1[1], side_1[2], lm, kp1, d1, sf), side_2)
+    assert n == 0
+
+
+def test_triangulation_search_semantics(oracle):
+    """match/robust.cc:18-178 hand-built cases for the port: an equal distance replaces the best (:108), the 0.2 degree x scale
+    band of check_epipolar_constraint with its one-sided residual (:329-340), the epipole gate for mono pairs (:112-123)."""
+    from oracle import pyoracle
+    kp1 = np.zeros(1, pyoracle.KP_DTYPE)
+    kp2 = np.zeros(3, pyoracle.KP_DTYPE)
+    d1 = np.zeros((1, 32), np.uint8)
+    d2 = np.zeros((3, 32), np.uint8)
+    d2[0, 0] = 0x01
+    d2[1, 0] = 0x02
+    d2[2, 0] = 0x07
+    z = np.array([0.0, 0.0, 1.0])
+    E = np.array([[0.0, 0.0, 0.0], [0.0, 0.0, -1.0], [0.0, 1.0, 0.0]])  # [t]x with t = x, R = I
+    vec1 = (np.array([3], np.uint32), np.array([0, 1], np.uint32), np.array([0], np.uint32))
+    vec2 = (np.array([3], np.uint32), np.array([0, 3], np.uint32), np.arange(3, dtype=np.uint32))
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    mono1, mono2 = np.array([-1.0], np.float32), np.full(3, -1.0, np.float32)
+
+    def run(b1, b2, epi=(1.0, 0.0, 0.0), x1=mono1, x2=mono2, h2=np.zeros(3, np.uint8)):
+        return oracle.match_triangulation(vec1, vec2, (kp1, d1, np.asarray([b1], np.float64), x1, np.zeros(1, np.uint8), sf),
+                                          (kp2, d2, np.asarray(b2, np.float64), x2, h2), E, np.asarray(epi, np.float64), False)
+
+    out, n = run(z, [z, z, z])
+    assert n == 1 and out[0] == 1                      # distances 1, 1, 3: the later of the two equal ones
+    out, n = run(z, [z, z, z], h2=np.array([0, 1, 0], np.uint8))
+    assert out[0] == 0                                 # a keypoint with a landmark is not a candidate
+    # epipolar plane normal of bearing_2 = z is E z = (0, -1, 0); bearing_1 tilted towards +y by 0.3 degree: the residual
+    # pi/2 - acos(-sin) is negative and passes, tilted towards -y it is +0.3 degree > 0.2 degree and fails
+    a = np.deg2rad(0.3)
+    out, n = run([0.0, np.sin(a), np.cos(a)], [z, z, z])
+    assert n == 1
+    out, n = run([0.0, -np.sin(a), np.cos(a)], [z, z, z])
+    assert n == 0
+    a = np.deg2rad(0.15)
+    out, n = run([0.0, -np.sin(a), np.cos(a)], [z, z, z])
+    assert n == 1
+    # epipole along the candidates' bearing: mono-mono pairs within 3 degrees of it are refused, a stereo keypoint is not
+    out, n = run(z, [z, z, z], epi=(0.0, 0.0, 1.0))
+    assert n == 0
+    out, n = run(z, [z, z, z], epi=(0.0, 0.0, 1.0), x2=np.array([-1.0, -1.0, 5.0], np.float32))
+    assert n == 1 and out[0] == 2
