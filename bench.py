@@ -152,7 +152,7 @@ def gpu_arm(args):
         raise RuntimeError("bench.py needs a CUDA device: liblpslam_cuda has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"  # the version banner would otherwise land on stdout next to the JSON line
+        os.environ.setdefault("NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch  # stereo pairs per step and per GPU
     L = lib()
@@ -315,6 +315,19 @@ def gpu_arm(args):
         gbs = alg[k] * frames_img / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
         per_stage[k] = {"kernel": KERNEL_OF_STAGE[k], "ms": round(stage[k], 4), "alg_bytes": alg[k] * frames_img,
                         "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4), "traffic": traffic.get(KERNEL_OF_STAGE[k])}
+    # k_fast_cells is bound by instruction issue, not by HBM: its warp instructions per launch (ncu, profiles/warp_instr.json,
+    # a property of the workload) over the live stage time, against 4 issue slots per SM per clock at the maximum SM clock
+    try:
+        wi = json.load(open(os.path.join(ROOT, "profiles", "warp_instr.json")))
+        if stage["fast"] > 0 and frames_img == wi["frames"]:
+            sm_clock_ghz = torch.cuda.get_device_properties(local).clock_rate / 1e6  # kHz -> GHz
+            ginstr = wi["k_fast_cells"] / (stage["fast"] * 1e-3) / 1e9
+            peak_issue = torch.cuda.get_device_properties(local).multi_processor_count * 4 * sm_clock_ghz
+            per_stage["fast"]["issue"] = {"warp_instr_per_launch": wi["k_fast_cells"], "achieved": round(ginstr, 1),
+                                          "peak": round(peak_issue, 1), "unit": "1e9 warp instructions/s", "frac": round(ginstr / peak_issue, 4),
+                                          "peak_source": "SMs x 4 schedulers x max SM clock"}
+    except (OSError, KeyError, ValueError):
+        pass
     dom = max(stage, key=stage.get)
     rk = dom if dom in per_stage else "blur"
     roofline = {"bound": "hbm", "kernel": per_stage[rk]["kernel"], "achieved": per_stage[rk]["achieved_gbs"], "peak": peak,
@@ -399,7 +412,17 @@ def main():
         print(json.dumps(line), flush=True)
         return
 
-    out, rank = gpu_arm(args)
+    # stdout carries ONE line, the JSON: whatever libraries write to file descriptor 1 while the bench runs (NCCL prints its
+    # version banner there at NCCL_DEBUG=VERSION / WARN, its log at INFO) is sent to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        out, rank = gpu_arm(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if rank == 0:
         if args.gpus == 1 and not args.no_cpu_baseline:
             v, cores, ms, kind, took = cpu_reference_arm(2, 0)
