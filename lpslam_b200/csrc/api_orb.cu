@@ -64,12 +64,16 @@ int lpslam_orb_create(lpslam_orb_ctx** out, const lpslam_orb_params* p, int devi
     for (uint32_t i = 0; i < p->num_mask_rects; ++i)
         c->mask_rects.push_back({p->mask_rects[4 * i], p->mask_rects[4 * i + 1], p->mask_rects[4 * i + 2], p->mask_rects[4 * i + 3]});
     c->initialize_tables();
-    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking);
+    // greatest priority for everything but FAST (launch_fast lowers its own launch): see fast.cu
+    int prio_least = 0, prio_greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+    if (const char* env = getenv("LPSLAM_FAST_LOW_PRIORITY")) if (atoi(env) == 0) prio_greatest = prio_least;
+    cudaError_t e = cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_greatest);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_greatest);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
     for (int i = 0; i < 3 && e == cudaSuccess; ++i) {
-        e = cudaStreamCreateWithFlags(&c->chain[i], cudaStreamNonBlocking);
+        e = cudaStreamCreateWithPriority(&c->chain[i], cudaStreamNonBlocking, prio_greatest);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_join[i], cudaEventDisableTiming);
     }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_fork, cudaEventDisableTiming);

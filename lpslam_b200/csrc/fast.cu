@@ -10,6 +10,7 @@
 // a second time at the lower threshold if the first pass left the cell empty. Candidates leave in raster order into
 // the cell's slot block (<= 1024 entries: strict 8-neighbourhood maxima cannot be denser than one per 2x2).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace lps {
 
@@ -171,14 +172,19 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
         }
         __syncthreads();
         const int n = s_nlist;
-        // 2. exact best, two listed pixels per thread
-        for (int i = tid; 2 * i < n; i += 256) {
-            const int ida = s_list[2 * i], idb = (2 * i + 1 < n) ? s_list[2 * i + 1] : ida;
+        // 2. exact best, two listed pixels per thread. A warp takes 64 consecutive list entries per round and a lane the
+        //    entries (lane, lane + 32) of them: the 32 pixels one shared-memory byte load touches are then neighbours in
+        //    raster order (two or three window rows, few bank conflicts) instead of every other entry of a 64-entry run.
+        //    The arc network runs on the raw ring values; the centre is subtracted from its two results only.
+        for (int base = 64 * warp; base < n; base += 64 * 8) {
+            const int ia = min(base + lane, n - 1), ib = min(base + 32 + lane, n - 1);
+            const bool va = base + lane < n, vb = base + 32 + lane < n;
+            const int ida = s_list[ia], idb = s_list[ib];
             const uint8_t* pa = &s_win[(ida >> 6) + 3][(ida & 63) + 6];
             const uint8_t* pb = &s_win[(idb >> 6) + 3][(idb & 63) + 6];
-            const uint32_t C = ((uint32_t)pa[0] + 256u) | (((uint32_t)pb[0] + 256u) << 16);
+            const int ca = pa[0], cb = pb[0];
             uint32_t d[16];
-#define RING(k, off) d[k] = C - ((uint32_t)pa[off] | ((uint32_t)pb[off] << 16))
+#define RING(k, off) d[k] = (uint32_t)pa[off] | ((uint32_t)pb[off] << 16)
             RING(0, 3 * WP);      RING(1, 3 * WP + 1);   RING(2, 2 * WP + 2);   RING(3, WP + 3);
             RING(4, 3);           RING(5, -WP + 3);      RING(6, -2 * WP + 2);  RING(7, -3 * WP + 1);
             RING(8, -3 * WP);     RING(9, -3 * WP - 1);  RING(10, -2 * WP - 2); RING(11, -WP - 3);
@@ -205,15 +211,15 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
             }
             A = __vmaxu2(A, lo9[15]);
             Bm = __vminu2(Bm, hi9[15]);
-            // halves hold d + 256: best = max(A - 256, 256 - Bm)
-            const int ba = max((int)(A & 0xFFFFu) - 256, 256 - (int)(Bm & 0xFFFFu));
-            const int bb = max((int)(A >> 16) - 256, 256 - (int)(Bm >> 16));
+            // A = brightest "darkest pixel of an arc", Bm = darkest "brightest pixel of an arc": best = max(A - c, c - Bm)
+            const int ba = max((int)(A & 0xFFFFu) - ca, ca - (int)(Bm & 0xFFFFu));
+            const int bb = max((int)(A >> 16) - cb, cb - (int)(Bm >> 16));
             // strengths at or below the threshold are stored as 0: a corner beats such a neighbour anyway (its score is 0)
-            s_best[(ida >> 6) + 1][(ida & 63) + 1] = (uint8_t)(ba > thr ? ba : 0);
-            s_best[(idb >> 6) + 1][(idb & 63) + 1] = (uint8_t)(bb > thr ? bb : 0);
+            if (va) s_best[(ida >> 6) + 1][(ida & 63) + 1] = (uint8_t)(ba > thr ? ba : 0);
+            if (vb) s_best[(idb >> 6) + 1][(idb & 63) + 1] = (uint8_t)(bb > thr ? bb : 0);
             // corners go into a second list: only they are looked at by the suppression
-            if (ba > thr) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)ida;
-            if (bb > thr && 2 * i + 1 < n) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)idb;
+            if (va && ba > thr) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)ida;
+            if (vb && bb > thr) s_corner[atomicAdd(&s_ncorner, 1)] = (uint16_t)idb;
         }
         __syncthreads();
         // 3. suppression around the corners (every other pixel scores 0)
@@ -301,7 +307,25 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
 
 void launch_fast(const FastArgs& a, cudaStream_t st) {
     if (a.num_cells == 0) return;
-    k_fast_cells<<<dim3(a.num_cells, a.batch), 256, 0, st>>>(a);
+    // The context's streams are created at the device's greatest priority (api_orb.cu); FAST, the one issue-bound kernel of
+    // the step, is launched at the least: when several contexts run side by side, another context's latency-bound tail
+    // (quadtree, descriptors, stereo) gets the SM slots FAST blocks free before further FAST blocks do.
+    static const int low_prio = [] {
+        int least = 0, greatest = 0;
+        cudaDeviceGetStreamPriorityRange(&least, &greatest);
+        const char* env = getenv("LPSLAM_FAST_LOW_PRIORITY");
+        return (env && atoi(env) == 0) ? greatest : least;
+    }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(a.num_cells, a.batch);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributePriority;
+    at[0].val.priority = low_prio;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, k_fast_cells, a);
 }
 
 }  // namespace lps
