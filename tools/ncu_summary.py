@@ -16,6 +16,7 @@ KEYS = [("gpu__time_duration.sum", "us"), ("dram__bytes_read.sum", "dram rd MB")
         ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma %"),
         ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu %"),
         ("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "xu %"),
+        ("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "lsu data pipe %"),
         ("l1tex__t_sector_hit_rate.pct", "L1 hit %"), ("lts__t_sector_hit_rate.pct", "L2 hit %")]
 rows_out, traffic = [], {}
 for rep in reps:
