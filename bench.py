@@ -374,6 +374,9 @@ def gpu_arm(args):
                                   "resident batch); e2e: %d contexts per GPU" % (len(dev_ctx), len(halves))},
            "e2e": {"value": pairs_total / (e2e_ms * 1e-3), "unit": "stereo frames/s", "ms_per_step": e2e_ms / args.steps,
                    "h2d_bytes_per_step": 2 * B * W * H, "d2h_bytes_per_step": n_kp * (28 + 32 + 8) + 4 * (2 * B + 2),
+                   # the end-to-end leg is bound by the host link: pinned H2D alone runs at 48-54 GB/s on this box
+                   # (tools/pcie_rate.py), i.e. 1.1-1.2 ms for one step's 59 MB of images
+                   "h2d_gbs_achieved": 2 * B * W * H / (e2e_ms / args.steps * 1e-3) / 1e9,
                    "timing": "wall clock around the blocking host-buffer C-ABI calls: %d contexts per GPU, each replayed by its own host thread (its share of every step, back to back), max over ranks" % len(halves)},
            "gpu_launches": args.steps * LAUNCHES_PER_STEP, "clocks": clk, "roofline": roofline, "knn": knn_out}
     pool.shutdown()

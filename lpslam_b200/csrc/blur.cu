@@ -24,6 +24,9 @@ namespace {
 constexpr int SW = 8;           // strip width (pixels per thread-row)
 constexpr int MACRO_ROWS = 10;  // rows per macro iteration: 5 row pairs = one full rotation of the pair window
 constexpr int BLUR_THREADS = 128;
+#ifndef LPS_BLUR_MAX_MACROS
+#define LPS_BLUR_MAX_MACROS 2  // longest strip a thread walks, in macro iterations of 10 rows (measured on 64 frames of 1280x720: 1 -> 0.1126, 2 -> 0.1065, 3 -> 0.1085, 4 -> 0.1106, 6 -> 0.1126, 8 -> 0.1229, 12 -> 0.127 ms)
+#endif
 
 struct BlurTable {
     int num_levels;
@@ -229,7 +232,7 @@ void launch_blur(const LevelGeom* lv_dev, const LevelGeom* lv_host, int num_leve
     for (int l = 0; l < num_levels; ++l) px += (long)lv_host[l].w * lv_host[l].h;
     const long threads_at_10 = px * batch / (SW * MACRO_ROWS);  // threads if every thread took one macro
     int macros = (int)(threads_at_10 / (148L * 1024));
-    macros = macros < 1 ? 1 : (macros > 4 ? 4 : macros);
+    macros = macros < 1 ? 1 : (macros > LPS_BLUR_MAX_MACROS ? LPS_BLUR_MAX_MACROS : macros);
     tab.rows_per_thread = macros * MACRO_ROWS;
     int total = 0;
     for (int l = 0; l < num_levels; ++l) {
