@@ -101,9 +101,7 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
     for (int attempt = 0; attempt < 2; ++attempt) {
         {   // 1a. pre-test -> s_pass
             const int w = tid & 15, lx = 4 * w;
-            const uint32_t kC = 0x01000100u;
-            const uint32_t kHi = (uint32_t)(0x7FFF - 256 - thr) * 0x00010001u;   // bit15 set iff half >= 257 + thr
-            const uint32_t kLo = (uint32_t)(0x8000 + 255 - thr) * 0x00010001u;   // bit15 set iff half <= 255 - thr
+            const uint32_t kT = (uint32_t)(0x8000 - 1 - thr) * 0x00010001u;  // bit15 of (x + kT) set iff half x >= thr + 1
             const int nv = vw - lx;
             const uint32_t vmask = nv >= 4 ? 0xFu : (nv <= 0 ? 0u : ((1u << nv) - 1u));
 #pragma unroll
@@ -122,12 +120,14 @@ __global__ void __launch_bounds__(256, LPS_FAST_MINBLOCKS) k_fast_cells(FastArgs
 #pragma unroll
                     for (int hf = 0; hf < 2; ++hf) {
                         const uint32_t sel = hf ? 0x4342u : 0x4140u;
-                        const uint32_t c16 = __byte_perm(C, 0, sel) + kC;
-                        const uint32_t d0 = c16 - __byte_perm(N, 0, sel), d4 = c16 - __byte_perm(E, 0, sel);
-                        const uint32_t d8 = c16 - __byte_perm(S, 0, sel), d12 = c16 - __byte_perm(Wt, 0, sel);
-                        const uint32_t mm = __vmaxu2(__vmaxu2(__vminu2(d0, d4), __vminu2(d4, d8)), __vmaxu2(__vminu2(d8, d12), __vminu2(d12, d0)));
-                        const uint32_t nm = __vminu2(__vminu2(__vmaxu2(d0, d4), __vmaxu2(d4, d8)), __vminu2(__vmaxu2(d8, d12), __vmaxu2(d12, d0)));
-                        f[hf] = ((mm + kHi) | (kLo - nm)) & 0x80008000u;
+                        // raw 16-bit lanes: M = brightest "darker one of two adjacent compass pixels", X = darkest
+                        // "brighter one"; bright arc possible iff M - c > thr, dark arc iff c - X > thr
+                        const uint32_t c16 = __byte_perm(C, 0, sel);
+                        const uint32_t pn = __byte_perm(N, 0, sel), pe = __byte_perm(E, 0, sel);
+                        const uint32_t ps = __byte_perm(S, 0, sel), pw = __byte_perm(Wt, 0, sel);
+                        const uint32_t M = __vmaxu2(__vimax3_u16x2(__vminu2(pn, pe), __vminu2(pe, ps), __vminu2(ps, pw)), __vminu2(pw, pn));
+                        const uint32_t X = __vminu2(__vimin3_u16x2(__vmaxu2(pn, pe), __vmaxu2(pe, ps), __vmaxu2(ps, pw)), __vmaxu2(pw, pn));
+                        f[hf] = ((M + kT - c16) | (c16 + kT - X)) & 0x80008000u;
                     }
                     nib = ((f[0] >> 15) & 1u) | ((f[0] >> 30) & 2u) | ((f[1] >> 13) & 4u) | ((f[1] >> 28) & 8u);
                     nib &= vmask;
