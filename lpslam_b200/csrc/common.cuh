@@ -127,6 +127,11 @@ void launch_pad_borders(const LevelGeom* lv_dev_table, const LevelGeom* lv_host,
                         cudaStream_t st);
 bool resize_writes_apron(const LevelGeom& src, const LevelGeom& dst);
 void launch_blur(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
+// TMA-staged blur (blur_tma.cu): tensor maps over the level images of one arena, unit tables per batch size
+struct BlurPlan;
+BlurPlan* blur_plan_create(const LevelGeom* lv_host, int num_levels, int max_batch);
+void blur_plan_destroy(BlurPlan* p);
+int launch_blur_tma(BlurPlan* p, const LevelGeom* lv_dev_table, int batch, cudaStream_t st);
 
 struct FastArgs {
     const LevelGeom* lv;      // device table

@@ -98,6 +98,8 @@ void lpslam_orb_ctx::initialize_tables() {
 }
 
 void lpslam_orb_ctx::release_geometry() {
+    lps::blur_plan_destroy(blur_plan);
+    blur_plan = nullptr;
     if (arena) cudaFree(arena);
     arena = nullptr;
     arena_bytes = 0;
@@ -440,6 +442,13 @@ int lpslam_orb_ctx::configure(int width, int height) {
     stereo.row_start = (uint32_t*)(arena + off_srows);
     stereo.rows0 = height;
     LPS_CUDA(cudaStreamSynchronize(stream));  // the host-side tables go out of scope
+    {
+        static const bool blur_v1 = getenv("LPS_BLUR_V1") != nullptr;  // A/B switch: the ld.global version of blur.cu
+        if (!blur_v1) {
+            blur_plan = blur_plan_create(lv, L, (int)max_batch);
+            if (!blur_plan) return LPSLAM_ERR_CUDA;
+        }
+    }
     w = width;
     h = height;
     return LPSLAM_OK;
@@ -483,7 +492,10 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
         LPS_CUDA(cudaEventRecord(ev_fork, stream));
         LPS_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
         launch_pad_borders(lv_dev, lv, L, pad_mask, B, side);
-        launch_blur(lv_dev, lv, L, B, side);
+        if (blur_plan) {
+            if (int r = launch_blur_tma(blur_plan, lv_dev, B, side)) return r;
+        }
+        else launch_blur(lv_dev, lv, L, B, side);
         LPS_CUDA(cudaEventRecord(ev_join, side));
     }
     else {
@@ -533,6 +545,9 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     mark();  // 3
     if (fork)
         LPS_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+    else if (blur_plan) {
+        if (int r = launch_blur_tma(blur_plan, lv_dev, B, stream)) return r;
+    }
     else
         launch_blur(lv_dev, lv, L, B, stream);
     mark();  // 4
