@@ -127,6 +127,15 @@ void launch_pad_borders(const LevelGeom* lv_dev_table, const LevelGeom* lv_host,
                         cudaStream_t st);
 bool resize_writes_apron(const LevelGeom& src, const LevelGeom& dst);
 void launch_blur(const LevelGeom* lv_dev_table, const LevelGeom* lv_host, int num_levels, int batch, cudaStream_t st);
+// OpenCV's INTER_LINEAR 8-bit coefficient tables of one axis (ctx.cu): source offset and (c0, c1) per destination index
+void make_axis_tab(int sn, int dn, bool clamp_reset, std::vector<int>& ofs, std::vector<short2>& coef);
+// TMA-staged pyramid (pyramid_tma.cu): levels 1 .. L-1 of a batch in ONE launch, level l+1 of a frame starts when level l of
+// that frame is complete (device counters). nullptr when the geometry is outside what the kernel covers (the per-level
+// k_resize_walk chain stays the general path).
+struct PyramidPlan;
+PyramidPlan* pyramid_plan_create(const LevelGeom* lv_host, int num_levels, int max_batch);
+void pyramid_plan_destroy(PyramidPlan* p);
+int launch_pyramid_tma(PyramidPlan* p, const LevelGeom* lv_dev_table, int batch, cudaStream_t st);
 // TMA-staged blur (blur_tma.cu): tensor maps over the level images of one arena, unit tables per batch size
 struct BlurPlan;
 BlurPlan* blur_plan_create(const LevelGeom* lv_host, int num_levels, int max_batch);

@@ -29,6 +29,17 @@ int floor_int(double v) {
     return i - (v < i);
 }
 
+struct ArenaPlan {
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        const size_t o = off;
+        off = align_up(off + bytes, 256);
+        return o;
+    }
+};
+
+}  // namespace
+
 // OpenCV resizeGeneric_ coefficient tables for INTER_LINEAR, 8-bit. `clamp_reset` is the
 // horizontal-axis behaviour (offset clamped AND coefficient reset at both ends); rows are only clamped when read.
 void make_axis_tab(int sn, int dn, bool clamp_reset, std::vector<int>& ofs, std::vector<short2>& coef) {
@@ -57,16 +68,6 @@ void make_axis_tab(int sn, int dn, bool clamp_reset, std::vector<int>& ofs, std:
     }
 }
 
-struct ArenaPlan {
-    size_t off = 0;
-    size_t take(size_t bytes) {
-        const size_t o = off;
-        off = align_up(off + bytes, 256);
-        return o;
-    }
-};
-
-}  // namespace
 }  // namespace lps
 
 using namespace lps;
@@ -100,6 +101,8 @@ void lpslam_orb_ctx::initialize_tables() {
 void lpslam_orb_ctx::release_geometry() {
     lps::blur_plan_destroy(blur_plan);
     blur_plan = nullptr;
+    lps::pyramid_plan_destroy(pyr_plan);
+    pyr_plan = nullptr;
     if (arena) cudaFree(arena);
     arena = nullptr;
     arena_bytes = 0;
@@ -448,6 +451,7 @@ int lpslam_orb_ctx::configure(int width, int height) {
             blur_plan = blur_plan_create(lv, L, (int)max_batch);
             if (!blur_plan) return LPSLAM_ERR_CUDA;
         }
+        pyr_plan = pyramid_plan_create(lv, L, (int)max_batch);  // nullptr = geometry outside the kernel's range
     }
     w = width;
     h = height;
@@ -463,9 +467,12 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     };
     mark();  // 0: start of pyramid
     uint32_t pad_mask = 1u;  // level 0 arrives without its apron; so do levels made by the exact-half / copy / wide-ratio paths
-    for (int l = 1; l < L; ++l)
+    for (int l = 1; l < L && !pyr_plan; ++l)
         if (!resize_writes_apron(lv[l - 1], lv[l])) pad_mask |= 1u << l;
-    {
+    if (pyr_plan) {
+        if (int r = launch_pyramid_tma(pyr_plan, lv_dev, B, stream)) return r;
+    }
+    else {
         const int chains = std::min(pyr_chains, B);
         auto run_chain = [&](int f0, int f1, cudaStream_t st) {
             for (int l = 1; l < L; ++l) {

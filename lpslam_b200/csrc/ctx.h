@@ -31,6 +31,7 @@ struct lpslam_orb_ctx {
     int w = 0, h = 0;
     lps::LevelGeom lv[lps::kMaxLevels];
     lps::LevelGeom* lv_dev = nullptr;
+    lps::PyramidPlan* pyr_plan = nullptr;  // single-launch TMA pyramid of this geometry (nullptr: per-level k_resize_walk chain)
     lps::BlurPlan* blur_plan = nullptr;  // TMA-staged blur of this geometry (nullptr: LPS_BLUR_V1 forces the ld.global version)
     std::vector<lps::CellDesc> cells;
     lps::CellDesc* cells_dev = nullptr;

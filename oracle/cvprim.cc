@@ -3,6 +3,8 @@
 // (the reference builds with BUILD_WITH_MARCH_NATIVE OFF, /root/reference/CMakeLists.txt:155).
 #include "cvprim.h"
 
+#include <limits>
+
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -228,6 +230,50 @@ void fill_rect_zero(uint8_t* img, int w, int h, size_t pitch, int x0, int y0, in
     y1 = std::min(y1, h - 1);
     for (int y = y0; y <= y1; ++y)
         for (int x = x0; x <= x1; ++x) img[static_cast<size_t>(y) * pitch + x] = 0;
+}
+
+// cv::undistortPoints (calib3d, cvUndistortPointsInternal) for one point of a 5-coefficient Brown-Conrady model; the
+// rational and thin-prism terms of the general model are zero and are kept as literal zeros so that the floating-point
+// expression trees stay those of OpenCV. Pinned bit-for-bit against cv2 4.13 in tests/test_oracle_vs_cv2.py.
+void undistort_point(const double K[4], const double dist[5], const double P[4], int max_count, double eps, float uf, float vf,
+                     float* out_x, float* out_y) {
+    const double fx = K[0], fy = K[1], cx = K[2], cy = K[3];
+    const double k0 = dist[0], k1 = dist[1], p1 = dist[2], p2 = dist[3], k4 = dist[4];
+    const double ifx = 1.0 / fx, ify = 1.0 / fy;
+    const double u = uf, v = vf;
+    double x = (u - cx) * ifx, y = (v - cy) * ify;
+    const double x0 = x, y0 = y;
+    double error = std::numeric_limits<double>::max();
+    for (int j = 0;; ++j) {
+        if (j >= max_count) break;
+        if (error < eps) break;
+        double r2 = x * x + y * y;
+        const double icdist = (1 + ((0.0 * r2 + 0.0) * r2 + 0.0) * r2) / (1 + ((k4 * r2 + k1) * r2 + k0) * r2);
+        if (icdist < 0) {
+            x = (u - cx) * ifx;
+            y = (v - cy) * ify;
+            break;
+        }
+        const double deltaX = 2 * p1 * x * y + p2 * (r2 + 2 * x * x) + 0.0 * r2 + 0.0 * r2 * r2;
+        const double deltaY = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y + 0.0 * r2 + 0.0 * r2 * r2;
+        x = (x0 - deltaX) * icdist;
+        y = (y0 - deltaY) * icdist;
+        {
+            r2 = x * x + y * y;
+            const double r4 = r2 * r2, r6 = r4 * r2;
+            const double a1 = 2 * x * y, a2 = r2 + 2 * x * x, a3 = r2 + 2 * y * y;
+            const double cdist = 1 + k0 * r2 + k1 * r4 + k4 * r6;
+            const double icdist2 = 1. / (1 + 0.0 * r2 + 0.0 * r4 + 0.0 * r6);
+            const double xd0 = x * cdist * icdist2 + p1 * a1 + p2 * a2 + 0.0 * r2 + 0.0 * r4;
+            const double yd0 = y * cdist * icdist2 + p1 * a3 + p2 * a1 + 0.0 * r2 + 0.0 * r4;
+            const double x_proj = xd0 * fx + cx, y_proj = yd0 * fy + cy;
+            error = std::sqrt((x_proj - u) * (x_proj - u) + (y_proj - v) * (y_proj - v));
+        }
+    }
+    // new camera matrix P, R = identity: RR = P * I
+    const double xx = P[0] * x + 0.0 * y + P[2], yy = 0.0 * x + P[1] * y + P[3], ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+    *out_x = static_cast<float>(xx * ww);
+    *out_y = static_cast<float>(yy * ww);
 }
 
 } // namespace cvprim

@@ -52,6 +52,11 @@ float fast_atan2(float y, float x);
 // rectangle the anti-aliased fill degenerates to an exact inclusive fill (checked against cv2 in the tests).
 void fill_rect_zero(uint8_t* img, int w, int h, size_t pitch, int x0, int y0, int x1, int y1);
 
+// cv::undistortPoints for one point: K = (fx, fy, cx, cy), dist = (k1, k2, p1, p2, k3), new camera matrix P = (fx', fy', cx', cy'),
+// R = identity, termination after max_count iterations or a reprojection error below eps (calib3d cvUndistortPointsInternal).
+void undistort_point(const double K[4], const double dist[5], const double P[4], int max_count, double eps, float u, float v,
+                     float* out_x, float* out_y);
+
 } // namespace cvprim
 
 #endif

@@ -19,47 +19,10 @@ extern "C" {
 // cv::KeyPoint defaults (0, -1).
 void orc_undistort_keypoints(double fx, double fy, double cx, double cy, const double* dist5, uint32_t n, const orc_keypoint* in,
                              orc_keypoint* out) {
-    const double k0 = dist5[0], k1 = dist5[1], p1 = dist5[2], p2 = dist5[3], k4 = dist5[4];
-    const double ifx = 1.0 / fx, ify = 1.0 / fy;
-    const int max_count = 20;
-    const double eps = 1e-6;
+    const double K[4] = {fx, fy, cx, cy};
     for (uint32_t i = 0; i < n; ++i) {
-        const double u = in[i].x, v = in[i].y;
-        double x = (u - cx) * ifx, y = (v - cy) * ify;
-        const double x0 = x, y0 = y;
-        double error = std::numeric_limits<double>::max();
-        for (int j = 0;; ++j) {
-            if (j >= max_count) break;
-            if (error < eps) break;
-            double r2 = x * x + y * y;
-            // rational terms k[5..7] are zero for a 5-coefficient model
-            const double icdist = (1 + ((0.0 * r2 + 0.0) * r2 + 0.0) * r2) / (1 + ((k4 * r2 + k1) * r2 + k0) * r2);
-            if (icdist < 0) {
-                x = (u - cx) * ifx;
-                y = (v - cy) * ify;
-                break;
-            }
-            const double deltaX = 2 * p1 * x * y + p2 * (r2 + 2 * x * x) + 0.0 * r2 + 0.0 * r2 * r2;
-            const double deltaY = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y + 0.0 * r2 + 0.0 * r2 * r2;
-            x = (x0 - deltaX) * icdist;
-            y = (y0 - deltaY) * icdist;
-            {
-                r2 = x * x + y * y;
-                const double r4 = r2 * r2, r6 = r4 * r2;
-                const double a1 = 2 * x * y, a2 = r2 + 2 * x * x, a3 = r2 + 2 * y * y;
-                const double cdist = 1 + k0 * r2 + k1 * r4 + k4 * r6;
-                const double icdist2 = 1. / (1 + 0.0 * r2 + 0.0 * r4 + 0.0 * r6);
-                const double xd0 = x * cdist * icdist2 + p1 * a1 + p2 * a2 + 0.0 * r2 + 0.0 * r4;
-                const double yd0 = y * cdist * icdist2 + p1 * a3 + p2 * a1 + 0.0 * r2 + 0.0 * r4;
-                const double x_proj = xd0 * fx + cx, y_proj = yd0 * fy + cy;
-                error = std::sqrt((x_proj - u) * (x_proj - u) + (y_proj - v) * (y_proj - v));
-            }
-        }
-        // new camera matrix P = K, R = identity: RR = P * I
-        const double xx = fx * x + 0.0 * y + cx, yy = 0.0 * x + fy * y + cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
         out[i] = in[i];
-        out[i].x = static_cast<float>(xx * ww);
-        out[i].y = static_cast<float>(yy * ww);
+        cvprim::undistort_point(K, dist5, K, 20, 1e-6, in[i].x, in[i].y, &out[i].x, &out[i].y);
         out[i].response = 0.0f;
         out[i].class_id = -1;
     }

@@ -6,6 +6,7 @@
 #pragma once
 
 #include <algorithm>
+#include <array>
 #include <cassert>
 #include <climits>
 #include <cmath>
@@ -24,6 +25,7 @@ typedef unsigned char uchar;
 #define CV_8UC1 CV_8U
 #define CV_32FC1 CV_32F
 #define CV_SSE3 0
+#define CV_MAJOR_VERSION 4
 
 inline int cvRound(double v) { return cvprim::round_half_even(v); }
 inline int cvRound(float v) { return cvprim::round_half_even(v); }
@@ -112,6 +114,15 @@ public:
         data = owner_.get();
     }
     void release() { *this = Mat(); }
+    // reshape(cn): same rows, the row's elements regrouped into cn channels (camera/perspective.h:36-43 turns an N x 2 float
+    // matrix into N two-channel points and back)
+    Mat reshape(int cn) const {
+        Mat m(*this);
+        m.cols = cols * channels_ / cn;
+        m.channels_ = cn;
+        return m;
+    }
+    int channels() const { return channels_; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     int type() const { return type_; }
     size_t elem() const { return type_ == CV_32F ? 4 : 1; }
@@ -187,7 +198,45 @@ private:
             }
     }
     int type_ = CV_8U;
+    int channels_ = 1;
     std::shared_ptr<uchar> owner_;
+};
+
+// cv::Mat_<float>(r, c) << a, b, ... (camera/perspective.cc:21-22): values are converted to float one by one
+template<typename T>
+class Mat_ : public Mat {
+public:
+    Mat_(int r, int c) : Mat(r, c, CV_32F) {}
+};
+template<typename T>
+class MatCommaInit_ {
+public:
+    MatCommaInit_(Mat_<T>& m, T first) : m_(m), n_(0) { put(first); }
+    template<typename U>
+    MatCommaInit_& operator,(U v) {
+        put(static_cast<T>(v));
+        return *this;
+    }
+    operator Mat() const { return m_; }
+
+private:
+    void put(T v) {
+        m_.template at<T>(n_ / m_.cols, n_ % m_.cols) = v;
+        ++n_;
+    }
+    Mat_<T> m_;
+    int n_;
+};
+template<typename T, typename U>
+MatCommaInit_<T> operator<<(Mat_<T> m, U first) {
+    return MatCommaInit_<T>(m, static_cast<T>(first));
+}
+
+struct TermCriteria {
+    enum { COUNT = 1, MAX_ITER = COUNT, EPS = 2 };
+    int type, maxCount;
+    double epsilon;
+    TermCriteria(int t, int c, double e) : type(t), maxCount(c), epsilon(e) {}
 };
 
 inline Mat operator*(float s, const Mat& m) {

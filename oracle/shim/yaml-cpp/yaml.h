@@ -1,5 +1,6 @@
-// TEST INFRASTRUCTURE - stub of yaml-cpp for compiling the reference's feature/orb_params.{h,cc} unmodified.
-// The oracle never builds parameters from YAML; a Node therefore always yields the caller's default.
+// TEST INFRASTRUCTURE - stub of yaml-cpp for compiling the reference's feature/orb_params.{h,cc}, camera/base.{h,cc} and
+// camera/perspective.{h,cc} unmodified. The oracle never builds parameters from YAML: a Node is always undefined, yields
+// the caller's default (or a value-initialised T) and converts to false.
 #pragma once
 #include <string>
 #include <vector>
@@ -10,5 +11,9 @@ public:
     Node operator[](const char*) const { return Node(); }
     template<typename T>
     T as(const T& fallback) const { return fallback; }
+    template<typename T>
+    T as() const { return T(); }
+    explicit operator bool() const { return false; }
+    bool operator!() const { return true; }
 };
 }  // namespace YAML
