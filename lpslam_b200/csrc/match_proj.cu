@@ -547,15 +547,18 @@ __device__ __forceinline__ double dm(double a, double b) { return __dmul_rn(a, b
 __device__ __forceinline__ double da(double a, double b) { return __dadd_rn(a, b); }
 __device__ __forceinline__ double ds(double a, double b) { return __dsub_rn(a, b); }
 
-__global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lpslam_keypoint* __restrict__ in,
+// `mu` = the model as cv::undistortPoints sees it: camera/perspective.cc:21-22 stores the camera matrix and the distortion
+// vector as cv::Mat_<float>, so every intrinsic goes through float before the double arithmetic; `m` = the double members the
+// bearing conversion (:132-141) uses.
+__global__ void k_undistort_bearings(lpslam_perspective mu, lpslam_perspective m, uint32_t n, const lpslam_keypoint* __restrict__ in,
                                      lpslam_keypoint* __restrict__ out, double* __restrict__ bearings) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     lpslam_keypoint k = in[i];
-    const double k0 = m.dist[0], k1 = m.dist[1], p1 = m.dist[2], p2 = m.dist[3], k4 = m.dist[4];
-    const double ifx = __ddiv_rn(1.0, m.fx), ify = __ddiv_rn(1.0, m.fy);
+    const double k0 = mu.dist[0], k1 = mu.dist[1], p1 = mu.dist[2], p2 = mu.dist[3], k4 = mu.dist[4];
+    const double ifx = __ddiv_rn(1.0, mu.fx), ify = __ddiv_rn(1.0, mu.fy);
     const double u = (double)k.x, v = (double)k.y;
-    double x = dm(ds(u, m.cx), ifx), y = dm(ds(v, m.cy), ify);
+    double x = dm(ds(u, mu.cx), ifx), y = dm(ds(v, mu.cy), ify);
     const double x0 = x, y0 = y;
     double error = 1.7976931348623157e308;
     for (int j = 0; j < 20; ++j) {
@@ -563,8 +566,8 @@ __global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lps
         double r2 = da(dm(x, x), dm(y, y));
         const double icdist = __ddiv_rn(1.0, da(1.0, dm(da(dm(da(dm(k4, r2), k1), r2), k0), r2)));
         if (icdist < 0) {  // calib3d regression 14583: fall back to the un-iterated point
-            x = dm(ds(u, m.cx), ifx);
-            y = dm(ds(v, m.cy), ify);
+            x = dm(ds(u, mu.cx), ifx);
+            y = dm(ds(v, mu.cy), ify);
             break;
         }
         const double dX = da(dm(dm(dm(2.0, p1), x), y), dm(p2, da(r2, dm(dm(2.0, x), x))));
@@ -577,11 +580,11 @@ __global__ void k_undistort_bearings(lpslam_perspective m, uint32_t n, const lps
         const double cdist = da(da(da(1.0, dm(k0, r2)), dm(k1, r4)), dm(k4, r6));
         const double xd0 = da(da(dm(dm(x, cdist), 1.0), dm(p1, a1)), dm(p2, a2));
         const double yd0 = da(da(dm(dm(y, cdist), 1.0), dm(p1, a3)), dm(p2, a1));
-        const double ex = ds(da(dm(xd0, m.fx), m.cx), u), ey = ds(da(dm(yd0, m.fy), m.cy), v);
+        const double ex = ds(da(dm(xd0, mu.fx), mu.cx), u), ey = ds(da(dm(yd0, mu.fy), mu.cy), v);
         error = __dsqrt_rn(da(dm(ex, ex), dm(ey, ey)));
     }
-    k.x = (float)da(dm(m.fx, x), m.cx);
-    k.y = (float)da(dm(m.fy, y), m.cy);
+    k.x = (float)da(dm(mu.fx, x), mu.cx);
+    k.y = (float)da(dm(mu.fy, y), mu.cy);
     k.response = 0.f;   // cv::KeyPoint defaults: undistort_keypoints copies pt, angle, size, octave only
     k.class_id = -1;
     out[i] = k;
@@ -984,7 +987,10 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
     do {
         if ((e = cudaMemcpy(dev + o_in, keypts, sizeof(lpslam_keypoint) * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
         if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
-        k_undistort_bearings<<<(n + 127) / 128, 128>>>(*model, n, (const lpslam_keypoint*)(dev + o_in), (lpslam_keypoint*)(dev + o_out),
+        lpslam_perspective mu = *model;  // camera/perspective.cc:21-22: the OpenCV copies of the intrinsics are float matrices
+        mu.fx = (double)(float)mu.fx, mu.fy = (double)(float)mu.fy, mu.cx = (double)(float)mu.cx, mu.cy = (double)(float)mu.cy;
+        for (int i = 0; i < 5; ++i) mu.dist[i] = (double)(float)mu.dist[i];
+        k_undistort_bearings<<<(n + 127) / 128, 128>>>(mu, *model, n, (const lpslam_keypoint*)(dev + o_in), (lpslam_keypoint*)(dev + o_out),
                                                       (double*)(dev + o_b));
         ProjArgs a = {};
         a.cam = *cam;

@@ -547,8 +547,8 @@ def make_camera(fx, fy, cx, cy, cols, rows, focal_x_baseline=0.0, true_baseline=
     cam.focal_x_baseline, cam.true_baseline = focal_x_baseline, true_baseline
     cam.min_x, cam.max_x, cam.min_y, cam.max_y = 0.0, float(cols), 0.0, float(rows)
     cam.grid_cols, cam.grid_rows = grid_cols, grid_rows
-    cam.inv_cell_width = float(grid_cols) / (np.float32(cols) - np.float32(0))
-    cam.inv_cell_height = float(grid_rows) / (np.float32(rows) - np.float32(0))
+    cam.inv_cell_width = float(grid_cols) / float(np.float32(cols) - np.float32(0))  # double division of a float difference (perspective.cc:29-30)
+    cam.inv_cell_height = float(grid_rows) / float(np.float32(rows) - np.float32(0))
     cam.is_monocular = int(is_monocular)
     cam.num_scale_levels = num_levels
     return cam

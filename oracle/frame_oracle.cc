@@ -19,10 +19,14 @@ extern "C" {
 // cv::KeyPoint defaults (0, -1).
 void orc_undistort_keypoints(double fx, double fy, double cx, double cy, const double* dist5, uint32_t n, const orc_keypoint* in,
                              orc_keypoint* out) {
-    const double K[4] = {fx, fy, cx, cy};
+    // camera/perspective.cc:21-22: cv_cam_matrix_ and cv_dist_params_ are cv::Mat_<float>, so the intrinsics reach
+    // cv::undistortPoints rounded to float (pinned by the reference build, tests/test_match_ref.py)
+    const double K[4] = {(double)(float)fx, (double)(float)fy, (double)(float)cx, (double)(float)cy};
+    double D[5];
+    for (int i = 0; i < 5; ++i) D[i] = (double)(float)dist5[i];
     for (uint32_t i = 0; i < n; ++i) {
         out[i] = in[i];
-        cvprim::undistort_point(K, dist5, K, 20, 1e-6, in[i].x, in[i].y, &out[i].x, &out[i].y);
+        cvprim::undistort_point(K, D, K, 20, 1e-6, in[i].x, in[i].y, &out[i].x, &out[i].y);
         out[i].response = 0.0f;
         out[i].class_id = -1;
     }

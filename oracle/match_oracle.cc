@@ -52,7 +52,7 @@ unsigned hamming_64(const uint8_t* a, const uint8_t* b) {
 // match/angle_checker.h:60-134, histogram_length = 30, num_bins_thr = 3
 struct AngleHistogram {
     static constexpr unsigned kLen = 30;
-    static constexpr unsigned kTop = 3;
+    unsigned kTop = 3;
     std::vector<std::vector<int>> bins = std::vector<std::vector<int>>(kLen);
     const float inv_len = 1.0f / kLen;
 
@@ -87,6 +87,16 @@ uint32_t orc_hamming_64(const uint8_t* a, const uint8_t* b) { return hamming_64(
 
 int orc_angle_invalid(const float* delta_angles, const int32_t* ids, int n, int32_t* invalid_out) {
     AngleHistogram h;
+    for (int i = 0; i < n; ++i) h.append(delta_angles[i], ids[i]);
+    const auto inv = h.invalid();
+    std::copy(inv.begin(), inv.end(), invalid_out);
+    return static_cast<int>(inv.size());
+}
+
+// angle_checker<int>(30, num_bins_thr): valid and invalid ids (test/openvslam/match/angle_checker.cc runs thresholds 1, 2, 3, 30)
+int orc_angle_check(const float* delta_angles, const int32_t* ids, int n, unsigned num_bins_thr, int32_t* invalid_out) {
+    AngleHistogram h;
+    h.kTop = num_bins_thr;
     for (int i = 0; i < n; ++i) h.append(delta_angles[i], ids[i]);
     const auto inv = h.invalid();
     std::copy(inv.begin(), inv.end(), invalid_out);

@@ -55,6 +55,7 @@ uint32_t orc_hamming_64(const uint8_t* a, const uint8_t* b); /* match/base.h:43-
 
 /* match/angle_checker.h: ids whose bin is not among the num_bins_thr fullest; returns count, writes ids in bin order */
 int orc_angle_invalid(const float* delta_angles, const int32_t* ids, int n, int32_t* invalid_out);
+int orc_angle_check(const float* delta_angles, const int32_t* ids, int n, unsigned num_bins_thr, int32_t* invalid_out);
 
 /* match/robust.cc:215-321 over flat arrays. Rows of desc_2 with valid_2[i]==0 are skipped (no live landmark).
  * match_2_in_1[nq] receives the keyframe index matched to each frame keypoint or -1. Returns the number of matches. */

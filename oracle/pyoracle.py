@@ -26,7 +26,7 @@ def build(force=False):
     """Compile the port (always) and the reference build (when /root/reference is present)."""
     if force or not os.path.exists(PORT_SO):
         subprocess.check_call(["make", "-s", "-f", os.path.join(HERE, "Makefile"), PORT_SO])
-    if os.path.isdir("/root/reference/external/openvslam/src/openvslam/feature") and os.path.exists(os.path.join(HERE, "ref_glue.cc")):
+    if os.path.isdir("/root/reference/external/openvslam/src/openvslam/feature") and os.path.exists(os.path.join(HERE, "ref_glue.cc")):  # liborb_ref.so + libmatch_ref.so
         subprocess.check_call(["make", "-s", "-f", os.path.join(HERE, "Makefile"), "ref"])
 
 
@@ -51,8 +51,8 @@ def make_camera(fx, fy, cx, cy, cols, rows, focal_x_baseline=0.0, true_baseline=
     cam.focal_x_baseline, cam.true_baseline = focal_x_baseline, true_baseline
     cam.min_x, cam.max_x, cam.min_y, cam.max_y = 0.0, float(cols), 0.0, float(rows)
     cam.grid_cols, cam.grid_rows = grid_cols, grid_rows
-    cam.inv_cell_width = float(grid_cols) / (np.float32(cols) - np.float32(0))
-    cam.inv_cell_height = float(grid_rows) / (np.float32(rows) - np.float32(0))
+    cam.inv_cell_width = float(grid_cols) / float(np.float32(cols) - np.float32(0))  # double division of a float difference (perspective.cc:29-30)
+    cam.inv_cell_height = float(grid_rows) / float(np.float32(rows) - np.float32(0))
     cam.is_monocular = int(is_monocular)
     cam.num_scale_levels = num_levels
     return cam
@@ -170,6 +170,14 @@ class Oracle:
         ids = np.ascontiguousarray(ids, np.int32)
         out = np.empty(len(ids), np.int32)
         n = self.lib.orc_angle_invalid(_ptr(deltas, f32p), _ptr(ids, i32p), len(ids), _ptr(out, i32p))
+        return out[:n].copy()
+
+    def angle_check(self, deltas, ids, num_bins_thr):
+        deltas = np.ascontiguousarray(deltas, np.float32)
+        ids = np.ascontiguousarray(ids, np.int32)
+        out = np.empty(max(len(ids), 1), np.int32)
+        self.lib.orc_angle_check.argtypes = [f32p, i32p, C.c_int, C.c_uint, i32p]
+        n = self.lib.orc_angle_check(_ptr(deltas, f32p), _ptr(ids, i32p), len(ids), num_bins_thr, _ptr(out, i32p))
         return out[:n].copy()
 
     def match_bruteforce(self, desc_1, desc_2, valid_2=None, angle_1=None, angle_2=None, lowe_ratio=0.8,

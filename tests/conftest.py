@@ -12,10 +12,94 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
 
+class PinnedOracle:
+    """The port (oracle/liborb_oracle.so), with every matcher / frame post-processing call ALSO run through the reference's own
+    sources (oracle/_ref/libmatch_ref.so, built by oracle/Makefile from /root/reference) when that library is present: the two
+    results must be identical, so whatever a test then holds against the returned value is held against the reference."""
+
+    PINNED = ("hamming", "angle_invalid", "match_bruteforce", "match_projection", "match_landmarks", "match_sim3", "match_mutual",
+              "match_bow", "match_bow_keyframes", "match_triangulation", "match_area", "assign_grid",
+              "undistort_keypoints", "keypoints_to_bearings")
+
+    def __init__(self, port, ref):
+        self._port, self._ref = port, ref
+        self.pinned_calls = 0
+
+    @staticmethod
+    def _same(a, b):
+        import numpy as np
+        if a is None or b is None:
+            return True
+        if isinstance(a, (tuple, list)):
+            return len(a) == len(b) and all(PinnedOracle._same(x, y) for x, y in zip(a, b))
+        return np.array_equal(np.asarray(a), np.asarray(b), equal_nan=isinstance(a, float))
+
+    def _check(self, name, got, want_ref, args):
+        assert self._same(got, want_ref), f"port and reference build disagree in {name}"
+        self.pinned_calls += 1
+
+    def __getattr__(self, name):
+        fn = getattr(self._port, name)
+        if self._ref is None:
+            return fn
+        if name in self.PINNED:
+            rfn = getattr(self._ref, name)
+
+            def both(*a, **k):
+                got = fn(*a, **k)
+                self._check(name, got, rfn(*a, **k), a)
+                return got
+            return both
+        if name == "match_reprojected":
+            def both(cam, margin, lowe_ratio, hamm_thr, level_lo, level_hi, use_ratio, use_x_right, lm_active, lm_reproj, lm_x_right,
+                     lm_scale_level, lm_desc, kp, kp_desc, kp_x_right, kp_taken, scale, lm_has_observation=None, lm_angle=None):
+                got = fn(cam, margin, lowe_ratio, hamm_thr, level_lo, level_hi, use_ratio, use_x_right, lm_active, lm_reproj, lm_x_right,
+                         lm_scale_level, lm_desc, kp, kp_desc, kp_x_right, kp_taken, scale, lm_has_observation, lm_angle)
+                if (level_lo, level_hi, bool(use_ratio), bool(use_x_right)) == (-1, 1, False, False) and lm_has_observation is None:
+                    # projection::match_frame_and_keyframe (projection.cc:210-312)
+                    self._check(name, got, self._ref.match_frame_and_keyframe(cam, margin, hamm_thr, lm_active, lm_reproj, lm_scale_level,
+                                                                              lm_desc, lm_angle, kp, kp_desc, kp_taken, scale), None)
+                elif (level_lo, level_hi, bool(use_ratio), bool(use_x_right), hamm_thr) == (-1, 0, True, True, 100) and lm_angle is None:
+                    # projection::match_frame_and_landmarks (projection.cc:11-83)
+                    self._check(name, got, self._ref.match_landmarks(cam, lm_active, lm_reproj, lm_x_right, lm_scale_level, lm_desc, kp,
+                                                                     kp_desc, kp_x_right, kp_taken, scale, margin, lowe_ratio,
+                                                                     lm_has_observation), None)
+                return got
+            return both
+        if name == "match_fuse":
+            def both(cam, margin, chi_gate, unsigned_levels, *rest):
+                got = fn(cam, margin, chi_gate, unsigned_levels, *rest)
+                if bool(chi_gate) == bool(unsigned_levels):  # detect_duplication / replace_duplication: the two combinations the reference has
+                    best, _, n = self._ref.match_fuse(cam, margin, chi_gate, unsigned_levels, *rest)
+                    self._check(name, (got[0], got[2]), (best, n), None)
+                return got
+            return both
+        if name == "landmark_descriptor":
+            def both(descs):
+                import numpy as np
+                got = fn(descs)
+                d = np.ascontiguousarray(descs, np.uint8).reshape(-1, 32)
+                assert np.array_equal(d[got], self._ref.landmark_descriptor_bytes(d)), "port and reference build disagree in compute_descriptor"
+                self.pinned_calls += 1
+                return got
+            return both
+        return fn
+
+
 @pytest.fixture(scope="session")
 def oracle():
-    from oracle import pyoracle
-    return pyoracle.port()
+    from oracle import pymatchref, pyoracle
+    return PinnedOracle(pyoracle.port(), pymatchref.match_ref())
+
+
+@pytest.fixture(scope="session")
+def match_ref():
+    from oracle import pymatchref, pyoracle
+    pyoracle.build()
+    r = pymatchref.match_ref()
+    if r is None:
+        pytest.skip("oracle/_ref/libmatch_ref.so not built (needs /root/reference)")
+    return r
 
 
 @pytest.fixture(scope="session")

@@ -1,4 +1,9 @@
-"""Loader for tests/golden/*.npz (written by tools/gen_golden.py from the reference's own sources, oracle/_ref)."""
+"""Loader for tests/golden/*.npz (written by tools/gen_golden.py / tools/gen_golden_match.py from the reference's own sources,
+oracle/_ref). Provenance of the fields: keypoints, descriptors, pyramid levels, quadtree selections, stereo and matcher outputs come
+from the reference build; `cand_crc` (FAST candidates before the quadtree) and `blur_crc` (blurred levels) are locals of the
+reference's extract() that its interface does not expose (oracle/ref_glue.cc: ref_level_candidates / blurred ref_level_copy return
+an error), so those two come from the PORT, whose FAST and Gaussian primitives are pinned bit-for-bit against cv2 and whose final
+keypoints / descriptors, which depend on both, are asserted equal to the reference build on every fixture."""
 import glob
 import os
 import zlib
@@ -9,7 +14,8 @@ from lpslam_b200.synth import noise_image, synth_image, synth_stereo_pair
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 EXTRACT_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                          if not os.path.basename(p).startswith("stereo_"))
+                          if not os.path.basename(p).startswith(("stereo_", "match_")))
+MATCH_FIXTURES = sorted(os.path.basename(p)[6:-4] for p in glob.glob(os.path.join(GOLDEN, "match_*.npz")))
 STEREO_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "stereo_*.npz")))
 
 

@@ -93,7 +93,9 @@ def test_undistort_points_vs_cv2():
         kp["octave"], kp["angle"], kp["size"] = rng.integers(0, 8, 20000), rng.uniform(0, 360, 20000), 31.0
         got = o.undistort_keypoints(700.0, 705.0, 640.0, 360.0, dist, kp)
         src = np.stack([kp["x"], kp["y"]], 1).astype(np.float32).reshape(-1, 1, 2)
-        want = cv2.undistortPointsIter(src, K, np.array(dist, np.float64), None, K, crit).reshape(-1, 2)
+        # camera/perspective.cc:21-22: the reference hands OpenCV FLOAT matrices (cv::Mat_<float>) for K and the distortion vector
+        Kf = K.astype(np.float32)
+        want = cv2.undistortPointsIter(src, Kf, np.array(dist, np.float32), None, Kf, crit).reshape(-1, 2)
         assert np.array_equal(got["x"], want[:, 0]) and np.array_equal(got["y"], want[:, 1]), dist
         assert np.array_equal(got["octave"], kp["octave"]) and np.array_equal(got["angle"], kp["angle"])
         assert (got["response"] == 0).all() and (got["class_id"] == -1).all()
