@@ -76,6 +76,14 @@ def test_python_mirror_param_errors():
         orb.orb_params(mask_rects=[[0.1, 0.2, 0.7, 0.6]])
     with pytest.raises(RuntimeError):
         orb.orb_params(mask_rects=[[0.1, 0.2, 0.7]])
+    # the five exception vectors of the reference's own test/openvslam/feature/orb_params.cc:60-166
+    for bad in ([0.28, 0.59, 0.1], [0.28, 0.28, 0.1, 0.2], [0.25, 0.21, 0.1, 0.2], [0.28, 0.59, 0.8, 0.8], [0.28, 0.59, 0.7, 0.2]):
+        with pytest.raises(RuntimeError):
+            orb.orb_params(mask_rects=[[0.2, 0.5, 0.3, 0.8], bad])
+    ok = orb.orb_params(max_num_keypts=3000, ini_max_num_keypts=5000, scale_factor=1.3, num_levels=12, ini_fast_thr=25, min_fast_thr=9,
+                        mask_rects=[[0.2, 0.5, 0.3, 0.8], [0.28, 0.59, 0.1, 0.2]])  # :24-58
+    assert (ok.max_num_keypts_, ok.ini_max_num_keypts_, ok.num_levels_, ok.ini_fast_thr_, ok.min_fast_thr) == (3000, 5000, 12, 25, 9)
+    assert len(ok.mask_rects_) == 2 and np.float32(ok.mask_rects_[1][1]) == np.float32(0.59)
     p = orb.orb_params()
     assert (p.max_num_keypts_, p.num_levels_, p.ini_fast_thr_, p.min_fast_thr) == (2000, 8, 20, 7)
     assert np.float32(p.scale_factor_) == np.float32(1.2)

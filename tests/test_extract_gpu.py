@@ -112,3 +112,12 @@ def test_clustered_corners_deep_tree(orb, oracle, seed):
         img[y0:y0 + 48, x0:x0 + 56] = rng.integers(0, 256, (48, 56), dtype=np.uint8)
     for n in (300, 1000, 3000):
         assert compare(orb, oracle, img, n) > 50
+
+
+def test_scale_tables_reference_cases(orb, oracle):
+    # test/openvslam/feature/orb_params.cc:168-213: 10 levels, scale 1.26 (the port is held against the reference build in
+    # tests/test_oracle_golden.py::test_scale_tables_reference_cases)
+    e = orb.orb_extractor(max_num_keypts=1000, scale_factor=1.26, num_levels=10)
+    o = oracle.extractor(max_kpts=1000, scale_factor=1.26, num_levels=10)
+    for got, which in ((e.get_scale_factors(), 0), (e.get_inv_scale_factors(), 1), (e.get_level_sigma_sq(), 2), (e.get_inv_level_sigma_sq(), 3)):
+        assert np.array_equal(np.asarray(got, np.float32), o.table(which)), which

@@ -295,3 +295,23 @@ def test_triangulation_search_semantics(oracle):
     assert n == 0
     out, n = run(z, [z, z, z], epi=(0.0, 0.0, 1.0), x2=np.array([-1.0, -1.0, 5.0], np.float32))
     assert n == 1 and out[0] == 2
+
+
+def test_scale_tables_reference_cases(oracle, ref_oracle):
+    """test/openvslam/feature/orb_params.cc:168-213 (calc_scale_factors / calc_inv_scale_factors / calc_level_sigma_sq /
+    calc_inv_level_sigma_sq with 10 levels and scale 1.26): on the reference build with EXPECT_FLOAT_EQ's 4-ulp bar, and
+    port == reference build bit for bit."""
+    def ulps(a, b):
+        a, b = np.asarray(a, np.float32), np.asarray(b, np.float32)
+        return np.abs(a.view(np.int32).astype(np.int64) - b.view(np.int32).astype(np.int64)).max()
+
+    L, sf = 10, np.float32(1.26)
+    r, p = ref_oracle.extractor(max_kpts=1000, scale_factor=float(sf), num_levels=L), oracle.extractor(max_kpts=1000, scale_factor=float(sf), num_levels=L)
+    for which in range(5):
+        assert np.array_equal(r.table(which), p.table(which)), which
+    lv = np.arange(L)
+    assert ulps(r.table(0), np.power(sf, lv, dtype=np.float32)) <= 4
+    assert ulps(r.table(1), np.power(np.float32(1.0) / sf, lv, dtype=np.float32)) <= 4
+    s = np.cumprod(np.concatenate([[np.float32(1.0)], np.full(L - 1, sf, np.float32)]), dtype=np.float32)
+    assert ulps(r.table(2), s * s) <= 4
+    assert ulps(r.table(3), np.float32(1.0) / (s * s)) <= 4

@@ -111,7 +111,17 @@ def main():
         ("rectmask_640x480", dict(kind="synth", h=480, w=640, seed=21),
          default_params(mask_rects=[[0.2, 0.5, 0.1, 0.6], [0.7, 0.9, 0.7, 0.95]]), None),
         ("imgmask_640x480", dict(kind="synth", h=480, w=640, seed=21), default_params(), "box"),
+        # BASELINE configs[2]: 4K, 4000 keypoints
+        ("c3_synth_3840x2160", dict(kind="synth", h=2160, w=3840, seed=3000), default_params(max_kpts=4000), None),
+        # the parameter set of the reference's own test/openvslam/feature/orb_params.cc:5-58 (3000 keypoints, scale 1.3, 12 levels,
+        # thresholds 25 / 9, its two mask rectangles), on an image large enough for level 11 (1280 / 1.3^11 = 71 px)
+        ("params_ref_test_1280x960", dict(kind="synth", h=960, w=1280, seed=41),
+         default_params(max_kpts=3000, scale_factor=1.3, num_levels=12, ini_fast_thr=25, min_fast_thr=9,
+                        mask_rects=[[0.2, 0.5, 0.3, 0.8], [0.28, 0.59, 0.1, 0.2]]), None),
     ]
+    only = [a for a in sys.argv[1:] if not a.startswith("-")]
+    if only:
+        cases = [c for c in cases if c[0] in only]
     for name, spec, params, mask_kind in cases:
         store = {}
         img = make_input(spec, store)
@@ -126,6 +136,8 @@ def main():
         np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
         print(f"{name}: {len(out['kp'])} keypoints, candidates {out['cand_n'].tolist()}")
 
+    if only:
+        return
     # the reference's own real test image (test/data/equirectangular_image_001.jpg, decoded as its tests do,
     # test/openvslam/feature/orb_extractor.cc:83), cropped so the fixture stays small; pixels are stored.
     try:
