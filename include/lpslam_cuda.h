@@ -166,6 +166,16 @@ int lpslam_stereo_frames(lpslam_orb_ctx* ctx, const uint8_t* const* imgs_l, cons
                          int width, int height, size_t pitch, float focal_x_baseline, float true_baseline,
                          lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets,
                          float* stereo_x_right, float* depths);
+/* the same, asynchronous: TWO batches in flight on one context, so that ONE host thread keeps the host link and the SMs busy
+ * (what LP/Manager/ReplayEngine.h:40-53 does with a reader thread in front of the tracker: the next chunk is read while the
+ * current one is processed). submit enqueues the host -> device copies of the batch (pinned host images; images that follow one
+ * another in memory go out as one copy), the whole pipeline and a device-side copy of its results, and returns a ticket without
+ * waiting; collect blocks until that batch is done and reads its results back. The image buffers must stay valid and unchanged
+ * until their ticket is collected. At most two tickets may be outstanding (LPSLAM_ERR_STATE otherwise); collect in submit order. */
+int lpslam_stereo_frames_submit(lpslam_orb_ctx* ctx, const uint8_t* const* imgs_l, const uint8_t* const* imgs_r, uint32_t n_pairs,
+                                int width, int height, size_t pitch, float focal_x_baseline, float true_baseline, uint64_t* ticket);
+int lpslam_stereo_frames_collect(lpslam_orb_ctx* ctx, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
+                                 uint32_t* offsets, float* stereo_x_right, float* depths);
 /* device-resident variant: imgs_dev holds 2 * n_pairs frames, left / right interleaved. Enqueues only. */
 int lpslam_stereo_frames_dev(lpslam_orb_ctx* ctx, const uint8_t* imgs_dev, uint32_t n_pairs, int width, int height,
                              size_t pitch, float focal_x_baseline, float true_baseline);

@@ -75,6 +75,131 @@ int lpslam_stereo_frames(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const 
     return LPSLAM_OK;
 }
 
+namespace {
+
+// packed results of a finished batch -> the slot's own arrays (exact sizes are only known on the device)
+__global__ void k_copy_results(const lpslam_keypoint* __restrict__ kp, const uint8_t* __restrict__ desc, const float* __restrict__ xr,
+                               const float* __restrict__ dep, const uint32_t* __restrict__ off, uint32_t nf, uint32_t n_off,
+                               lpslam_keypoint* __restrict__ kp_o, uint8_t* __restrict__ desc_o, float* __restrict__ xr_o,
+                               float* __restrict__ dep_o, uint32_t* __restrict__ off_o) {
+    const uint32_t total = off[nf];
+    const uint32_t stride = gridDim.x * blockDim.x, i0 = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t i = i0; i < n_off; i += stride) off_o[i] = off[i];
+    const uint32_t* ks = reinterpret_cast<const uint32_t*>(kp);
+    uint32_t* kd = reinterpret_cast<uint32_t*>(kp_o);
+    for (uint32_t i = i0; i < total * 7u; i += stride) kd[i] = ks[i];
+    const uint4* ds = reinterpret_cast<const uint4*>(desc);
+    uint4* dd = reinterpret_cast<uint4*>(desc_o);
+    for (uint32_t i = i0; i < total * 2u; i += stride) dd[i] = ds[i];
+    for (uint32_t i = i0; i < total; i += stride) {
+        xr_o[i] = xr[i];
+        dep_o[i] = dep[i];
+    }
+}
+
+int ensure_async(lpslam_orb_ctx* c, int width, int height) {
+    const size_t need = (size_t)c->max_batch * width * height;
+    if (c->async_ready && c->landing_bytes >= need) return LPSLAM_OK;
+    c->release_async();
+    int least = 0, greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&least, &greatest);
+    LPS_CUDA(cudaStreamCreateWithPriority(&c->copy_in, cudaStreamNonBlocking, greatest));
+    LPS_CUDA(cudaStreamCreateWithPriority(&c->copy_out, cudaStreamNonBlocking, greatest));
+    for (auto& sl : c->slot) {
+        LPS_CUDA(cudaMalloc(&sl.landing, need));
+        LPS_CUDA(cudaMalloc(&sl.kp, sizeof(lpslam_keypoint) * (size_t)c->out_cap));
+        LPS_CUDA(cudaMalloc(&sl.desc, 32 * (size_t)c->out_cap));
+        LPS_CUDA(cudaMalloc(&sl.xr, 4 * (size_t)c->out_cap));
+        LPS_CUDA(cudaMalloc(&sl.dep, 4 * (size_t)c->out_cap));
+        LPS_CUDA(cudaMalloc(&sl.off_dev, 4 * (size_t)(c->max_batch + 2)));
+        LPS_CUDA(cudaHostAlloc((void**)&sl.h_off, 4 * (size_t)(c->max_batch + 2), cudaHostAllocDefault));
+        LPS_CUDA(cudaEventCreateWithFlags(&sl.ev_in, cudaEventDisableTiming));
+        LPS_CUDA(cudaEventCreateWithFlags(&sl.ev_landing_free, cudaEventDisableTiming));
+        LPS_CUDA(cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+    }
+    c->landing_bytes = need;
+    c->async_ready = true;
+    return LPSLAM_OK;
+}
+
+}  // namespace
+
+int lpslam_stereo_frames_submit(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const uint8_t* const* imgs_r, uint32_t n_pairs, int width,
+                                int height, size_t pitch, float focal_x_baseline, float true_baseline, uint64_t* ticket) {
+    LPS_ARG(c && imgs_l && imgs_r && ticket, "null argument");
+    LPS_ARG(n_pairs >= 1 && 2 * n_pairs <= c->max_batch, "2 * n_pairs exceeds the context's max_batch");
+    LPS_ARG(width > 0 && height > 0 && pitch >= (size_t)width, "bad image geometry");
+    LPS_CUDA(cudaSetDevice(c->device));
+    int rc = c->configure(width, height);
+    if (rc) return rc;
+    if ((rc = ensure_async(c, width, height))) return rc;
+    lpslam_orb_ctx::AsyncSlot& sl = c->slot[c->seq & 1];
+    if (sl.busy) {
+        set_error("both in-flight slots are taken: collect the oldest ticket first");
+        return LPSLAM_ERR_STATE;
+    }
+    // images -> landing buffer (dense rows) on the copy-in stream, once the previous user of the buffer has consumed it
+    if (sl.landing_used) LPS_CUDA(cudaStreamWaitEvent(c->copy_in, sl.ev_landing_free, 0));
+    const size_t img = (size_t)width * height;
+    uint32_t f = 0;
+    const uint32_t nf = 2 * n_pairs;
+    auto src_of = [&](uint32_t k) { return (k & 1) ? imgs_r[k >> 1] : imgs_l[k >> 1]; };
+    for (uint32_t k = 0; k < nf; ++k) LPS_ARG(src_of(k), "null image pointer");
+    while (f < nf) {  // images that follow one another in host memory go out as one copy
+        uint32_t g = f + 1;
+        if (pitch == (size_t)width)
+            while (g < nf && src_of(g) == src_of(g - 1) + img) ++g;
+        if (pitch == (size_t)width)
+            LPS_CUDA(cudaMemcpyAsync(sl.landing + f * img, src_of(f), (g - f) * img, cudaMemcpyHostToDevice, c->copy_in));
+        else
+            LPS_CUDA(cudaMemcpy2DAsync(sl.landing + f * img, width, src_of(f), pitch, width, height, cudaMemcpyHostToDevice, c->copy_in));
+        f = g;
+    }
+    LPS_CUDA(cudaEventRecord(sl.ev_in, c->copy_in));
+    LPS_CUDA(cudaStreamWaitEvent(c->stream, sl.ev_in, 0));
+    launch_copy_level0(sl.landing, width, img, c->lv[0], (int)nf, c->stream);
+    LPS_CUDA(cudaEventRecord(sl.ev_landing_free, c->stream));
+    sl.landing_used = true;
+    rc = lpslam_stereo_frames_dev(c, c->lv[0].img, n_pairs, width, height, c->lv[0].pitch, focal_x_baseline, true_baseline);
+    if (rc) return rc;
+    k_copy_results<<<256, 256, 0, c->stream>>>(c->desc.kp, c->desc.desc, c->stereo.x_right, c->stereo.depth, c->desc.frame_off, nf,
+                                               c->max_batch + 2, sl.kp, sl.desc, sl.xr, sl.dep, sl.off_dev);
+    LPS_CUDA(cudaMemcpyAsync(sl.h_off, sl.off_dev, 4 * (size_t)(c->max_batch + 2), cudaMemcpyDeviceToHost, c->stream));
+    LPS_CUDA(cudaEventRecord(sl.ev_done, c->stream));
+    sl.busy = true;
+    sl.n_pairs = n_pairs;
+    *ticket = c->seq++;
+    return LPSLAM_OK;
+}
+
+int lpslam_stereo_frames_collect(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
+                                 uint32_t* offsets, float* stereo_x_right, float* depths) {
+    LPS_ARG(c && offsets && kp_out && desc_out && stereo_x_right && depths, "null argument");
+    LPS_ARG(c->async_ready && ticket < c->seq && ticket + 2 >= c->seq, "unknown ticket");
+    lpslam_orb_ctx::AsyncSlot& sl = c->slot[ticket & 1];
+    if (!sl.busy) {
+        set_error("ticket already collected");
+        return LPSLAM_ERR_STATE;
+    }
+    LPS_CUDA(cudaSetDevice(c->device));
+    LPS_CUDA(cudaEventSynchronize(sl.ev_done));
+    sl.busy = false;
+    const uint32_t nf = 2 * sl.n_pairs, total = sl.h_off[nf];
+    for (uint32_t f = 0; f <= nf; ++f) offsets[f] = sl.h_off[f];
+    if (sl.h_off[c->max_batch + 1] != 0 || total > cap) {
+        set_error("output capacity too small for the extracted keypoints");
+        return LPSLAM_ERR_CAPACITY;
+    }
+    if (total) {
+        LPS_CUDA(cudaMemcpyAsync(kp_out, sl.kp, sizeof(lpslam_keypoint) * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
+        LPS_CUDA(cudaMemcpyAsync(desc_out, sl.desc, 32 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
+        LPS_CUDA(cudaMemcpyAsync(stereo_x_right, sl.xr, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
+        LPS_CUDA(cudaMemcpyAsync(depths, sl.dep, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
+        LPS_CUDA(cudaStreamSynchronize(c->copy_out));
+    }
+    return LPSLAM_OK;
+}
+
 int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r, const int* level_w, const int* level_h,
                         const size_t* pitch_l, const size_t* pitch_r, uint32_t num_levels, const lpslam_keypoint* kp_l,
                         uint32_t nl, const lpslam_keypoint* kp_r, uint32_t nr, const uint8_t* desc_l, const uint8_t* desc_r,

@@ -98,7 +98,30 @@ void lpslam_orb_ctx::initialize_tables() {
     quota[num_levels - 1] = (unsigned)std::max((int)max_kpts - (int)total, 0);
 }
 
+void lpslam_orb_ctx::release_async() {
+    for (auto& sl : slot) {
+        if (sl.ev_done && sl.busy) cudaEventSynchronize(sl.ev_done);
+        cudaFree(sl.landing);
+        cudaFree(sl.kp);
+        cudaFree(sl.desc);
+        cudaFree(sl.xr);
+        cudaFree(sl.dep);
+        cudaFree(sl.off_dev);
+        if (sl.h_off) cudaFreeHost(sl.h_off);
+        if (sl.ev_in) cudaEventDestroy(sl.ev_in);
+        if (sl.ev_landing_free) cudaEventDestroy(sl.ev_landing_free);
+        if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+        sl = AsyncSlot{};
+    }
+    if (copy_in) cudaStreamDestroy(copy_in);
+    if (copy_out) cudaStreamDestroy(copy_out);
+    copy_in = copy_out = nullptr;
+    async_ready = false;
+    landing_bytes = 0;
+}
+
 void lpslam_orb_ctx::release_geometry() {
+    release_async();
     lps::blur_plan_destroy(blur_plan);
     blur_plan = nullptr;
     lps::pyramid_plan_destroy(pyr_plan);

@@ -57,6 +57,28 @@ struct lpslam_orb_ctx {
     uint32_t last_batch = 0;
     bool has_result = false;
 
+    // asynchronous stereo frames (lpslam_stereo_frames_submit / _collect): two batches in flight on one context. A slot owns a
+    // device landing buffer for the next batch's images (filled by the copy-in stream while the previous batch computes) and a
+    // copy of a finished batch's packed results (read back by the copy-out stream while the next batch computes).
+    struct AsyncSlot {
+        uint8_t* landing = nullptr;
+        lpslam_keypoint* kp = nullptr;
+        uint8_t* desc = nullptr;
+        float* xr = nullptr;
+        float* dep = nullptr;
+        uint32_t* off_dev = nullptr;   // max_batch + 2 (last = overflow flag)
+        uint32_t* h_off = nullptr;     // pinned mirror
+        cudaEvent_t ev_in = nullptr, ev_landing_free = nullptr, ev_done = nullptr;
+        bool busy = false, landing_used = false;
+        uint32_t n_pairs = 0;
+    };
+    AsyncSlot slot[2];
+    size_t landing_bytes = 0;
+    bool async_ready = false;
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    uint64_t seq = 0;
+    void release_async();
+
     // optional stage timing
     bool timing = false;
     cudaEvent_t ev[8] = {};

@@ -14,6 +14,10 @@ register("lpslam_match_stereo", C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_v
 register("lpslam_stereo_frames", C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_uint32, C.c_int,
                                            C.c_int, C.c_size_t, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_uint32,
                                            C.c_void_p, C.c_void_p, C.c_void_p])
+register("lpslam_stereo_frames_submit", C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_uint32, C.c_int, C.c_int,
+                                                  C.c_size_t, C.c_float, C.c_float, C.POINTER(C.c_uint64)])
+register("lpslam_stereo_frames_collect", C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p])
 register("lpslam_stereo_frames_dev", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_size_t, C.c_float,
                                                C.c_float])
 register("lpslam_stereo_result_dev", C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)])
@@ -71,6 +75,39 @@ def stereo_frames(extractor, lefts, rights, focal_x_baseline, true_baseline, cap
     pr = (C.c_void_p * n)(*[a.ctypes.data for a in rights])
     check(lib().lpslam_stereo_frames(extractor._h, pl, pr, n, w, h, w, focal_x_baseline, true_baseline, kp.ctypes.data,
                                      desc.ctypes.data, cap, offs.ctypes.data, xr.ctypes.data, dep.ctypes.data))
+    out = []
+    for p in range(n):
+        a, b, c = int(offs[2 * p]), int(offs[2 * p + 1]), int(offs[2 * p + 2])
+        out.append(dict(keypts_left=kp[a:b].copy(), descs_left=desc[a:b].copy(), keypts_right=kp[b:c].copy(),
+                        descs_right=desc[b:c].copy(), stereo_x_right=xr[a:b].copy(), depths=dep[a:b].copy()))
+    return out
+
+
+def stereo_frames_submit(extractor, lefts, rights, focal_x_baseline, true_baseline):
+    """lpslam_stereo_frames_submit: enqueue a batch of pairs, return (ticket, keep_alive). The arrays in keep_alive are the buffers
+    the copies read from: hold on to them until the ticket is collected."""
+    n = len(lefts)
+    lefts = [np.ascontiguousarray(a, np.uint8) for a in lefts]
+    rights = [np.ascontiguousarray(a, np.uint8) for a in rights]
+    h, w = lefts[0].shape
+    pl = (C.c_void_p * n)(*[a.ctypes.data for a in lefts])
+    pr = (C.c_void_p * n)(*[a.ctypes.data for a in rights])
+    t = C.c_uint64(0)
+    check(lib().lpslam_stereo_frames_submit(extractor._h, pl, pr, n, w, h, w, focal_x_baseline, true_baseline, C.byref(t)))
+    return t.value, (lefts, rights, n)
+
+
+def stereo_frames_collect(extractor, ticket, keep_alive, cap_per_frame=None):
+    """lpslam_stereo_frames_collect: wait for a submitted batch and return the same list of dicts as stereo_frames."""
+    n = keep_alive[2]
+    cap = 2 * n * (int(cap_per_frame) if cap_per_frame else 8 * extractor.orb_params_.max_num_keypts_ + 256)
+    kp = np.empty(cap, KP_DTYPE)
+    desc = np.empty((cap, 32), np.uint8)
+    xr = np.empty(cap, np.float32)
+    dep = np.empty(cap, np.float32)
+    offs = np.zeros(2 * n + 1, np.uint32)
+    check(lib().lpslam_stereo_frames_collect(extractor._h, ticket, kp.ctypes.data, desc.ctypes.data, cap, offs.ctypes.data, xr.ctypes.data,
+                                             dep.ctypes.data))
     out = []
     for p in range(n):
         a, b, c = int(offs[2 * p]), int(offs[2 * p + 1]), int(offs[2 * p + 2])

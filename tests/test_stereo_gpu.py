@@ -51,3 +51,33 @@ def test_empty_right(oracle):
     pl = [o.level(l) for l in range(8)]
     xr, dep = match.stereo(pl, pl, kl, kl[:0], dl, dl[:0], o.table(0), o.table(1), FX_B, B).compute()
     assert (xr == -1).all() and (dep == -1).all()
+
+
+def test_stereo_frames_submit_collect():
+    """lpslam_stereo_frames_submit / _collect: two batches in flight on one context give the results of the blocking call;
+    a third submit before a collect is refused, tickets are collected in order."""
+    from lpslam_b200 import _lib, match, orb
+    from lpslam_b200.synth import synth_stereo_pair
+    e = orb.orb_extractor(max_num_keypts=600, max_batch=4)
+    batches = [[synth_stereo_pair(240, 320, 300 + 2 * b + k) for k in range(2)] for b in range(4)]
+    want = [match.stereo_frames(e, [p[0] for p in bt], [p[1] for p in bt], 84.0, 0.12) for bt in batches]
+    tickets = []
+    got = []
+    for b, bt in enumerate(batches):
+        tickets.append(match.stereo_frames_submit(e, [p[0] for p in bt], [p[1] for p in bt], 84.0, 0.12))
+        if len(tickets) == 2:
+            with pytest.raises(_lib.LpslamCudaError):  # both slots taken
+                match.stereo_frames_submit(e, [p[0] for p in bt], [p[1] for p in bt], 84.0, 0.12)
+            t, keep = tickets.pop(0)
+            got.append(match.stereo_frames_collect(e, t, keep))
+    while tickets:
+        t, keep = tickets.pop(0)
+        got.append(match.stereo_frames_collect(e, t, keep))
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        for a, b in zip(g, w):
+            for k in a:
+                assert np.array_equal(a[k], b[k], equal_nan=True) if a[k].dtype.kind == "f" else a[k].tobytes() == b[k].tobytes(), k
+    # the blocking entry point still works on the same context afterwards
+    again = match.stereo_frames(e, [p[0] for p in batches[0]], [p[1] for p in batches[0]], 84.0, 0.12)
+    assert again[0]["keypts_left"].tobytes() == want[0][0]["keypts_left"].tobytes()
