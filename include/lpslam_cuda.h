@@ -147,6 +147,13 @@ int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* d
                             const float* angle_1, const float* angle_2, float lowe_ratio, int check_orientation,
                             int32_t* match_2_in_1, uint32_t* n_matches);
 
+/* robust::brute_force_match between CONSECUTIVE frames of the batch a context extracted last (module/frame_tracker.cc:162 calls
+ * it with ratio 0.8 and the orientation check off, once per tracked frame): frame f is the "frame" side, frame f - 1 the
+ * "keyframe" side with every keypoint holding a landmark. Descriptors never leave the device. match_prev_in_cur has one entry per
+ * packed keypoint row of the batch (frame 0: -1): index, inside frame f - 1, of the keypoint matched to that row, or -1.
+ * n_matches has one entry per frame (entry 0 = 0). */
+int lpslam_match_consecutive_frames(lpslam_orb_ctx* ctx, float lowe_ratio, int32_t* match_prev_in_cur, uint32_t* n_matches);
+
 /* match::stereo::compute (match/stereo.cc:18-249; ctor match/stereo.h:18-29). Pyramids are arrays of num_levels host
  * level pointers with per-level width/height/pitch (the extractors' image_pyramid_). Outputs: stereo_x_right[nl],
  * depths[nl], -1 = no match. */
@@ -176,6 +183,11 @@ int lpslam_stereo_frames_submit(lpslam_orb_ctx* ctx, const uint8_t* const* imgs_
                                 int width, int height, size_t pitch, float focal_x_baseline, float true_baseline, uint64_t* ticket);
 int lpslam_stereo_frames_collect(lpslam_orb_ctx* ctx, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
                                  uint32_t* offsets, float* stereo_x_right, float* depths);
+/* extraction only, same protocol and the same two slots (frame-parallel replay of a log: LP/Manager/ReplayEngine.h:40-53) */
+int lpslam_orb_extract_batch_submit(lpslam_orb_ctx* ctx, const uint8_t* const* imgs, uint32_t n_frames, int width, int height,
+                                    size_t pitch, uint64_t* ticket);
+int lpslam_orb_extract_batch_collect(lpslam_orb_ctx* ctx, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
+                                     uint32_t* offsets);
 /* device-resident variant: imgs_dev holds 2 * n_pairs frames, left / right interleaved. Enqueues only. */
 int lpslam_stereo_frames_dev(lpslam_orb_ctx* ctx, const uint8_t* imgs_dev, uint32_t n_pairs, int width, int height,
                              size_t pitch, float focal_x_baseline, float true_baseline);

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <vector>
 
 using namespace lps;
 
@@ -124,10 +125,11 @@ int ensure_async(lpslam_orb_ctx* c, int width, int height) {
 
 }  // namespace
 
-int lpslam_stereo_frames_submit(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const uint8_t* const* imgs_r, uint32_t n_pairs, int width,
-                                int height, size_t pitch, float focal_x_baseline, float true_baseline, uint64_t* ticket) {
-    LPS_ARG(c && imgs_l && imgs_r && ticket, "null argument");
-    LPS_ARG(n_pairs >= 1 && 2 * n_pairs <= c->max_batch, "2 * n_pairs exceeds the context's max_batch");
+namespace {
+
+// frames[k] = host image of frame k (stereo: left / right interleaved). n_pairs == 0: extraction only.
+int submit_frames(lpslam_orb_ctx* c, const uint8_t* const* frames, uint32_t nf, uint32_t n_pairs, int width, int height, size_t pitch,
+                  float focal_x_baseline, float true_baseline, uint64_t* ticket) {
     LPS_ARG(width > 0 && height > 0 && pitch >= (size_t)width, "bad image geometry");
     LPS_CUDA(cudaSetDevice(c->device));
     int rc = c->configure(width, height);
@@ -138,21 +140,19 @@ int lpslam_stereo_frames_submit(lpslam_orb_ctx* c, const uint8_t* const* imgs_l,
         set_error("both in-flight slots are taken: collect the oldest ticket first");
         return LPSLAM_ERR_STATE;
     }
+    for (uint32_t k = 0; k < nf; ++k) LPS_ARG(frames[k], "null image pointer");
     // images -> landing buffer (dense rows) on the copy-in stream, once the previous user of the buffer has consumed it
     if (sl.landing_used) LPS_CUDA(cudaStreamWaitEvent(c->copy_in, sl.ev_landing_free, 0));
     const size_t img = (size_t)width * height;
     uint32_t f = 0;
-    const uint32_t nf = 2 * n_pairs;
-    auto src_of = [&](uint32_t k) { return (k & 1) ? imgs_r[k >> 1] : imgs_l[k >> 1]; };
-    for (uint32_t k = 0; k < nf; ++k) LPS_ARG(src_of(k), "null image pointer");
     while (f < nf) {  // images that follow one another in host memory go out as one copy
         uint32_t g = f + 1;
-        if (pitch == (size_t)width)
-            while (g < nf && src_of(g) == src_of(g - 1) + img) ++g;
-        if (pitch == (size_t)width)
-            LPS_CUDA(cudaMemcpyAsync(sl.landing + f * img, src_of(f), (g - f) * img, cudaMemcpyHostToDevice, c->copy_in));
+        if (pitch == (size_t)width) {
+            while (g < nf && frames[g] == frames[g - 1] + img) ++g;
+            LPS_CUDA(cudaMemcpyAsync(sl.landing + f * img, frames[f], (g - f) * img, cudaMemcpyHostToDevice, c->copy_in));
+        }
         else
-            LPS_CUDA(cudaMemcpy2DAsync(sl.landing + f * img, width, src_of(f), pitch, width, height, cudaMemcpyHostToDevice, c->copy_in));
+            LPS_CUDA(cudaMemcpy2DAsync(sl.landing + f * img, width, frames[f], pitch, width, height, cudaMemcpyHostToDevice, c->copy_in));
         f = g;
     }
     LPS_CUDA(cudaEventRecord(sl.ev_in, c->copy_in));
@@ -160,21 +160,25 @@ int lpslam_stereo_frames_submit(lpslam_orb_ctx* c, const uint8_t* const* imgs_l,
     launch_copy_level0(sl.landing, width, img, c->lv[0], (int)nf, c->stream);
     LPS_CUDA(cudaEventRecord(sl.ev_landing_free, c->stream));
     sl.landing_used = true;
-    rc = lpslam_stereo_frames_dev(c, c->lv[0].img, n_pairs, width, height, c->lv[0].pitch, focal_x_baseline, true_baseline);
+    if (n_pairs)
+        rc = lpslam_stereo_frames_dev(c, c->lv[0].img, n_pairs, width, height, c->lv[0].pitch, focal_x_baseline, true_baseline);
+    else
+        rc = lpslam_orb_extract_batch_dev(c, c->lv[0].img, nf, width, height, c->lv[0].pitch);
     if (rc) return rc;
+    // (extraction only: the stereo arrays are copied too, rows of an earlier stereo call or never-read scratch)
     k_copy_results<<<256, 256, 0, c->stream>>>(c->desc.kp, c->desc.desc, c->stereo.x_right, c->stereo.depth, c->desc.frame_off, nf,
                                                c->max_batch + 2, sl.kp, sl.desc, sl.xr, sl.dep, sl.off_dev);
     LPS_CUDA(cudaMemcpyAsync(sl.h_off, sl.off_dev, 4 * (size_t)(c->max_batch + 2), cudaMemcpyDeviceToHost, c->stream));
     LPS_CUDA(cudaEventRecord(sl.ev_done, c->stream));
     sl.busy = true;
     sl.n_pairs = n_pairs;
+    sl.n_frames = nf;
     *ticket = c->seq++;
     return LPSLAM_OK;
 }
 
-int lpslam_stereo_frames_collect(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
-                                 uint32_t* offsets, float* stereo_x_right, float* depths) {
-    LPS_ARG(c && offsets && kp_out && desc_out && stereo_x_right && depths, "null argument");
+int collect_frames(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap, uint32_t* offsets,
+                   float* stereo_x_right, float* depths) {
     LPS_ARG(c->async_ready && ticket < c->seq && ticket + 2 >= c->seq, "unknown ticket");
     lpslam_orb_ctx::AsyncSlot& sl = c->slot[ticket & 1];
     if (!sl.busy) {
@@ -184,7 +188,7 @@ int lpslam_stereo_frames_collect(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keyp
     LPS_CUDA(cudaSetDevice(c->device));
     LPS_CUDA(cudaEventSynchronize(sl.ev_done));
     sl.busy = false;
-    const uint32_t nf = 2 * sl.n_pairs, total = sl.h_off[nf];
+    const uint32_t nf = sl.n_frames, total = sl.h_off[nf];
     for (uint32_t f = 0; f <= nf; ++f) offsets[f] = sl.h_off[f];
     if (sl.h_off[c->max_batch + 1] != 0 || total > cap) {
         set_error("output capacity too small for the extracted keypoints");
@@ -193,11 +197,44 @@ int lpslam_stereo_frames_collect(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keyp
     if (total) {
         LPS_CUDA(cudaMemcpyAsync(kp_out, sl.kp, sizeof(lpslam_keypoint) * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
         LPS_CUDA(cudaMemcpyAsync(desc_out, sl.desc, 32 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
-        LPS_CUDA(cudaMemcpyAsync(stereo_x_right, sl.xr, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
-        LPS_CUDA(cudaMemcpyAsync(depths, sl.dep, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
+        if (stereo_x_right) LPS_CUDA(cudaMemcpyAsync(stereo_x_right, sl.xr, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
+        if (depths) LPS_CUDA(cudaMemcpyAsync(depths, sl.dep, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->copy_out));
         LPS_CUDA(cudaStreamSynchronize(c->copy_out));
     }
     return LPSLAM_OK;
+}
+
+}  // namespace
+
+int lpslam_stereo_frames_submit(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const uint8_t* const* imgs_r, uint32_t n_pairs, int width,
+                                int height, size_t pitch, float focal_x_baseline, float true_baseline, uint64_t* ticket) {
+    LPS_ARG(c && imgs_l && imgs_r && ticket, "null argument");
+    LPS_ARG(n_pairs >= 1 && 2 * n_pairs <= c->max_batch, "2 * n_pairs exceeds the context's max_batch");
+    std::vector<const uint8_t*> frames(2 * (size_t)n_pairs);
+    for (uint32_t p = 0; p < n_pairs; ++p) {
+        frames[2 * p] = imgs_l[p];
+        frames[2 * p + 1] = imgs_r[p];
+    }
+    return submit_frames(c, frames.data(), 2 * n_pairs, n_pairs, width, height, pitch, focal_x_baseline, true_baseline, ticket);
+}
+
+int lpslam_orb_extract_batch_submit(lpslam_orb_ctx* c, const uint8_t* const* imgs, uint32_t n_frames, int width, int height, size_t pitch,
+                                    uint64_t* ticket) {
+    LPS_ARG(c && imgs && ticket, "null argument");
+    LPS_ARG(n_frames >= 1 && n_frames <= c->max_batch, "n_frames exceeds the context's max_batch");
+    return submit_frames(c, imgs, n_frames, 0, width, height, pitch, 0.f, 0.f, ticket);
+}
+
+int lpslam_orb_extract_batch_collect(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
+                                     uint32_t* offsets) {
+    LPS_ARG(c && offsets && kp_out && desc_out, "null argument");
+    return collect_frames(c, ticket, kp_out, desc_out, cap, offsets, nullptr, nullptr);
+}
+
+int lpslam_stereo_frames_collect(lpslam_orb_ctx* c, uint64_t ticket, lpslam_keypoint* kp_out, uint8_t* desc_out, uint32_t cap,
+                                 uint32_t* offsets, float* stereo_x_right, float* depths) {
+    LPS_ARG(c && offsets && kp_out && desc_out && stereo_x_right && depths, "null argument");
+    return collect_frames(c, ticket, kp_out, desc_out, cap, offsets, stereo_x_right, depths);
 }
 
 int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r, const int* level_w, const int* level_h,

@@ -70,7 +70,7 @@ struct lpslam_orb_ctx {
         uint32_t* h_off = nullptr;     // pinned mirror
         cudaEvent_t ev_in = nullptr, ev_landing_free = nullptr, ev_done = nullptr;
         bool busy = false, landing_used = false;
-        uint32_t n_pairs = 0;
+        uint32_t n_pairs = 0, n_frames = 0;
     };
     AsyncSlot slot[2];
     size_t landing_bytes = 0;

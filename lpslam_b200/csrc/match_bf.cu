@@ -10,6 +10,7 @@
 //                 first conflict). A row whose top-4 list runs out of unclaimed entries before the decision is certain is
 //                 rescanned exactly by the warp.
 #include "common.cuh"
+#include "ctx.h"
 
 #include <algorithm>
 #include <cmath>
@@ -285,6 +286,68 @@ int lpslam_match_bruteforce(const uint8_t* desc_1, uint32_t n1, const uint8_t* d
         }
     }
     return rc;
+}
+
+int lpslam_match_consecutive_frames(lpslam_orb_ctx* c, float lowe_ratio, int32_t* match_prev_in_cur, uint32_t* n_matches) {
+    LPS_ARG(c && match_prev_in_cur && n_matches, "null argument");
+    if (!c->has_result) {
+        set_error("no extraction has run on this context");
+        return LPSLAM_ERR_STATE;
+    }
+    LPS_CUDA(cudaSetDevice(c->device));
+    const uint32_t nf = c->last_batch;
+    LPS_CUDA(cudaMemcpyAsync(c->h_frame_off, c->desc.frame_off, sizeof(uint32_t) * (c->max_batch + 2), cudaMemcpyDeviceToHost, c->stream));
+    LPS_CUDA(cudaStreamSynchronize(c->stream));
+    const uint32_t* off = c->h_frame_off;
+    const uint32_t total = off[nf];
+    n_matches[0] = 0;
+    if (total == 0) return LPSLAM_OK;
+    uint32_t max_rows = 0;
+    for (uint32_t f = 0; f < nf; ++f) {
+        const uint32_t n = off[f + 1] - off[f];
+        LPS_ARG(n <= 65535, "more than 65535 keypoints per frame are not supported by this matcher");
+        max_rows = std::max(max_rows, n);
+    }
+    // scratch: kept candidates per pair (one block of max_rows per pair, so that the pairs' kernels are independent), the packed
+    // match array and one counter per frame
+    uint8_t* dev = nullptr;
+    const size_t o_top = 0, top_stride = align_up(16 * (size_t)max_rows, 256);
+    const size_t o_m = o_top + top_stride * nf, o_n = o_m + align_up(4 * (size_t)total, 256);
+    LPS_CUDA(scratch_alloc((void**)&dev, o_n + align_up(4 * (size_t)nf, 256)));
+    cudaError_t e = cudaSuccess;
+    do {
+        if ((e = cudaMemsetAsync(dev + o_m, 0xFF, 4 * (size_t)total, c->stream)) != cudaSuccess) break;
+        if ((e = cudaMemsetAsync(dev + o_n, 0, 4 * (size_t)nf, c->stream)) != cudaSuccess) break;
+        // the pairs are independent and each resolve is one serial warp: they are spread over the context's five streams
+        cudaStream_t lanes[5] = {c->stream, c->side, c->chain[0], c->chain[1], c->chain[2]};
+        cudaEvent_t joins[5] = {nullptr, c->ev_join, c->ev_chain_join[0], c->ev_chain_join[1], c->ev_chain_join[2]};
+        if ((e = cudaEventRecord(c->ev_chain_fork, c->stream)) != cudaSuccess) break;
+        for (int k = 1; k < 5; ++k) cudaStreamWaitEvent(lanes[k], c->ev_chain_fork, 0);
+        for (uint32_t f = 1; f < nf; ++f) {
+            cudaStream_t st = lanes[f % 5];
+            // side 1 = the current frame f (its keypoints are claimed), side 2 = the previous frame f - 1 (every row valid)
+            const uint32_t n1 = off[f + 1] - off[f], n2 = off[f] - off[f - 1];
+            if (n1 == 0 || n2 == 0) continue;
+            const uint8_t* d1 = c->desc.desc + 32 * (size_t)off[f];
+            const uint8_t* d2 = c->desc.desc + 32 * (size_t)off[f - 1];
+            uint4* top = (uint4*)(dev + o_top + top_stride * f);
+            k_bf_topk<<<(n2 + 7) / 8, 256, 0, st>>>(d1, n1, d2, n2, nullptr, top);
+            const int first_in_smem = n1 <= 10000;
+            k_bf_resolve<<<1, 32, ((n1 + 31) / 32) * 4 + (first_in_smem ? 4 * (size_t)n1 : 0), st>>>(
+                d1, n1, d2, n2, top, lowe_ratio, first_in_smem, (int32_t*)(dev + o_m) + off[f], (uint32_t*)(dev + o_n) + f);
+        }
+        for (int k = 1; k < 5; ++k) {
+            cudaEventRecord(joins[k], lanes[k]);
+            cudaStreamWaitEvent(c->stream, joins[k], 0);
+        }
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(match_prev_in_cur, dev + o_m, 4 * (size_t)total, cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(n_matches, dev + o_n, 4 * (size_t)nf, cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) break;
+        e = cudaStreamSynchronize(c->stream);
+    } while (false);
+    scratch_free(dev);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_consecutive_frames", __FILE__, __LINE__);
+    return LPSLAM_OK;
 }
 
 int lpslam_hamming_pairs(const uint8_t* a, const uint8_t* b, uint32_t n, uint32_t* dist) {

@@ -118,6 +118,7 @@ def stereo_frames_collect(extractor, ticket, keep_alive, cap_per_frame=None):
 
 register("lpslam_match_bruteforce", C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.c_float, C.c_int, C.c_void_p, _lib.u32p])
+register("lpslam_match_consecutive_frames", C.c_int, [C.c_void_p, C.c_float, C.c_void_p, C.c_void_p])
 register("lpslam_hamming_pairs", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p])
 register("lpslam_match_projection", C.c_int, [C.POINTER(_lib.Camera), C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
@@ -463,6 +464,14 @@ def compute_landmark_descriptors(obs_descs, offsets):
     out = np.zeros((n, 32), np.uint8)
     check(lib().lpslam_landmark_descriptors(d.ctypes.data, off.ctypes.data, n, best.ctypes.data, out.ctypes.data))
     return best, out
+
+
+def match_consecutive_frames(extractor, n_rows, n_frames, lowe_ratio=0.8):
+    """lpslam_match_consecutive_frames on the batch `extractor` extracted last: (match_prev_in_cur[n_rows], n_matches[n_frames])"""
+    out = np.full(max(n_rows, 1), -1, np.int32)
+    cnt = np.zeros(n_frames, np.uint32)
+    check(lib().lpslam_match_consecutive_frames(extractor._h, float(lowe_ratio), out.ctypes.data, cnt.ctypes.data))
+    return out[:n_rows], cnt
 
 
 def compute_descriptor_distance_32(desc_1, desc_2):

@@ -630,3 +630,18 @@ def test_match_for_triangulation_clustered(oracle, seed):
     _, got = match.robust(0.6, True).match_for_triangulation(vec1, s1, vec2, s2, E, np.array([1.0, 0.0, 0.0]))
     assert np.array_equal(got, want)
     assert nw > 200
+
+
+def test_match_consecutive_frames(oracle):
+    # robust::brute_force_match between consecutive frames of a device-resident batch == the host-buffer matcher per pair
+    from lpslam_b200 import match, orb
+    imgs = [np.roll(synth_image(480, 640, 77), (2 * k, 3 * k), axis=(0, 1)) for k in range(5)]
+    e = orb.orb_extractor(max_num_keypts=1000, max_batch=5)
+    res = e.extract_batch(imgs)
+    n_rows = sum(len(k) for k, _ in res)
+    got, cnt = match.match_consecutive_frames(e, n_rows, len(imgs), 0.8)
+    off = np.concatenate([[0], np.cumsum([len(k) for k, _ in res])])
+    assert (got[: off[1]] == -1).all() and cnt[0] == 0
+    for f in range(1, len(imgs)):
+        want, nw = oracle.match_bruteforce(res[f][1], res[f - 1][1], None, None, None, 0.8, False)
+        assert np.array_equal(got[off[f]:off[f + 1]], want) and cnt[f] == nw and nw > 100
