@@ -258,9 +258,9 @@ void blur_plan_destroy(BlurPlan* p) {
 static int build_units(const BlurPlan* p, int batch, std::vector<BlurUnit>& out) {
     static const int seg_rows_env = [] {
         const char* e = getenv("LPS_BLUR_SEG_ROWS");
-        return e ? atoi(e) : 60;
+        return e ? atoi(e) : 50;
     }();
-    int target = seg_rows_env > 0 ? seg_rows_env : 60;
+    int target = seg_rows_env > 0 ? seg_rows_env : 50;
     for (;;) {
         out.clear();
         for (int l = 0; l < p->num_levels; ++l) {

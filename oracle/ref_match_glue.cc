@@ -34,10 +34,12 @@
 #include "openvslam/data/keyframe.h"
 #include "openvslam/data/map_database.h"
 #include "openvslam/match/angle_checker.h"
-#include "openvslam/match/area.h"
 #include "openvslam/match/base.h"
+#ifndef DROPIN_SUBSET
+#include "openvslam/match/area.h"
 #include "openvslam/match/bow_tree.h"
 #include "openvslam/match/fuse.h"
+#endif
 #include "openvslam/match/projection.h"
 #include "openvslam/match/robust.h"
 
@@ -283,6 +285,7 @@ int ref_match_projection(const orc_camera* cam, const double* pose_cw_curr, cons
     return static_cast<int>(num);
 }
 
+#ifndef DROPIN_SUBSET
 // match/projection.cc:11-83
 int ref_match_landmarks(const orc_camera* cam, uint32_t n_lm, const uint8_t* lm_active, const double* lm_reproj, const float* lm_x_right,
                         const int32_t* lm_scale_level, const uint8_t* lm_desc, const uint8_t* lm_has_observation, uint32_t n_kp,
@@ -581,6 +584,7 @@ int ref_match_area(const orc_camera* cam, uint32_t n1, const orc_keypoint* kp1, 
     return static_cast<int>(num);
 }
 
+#endif  // DROPIN_SUBSET
 // data/landmark.cc:127-183: index (in the given order) of the representative descriptor. observations_ is a std::map keyed
 // by keyframe ADDRESS: the keyframes sit in one array, so address order = given order.
 uint32_t ref_landmark_descriptor(const uint8_t* descs, uint32_t n) {

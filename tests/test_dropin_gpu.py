@@ -52,3 +52,32 @@ def test_dropin_classes_match_oracle(oracle, tmp_path):
     if (dl == odl).all() and (dr == odr).all():
         assert np.array_equal(xr, oxr) and np.array_equal(dep, odep)
     assert (xr >= 0).sum() > 50
+
+
+def test_dropin_matcher_classes_match_reference(oracle):
+    """cpp/openvslam/match/robust_cuda.cc and projection_cuda.cc: the class methods robust::brute_force_match and
+    projection::match_current_and_last_frames, called on data::frame / data::keyframe / data::landmark objects exactly as the
+    reference's own classes are in oracle/_ref/libmatch_ref.so (same glue, same object construction), here running on the GPU.
+    Held against the port, which conftest.PinnedOracle holds against the reference build."""
+    import test_match_gpu as tm
+    from oracle import pymatchref, pyoracle
+    lib = os.path.join(ROOT, "cpp", "build", "libdropin_match.so")
+    if not os.path.exists(lib):
+        pytest.skip("cpp/build/libdropin_match.so not built (needs /root/reference at build time)")
+    d = pymatchref.MatchRef(lib)
+    for n1, n2, seed in ((1000, 1000, 1), (2000, 2000, 2), (37, 500, 4)):
+        d1, d2 = tm.frame_pair(n1, n2, seed)
+        rng = np.random.default_rng(seed + 100)
+        valid = (rng.random(n2) < 0.8).astype(np.uint8)
+        a1, a2 = rng.uniform(0, 360, n1).astype(np.float32), rng.uniform(0, 360, n2).astype(np.float32)
+        for chk in (False, True):
+            want, nw = oracle.match_bruteforce(d1, d2, valid, a1, a2, 0.8, chk)
+            got, ng = d.match_bruteforce(d1, d2, valid, a1, a2, 0.8, chk)
+            assert np.array_equal(got, want) and ng == nw
+    for seed, stereo, temps in ((1, False, False), (2, True, False), (3, True, True)):
+        args, Tc, Tl, has, outl, pos, ldesc, loct, lang, kp, desc, xr, taken, sf, obs = tm.projection_case(oracle, seed, stereo, temps)
+        for margin, chk in ((10.0, True), (20.0, False)):
+            cam = pyoracle.make_camera(**args)
+            want, nw = oracle.match_projection(cam, Tc, Tl, has, outl, pos, ldesc, loct, lang, kp, desc, xr, taken, sf, margin, chk, obs)
+            got, ng = d.match_projection(cam, Tc, Tl, has, outl, pos, ldesc, loct, lang, kp, desc, xr, taken, sf, margin, chk, obs)
+            assert np.array_equal(got, want) and ng == nw and nw > 50
