@@ -411,6 +411,12 @@ int lpslam_knn_merge_dev(const uint64_t* gathered_dev, uint32_t n_shards, uint32
  * (peer-mapped); the kernel reads the peers' blocks directly and merges. */
 int lpslam_knn_merge_peer_dev(const uint64_t* const* shard_keys_dev, uint32_t n_shards, uint32_t nq, uint64_t* merged_dev,
                               void* stream);
+/* the whole sharded query below the C ABI (BASELINE configs[4]): every rank of the NCCL communicator calls this with the same
+ * queries; per-shard top-2 on the rank's own shard, ncclAllGather of the (nq, 2) keys into gathered_dev[world][nq][2], merge
+ * into merged_dev[nq][2] (the same on every rank). nccl_comm is the caller's ncclComm_t; ncclAllGather is resolved at run time
+ * from the libnccl the process has loaded, so liblpslam_cuda links against no particular NCCL. Enqueues on `stream`. */
+int lpslam_knn_sharded_query_dev(lpslam_knn_db* db, void* nccl_comm, uint32_t world, const uint8_t* q_dev, uint32_t nq,
+                                 uint64_t* gathered_dev, uint64_t* merged_dev, void* stream);
 /* unpack merged keys on the device into the host-facing triplets */
 int lpslam_knn_unpack(const uint64_t* merged_dev, uint32_t nq, int64_t* best_idx, uint32_t* best_dist,
                       uint32_t* second_dist, void* stream);

@@ -9,6 +9,8 @@
 //   k_knn_reduce  two smallest keys over the chunk (or shard) partials of every query.
 #include "common.cuh"
 
+#include <dlfcn.h>
+
 #include <algorithm>
 
 struct lpslam_knn_db {
@@ -154,19 +156,30 @@ __global__ void k_knn_unpack(const uint64_t* __restrict__ keys, uint32_t nq, int
 }
 
 int ensure_scratch(lpslam_knn_db* db, uint32_t nq, uint32_t chunks) {
-    if (nq > db->nq_cap || chunks > db->chunks_cap) {
-        if (db->partial) cudaFree(db->partial);
-        if (db->q_dev) cudaFree(db->q_dev);
-        if (db->keys_dev) cudaFree(db->keys_dev);
-        db->partial = nullptr;
-        db->q_dev = nullptr;
-        db->keys_dev = nullptr;
-        db->nq_cap = std::max(nq, db->nq_cap);
-        db->chunks_cap = std::max(chunks, db->chunks_cap);
-        LPS_CUDA(cudaMalloc(&db->partial, (size_t)db->chunks_cap * db->nq_cap * 16));
-        LPS_CUDA(cudaMalloc(&db->q_dev, (size_t)db->nq_cap * 32));
-        LPS_CUDA(cudaMalloc(&db->keys_dev, (size_t)db->nq_cap * 16));
+    if (nq <= db->nq_cap && chunks <= db->chunks_cap) return LPSLAM_OK;
+    // allocate into temporaries and commit pointers and capacities together: a failed allocation must not leave enlarged
+    // capacities over null buffers (the next query would skip this function and scan into a null pointer)
+    const uint32_t nq_cap = std::max(nq, db->nq_cap), chunks_cap = std::max(chunks, db->chunks_cap);
+    uint64_t* partial = nullptr;
+    uint8_t* q_dev = nullptr;
+    uint64_t* keys_dev = nullptr;
+    cudaError_t e = cudaMalloc(&partial, (size_t)chunks_cap * nq_cap * 16);
+    if (e == cudaSuccess) e = cudaMalloc(&q_dev, (size_t)nq_cap * 32);
+    if (e == cudaSuccess) e = cudaMalloc(&keys_dev, (size_t)nq_cap * 16);
+    if (e != cudaSuccess) {
+        cudaFree(partial);
+        cudaFree(q_dev);
+        cudaFree(keys_dev);
+        return cuda_fail(e, "kNN scratch allocation", __FILE__, __LINE__);
     }
+    cudaFree(db->partial);
+    cudaFree(db->q_dev);
+    cudaFree(db->keys_dev);
+    db->partial = partial;
+    db->q_dev = q_dev;
+    db->keys_dev = keys_dev;
+    db->nq_cap = nq_cap;
+    db->chunks_cap = chunks_cap;
     return LPSLAM_OK;
 }
 
@@ -288,6 +301,43 @@ int lpslam_knn_merge_peer_dev(const uint64_t* const* shard_keys_dev, uint32_t n_
     k_knn_reduce<<<(nq + 255) / 256, 256, 0, (cudaStream_t)stream>>>(nullptr, ptrs, n_shards, nq, nq, merged_dev);
     LPS_CUDA(cudaGetLastError());
     return LPSLAM_OK;
+}
+
+// ---- sharded query with the exchange below the C ABI: per-shard top-2, ncclAllGather of the (nq, 2) keys, merge. NCCL is resolved at
+// run time (dlopen / dlsym) from the libnccl the process already has (e.g. the one torch loaded) or the system's, so that the
+// library carries no link-time dependency on one NCCL build and still loads on a machine without NCCL.
+namespace {
+typedef int (*NcclAllGatherFn)(const void*, void*, size_t, int /*ncclDataType_t*/, void* /*ncclComm_t*/, cudaStream_t);
+NcclAllGatherFn nccl_all_gather() {
+    static NcclAllGatherFn fn = [] {
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        return h ? reinterpret_cast<NcclAllGatherFn>(dlsym(h, "ncclAllGather")) : nullptr;
+    }();
+    return fn;
+}
+}  // namespace
+
+int lpslam_knn_sharded_query_dev(lpslam_knn_db* db, void* nccl_comm, uint32_t world, const uint8_t* q_dev, uint32_t nq,
+                                 uint64_t* gathered_dev, uint64_t* merged_dev, void* stream) {
+    LPS_ARG(db && nccl_comm && world >= 1 && (nq == 0 || (q_dev && gathered_dev && merged_dev)), "null argument");
+    if (nq == 0) return LPSLAM_OK;
+    NcclAllGatherFn all_gather = nccl_all_gather();
+    if (!all_gather) {
+        set_error("libnccl.so.2 (ncclAllGather) could not be loaded");
+        return LPSLAM_ERR_STATE;
+    }
+    // the rank's own keys go straight into its slot... ncclAllGather wants a separate send buffer unless it is that slot
+    uint64_t* mine = merged_dev;  // used as the send buffer, overwritten by the merge afterwards
+    int rc = lpslam_knn_query_dev(db, q_dev, nq, mine, stream);
+    if (rc) return rc;
+    const int nccl_rc = all_gather(mine, gathered_dev, (size_t)nq * 2, 5 /* ncclUint64 */, nccl_comm, (cudaStream_t)stream);
+    if (nccl_rc != 0) {
+        set_error("ncclAllGather failed with ncclResult_t " + std::to_string(nccl_rc));
+        return LPSLAM_ERR_CUDA;
+    }
+    return lpslam_knn_merge_dev(gathered_dev, world, nq, merged_dev, stream);
 }
 
 int lpslam_knn_unpack(const uint64_t* merged_dev, uint32_t nq, int64_t* best_idx, uint32_t* best_dist, uint32_t* second_dist, void* stream) {

@@ -17,6 +17,8 @@ register("lpslam_knn_query", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_v
 register("lpslam_knn_query_dev", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p])
 register("lpslam_knn_merge_dev", C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p])
 register("lpslam_knn_merge_peer_dev", C.c_int, [C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p])
+register("lpslam_knn_sharded_query_dev", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p])
 register("lpslam_knn_unpack", C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p])
 
 EMPTY_KEY = 0xFFFFFFFFFFFFFFFF
@@ -93,6 +95,8 @@ def sharded_query(db, q_dev, nq, stream_ptr=None):
     merged keys on every rank."""
     import torch
     import torch.distributed as dist
+    if stream_ptr is None:  # the scan, the all_gather and the merge must be ordered on ONE stream: torch's current one
+        stream_ptr = torch.cuda.current_stream(q_dev.device).cuda_stream
     keys = torch.empty((nq, 2), dtype=torch.int64, device=q_dev.device)
     db.query_dev(q_dev.data_ptr(), nq, keys.data_ptr(), stream_ptr)
     world = dist.get_world_size() if dist.is_initialized() else 1

@@ -51,3 +51,17 @@ def test_shards_merge_like_one_scan(oracle):
     assert np.array_equal(bi, obi) and np.array_equal(bd, obd) and np.array_equal(sd, osd)
     host = knn.merge_keys_host(keys.cpu().numpy().view(np.uint64))
     assert np.array_equal(host, merged.cpu().numpy().view(np.uint64))
+
+
+def test_sharded_query_below_the_c_abi_all_gpus():
+    """cpp/knn_nccl_test.cc: a C++ host (one thread per GPU, ncclCommInitAll) runs lpslam_knn_sharded_query_dev on every visible GPU
+    and lpslam_knn_merge_peer_dev across real peers; every rank's merged result is held against the planted neighbours. With one
+    GPU the communicator has one rank (the exchange degenerates, the code path is the same)."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cpp", "build", "knn_nccl_test")
+    if not os.path.exists(exe):
+        pytest.skip("cpp/build/knn_nccl_test not built")
+    r = subprocess.run([exe, "200000", "2000"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert " ok " in r.stdout
