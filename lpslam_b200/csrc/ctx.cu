@@ -1,6 +1,8 @@
 // Host side of the extractor context: parameter tables, level / cell / quadtree geometry, device arena, launch sequence.
 #include "ctx.h"
 
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX 3: ranges cost nothing unless a profiler injects itself
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -485,10 +487,17 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     const int L = (int)num_levels;
     const int B = (int)n_frames;
     int e = 0;
-    auto mark = [&]() {
-        if (timing) cudaEventRecord(ev[e++], stream);
+    // NVTX ranges around the six stages (what nsys / ncu --nvtx group by); the ranges bracket the ENQUEUE of a stage
+    static const char* const kStage[] = {"lpslam:pyramid", "lpslam:fast", "lpslam:quadtree", "lpslam:blur", "lpslam:describe"};
+    bool range_open = false;
+    auto mark = [&](int idx) {  // idx = stage that starts here (5 = end of the pipeline)
+        if (timing) cudaEventRecord(ev[idx], stream);
+        if (range_open) nvtxRangePop();
+        range_open = idx < 5;
+        if (range_open) nvtxRangePushA(kStage[idx]);
     };
-    mark();  // 0: start of pyramid
+    (void)e;
+    mark(0);  // start of pyramid
     uint32_t pad_mask = 1u;  // level 0 arrives without its apron; so do levels made by the exact-half / copy / wide-ratio paths
     for (int l = 1; l < L && !pyr_plan; ++l)
         if (!resize_writes_apron(lv[l - 1], lv[l])) pad_mask |= 1u << l;
@@ -531,7 +540,7 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     else {
         launch_pad_borders(lv_dev, lv, L, pad_mask, B, stream);
     }
-    mark();  // 1
+    mark(1);
     FastArgs fa;
     fa.lv = lv_dev;
     fa.cells = cells_dev;
@@ -569,10 +578,10 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     }
     else {
         launch_fast(fa, stream);
-        mark();  // 2
+        mark(2);
         launch_quadtree(tree, lv, stream);
     }
-    mark();  // 3
+    mark(3);
     if (fork)
         LPS_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
     else if (blur_plan) {
@@ -580,12 +589,12 @@ int lpslam_orb_ctx::run_pipeline(uint32_t n_frames, const uint8_t* mask_ptr, siz
     }
     else
         launch_blur(lv_dev, lv, L, B, stream);
-    mark();  // 4
+    mark(4);
     desc.batch = B;
     LPS_CUDA(cudaMemsetAsync(desc.overflow, 0, 4, stream));
     launch_offsets(desc, stream);
     launch_describe(desc, stream);
-    mark();  // 5
+    mark(5);
     LPS_CUDA(cudaGetLastError());
     last_batch = n_frames;
     has_result = true;

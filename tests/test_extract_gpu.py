@@ -121,3 +121,25 @@ def test_scale_tables_reference_cases(orb, oracle):
     o = oracle.extractor(max_kpts=1000, scale_factor=1.26, num_levels=10)
     for got, which in ((e.get_scale_factors(), 0), (e.get_inv_scale_factors(), 1), (e.get_level_sigma_sq(), 2), (e.get_inv_level_sigma_sq(), 3)):
         assert np.array_equal(np.asarray(got, np.float32), o.table(which)), which
+
+
+def test_repeatable_under_shared_memory_protocols(orb):
+    """compute-sanitizer is closed on this pool (profiles/r2_sanitizer.md). Stand-in for racecheck / initcheck on the kernels with
+    hand-rolled shared-memory protocols (k_fast_cells' corner list and kept bitmap, k_quadtree's bins and scatter, the claim tables of
+    the resolve kernels): 25 runs of the same batch on ONE context, a different image (uniform noise, so every scratch array holds
+    other data) extracted in between; every output byte must repeat."""
+    from lpslam_b200 import match
+    from lpslam_b200.synth import noise_image, synth_stereo_pair
+    e = orb.orb_extractor(max_num_keypts=1000, max_batch=4)
+    pairs = [synth_stereo_pair(360, 640, 900 + k) for k in range(2)]
+    other = [noise_image(360, 640, 5 + k) for k in range(4)]
+    first = None
+    for rep in range(25):
+        res = match.stereo_frames(e, [p[0] for p in pairs], [p[1] for p in pairs], 84.0, 0.12)
+        n_rows = sum(len(r["keypts_left"]) + len(r["keypts_right"]) for r in res)
+        m, cnt = match.match_consecutive_frames(e, n_rows, 4, 0.8)
+        sig = b"".join(r[k].tobytes() for r in res for k in sorted(r)) + m.tobytes() + cnt.tobytes()
+        if first is None:
+            first = sig
+        assert sig == first, f"run {rep} differs from run 0"
+        e.extract_batch(other)
