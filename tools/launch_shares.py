@@ -15,7 +15,7 @@ for r in rows:
     t[name] += float(r[14]) / 1e3
     n[name] += 1
 tot = sum(t.values())
-stage_of = {"k_resize_walk": "pyramid", "k_pad_borders": "blur", "k_gauss7": "blur", "k_fast_cells": "fast", "k_quadtree": "quadtree",
+stage_of = {"k_resize_walk": "pyramid", "k_pad_borders": "blur", "k_gauss7": "blur", "k_gauss7_tma": "blur", "k_copy2d": "pyramid", "k_fast_cells": "fast", "k_quadtree": "quadtree",
             "k_offsets": "describe", "k_describe": "describe", "k_stereo_prep": "describe", "k_stereo_rows": "describe",
             "k_stereo_match": "describe", "k_stereo_median": "describe"}
 st = collections.defaultdict(float)

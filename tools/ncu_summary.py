@@ -44,8 +44,9 @@ for rep in reps:
                          if "average_warps_issue_stalled" in k and k.endswith(".ratio") and v not in ("", "n/a")), reverse=True)[:3]
         rec["top stalls (warps per issue)"] = ", ".join(f"{n} {v:.2f}" for v, n in stalls)
         rows_out.append(rec)
-        if name not in traffic:  # first launch of each kernel
-            traffic[name] = int((rec["dram rd MB"] + rec["dram wr MB"]) * 1e6)
+        # DRAM bytes of ALL launches of the kernel in the captured step (the capture holds exactly one step: the seven pyramid
+        # launches add up), so that the figure describes the same thing as bench.py's algorithmic bytes per step
+        traffic[name] = traffic.get(name, 0) + int((rec["dram rd MB"] + rec["dram wr MB"]) * 1e6)
 cols = ["kernel", "grid", "block"] + [l for _, l in KEYS] + ["top stalls (warps per issue)"]
 with open(out_prefix + "_ncu_summary.md", "w") as f:
     f.write("ncu --set full --clock-control none, one step of 32 stereo pairs (64 frames of 1280x720), tools/profile_step.py\n\n")
@@ -55,5 +56,6 @@ with open(out_prefix + "_ncu_summary.md", "w") as f:
 tj = os.path.join(os.path.dirname(out_prefix), "traffic.json")
 old = json.load(open(tj)) if os.path.exists(tj) else {}
 old.update(traffic)
+old["_source"] = "dram__bytes_read.sum + dram__bytes_write.sum summed over every launch of the kernel in ONE step, " + os.path.basename(out_prefix) + "_ncu_summary.md"
 json.dump(old, open(tj, "w"), indent=1, sort_keys=True)
 print(open(out_prefix + "_ncu_summary.md").read())
