@@ -97,8 +97,7 @@ __device__ __forceinline__ void make_pair(const uint8_t* st, int i, uint32_t (&p
 }
 
 __global__ void __launch_bounds__(BT_WARPS * 32, LPS_BT_MINB * 4 / BT_WARPS) k_gauss7_tma(const __grid_constant__ BlurMaps maps, const LevelGeom* __restrict__ lvs,
-                                                                             const BlurUnit* __restrict__ units, int n_units, int batch,
-                                                                             uint32_t* __restrict__ sched, int mode) {
+                                                                             const BlurUnit* __restrict__ units, int n_units, int batch) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t s_full[BT_WARPS][BT_STAGES];
     // TMA destinations must be 128-byte aligned: the dynamic segment starts behind the static one, so align by hand
@@ -117,18 +116,13 @@ __global__ void __launch_bounds__(BT_WARPS * 32, LPS_BT_MINB * 4 / BT_WARPS) k_g
     const uint8_t* const lane_smem = warp_smem + half * BT_HALF_STRIDE + 16 + hl * SW;
     const uint32_t total_work = (uint32_t)n_units * (uint32_t)batch;
     uint32_t ph0 = 0, ph1 = 0;  // parity the next completion of stage 0 / 1 will have
-    // Warps are independent workers (no block-level barrier anywhere): every warp draws (unit, frame) items from a device
-    // counter, longest units first, so the tail of the grid is made of short items.
-    const bool persistent = (mode & 1) != 0, frame_major = (mode & 2) != 0;
-    uint32_t g_next = blockIdx.x * BT_WARPS + warp;
-    if (persistent && lane == 0) g_next = atomicAdd(&sched[0], 1u);
-    for (;;) {
-        const uint32_t g = __shfl_sync(0xffffffffu, g_next, 0);
-        if (g >= total_work) break;
-        g_next = total_work;
-        if (persistent && lane == 0) g_next = atomicAdd(&sched[0], 1u);  // drawn one item ahead
-        const BlurUnit u = units[frame_major ? g % (uint32_t)n_units : g / (uint32_t)batch];
-        const int frame = (int)(frame_major ? g / (uint32_t)n_units : g % (uint32_t)batch);
+    // Warps are independent workers (no block-level barrier anywhere): warp g of the grid owns item g = unit * batch + frame, longest
+    // units first, so the tail of the grid is made of short items. A persistent grid drawing items from a device counter measured
+    // slower (0.112 against 0.096 ms, profiles/r2_blur_tma.md), so the hardware block scheduler does the balancing.
+    const uint32_t g = blockIdx.x * BT_WARPS + warp;
+    if (g < total_work) {
+        const BlurUnit u = units[g / (uint32_t)batch];
+        const int frame = (int)(g % (uint32_t)batch);
         const int h = lvs[u.level].h, pitch = lvs[u.level].pitch;
         const int total = u.macros + 1;  // stage 0 is the 8-row run-in (rows y0 - 4 .. y0 + 3 sit in rows 2 .. 9 of the stage)
         const CUtensorMap* map = &maps.m[u.level];
@@ -199,14 +193,6 @@ __global__ void __launch_bounds__(BT_WARPS * 32, LPS_BT_MINB * 4 / BT_WARPS) k_g
             if (lane == 0 && it + BT_STAGES < total) issue(it + BT_STAGES);
         }
     }
-    // the last warp out re-arms the counters for the next launch (stream order makes that safe)
-    if (persistent && lane == 0) {
-        const uint32_t done = atomicAdd(&sched[1], 1u);
-        if (done == gridDim.x * BT_WARPS - 1) {
-            sched[0] = 0;
-            sched[1] = 0;
-        }
-    }
 }
 
 }  // namespace
@@ -220,21 +206,12 @@ struct BlurPlan {
         int n = 0;
     };
     std::map<int, Table> tables;  // by batch size
-    uint32_t* sched = nullptr;    // work counter + exit counter of the persistent grid (re-armed by the kernel itself)
-    int sm_count = 148;
 };
 
 BlurPlan* blur_plan_create(const LevelGeom* lv_host, int num_levels, int max_batch) {
     BlurPlan* p = new BlurPlan;
     p->num_levels = num_levels;
     p->lv.assign(lv_host, lv_host + num_levels);
-    if (cudaMalloc(&p->sched, 8) != cudaSuccess || cudaMemset(p->sched, 0, 8) != cudaSuccess) {
-        delete p;
-        return nullptr;
-    }
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&p->sm_count, cudaDevAttrMultiProcessorCount, dev);
     for (int l = 0; l < num_levels; ++l) {
         const LevelGeom& g = lv_host[l];
         const uint64_t dims[3] = {(uint64_t)g.pitch, (uint64_t)(g.h + 2 * kApron), (uint64_t)max_batch};
@@ -251,7 +228,6 @@ BlurPlan* blur_plan_create(const LevelGeom* lv_host, int num_levels, int max_bat
 void blur_plan_destroy(BlurPlan* p) {
     if (!p) return;
     for (auto& t : p->tables) cudaFree(t.second.dev);
-    cudaFree(p->sched);
     delete p;
 }
 
@@ -309,15 +285,9 @@ int launch_blur_tma(BlurPlan* p, const LevelGeom* lv_dev, int batch, cudaStream_
     }
     const BlurPlan::Table& t = it->second;
     if (t.n == 0) return LPSLAM_OK;
-    // persistent grid: as many blocks as can be resident (LPS_BT_MINB per SM), or fewer when there is less work
-    const long work = (long)t.n * batch;
-    static const int mode = [] {
-        const char* e = getenv("LPS_BLUR_MODE");
-        return e ? atoi(e) : 0;
-    }();
-    int blocks = (int)((work + BT_WARPS - 1) / BT_WARPS);
-    if (mode & 1) blocks = (int)std::min<long>(blocks, (long)p->sm_count * LPS_BT_MINB);
-    k_gauss7_tma<<<blocks, BT_WARPS * 32, BT_WARPS * BT_WARP_BYTES + 128, st>>>(p->maps, lv_dev, t.dev, t.n, batch, p->sched, mode);
+    const long work = (long)t.n * batch;  // one warp per (unit, frame)
+    const int blocks = (int)((work + BT_WARPS - 1) / BT_WARPS);
+    k_gauss7_tma<<<blocks, BT_WARPS * 32, BT_WARPS * BT_WARP_BYTES + 128, st>>>(p->maps, lv_dev, t.dev, t.n, batch);
     return LPSLAM_OK;
 }
 
