@@ -266,42 +266,36 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
         img_bytes += 2 * lv[l].frame_stride;
     }
     const uint32_t rows = nl + nr;
-    uint8_t* dev = nullptr;
-    size_t o_lv = align_up(img_bytes, 256), o_kp = o_lv + align_up(sizeof lv, 256);
-    size_t o_desc = o_kp + align_up(sizeof(lpslam_keypoint) * (size_t)rows, 256), o_off = o_desc + align_up(32 * (size_t)rows, 256);
-    size_t o_rec = o_off + 256, o_xr = o_rec + align_up(8 * (size_t)rows, 256), o_dep = o_xr + align_up(4 * (size_t)rows, 256);
-    size_t o_corr = o_dep + align_up(4 * (size_t)rows, 256), o_perm = o_corr + align_up(4 * (size_t)rows, 256);
-    size_t o_rows = o_perm + align_up(16 * (size_t)rows, 256), total = o_rows + align_up(4 * (size_t)(level_h[0] + 1), 256);
-    LPS_CUDA(scratch_alloc((void**)&dev, total));
-    cudaStream_t st = nullptr;
-    int rc = LPSLAM_OK;
-    auto fail = [&](cudaError_t e, const char* what) {
-        rc = cuda_fail(e, what, __FILE__, __LINE__);
-        return rc;
-    };
-#define TRY(call)                                \
-    do {                                         \
-        cudaError_t e__ = (call);                \
-        if (e__ != cudaSuccess) {                \
-            fail(e__, #call);                    \
-            goto done;                           \
-        }                                        \
-    } while (0)
-    {
-        const uint32_t h_off[3] = {0, nl, rows};
-        std::vector<int> corr(nl);
+    // one packed copy in (both pyramids, level table, keypoints, descriptors, offsets), one copy out (x_right, depth)
+    ArenaBump ar;
+    const size_t o_img = ar.take(img_bytes), o_lv = ar.take(sizeof lv), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)rows);
+    const size_t o_desc = ar.take(32 * (size_t)rows), o_off = ar.take(12), in_end = ar.off;
+    const size_t o_rec = ar.take(8 * (size_t)rows), o_corr = ar.take(4 * (size_t)rows), o_perm = ar.take(16 * (size_t)rows);
+    const size_t o_rows = ar.take(4 * (size_t)(level_h[0] + 1)), o_xr = ar.take(4 * (size_t)rows), o_dep = ar.take(4 * (size_t)rows);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
+    cudaError_t e = cudaSuccess;
+    do {
         for (uint32_t l = 0; l < num_levels; ++l) {
-            lv[l].img = dev + off[l];
-            TRY(cudaMemcpy2D(lv[l].img, lv[l].pitch, pyr_l[l], pitch_l[l], lv[l].w, lv[l].h, cudaMemcpyHostToDevice));
-            TRY(cudaMemcpy2D(lv[l].img + lv[l].frame_stride, lv[l].pitch, pyr_r[l], pitch_r[l], lv[l].w, lv[l].h,
-                             cudaMemcpyHostToDevice));
+            lv[l].img = dev + o_img + off[l];
+            for (int eye = 0; eye < 2; ++eye) {
+                const uint8_t* src = eye ? pyr_r[l] : pyr_l[l];
+                const size_t sp = eye ? pitch_r[l] : pitch_l[l];
+                uint8_t* dst = cs.host + o_img + off[l] + eye * lv[l].frame_stride;
+                if (sp == (size_t)lv[l].pitch) memcpy(dst, src, sp * (size_t)(lv[l].h - 1) + lv[l].w);
+                else
+                    for (int y = 0; y < lv[l].h; ++y) memcpy(dst + (size_t)y * lv[l].pitch, src + (size_t)y * sp, lv[l].w);
+            }
         }
-        TRY(cudaMemcpy(dev + o_lv, lv, sizeof lv, cudaMemcpyHostToDevice));
-        TRY(cudaMemcpy(dev + o_kp, kp_l, sizeof(lpslam_keypoint) * (size_t)nl, cudaMemcpyHostToDevice));
-        if (nr) TRY(cudaMemcpy(dev + o_kp + sizeof(lpslam_keypoint) * (size_t)nl, kp_r, sizeof(lpslam_keypoint) * (size_t)nr, cudaMemcpyHostToDevice));
-        TRY(cudaMemcpy(dev + o_desc, desc_l, 32 * (size_t)nl, cudaMemcpyHostToDevice));
-        if (nr) TRY(cudaMemcpy(dev + o_desc + 32 * (size_t)nl, desc_r, 32 * (size_t)nr, cudaMemcpyHostToDevice));
-        TRY(cudaMemcpy(dev + o_off, h_off, sizeof h_off, cudaMemcpyHostToDevice));
+        const uint32_t h_off[3] = {0, nl, rows};
+        cs.put(o_lv, lv, sizeof lv);
+        cs.put(o_kp, kp_l, sizeof(lpslam_keypoint) * (size_t)nl);
+        cs.put(o_kp + sizeof(lpslam_keypoint) * (size_t)nl, kp_r, sizeof(lpslam_keypoint) * (size_t)nr);
+        cs.put(o_desc, desc_l, 32 * (size_t)nl);
+        cs.put(o_desc + 32 * (size_t)nl, desc_r, 32 * (size_t)nr);
+        cs.put(o_off, h_off, sizeof h_off);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         StereoArgs a{};
         a.lv = (const LevelGeom*)(dev + o_lv);
         a.num_levels = (int)num_levels;
@@ -319,20 +313,19 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
         a.focal_x_baseline = focal_x_baseline;
         a.true_baseline = true_baseline;
         a.rows0 = level_h[0];
-        launch_stereo(a, st);
-        TRY(cudaGetLastError());
-        TRY(cudaMemcpy(stereo_x_right, a.x_right, 4 * (size_t)nl, cudaMemcpyDeviceToHost));
-        TRY(cudaMemcpy(depths, a.depth, 4 * (size_t)nl, cudaMemcpyDeviceToHost));
+        launch_stereo(a, cs.st);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cs.download(o_xr, ar.off)) != cudaSuccess) break;
+        memcpy(stereo_x_right, cs.out<float>(o_xr), 4 * (size_t)nl);
+        memcpy(depths, cs.out<float>(o_dep), 4 * (size_t)nl);
         if (n_matches) {
             uint32_t n = 0;
             for (uint32_t i = 0; i < nl; ++i) n += !(depths[i] == -1.0f && stereo_x_right[i] == -1.0f);
             *n_matches = n;
         }
-    }
-done:
-#undef TRY
-    scratch_free(dev);
-    return rc;
+    } while (false);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_stereo", __FILE__, __LINE__);
+    return LPSLAM_OK;
 }
 
 }  // extern "C"

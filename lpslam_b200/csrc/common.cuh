@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <cstring>
 #include <stdint.h>
 #include <stddef.h>
 
@@ -49,6 +50,42 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // per-thread, grow-only device scratch for the short entry points (scratch.cu); scratch_free must follow every scratch_alloc
 cudaError_t scratch_alloc(void** out, size_t bytes);
 void scratch_free(void* p);
+
+// One short call (a matcher, frame post-processing, ...) = one copy in, kernels, one copy out, all on a stream of the calling
+// thread: `dev` is a device arena and `host` a page-locked mirror of it with the same offsets. The caller packs its inputs with
+// put() / zero(), sends the input prefix with upload(), launches on `st`, and fetches the output suffix with download()
+// (which also waits for the stream). Both buffers and the stream belong to the host thread and only grow (scratch.cu).
+struct CallStage {
+    uint8_t* dev = nullptr;
+    uint8_t* host = nullptr;
+    cudaStream_t st = nullptr;
+    cudaError_t open(size_t bytes);
+    void put(size_t off, const void* src, size_t bytes) {
+        if (bytes) memcpy(host + off, src, bytes);
+    }
+    void zero(size_t off, size_t bytes) { memset(host + off, 0, bytes); }
+    cudaError_t upload(size_t begin, size_t end) {
+        return end > begin ? cudaMemcpyAsync(dev + begin, host + begin, end - begin, cudaMemcpyHostToDevice, st) : cudaSuccess;
+    }
+    cudaError_t download(size_t begin, size_t end) {
+        if (end > begin) {
+            const cudaError_t e = cudaMemcpyAsync(host + begin, dev + begin, end - begin, cudaMemcpyDeviceToHost, st);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaStreamSynchronize(st);
+    }
+    template <class T>
+    const T* out(size_t off) const {
+        return reinterpret_cast<const T*>(host + off);
+    }
+    CallStage() = default;
+    CallStage(const CallStage&) = delete;
+    CallStage& operator=(const CallStage&) = delete;
+    ~CallStage();
+
+private:
+    bool owned_ = false;  // true when the thread's buffers were busy (nested call) and this stage allocated its own
+};
 
 // bump planner for one-shot device scratch (offsets aligned to 256 bytes)
 struct ArenaBump {

@@ -12,6 +12,8 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 namespace lps {
 
@@ -69,7 +71,7 @@ struct ProjArgs {
     const uint32_t* cand_begin;
     const uint32_t* cand_end;
     const uint32_t* cand_items;
-    int claim_in_smem;  // k_lm_resolve: a per-keypoint claim table follows the bitmap in shared memory
+    int claim_in_smem;  // k_lm_resolve: versioned owner table + claim table in shared memory (else a bitmap, serial loop only)
     // fuse::replace_duplication's reprojection-error gate (fuse.cc:199-222)
     int chi_gate;
     const float* inv_sigma_sq;
@@ -85,6 +87,7 @@ struct ProjArgs {
     const uint8_t* kp_stereo;
     const float* row_scale;     // scale_factors_.at(keypt_1.octave)
     double E[9], epi[3];
+    int debug;  // LPS_RESOLVE_DEBUG: k_lm_resolve prints its round count
 };
 
 // robust.cc:323-341 check_epipolar_constraint: double arithmetic in source order, no contraction
@@ -271,17 +274,35 @@ __device__ Projected cell_window(const ProjArgs& a, Projected p) {
     return p;
 }
 
-// visits the candidates of landmark il in reference order; f(seq, idx, dist) for every candidate that passes the gates
+// Visits the candidates of row il that pass the gates: f(ord, idx, dist, octave). `ord` grows with the reference's visit order
+// (get_keypoints_in_cell: cells x-outer / y-inner, insertion order inside a cell; candidate lists front to back), so the smallest
+// (dist, ord) is the candidate the reference's strict '<' update keeps. part / parts splits the walk between lanes (cell t or list
+// entry t goes to lane t % parts); part = 0, parts = 1 is the reference's own sequential order.
+constexpr int ORD_BITS = 44;  // key = dist << ORD_BITS | ord
+
+// Which keypoints are no longer available to a row. versioned: p[c] = EMPTY (free), 0 (taken before the call) or row + 1 of the
+// row that took it - for row r a keypoint taken by a LATER row (the parallel rounds commit out of order) still counts as free,
+// as it was when the sequential loop reached r. Otherwise p is a plain bitmap (tables too large for shared memory: serial only).
+struct TakenSet {
+    uint32_t* p;
+    bool versioned;
+    __device__ __forceinline__ bool taken(uint32_t c, uint32_t row) const {
+        return versioned ? p[c] <= row : ((p[c >> 5] >> (c & 31)) & 1u) != 0;
+    }
+    __device__ __forceinline__ void take(uint32_t c, uint32_t row) const {
+        if (versioned) p[c] = row + 1;  // one writer per keypoint
+        else atomicOr(&p[c >> 5], 1u << (c & 31));
+    }
+};
 template <typename F>
-__device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const uint32_t* taken_bits, F f) {
+__device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const TakenSet* taken, int part, int parts, F f) {
     const uint4* dl = reinterpret_cast<const uint4*>(a.last_desc + (size_t)il * 32);
     const uint4 l0 = __ldg(dl), l1 = __ldg(dl + 1);
-    uint32_t seq = 0;
     if (a.mode == 3) {
-        for (uint32_t q = a.cand_begin[il]; q < a.cand_end[il]; ++q) {
+        const uint32_t q0 = a.cand_begin[il], q1 = a.cand_end[il];
+        for (uint32_t q = q0 + part; q < q1; q += parts) {
             const uint32_t i = a.cand_items[q];
-            ++seq;
-            if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
+            if (taken && taken->taken(i, il)) continue;
             const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
             const unsigned d = hamming256(l0, l1, __ldg(dc), __ldg(dc + 1));
             if (a.tri) {
@@ -293,49 +314,52 @@ __device__ void visit(const ProjArgs& a, uint32_t il, const Projected& p, const 
                 }
                 if (!epipolar_inlier(a.E, a.row_bearing + 3 * (size_t)il, b2, a.row_scale[il])) continue;
             }
-            f(seq, i, d, 0);
+            const uint64_t ord = q - q0;
+            f(a.last_wins ? ((1ull << ORD_BITS) - 1 - ord) : ord, i, d, 0);  // last_wins: an equal distance later in the list wins
         }
         return;
     }
     const bool check_level = (0 < p.min_level) || (0 <= p.max_level);
-    for (int cx = p.min_cx; cx <= p.max_cx; ++cx)
-        for (int cy = p.min_cy; cy <= p.max_cy; ++cy) {
-            const uint32_t c = cx * a.cam.grid_rows + cy;
-            for (uint32_t q = a.cell_start[c]; q < a.cell_start[c + 1]; ++q) {
-                const uint32_t i = a.cell_items[q];
-                const lpslam_keypoint k = a.kp[i];
-                if (check_level) {
-                    if (k.octave < p.min_level) continue;
-                    if (0 <= p.max_level && p.max_level < k.octave) continue;
-                }
-                if (!(fabsf(__fsub_rn(k.x, p.ref_x)) < p.m && fabsf(__fsub_rn(k.y, p.ref_y)) < p.m)) continue;
-                ++seq;
-                if (taken_bits && ((taken_bits[i >> 5] >> (i & 31)) & 1u)) continue;
-                if (a.mode == 0 || (a.mode == 1 && a.use_xr)) {
-                    const float xr = a.x_right[i];
-                    if (xr > 0) {
-                        if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
-                    }
-                }
-                if (a.chi_gate) {
-                    // double (reprojection) - float (keypoint) differences, float x_right difference, summed in the
-                    // reference's order; 3 degrees of freedom when the keypoint has a stereo match, 2 otherwise
-                    const double ex = __dsub_rn(a.lm_reproj[2 * (size_t)il], (double)k.x);
-                    const double ey = __dsub_rn(a.lm_reproj[2 * (size_t)il + 1], (double)k.y);
-                    double sq = __dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey));
-                    const float kxr = a.x_right[i];
-                    double chi = (double)5.99146f;
-                    if (kxr >= 0) {
-                        const float exr = __fsub_rn(a.lm_x_right[il], kxr);
-                        sq = __dadd_rn(sq, (double)__fmul_rn(exr, exr));
-                        chi = (double)7.81473f;
-                    }
-                    if (chi < __dmul_rn(sq, (double)a.inv_sigma_sq[k.octave])) continue;
-                }
-                const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
-                f(seq, i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)), k.octave);
+    const int ncy = p.max_cy - p.min_cy + 1, ncell = (p.max_cx - p.min_cx + 1) * ncy;
+    for (int t = part; t < ncell; t += parts) {
+        const int cx = p.min_cx + t / ncy, cy = p.min_cy + t % ncy;
+        const uint32_t c = cx * a.cam.grid_rows + cy;
+        const uint32_t q0 = a.cell_start[c], q1 = a.cell_start[c + 1];
+        for (uint32_t q = q0; q < q1; ++q) {
+            const uint32_t i = a.cell_items[q];
+            const lpslam_keypoint k = a.kp[i];
+            if (check_level) {
+                if (k.octave < p.min_level) continue;
+                if (0 <= p.max_level && p.max_level < k.octave) continue;
             }
+            if (!(fabsf(__fsub_rn(k.x, p.ref_x)) < p.m && fabsf(__fsub_rn(k.y, p.ref_y)) < p.m)) continue;
+            if (taken && taken->taken(i, il)) continue;
+            if (a.mode == 0 || (a.mode == 1 && a.use_xr)) {
+                const float xr = a.x_right[i];
+                if (xr > 0) {
+                    if (p.m < fabsf(__fsub_rn(p.x_right, xr))) continue;
+                }
+            }
+            if (a.chi_gate) {
+                // double (reprojection) - float (keypoint) differences, float x_right difference, summed in the
+                // reference's order; 3 degrees of freedom when the keypoint has a stereo match, 2 otherwise
+                const double ex = __dsub_rn(a.lm_reproj[2 * (size_t)il], (double)k.x);
+                const double ey = __dsub_rn(a.lm_reproj[2 * (size_t)il + 1], (double)k.y);
+                double sq = __dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey));
+                const float kxr = a.x_right[i];
+                double chi = (double)5.99146f;
+                if (kxr >= 0) {
+                    const float exr = __fsub_rn(a.lm_x_right[il], kxr);
+                    sq = __dadd_rn(sq, (double)__fmul_rn(exr, exr));
+                    chi = (double)7.81473f;
+                }
+                if (chi < __dmul_rn(sq, (double)a.inv_sigma_sq[k.octave])) continue;
+            }
+            const uint4* dc = reinterpret_cast<const uint4*>(a.desc + (size_t)i * 32);
+            // cells hold fewer than 2^20 keypoints (n_curr < 2^20) and a window fewer than 2^24 cells
+            f(((uint64_t)t << 20) | (q - q0), i, hamming256(l0, l1, __ldg(dc), __ldg(dc + 1)), k.octave);
         }
+    }
 }
 
 __device__ __forceinline__ void motion_flags(const ProjArgs& a, bool& forward, bool& backward) {
@@ -349,31 +373,58 @@ __device__ __forceinline__ void motion_flags(const ProjArgs& a, bool& forward, b
     backward = a.cam.is_monocular ? false : -z > a.cam.true_baseline;
 }
 
-__global__ void k_proj_topk(ProjArgs a) {
-    const uint32_t il = blockIdx.x * blockDim.x + threadIdx.x;
+constexpr uint64_t EMPTY64 = ~0ull;
+
+// One warp per row: the lanes split the row's cells (or candidate list), every lane keeps its 4 smallest (dist, ord) keys, four
+// rounds of "smallest head wins and pops" merge them. The stored key is dist << 20 | rank: the resolve kernels only compare the
+// kept four with each other and look at the distance.
+__global__ void __launch_bounds__(128) k_proj_topk(ProjArgs a) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t il = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (il >= a.n_last) return;
     bool fw, bw;
     motion_flags(a, fw, bw);
     const Projected p = project(a, il, fw, bw);
-    uint32_t key[K] = {EMPTY, EMPTY, EMPTY, EMPTY};
+    uint64_t key[K] = {EMPTY64, EMPTY64, EMPTY64, EMPTY64};
     int idx[K] = {-1, -1, -1, -1};
     if (p.ok) {
-        visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
-            const uint32_t kk = (d << 20) | (a.last_wins ? 0xFFFFFu - seq : seq);
+        visit(a, il, p, nullptr, lane, 32, [&](uint64_t ord, uint32_t i, unsigned d, int oct) {
+            const uint64_t kk = ((uint64_t)d << ORD_BITS) | ord;
             if (kk < key[3]) {
                 key[3] = kk;
                 idx[3] = (int)(i | ((uint32_t)(oct & 0x7F) << 24));  // octave rides along: the resolve loop never touches a.kp
 #pragma unroll
                 for (int q = 3; q > 0; --q)
                     if (key[q] < key[q - 1]) {
-                        const uint32_t tk = key[q]; key[q] = key[q - 1]; key[q - 1] = tk;
+                        const uint64_t tk = key[q]; key[q] = key[q - 1]; key[q - 1] = tk;
                         const int ti = idx[q]; idx[q] = idx[q - 1]; idx[q - 1] = ti;
                     }
             }
         });
     }
-    a.top_key[il] = make_uint4(key[0], key[1], key[2], key[3]);
-    a.top_idx[il] = make_int4(idx[0], idx[1], idx[2], idx[3]);
+    uint32_t okey[K];
+    int oidx[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        uint64_t m = key[0];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint64_t other = __shfl_xor_sync(0xFFFFFFFFu, m, o);
+            m = other < m ? other : m;
+        }
+        const bool win = m != EMPTY64 && key[0] == m;  // keys are unique: ord is
+        const uint32_t src = __ffs(__ballot_sync(0xFFFFFFFFu, win)) - 1;
+        oidx[r] = m == EMPTY64 ? -1 : __shfl_sync(0xFFFFFFFFu, idx[0], src & 31);
+        okey[r] = m == EMPTY64 ? EMPTY : (((uint32_t)(m >> ORD_BITS) << 20) | (uint32_t)r);
+        if (win) {
+            key[0] = key[1]; key[1] = key[2]; key[2] = key[3]; key[3] = EMPTY64;
+            idx[0] = idx[1]; idx[1] = idx[2]; idx[2] = idx[3]; idx[3] = -1;
+        }
+    }
+    if (lane == 0) {
+        a.top_key[il] = make_uint4(okey[0], okey[1], okey[2], okey[3]);
+        a.top_idx[il] = make_int4(oidx[0], oidx[1], oidx[2], oidx[3]);
+    }
 }
 
 // rows that do not compete for keypoints (match/fuse.cc): the first kept candidate is the answer
@@ -387,119 +438,233 @@ __global__ void k_rows_best(ProjArgs a) {
 }
 
 // Ordered resolve for the reprojection / candidate-list matchers (projection.cc:31-79, :145-190, :264-296,
-// bow_tree.cc:58-97). The reference loop is sequential because a matched keypoint is no longer available to later rows.
-// One warp replays it 32 rows at a time: every lane decides ITS row against the current "taken" bitmap (first and second
-// free entry of the row's four kept candidates, in (distance, visit order) = the strict '<' updates of the reference),
-// then the lanes are committed in row order up to the first lane whose candidates contain a keypoint that an earlier
-// lane of the batch just took; that lane and the ones behind it are decided again. Rows whose four kept candidates do
-// not settle the decision (too few free ones and the list was longer) are rescanned exactly by one lane.
-// A single warp running one row per iteration spent ~600 cycles per row on dependent shuffles and shared-memory reads;
-// the batch form needs a few hundred instructions per 32 rows when no conflict occurs.
-__global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
-    extern __shared__ uint32_t s_taken[];
-    const int lane = threadIdx.x;
-    const uint32_t words = (a.n_curr + 31) / 32;
-    for (uint32_t w = lane; w < words; w += 32) {
-        uint32_t bits = 0;
-        for (uint32_t b = 0; b < 32 && w * 32 + b < a.n_curr; ++b) bits |= (a.curr_taken[w * 32 + b] ? 1u : 0u) << b;
-        s_taken[w] = bits;
+// bow_tree.cc:58-97). The reference loop is sequential because a matched keypoint is no longer available to later rows:
+// row r takes the first free entry of its candidate list (in (distance, visit order) = the strict '<' updates of the
+// reference) if the threshold / ratio tests pass with the second free entry.
+//
+// Parallel rounds (one block of 1024 threads, rows dealt round-robin). A row can only ever TAKE a kept candidate whose
+// distance passes the threshold, so every unresolved row claims those (atomicMin of the row number on the keypoint). For row r a
+// free candidate is "own" when no earlier row claims it (it stays free until r's turn), "contested" otherwise (free or taken by
+// then). r is decided as soon as that cannot change the outcome: its first free candidate is own, and the second free one is
+// own too, or contested but the ratio test already passes with its distance (whatever replaces it is farther). All decided rows
+// of a round are committed together; rows that share a takeable candidate are thereby committed in row order. A row for which
+// some outcome of its contested candidates leaves the kept four insufficient (the list was longer) could reach for ANY keypoint
+// of its window: it blocks every later row until it is the first unresolved row, then it is rescanned exactly. Inputs where
+// everything wants the same keypoints degenerate to a row per round; after a few such rounds the rest goes to the serial loop.
+//
+// resolved rows: top_key[r].x = EMPTY, top_key[r].y = matched keypoint or EMPTY. The ordered event list is built at the end.
+struct RowDecision {
+    bool settled, accept;
+    int i1;
+};
+
+__device__ __forceinline__ RowDecision decide_row(const ProjArgs& a, uint32_t il, const uint32_t (&k)[K], const int (&raw)[K], const TakenSet& tk) {
+    uint32_t b1 = EMPTY, b2 = EMPTY;
+    int i1 = -1, i2 = -1, o1 = -1, o2 = -1;
+#pragma unroll
+    for (int q = 0; q < K; ++q) {
+        if (k[q] == EMPTY) continue;
+        const int ixq = raw[q] & 0x00FFFFFF;
+        if (tk.taken(ixq, il)) continue;
+        if (i1 < 0) {
+            b1 = k[q];
+            i1 = ixq;
+            o1 = raw[q] >> 24;
+        }
+        else if (i2 < 0) {
+            b2 = k[q];
+            i2 = ixq;
+            o2 = raw[q] >> 24;
+        }
     }
-    // optional claim table behind the bitmap (the launcher provides it while it fits: n_curr words)
-    uint32_t* s_claim = a.claim_in_smem ? s_taken + words : nullptr;
-    for (uint32_t i = lane; i < a.n_curr; i += 32) {
-        a.curr_match_last[i] = -1;
-        if (s_claim) s_claim[i] = 0xFFFFFFFFu;
+    RowDecision r;
+    r.settled = (a.use_ratio ? i2 >= 0 : i1 >= 0) || k[K - 1] == EMPTY;
+    if (!r.settled) {
+        // everything behind the kept four is at least as far as the fourth: that bound often settles the row
+        const unsigned lb = k[K - 1] >> 20;
+        if (i1 >= 0) {  // the second is missing
+            const unsigned bd = b1 >> 20;
+            if (a.hamm_thr < bd) r.settled = true;                                       // rejected whatever the second is
+            else if (!((float)bd > __fmul_rn(a.lowe_ratio, (float)lb))) r.settled = true;  // passes the ratio test for any second >= lb
+        }
+        else if (a.hamm_thr < lb) r.settled = true;  // no free candidate can be close enough
     }
-    __syncwarp();
-    bool fw = false, bw = false;
-    if (a.mode == 0) motion_flags(a, fw, bw);
-    const bool need_second = a.use_ratio != 0;
-    uint32_t num = 0;
-    for (uint32_t base = 0; base < a.n_last; base += 32) {
+    r.i1 = i1;
+    r.accept = i1 >= 0;
+    if (r.accept) {  // projection.cc:68-79 / :184-190 / :287-296, bow_tree.cc:80-97
+        const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
+        if (a.hamm_thr < best) r.accept = false;
+        else if (a.use_ratio) {
+            const bool same_level = a.mode == 3 || o1 == (i2 >= 0 ? o2 : -1);
+            if (same_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) r.accept = false;
+        }
+    }
+    return r;
+}
+
+// the exact decision of row il from its full candidate list in reference order (one thread)
+__device__ __noinline__ RowDecision rescan_row(const ProjArgs& a, uint32_t il, bool fw, bool bw, const TakenSet& tk) {
+    uint64_t b1 = EMPTY64, b2 = EMPTY64;
+    int i1 = -1, i2 = -1, o1 = -1, o2 = -1;
+    const Projected p = project(a, il, fw, bw);
+    visit(a, il, p, &tk, 0, 1, [&](uint64_t ord, uint32_t i, unsigned d, int oct) {
+        const uint64_t kk = ((uint64_t)d << ORD_BITS) | ord;
+        if (kk < b1) {
+            b2 = b1;
+            i2 = i1;
+            o2 = o1;
+            b1 = kk;
+            i1 = (int)i;
+            o1 = oct;
+        }
+        else if (kk < b2) {
+            b2 = kk;
+            i2 = (int)i;
+            o2 = oct;
+        }
+    });
+    RowDecision r;
+    r.settled = true;
+    r.i1 = i1;
+    r.accept = i1 >= 0;
+    if (r.accept) {
+        const unsigned best = (unsigned)(b1 >> ORD_BITS), second = i2 >= 0 ? (unsigned)(b2 >> ORD_BITS) : MAX_HAMMING_DIST;
+        if (a.hamm_thr < best) r.accept = false;
+        else if (a.use_ratio) {
+            const bool same_level = a.mode == 3 || o1 == (i2 >= 0 ? o2 : -1);
+            if (same_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) r.accept = false;
+        }
+    }
+    return r;
+}
+
+// records the decision of row il; set_taken = false defers the bitmap update (parallel rounds apply it after a barrier)
+__device__ __forceinline__ void commit_row(const ProjArgs& a, uint32_t il, const RowDecision& d, const TakenSet& tk, bool set_taken) {
+    uint32_t res = EMPTY;
+    if (d.accept) {
+        res = (uint32_t)d.i1;
+        a.curr_match_last[d.i1] = (int32_t)il;
+        const bool blocks = a.last_obs ? a.last_obs[il] != 0 : true;  // has_observation() of the row's landmark
+        if (blocks && set_taken) tk.take(d.i1, il);
+    }
+    uint32_t* key = reinterpret_cast<uint32_t*>(a.top_key) + 4 * (size_t)il;
+    key[1] = res;
+    key[0] = EMPTY;
+}
+
+// Row r in a parallel round. clear: the decision d is what the sequential loop will reach. may_rescan: some outcome of the
+// contested candidates leaves the kept four unable to settle the row.
+struct RowEval {
+    bool clear, may_rescan;
+    RowDecision d;
+};
+
+__device__ __forceinline__ RowEval eval_row(const ProjArgs& a, uint32_t r, const uint32_t (&k)[K], const int (&raw)[K],
+                                            const TakenSet& tk, const uint32_t* s_claim) {
+    RowEval e;
+    e.clear = false;
+    e.may_rescan = false;
+    e.d.settled = true;
+    e.d.accept = false;
+    e.d.i1 = -1;
+    const bool need2 = a.use_ratio != 0, is_long = k[K - 1] != EMPTY;
+    const unsigned lb = k[K - 1] >> 20;
+    auto single_ok = [&](unsigned bd) { return a.hamm_thr < bd || !((float)bd > __fmul_rn(a.lowe_ratio, (float)lb)); };
+    int qb = -1, qs = -1, n_own = 0;
+    bool b_own = false, s_own = false, contested_single_bad = false;
+    unsigned own_bd = 0;
+#pragma unroll
+    for (int q = 0; q < K; ++q) {
+        if (k[q] == EMPTY) continue;
+        const int c = raw[q] & 0x00FFFFFF;
+        if (tk.taken(c, r)) continue;
+        const bool own = s_claim[c] >= r;
+        if (own) {
+            if (n_own == 0) own_bd = k[q] >> 20;
+            ++n_own;
+        }
+        else if (!single_ok(k[q] >> 20)) contested_single_bad = true;
+        if (qb < 0) {
+            qb = q;
+            b_own = own;
+        }
+        else if (qs < 0) {
+            qs = q;
+            s_own = own;
+        }
+    }
+    if (is_long) {  // the outcomes with fewer free candidates than the decision needs
+        if (n_own == 0 && !(a.hamm_thr < lb)) e.may_rescan = true;  // nothing left free
+        if (need2 && n_own == 0 && contested_single_bad) e.may_rescan = true;
+        if (need2 && n_own == 1 && !single_ok(own_bd)) e.may_rescan = true;
+    }
+    if (qb < 0) {  // nothing free now: final when the list was complete or nothing behind it can be close enough
+        e.clear = !is_long || a.hamm_thr < lb;
+        return e;
+    }
+    if (!b_own) return e;
+    const unsigned bd = k[qb] >> 20;
+    e.d.i1 = raw[qb] & 0x00FFFFFF;
+    if (a.hamm_thr < bd) {  // rejected whatever the second is
+        e.clear = true;
+        return e;
+    }
+    if (!need2) {
+        e.clear = true;
+        e.d.accept = true;
+        return e;
+    }
+    if (qs >= 0) {
+        const unsigned sd = k[qs] >> 20;
+        if (s_own) {  // the second is exactly this one
+            const bool same_level = a.mode == 3 || (raw[qb] >> 24) == (raw[qs] >> 24);
+            e.clear = true;
+            e.d.accept = !(same_level && (float)bd > __fmul_rn(a.lowe_ratio, (float)sd));
+        }
+        else if (!((float)bd > __fmul_rn(a.lowe_ratio, (float)sd))) {  // passes for this second and for anything farther
+            e.clear = true;
+            e.d.accept = true;
+        }
+        return e;
+    }
+    if (!is_long) {  // no second at all: MAX_HAMMING_DIST, and a level of -1 that only candidate lists (mode 3) compare equal
+        e.clear = true;
+        e.d.accept = !(a.mode == 3 && (float)bd > __fmul_rn(a.lowe_ratio, (float)MAX_HAMMING_DIST));
+        return e;
+    }
+    if (!((float)bd > __fmul_rn(a.lowe_ratio, (float)lb))) {  // passes for any second behind the kept four
+        e.clear = true;
+        e.d.accept = true;
+    }
+    return e;  // otherwise: needs the exact list (may_rescan is set)
+}
+
+// Serial form, one warp: 32 unresolved rows are decided at a time against the current bitmap and committed in row order up to
+// the first lane whose candidates contain a keypoint that an earlier lane of the batch just took; that lane and the ones
+// behind it are decided again. A row whose four kept candidates do not settle the decision is rescanned by its lane when it
+// is the first pending row. s_claim (optional): lowest lane accepting a keypoint in the current round.
+__device__ void resolve_serial(const ProjArgs& a, const TakenSet& tk, uint32_t* s_claim, int lane, bool fw, bool bw, uint32_t first_row) {
+    for (uint32_t base = first_row; base < a.n_last; base += 32) {
         const uint32_t il = base + lane;
         const uint4 mk = il < a.n_last ? a.top_key[il] : make_uint4(EMPTY, EMPTY, EMPTY, EMPTY);
         const int4 mi = il < a.n_last ? a.top_idx[il] : make_int4(-1, -1, -1, -1);
-        const bool blocks = (a.last_obs && il < a.n_last) ? a.last_obs[il] != 0 : true;  // has_observation() of the row's landmark
         const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
         const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
-        uint32_t pending = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY && (mk.x >> 20) <= a.hamm_thr);
+        uint32_t pending = __ballot_sync(0xFFFFFFFFu, mk.x != EMPTY);
         while (pending) {
             const bool mine = (pending >> lane) & 1u;
-            // ---- decide this lane's row against the current bitmap ----
-            uint32_t b1 = EMPTY, b2 = EMPTY;
-            int i1 = -1, i2 = -1, o1 = -1, o2 = -1;
-            if (mine) {
-#pragma unroll
-                for (int q = 0; q < K; ++q) {
-                    if (k[q] == EMPTY) continue;
-                    const int ixq = raw[q] & 0x00FFFFFF;
-                    if ((s_taken[ixq >> 5] >> (ixq & 31)) & 1u) continue;
-                    if (i1 < 0) {
-                        b1 = k[q];
-                        i1 = ixq;
-                        o1 = raw[q] >> 24;
-                    }
-                    else if (i2 < 0) {
-                        b2 = k[q];
-                        i2 = ixq;
-                        o2 = raw[q] >> 24;
-                    }
-                }
-            }
-            bool settled = (need_second ? i2 >= 0 : i1 >= 0) || k[K - 1] == EMPTY;
-            if (mine && !settled) {
-                // everything behind the kept four is at least as far as the fourth: that bound often settles the row
-                const unsigned lb = k[K - 1] >> 20;
-                if (i1 >= 0) {  // the second is missing
-                    const unsigned bd = b1 >> 20;
-                    if (a.hamm_thr < bd) settled = true;                                     // rejected whatever the second is
-                    else if (!((float)bd > __fmul_rn(a.lowe_ratio, (float)lb))) settled = true;  // passes the ratio test for any second >= lb
-                }
-                else if (a.hamm_thr < lb) settled = true;  // no free candidate can be close enough
-            }
-            const bool rescan = mine && !settled;
+            RowDecision d = {true, false, -1};
+            if (mine) d = decide_row(a, il, k, raw, tk);
+            const bool rescan = mine && !d.settled;
             const int first = __ffs(pending) - 1;
-            if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first)) {
-                // the first pending row needs the exact list: its lane walks it in reference order, alone
-                if (lane == first) {
-                    b1 = b2 = EMPTY;
-                    i1 = i2 = o1 = o2 = -1;
-                    const Projected p = project(a, il, fw, bw);
-                    visit(a, il, p, s_taken, [&](uint32_t seq, uint32_t i, unsigned d, int oct) {
-                        const uint32_t kk = (d << 20) | (a.last_wins ? 0xFFFFFu - seq : seq);
-                        if (kk < b1) {
-                            b2 = b1;
-                            i2 = i1;
-                            o2 = o1;
-                            b1 = kk;
-                            i1 = (int)i;
-                            o1 = oct;
-                        }
-                        else if (kk < b2) {
-                            b2 = kk;
-                            i2 = (int)i;
-                            o2 = oct;
-                        }
-                    });
-                }
-            }
-            // ---- accept? (projection.cc:68-79 / :184-190 / :287-296, bow_tree.cc:80-97) ----
-            bool accept = mine && i1 >= 0 && (lane == first || !rescan);
-            if (accept) {
-                const unsigned best = b1 >> 20, second = i2 >= 0 ? (b2 >> 20) : MAX_HAMMING_DIST;
-                if (a.hamm_thr < best) accept = false;
-                else if (a.use_ratio) {
-                    const bool same_level = a.mode == 3 || o1 == (i2 >= 0 ? o2 : -1);
-                    if (same_level && (float)best > __fmul_rn(a.lowe_ratio, (float)second)) accept = false;
-                }
-            }
-            // ---- a lane waits when it is undecided, or when an earlier pending lane accepts one of its four candidates.
-            // Entries behind the ones a lane used cannot change its first / second free entry, so the kept four are all
-            // that matters for a lane that was decided from them; an undecided lane is only ever resolved as `first`.
+            if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first) && lane == first) d = rescan_row(a, il, fw, bw, tk);
+            const bool accept = mine && d.accept && (lane == first || !rescan);
+            // a lane waits when it is undecided, or when an earlier pending lane accepts one of its four candidates. Entries
+            // behind the ones a lane used cannot change its first / second free entry, so the kept four are all that matters
+            // for a lane that was decided from them; an undecided lane is only ever resolved as `first`.
             bool wait = mine && rescan && lane != first;
             if (s_claim) {
-                // claim table in shared memory: the lowest lane that accepts a keypoint in this round
-                if (mine && accept) atomicMin(&s_claim[i1], (uint32_t)lane);
+                if (accept) atomicMin(&s_claim[d.i1], (uint32_t)lane);
                 __syncwarp();
                 if (mine) {
 #pragma unroll
@@ -507,13 +672,13 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
                         if (k[q] != EMPTY && s_claim[raw[q] & 0x00FFFFFF] < (uint32_t)lane) wait = true;
                 }
                 __syncwarp();
-                if (mine && accept) s_claim[i1] = 0xFFFFFFFFu;
+                if (accept) s_claim[d.i1] = EMPTY;
             }
             else {
                 for (uint32_t mm = pending; mm; mm &= mm - 1) {
                     const int M = __ffs(mm) - 1;
                     const int accM = __shfl_sync(0xFFFFFFFFu, (int)accept, M);
-                    const int iM = __shfl_sync(0xFFFFFFFFu, i1, M);
+                    const int iM = __shfl_sync(0xFFFFFFFFu, d.i1, M);
                     if (mine && lane > M && accM) {
 #pragma unroll
                         for (int q = 0; q < K; ++q)
@@ -523,19 +688,188 @@ __global__ void __launch_bounds__(32) k_lm_resolve(ProjArgs a) {
             }
             const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, wait) & pending;
             const uint32_t commit = waiting ? (pending & ((1u << (__ffs(waiting) - 1)) - 1u)) : pending;  // rows before the first waiter
-            const bool go = (commit >> lane) & 1u;
-            const uint32_t acc_mask = __ballot_sync(0xFFFFFFFFu, go && accept);
-            if (go && accept) {
-                a.curr_match_last[i1] = (int32_t)il;
-                if (blocks) atomicOr(&s_taken[i1 >> 5], 1u << (i1 & 31));
-                if (a.events) a.events[num + __popc(acc_mask & ((1u << lane) - 1u))] = make_int2((int)il, i1);
+            if ((commit >> lane) & 1u) {
+                d.accept = accept;
+                commit_row(a, il, d, tk, true);
             }
-            num += __popc(acc_mask);
             pending &= ~commit;
             __syncwarp();
         }
     }
-    if (lane == 0) *a.n_events = num;
+}
+
+constexpr int RESOLVE_THREADS = 1024;
+
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
+    extern __shared__ uint32_t s_mem[];
+    __shared__ uint32_t s_barrier, s_minrow, s_warp_tot[RESOLVE_THREADS / 32], s_done;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // versioned owner table + claim table (n_curr words each) while they fit, else a bitmap (serial loop only)
+    const TakenSet tk = {s_mem, a.claim_in_smem != 0};
+    uint32_t* s_claim = tk.versioned ? s_mem + a.n_curr : nullptr;
+    if (tk.versioned) {
+        for (uint32_t i = tid; i < a.n_curr; i += RESOLVE_THREADS) {
+            s_mem[i] = a.curr_taken[i] ? 0u : EMPTY;
+            s_claim[i] = EMPTY;
+        }
+    }
+    else {
+        const uint32_t words = (a.n_curr + 31) / 32;
+        for (uint32_t w = tid; w < words; w += RESOLVE_THREADS) {
+            uint32_t bits = 0;
+            for (uint32_t b = 0; b < 32 && w * 32 + b < a.n_curr; ++b) bits |= (a.curr_taken[w * 32 + b] ? 1u : 0u) << b;
+            s_mem[w] = bits;
+        }
+    }
+    for (uint32_t i = tid; i < a.n_curr; i += RESOLVE_THREADS) a.curr_match_last[i] = -1;
+    bool fw = false, bw = false;
+    if (a.mode == 0) motion_flags(a, fw, bw);
+    // rows that can never match (no candidate, or the closest one beyond the threshold) are resolved here
+    for (uint32_t r = tid; r < a.n_last; r += RESOLVE_THREADS) {
+        const uint32_t k0 = a.top_key[r].x;
+        if (k0 == EMPTY || (k0 >> 20) > a.hamm_thr) {
+            reinterpret_cast<uint32_t*>(a.top_key)[4 * (size_t)r + 1] = EMPTY;
+            reinterpret_cast<uint32_t*>(a.top_key)[4 * (size_t)r] = EMPTY;
+        }
+    }
+    if (tid == 0) {
+        s_barrier = EMPTY;
+        s_minrow = EMPTY;
+        s_done = 0;
+    }
+    __syncthreads();
+
+    const bool parallel = s_claim != nullptr && a.n_last <= 32u * RESOLVE_THREADS;
+    if (parallel) {
+        uint32_t todo = 0;  // bit j: row tid + j * RESOLVE_THREADS is unresolved
+        for (uint32_t j = 0; tid + j * RESOLVE_THREADS < a.n_last; ++j)
+            if (a.top_key[tid + j * RESOLVE_THREADS].x != EMPTY) todo |= 1u << j;
+        int idle_rounds = 0, rounds = 0;
+        for (;;) {
+            const int active = __syncthreads_count(todo != 0);  // threads that still own an unresolved row
+            if (a.debug && tid == 0) printf("lm_resolve round %d: active threads %d\n", rounds, active);
+            ++rounds;
+            if (active == 0) break;
+            // A: claims on the candidates a row could take
+            if (todo) atomicMin(&s_minrow, (uint32_t)tid + (uint32_t)(__ffs(todo) - 1) * RESOLVE_THREADS);
+            for (uint32_t m = todo; m; m &= m - 1) {
+                const uint32_t r = tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS;
+                const uint4 mk = a.top_key[r];
+                const int4 mi = a.top_idx[r];
+                const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
+                const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
+#pragma unroll
+                for (int q = 0; q < K; ++q) {
+                    if (k[q] == EMPTY || (k[q] >> 20) > a.hamm_thr) continue;
+                    const int c = raw[q] & 0x00FFFFFF;
+                    if (!tk.taken(c, r)) atomicMin(&s_claim[c], r);
+                }
+            }
+            __syncthreads();
+            // B: the first row that may have to look beyond its kept four
+            for (uint32_t m = todo; m; m &= m - 1) {
+                const uint32_t r = tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS;
+                const uint4 mk = a.top_key[r];
+                const int4 mi = a.top_idx[r];
+                const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
+                const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
+                if (eval_row(a, r, k, raw, tk, s_claim).may_rescan) {
+                    atomicMin(&s_barrier, r);
+                    break;  // later rows of this thread are behind it
+                }
+            }
+            __syncthreads();
+            // C: decide against the bitmap of the round's start (updates wait for the barrier), record
+            const uint32_t barrier = s_barrier, minrow = s_minrow;
+            uint32_t done = 0;
+            for (uint32_t m = todo; m; m &= m - 1) {
+                const int j = __ffs(m) - 1;
+                const uint32_t r = tid + (uint32_t)j * RESOLVE_THREADS;
+                if (r > barrier) break;
+                const uint4 mk = a.top_key[r];
+                const int4 mi = a.top_idx[r];
+                const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
+                const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
+                RowEval e = eval_row(a, r, k, raw, tk, s_claim);
+                if (!e.clear) {
+                    if (r != minrow) continue;
+                    e.d = rescan_row(a, r, fw, bw, tk);  // every earlier row is resolved: the exact list decides
+                }
+                commit_row(a, r, e.d, tk, false);
+                done |= 1u << j;
+            }
+            if (done) atomicAdd(&s_done, (uint32_t)__popc(done));
+            __syncthreads();
+            // D: bitmap updates of the committed rows, claims withdrawn, re-arm
+            for (uint32_t m = done; m; m &= m - 1) {
+                const uint32_t r = tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS;
+                const uint32_t res = reinterpret_cast<const uint32_t*>(a.top_key)[4 * (size_t)r + 1];
+                if (res != EMPTY && (a.last_obs ? a.last_obs[r] != 0 : true)) tk.take(res, r);
+            }
+            for (uint32_t m = todo; m; m &= m - 1) {
+                const int4 mi = a.top_idx[tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS];
+                if (mi.x >= 0) s_claim[mi.x & 0x00FFFFFF] = EMPTY;
+                if (mi.y >= 0) s_claim[mi.y & 0x00FFFFFF] = EMPTY;
+                if (mi.z >= 0) s_claim[mi.z & 0x00FFFFFF] = EMPTY;
+                if (mi.w >= 0) s_claim[mi.w & 0x00FFFFFF] = EMPTY;
+            }
+            todo &= ~done;
+            const uint32_t n_done = s_done;
+            __syncthreads();
+            if (tid == 0) {
+                s_barrier = EMPTY;
+                s_minrow = EMPTY;
+                s_done = 0;
+            }
+            // contended (hundreds of rows left, a handful per round): the serial loop commits up to 32 rows per step without block barriers
+            idle_rounds = (n_done < 8 && active >= 64) ? idle_rounds + 1 : 0;
+            if (idle_rounds >= 4) break;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) s_minrow = EMPTY;
+    __syncthreads();
+    for (uint32_t r = tid; r < a.n_last; r += RESOLVE_THREADS)
+        if (a.top_key[r].x != EMPTY) {
+            atomicMin(&s_minrow, r);
+            break;
+        }
+    __syncthreads();
+    // whatever is left (everything when the claim table did not fit), from the first unresolved row on
+    if (warp == 0 && s_minrow != EMPTY) resolve_serial(a, tk, s_claim, lane, fw, bw, s_minrow & ~31u);
+    __syncthreads();
+
+    // ordered event list and count: rows in order, 1024 at a time
+    uint32_t num = 0;
+    for (uint32_t base = 0; base < a.n_last; base += RESOLVE_THREADS) {
+        const uint32_t r = base + tid;
+        const int res = r < a.n_last ? (int)reinterpret_cast<const uint32_t*>(a.top_key)[4 * (size_t)r + 1] : -1;
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, res >= 0);
+        if (lane == 0) s_warp_tot[warp] = __popc(bal);
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+        for (int w = 0; w < RESOLVE_THREADS / 32; ++w) {
+            const uint32_t t = s_warp_tot[w];
+            before += w < warp ? t : 0;
+            total += t;
+        }
+        if (res >= 0 && a.events) a.events[num + before + __popc(bal & ((1u << lane) - 1u))] = make_int2((int)r, res);
+        num += total;
+        __syncthreads();
+    }
+    if (tid == 0) *a.n_events = num;
+}
+
+constexpr uint32_t kResolveTableMax = 25000;  // 2 x 4 B per keypoint of shared memory
+
+cudaError_t launch_lm_resolve(const ProjArgs& a, uint32_t n_kp, cudaStream_t st) {
+    const size_t smem = a.claim_in_smem ? 8 * (size_t)n_kp : ((n_kp + 31) / 32) * 4;
+    if (smem > 48 * 1024) {
+        const cudaError_t e = cudaFuncSetAttribute(k_lm_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    k_lm_resolve<<<1, RESOLVE_THREADS, smem, st>>>(a);
+    return cudaGetLastError();
 }
 
 // ---- frame post-processing that follows extraction (data/frame.cc:37-51,75-92), perspective model --------------------
@@ -658,21 +992,24 @@ __global__ void __launch_bounds__(32) k_area_resolve(ProjArgs a) {
             if (__shfl_sync(0xFFFFFFFFu, (int)rescan, first)) {
                 // the kept four do not decide best and second: exact rescan in reference order by the row's lane
                 if (lane == first) {
-                    b1 = b2 = EMPTY;
+                    uint64_t w1 = EMPTY64, w2 = EMPTY64;
                     i1 = -1;
                     const Projected p = project(a, il, false, false);
-                    visit(a, il, p, nullptr, [&](uint32_t seq, uint32_t i, unsigned d, int) {
+                    visit(a, il, p, nullptr, 0, 1, [&](uint64_t ord, uint32_t i, unsigned d, int) {
                         if ((s_state[i] >> 20) <= d) return;
-                        const uint32_t kk = (d << 20) | seq;
-                        if (kk < b1) {
-                            b2 = b1;
-                            b1 = kk;
+                        const uint64_t kk = ((uint64_t)d << ORD_BITS) | ord;
+                        if (kk < w1) {
+                            w2 = w1;
+                            w1 = kk;
                             i1 = (int)i;
                         }
-                        else if (kk < b2) {
-                            b2 = kk;
+                        else if (kk < w2) {
+                            w2 = kk;
                         }
                     });
+                    // only the distances are looked at from here on
+                    b1 = w1 == EMPTY64 ? EMPTY : (uint32_t)(w1 >> ORD_BITS) << 20;
+                    b2 = w2 == EMPTY64 ? EMPTY : (uint32_t)(w2 >> ORD_BITS) << 20;
                 }
             }
             bool accept = mine && i1 >= 0 && (lane == first || !rescan);
@@ -746,35 +1083,36 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
         LPS_ARG(last_octave[i] >= 0 && (uint32_t)last_octave[i] < cam->num_scale_levels, "last-frame octave out of range");
 
     const uint32_t ncell = cam->grid_cols * cam->grid_rows;
-    ArenaBump ar;
+    ArenaBump ar;  // inputs | zeroed counters | work | outputs
     const size_t o_has = ar.take(n_last), o_out = ar.take(n_last), o_pos = ar.take(24 * (size_t)n_last), o_ld = ar.take(32 * (size_t)n_last);
     const size_t o_oct = ar.take(4 * (size_t)n_last), o_obs = ar.take(n_last), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_curr);
     const size_t o_desc = ar.take(32 * (size_t)n_curr), o_xr = ar.take(4 * (size_t)n_curr), o_tk = ar.take(n_curr);
-    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_cs = ar.take(4 * (size_t)(ncell + 1));
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_curr), o_tkey = ar.take(16 * (size_t)n_last);
-    const size_t o_tidx = ar.take(16 * (size_t)n_last), o_m = ar.take(4 * (size_t)n_curr), o_ev = ar.take(8 * (size_t)n_last);
-    const size_t o_ne = ar.take(4);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    const size_t o_tidx = ar.take(16 * (size_t)n_last), o_m = ar.take(4 * (size_t)n_curr), o_ne = ar.take(4);
+    const size_t o_ev = ar.take(8 * (size_t)n_last);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     int rc = LPSLAM_OK;
     cudaError_t e = cudaSuccess;
     std::vector<int2> events;
     uint32_t n_ev = 0;
     do {
-#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
-        UP(o_has, last_has_lm, n_last);
-        UP(o_out, last_outlier, n_last);
-        UP(o_pos, last_pos_w, 24 * (size_t)n_last);
-        UP(o_ld, last_lm_desc, 32 * (size_t)n_last);
-        UP(o_oct, last_octave, 4 * (size_t)n_last);
-        if (last_lm_has_observation) UP(o_obs, last_lm_has_observation, n_last);
-        UP(o_kp, curr_undist_kp, sizeof(lpslam_keypoint) * (size_t)n_curr);
-        UP(o_desc, curr_desc, 32 * (size_t)n_curr);
-        UP(o_xr, curr_x_right, 4 * (size_t)n_curr);
-        UP(o_tk, curr_has_observed_lm, n_curr);
-        UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
-#undef UP
-        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        cs.put(o_has, last_has_lm, n_last);
+        cs.put(o_out, last_outlier, n_last);
+        cs.put(o_pos, last_pos_w, 24 * (size_t)n_last);
+        cs.put(o_ld, last_lm_desc, 32 * (size_t)n_last);
+        cs.put(o_oct, last_octave, 4 * (size_t)n_last);
+        if (last_lm_has_observation) cs.put(o_obs, last_lm_has_observation, n_last);
+        cs.put(o_kp, curr_undist_kp, sizeof(lpslam_keypoint) * (size_t)n_curr);
+        cs.put(o_desc, curr_desc, 32 * (size_t)n_curr);
+        cs.put(o_xr, curr_x_right, 4 * (size_t)n_curr);
+        cs.put(o_tk, curr_has_observed_lm, n_curr);
+        cs.put(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+        cs.zero(o_cc, 4 * (size_t)ncell);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.cam = *cam;
         for (int i = 0; i < 16; ++i) {
@@ -804,25 +1142,24 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
         a.curr_match_last = (int32_t*)(dev + o_m);
         a.events = (int2*)(dev + o_ev);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_grid_count<<<(n_curr + 255) / 256, 256>>>(a);
-        k_grid_scan<<<1, 1024>>>(a);
-        k_grid_fill<<<(n_curr + 255) / 256, 256>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
-        k_proj_topk<<<(n_last + 127) / 128, 128>>>(a);
+        k_grid_count<<<(n_curr + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
+        k_grid_fill<<<(n_curr + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        k_proj_topk<<<(n_last + 3) / 4, 128, 0, cs.st>>>(a);
         a.hamm_thr = HAMMING_DIST_THR_HIGH;
         a.use_ratio = 0;
-        a.claim_in_smem = n_curr <= 10000;
-        k_lm_resolve<<<1, 32, ((n_curr + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_curr : 0)>>>(a);
+        a.claim_in_smem = n_curr <= kResolveTableMax;
+        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
+        if ((e = launch_lm_resolve(a, n_curr, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(curr_match_last, dev + o_m, 4 * (size_t)n_curr, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if (check_orientation && n_ev) {
-            events.resize(n_ev);
-            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        }
+        // matches + event count, and the event list (at most one event per row) only when the orientation check wants it
+        if ((e = cs.download(o_m, check_orientation ? ar.off : o_ev)) != cudaSuccess) break;
+        memcpy(curr_match_last, cs.out<int32_t>(o_m), 4 * (size_t)n_curr);
+        n_ev = *cs.out<uint32_t>(o_ne);
+        if (check_orientation) events.assign(cs.out<int2>(o_ev), cs.out<int2>(o_ev) + n_ev);
     } while (false);
     if (e != cudaSuccess) rc = cuda_fail(e, "lpslam_match_projection", __FILE__, __LINE__);
-    scratch_free(dev);
     if (rc) return rc;
     *n_matches = n_ev;
     if (check_orientation) {
@@ -865,33 +1202,34 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
                 "landmark scale level out of range");
 
     const uint32_t ncell = cam->grid_cols * cam->grid_rows;
-    ArenaBump ar;
+    ArenaBump ar;  // inputs | zeroed counters | work | outputs
     const size_t o_act = ar.take(n_lm), o_rp = ar.take(16 * (size_t)n_lm), o_lxr = ar.take(4 * (size_t)n_lm), o_lvl = ar.take(4 * (size_t)n_lm);
     const size_t o_ld = ar.take(32 * (size_t)n_lm), o_obs = ar.take(n_lm), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_kp);
     const size_t o_desc = ar.take(32 * (size_t)n_kp), o_xr = ar.take(4 * (size_t)n_kp), o_tk = ar.take(n_kp);
-    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_cs = ar.take(4 * (size_t)(ncell + 1));
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
     const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_m = ar.take(4 * (size_t)n_kp), o_ne = ar.take(4), o_ev = ar.take(8 * (size_t)n_lm);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
     std::vector<int2> events;
     do {
-#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
-        UP(o_act, lm_active, n_lm);
-        UP(o_rp, lm_reproj, 16 * (size_t)n_lm);
-        UP(o_lxr, lm_x_right, 4 * (size_t)n_lm);
-        UP(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
-        UP(o_ld, lm_desc, 32 * (size_t)n_lm);
-        if (lm_has_observation) UP(o_obs, lm_has_observation, n_lm);
-        UP(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
-        UP(o_desc, kp_desc, 32 * (size_t)n_kp);
-        UP(o_xr, kp_x_right, 4 * (size_t)n_kp);
-        UP(o_tk, kp_has_observed_lm, n_kp);
-        UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
-#undef UP
-        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        cs.put(o_act, lm_active, n_lm);
+        cs.put(o_rp, lm_reproj, 16 * (size_t)n_lm);
+        cs.put(o_lxr, lm_x_right, 4 * (size_t)n_lm);
+        cs.put(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
+        cs.put(o_ld, lm_desc, 32 * (size_t)n_lm);
+        if (lm_has_observation) cs.put(o_obs, lm_has_observation, n_lm);
+        cs.put(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
+        cs.put(o_desc, kp_desc, 32 * (size_t)n_kp);
+        cs.put(o_xr, kp_x_right, 4 * (size_t)n_kp);
+        cs.put(o_tk, kp_has_observed_lm, n_kp);
+        cs.put(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+        cs.zero(o_cc, 4 * (size_t)ncell);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.cam = *cam;
         a.mode = 1;
@@ -924,22 +1262,20 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
         a.top_idx = (int4*)(dev + o_tidx);
         a.curr_match_last = (int32_t*)(dev + o_m);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_grid_count<<<(n_kp + 255) / 256, 256>>>(a);
-        k_grid_scan<<<1, 1024>>>(a);
-        k_grid_fill<<<(n_kp + 255) / 256, 256>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
-        k_proj_topk<<<(n_lm + 127) / 128, 128>>>(a);
-        a.claim_in_smem = n_kp <= 10000;
-        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_kp : 0)>>>(a);
+        k_grid_count<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
+        k_grid_fill<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        k_proj_topk<<<(n_lm + 3) / 4, 128, 0, cs.st>>>(a);
+        a.claim_in_smem = n_kp <= kResolveTableMax;
+        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
+        if ((e = launch_lm_resolve(a, n_kp, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(kp_match_lm, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if (lm_angle && n_ev) {
-            events.resize(n_ev);
-            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        }
+        if ((e = cs.download(o_m, lm_angle ? ar.off : o_ev)) != cudaSuccess) break;
+        memcpy(kp_match_lm, cs.out<int32_t>(o_m), 4 * (size_t)n_kp);
+        n_ev = *cs.out<uint32_t>(o_ne);
+        if (lm_angle) events.assign(cs.out<int2>(o_ev), cs.out<int2>(o_ev) + n_ev);
     } while (false);
-    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_reprojected", __FILE__, __LINE__);
     *n_matches = n_ev;
     if (lm_angle) {  // angle_checker over (row angle - keypoint angle, keypoint), projection.cc:297-311
@@ -977,21 +1313,24 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
     *n_in_grid = 0;
     for (uint32_t c = 0; c <= ncell; ++c) cell_start[c] = 0;
     if (n == 0) return LPSLAM_OK;  // perspective.cc:100-103: empty input is passed through
-    ArenaBump ar;
-    const size_t o_in = ar.take(sizeof(lpslam_keypoint) * (size_t)n), o_out = ar.take(sizeof(lpslam_keypoint) * (size_t)n);
-    const size_t o_b = ar.take(24 * (size_t)n), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
-    const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    ArenaBump ar;  // input | zeroed counters | work | outputs
+    const size_t o_in = ar.take(sizeof(lpslam_keypoint) * (size_t)n), o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_cf = ar.take(4 * (size_t)ncell);
+    const size_t o_out = ar.take(sizeof(lpslam_keypoint) * (size_t)n), o_b = ar.take(24 * (size_t)n);
+    const size_t o_cs = ar.take(4 * (size_t)(ncell + 1)), o_ci = ar.take(4 * (size_t)n);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     cudaError_t e = cudaSuccess;
     do {
-        if ((e = cudaMemcpy(dev + o_in, keypts, sizeof(lpslam_keypoint) * (size_t)n, cudaMemcpyHostToDevice)) != cudaSuccess) break;
-        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        cs.put(o_in, keypts, sizeof(lpslam_keypoint) * (size_t)n);
+        cs.zero(o_cc, 4 * (size_t)ncell);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         lpslam_perspective mu = *model;  // camera/perspective.cc:21-22: the OpenCV copies of the intrinsics are float matrices
         mu.fx = (double)(float)mu.fx, mu.fy = (double)(float)mu.fy, mu.cx = (double)(float)mu.cx, mu.cy = (double)(float)mu.cy;
         for (int i = 0; i < 5; ++i) mu.dist[i] = (double)(float)mu.dist[i];
-        k_undistort_bearings<<<(n + 127) / 128, 128>>>(mu, *model, n, (const lpslam_keypoint*)(dev + o_in), (lpslam_keypoint*)(dev + o_out),
-                                                      (double*)(dev + o_b));
+        k_undistort_bearings<<<(n + 127) / 128, 128, 0, cs.st>>>(mu, *model, n, (const lpslam_keypoint*)(dev + o_in),
+                                                                 (lpslam_keypoint*)(dev + o_out), (double*)(dev + o_b));
         ProjArgs a = {};
         a.cam = *cam;
         a.n_curr = n;
@@ -1000,18 +1339,17 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
         a.cell_start = (uint32_t*)(dev + o_cs);
         a.cell_fill = (uint32_t*)(dev + o_cf);
         a.cell_items = (uint32_t*)(dev + o_ci);
-        k_grid_count<<<(n + 255) / 256, 256>>>(a);
-        k_grid_scan<<<1, 1024>>>(a);
-        k_grid_fill<<<(n + 255) / 256, 256>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
+        k_grid_count<<<(n + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
+        k_grid_fill<<<(n + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(undist_keypts, dev + o_out, sizeof(lpslam_keypoint) * (size_t)n, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(bearings, dev + o_b, 24 * (size_t)n, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(cell_start, dev + o_cs, 4 * (size_t)(ncell + 1), cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if (cell_start[ncell] > 0)
-            if ((e = cudaMemcpy(cell_items, dev + o_ci, 4 * (size_t)cell_start[ncell], cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cs.download(o_out, ar.off)) != cudaSuccess) break;
+        memcpy(undist_keypts, cs.out<uint8_t>(o_out), sizeof(lpslam_keypoint) * (size_t)n);
+        memcpy(bearings, cs.out<uint8_t>(o_b), 24 * (size_t)n);
+        memcpy(cell_start, cs.out<uint8_t>(o_cs), 4 * (size_t)(ncell + 1));
+        memcpy(cell_items, cs.out<uint8_t>(o_ci), 4 * (size_t)cell_start[ncell]);
     } while (false);
-    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_frame_postprocess", __FILE__, __LINE__);
     *n_in_grid = cell_start[ncell];
     return LPSLAM_OK;
@@ -1029,32 +1367,30 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
     LPS_ARG(n2 <= 24000 && n1 < (1u << 20) - 1, "too many keypoints (the per-keypoint state of frame 2 lives in shared memory)");
     for (uint32_t i = 0; i < n1; ++i) matched_indices_2_in_frm_1[i] = -1;
     if (n1 == 0 || n2 == 0) return LPSLAM_OK;
-    std::vector<uint8_t> use(n1);
-    std::vector<int32_t> zero_level(n1, 0);
-    for (uint32_t i = 0; i < n1; ++i) use[i] = kp1_undist[i].octave <= 0;  // area.cc:23-26
-
     const uint32_t ncell = cam->grid_cols * cam->grid_rows;
-    ArenaBump ar;
+    ArenaBump ar;  // inputs | zeroed counters | work | outputs
     const size_t o_use = ar.take(n1), o_pp = ar.take(8 * (size_t)n1), o_d1 = ar.take(32 * (size_t)n1), o_lvl = ar.take(4 * (size_t)n1);
     const size_t o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n2), o_d2 = ar.take(32 * (size_t)n2);
-    const size_t o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1)), o_cf = ar.take(4 * (size_t)ncell);
+    const size_t o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_cs = ar.take(4 * (size_t)(ncell + 1)), o_cf = ar.take(4 * (size_t)ncell);
     const size_t o_ci = ar.take(4 * (size_t)n2), o_tkey = ar.take(16 * (size_t)n1), o_tidx = ar.take(16 * (size_t)n1);
-    const size_t o_m21 = ar.take(4 * (size_t)n1), o_m12 = ar.take(4 * (size_t)n2), o_ev = ar.take(8 * (size_t)n1), o_ne = ar.take(8);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    const size_t o_m12 = ar.take(4 * (size_t)n2), o_m21 = ar.take(4 * (size_t)n1), o_ne = ar.take(8), o_ev = ar.take(8 * (size_t)n1);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     cudaError_t e = cudaSuccess;
     std::vector<int2> events;
     uint32_t ne[2] = {0, 0};
     do {
-#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
-        UP(o_use, use.data(), n1);
-        UP(o_pp, prev_matched_pts, 8 * (size_t)n1);
-        UP(o_d1, desc1, 32 * (size_t)n1);
-        UP(o_lvl, zero_level.data(), 4 * (size_t)n1);
-        UP(o_kp, kp2_undist, sizeof(lpslam_keypoint) * (size_t)n2);
-        UP(o_d2, desc2, 32 * (size_t)n2);
-#undef UP
-        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        uint8_t* use = cs.host + o_use;
+        for (uint32_t i = 0; i < n1; ++i) use[i] = kp1_undist[i].octave <= 0;  // area.cc:23-26
+        cs.put(o_pp, prev_matched_pts, 8 * (size_t)n1);
+        cs.put(o_d1, desc1, 32 * (size_t)n1);
+        cs.zero(o_lvl, 4 * (size_t)n1);
+        cs.put(o_kp, kp2_undist, sizeof(lpslam_keypoint) * (size_t)n2);
+        cs.put(o_d2, desc2, 32 * (size_t)n2);
+        cs.zero(o_cc, 4 * (size_t)ncell);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.cam = *cam;
         a.mode = 2;
@@ -1078,25 +1414,23 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
         a.match_1_of_2 = (int32_t*)(dev + o_m12);
         a.events = (int2*)(dev + o_ev);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_grid_count<<<(n2 + 255) / 256, 256>>>(a);
-        k_grid_scan<<<1, 1024>>>(a);
-        k_grid_fill<<<(n2 + 255) / 256, 256>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
-        k_proj_topk<<<(n1 + 127) / 128, 128>>>(a);
+        k_grid_count<<<(n2 + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
+        k_grid_fill<<<(n2 + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        k_proj_topk<<<(n1 + 3) / 4, 128, 0, cs.st>>>(a);
         const size_t smem = 8 * (size_t)n2;
         if (smem > 48 * 1024 &&
             (e = cudaFuncSetAttribute(k_area_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
             break;
-        k_area_resolve<<<1, 32, smem>>>(a);
+        k_area_resolve<<<1, 32, smem, cs.st>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(matched_indices_2_in_frm_1, dev + o_m21, 4 * (size_t)n1, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(ne, dev + o_ne, 8, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if (check_orientation && ne[0]) {
-            events.resize(ne[0]);
-            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)ne[0], cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        }
+        if ((e = cs.download(o_m21, check_orientation ? ar.off : o_ev)) != cudaSuccess) break;
+        memcpy(matched_indices_2_in_frm_1, cs.out<int32_t>(o_m21), 4 * (size_t)n1);
+        ne[0] = cs.out<uint32_t>(o_ne)[0];
+        ne[1] = cs.out<uint32_t>(o_ne)[1];
+        if (check_orientation) events.assign(cs.out<int2>(o_ev), cs.out<int2>(o_ev) + ne[0]);
     } while (false);
-    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_area", __FILE__, __LINE__);
     int num = (int)ne[1];
     if (check_orientation) {  // area.cc:87-101: every accepted row entered the histogram, also rows that lost their match later
@@ -1136,26 +1470,26 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
         LPS_ARG(row_cand_begin[r] <= row_cand_end[r] && row_cand_end[r] <= n_items, "candidate range out of bounds");
     for (uint32_t q = 0; q < n_items; ++q) LPS_ARG(cand_items[q] < n_kp, "candidate index out of range");
 
-    ArenaBump ar;
+    ArenaBump ar;  // inputs | work | outputs
     const size_t o_rd = ar.take(32 * (size_t)n_rows), o_cb = ar.take(4 * (size_t)n_rows), o_ce = ar.take(4 * (size_t)n_rows);
-    const size_t o_it = ar.take(4 * (size_t)n_items), o_kd = ar.take(32 * (size_t)n_kp), o_tk = ar.take(n_kp);
+    const size_t o_it = ar.take(4 * (size_t)n_items), o_kd = ar.take(32 * (size_t)n_kp), o_tk = ar.take(n_kp), in_end = ar.off;
     const size_t o_tkey = ar.take(16 * (size_t)n_rows), o_tidx = ar.take(16 * (size_t)n_rows), o_m = ar.take(4 * (size_t)n_kp);
-    const size_t o_ev = ar.take(8 * (size_t)n_rows), o_ne = ar.take(4);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    const size_t o_ne = ar.take(4), o_ev = ar.take(8 * (size_t)n_rows);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
     std::vector<int2> events;
     do {
-#define UP(off, src, bytes) if ((bytes) && (e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
-        UP(o_rd, row_desc, 32 * (size_t)n_rows);
-        UP(o_cb, row_cand_begin, 4 * (size_t)n_rows);
-        UP(o_ce, row_cand_end, 4 * (size_t)n_rows);
-        UP(o_it, cand_items, 4 * (size_t)n_items);
-        UP(o_kd, kp_desc, 32 * (size_t)n_kp);
-        if (kp_taken) UP(o_tk, kp_taken, n_kp);
-#undef UP
-        if (!kp_taken && (e = cudaMemset(dev + o_tk, 0, n_kp)) != cudaSuccess) break;
+        cs.put(o_rd, row_desc, 32 * (size_t)n_rows);
+        cs.put(o_cb, row_cand_begin, 4 * (size_t)n_rows);
+        cs.put(o_ce, row_cand_end, 4 * (size_t)n_rows);
+        cs.put(o_it, cand_items, 4 * (size_t)n_items);
+        cs.put(o_kd, kp_desc, 32 * (size_t)n_kp);
+        if (kp_taken) cs.put(o_tk, kp_taken, n_kp);
+        else cs.zero(o_tk, n_kp);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.mode = 3;
         a.n_last = n_rows;
@@ -1174,18 +1508,16 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
         a.curr_match_last = (int32_t*)(dev + o_m);
         a.events = row_angle ? (int2*)(dev + o_ev) : nullptr;
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_proj_topk<<<(n_rows + 127) / 128, 128>>>(a);
-        a.claim_in_smem = n_kp <= 10000;
-        k_lm_resolve<<<1, 32, ((n_kp + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_kp : 0)>>>(a);
+        k_proj_topk<<<(n_rows + 3) / 4, 128, 0, cs.st>>>(a);
+        a.claim_in_smem = n_kp <= kResolveTableMax;
+        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
+        if ((e = launch_lm_resolve(a, n_kp, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(kp_match_row, dev + o_m, 4 * (size_t)n_kp, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if (row_angle && n_ev) {
-            events.resize(n_ev);
-            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        }
+        if ((e = cs.download(o_m, row_angle ? ar.off : o_ev)) != cudaSuccess) break;
+        memcpy(kp_match_row, cs.out<int32_t>(o_m), 4 * (size_t)n_kp);
+        n_ev = *cs.out<uint32_t>(o_ne);
+        if (row_angle) events.assign(cs.out<int2>(o_ev), cs.out<int2>(o_ev) + n_ev);
     } while (false);
-    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_candidates", __FILE__, __LINE__);
     *n_matches = n_ev;
     if (row_angle) {  // bow_tree.cc:91-95,111-117
@@ -1229,33 +1561,34 @@ static int rows_best_search(const char* who, uint32_t hamm_thr, const lpslam_cam
         if (unsigned_levels && lm_scale_level[i] == 0) act[i] = 0;
     }
     const uint32_t ncell = cam->grid_cols * cam->grid_rows;
-    ArenaBump ar;
+    ArenaBump ar;  // inputs | zeroed counters | work | outputs
     const size_t o_act = ar.take(n_lm), o_rp = ar.take(16 * (size_t)n_lm), o_lxr = ar.take(4 * (size_t)n_lm), o_lvl = ar.take(4 * (size_t)n_lm);
     const size_t o_ld = ar.take(32 * (size_t)n_lm), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_kp);
     const size_t o_desc = ar.take(32 * (size_t)n_kp), o_xr = ar.take(4 * (size_t)n_kp), o_sc = ar.take(4 * kMaxLevels);
-    const size_t o_isq = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), o_cs = ar.take(4 * (size_t)(ncell + 1));
+    const size_t o_isq = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_cs = ar.take(4 * (size_t)(ncell + 1));
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
     const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_rb = ar.take(4 * (size_t)n_lm), o_rd = ar.take(4 * (size_t)n_lm);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     cudaError_t e = cudaSuccess;
-    std::vector<uint32_t> dist(n_lm);
+    const uint32_t* dist = nullptr;
     do {
-#define UP(off, src, bytes) if ((e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
-        UP(o_act, act.data(), n_lm);
-        UP(o_rp, lm_reproj, 16 * (size_t)n_lm);
-        UP(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
-        UP(o_ld, lm_desc, 32 * (size_t)n_lm);
-        UP(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
-        UP(o_desc, kp_desc, 32 * (size_t)n_kp);
-        UP(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+        cs.put(o_act, act.data(), n_lm);
+        cs.put(o_rp, lm_reproj, 16 * (size_t)n_lm);
+        cs.put(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
+        cs.put(o_ld, lm_desc, 32 * (size_t)n_lm);
+        cs.put(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
+        cs.put(o_desc, kp_desc, 32 * (size_t)n_kp);
+        cs.put(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
         if (chi_square_gate) {
-            UP(o_lxr, lm_x_right, 4 * (size_t)n_lm);
-            UP(o_xr, kp_x_right, 4 * (size_t)n_kp);
-            UP(o_isq, inv_level_sigma_sq, 4 * (size_t)cam->num_scale_levels);
+            cs.put(o_lxr, lm_x_right, 4 * (size_t)n_lm);
+            cs.put(o_xr, kp_x_right, 4 * (size_t)n_kp);
+            cs.put(o_isq, inv_level_sigma_sq, 4 * (size_t)cam->num_scale_levels);
         }
-#undef UP
-        if ((e = cudaMemset(dev + o_cc, 0, 4 * (size_t)ncell)) != cudaSuccess) break;
+        cs.zero(o_cc, 4 * (size_t)ncell);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.cam = *cam;
         a.mode = 1;
@@ -1285,17 +1618,17 @@ static int rows_best_search(const char* who, uint32_t hamm_thr, const lpslam_cam
         a.top_idx = (int4*)(dev + o_tidx);
         a.row_best = (int32_t*)(dev + o_rb);
         a.row_dist = (uint32_t*)(dev + o_rd);
-        k_grid_count<<<(n_kp + 255) / 256, 256>>>(a);
-        k_grid_scan<<<1, 1024>>>(a);
-        k_grid_fill<<<(n_kp + 255) / 256, 256>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256>>>(a);
-        k_proj_topk<<<(n_lm + 127) / 128, 128>>>(a);
-        k_rows_best<<<(n_lm + 255) / 256, 256>>>(a);
+        k_grid_count<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
+        k_grid_fill<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
+        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        k_proj_topk<<<(n_lm + 3) / 4, 128, 0, cs.st>>>(a);
+        k_rows_best<<<(n_lm + 255) / 256, 256, 0, cs.st>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(best_idx, dev + o_rb, 4 * (size_t)n_lm, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if ((e = cudaMemcpy(dist.data(), dev + o_rd, 4 * (size_t)n_lm, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        if ((e = cs.download(o_rb, ar.off)) != cudaSuccess) break;
+        memcpy(best_idx, cs.out<int32_t>(o_rb), 4 * (size_t)n_lm);
+        dist = cs.out<uint32_t>(o_rd);
     } while (false);
-    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, who, __FILE__, __LINE__);
     for (uint32_t i = 0; i < n_lm; ++i) {
         if (best_dist) best_dist[i] = dist[i];
@@ -1391,45 +1724,41 @@ extern "C" int lpslam_match_triangulation(uint32_t n_rows, const uint32_t* row_i
     }
     for (uint32_t q = 0; q < n_items; ++q) LPS_ARG(cand_items[q] < n_2, "candidate index out of range");
 
-    // per-row copies of the keyframe-1 fields (rows are keyframe-1 keypoints in feature-vector order)
-    std::vector<uint8_t> rdesc(32 * (size_t)n_rows), rstereo(n_rows), kstereo(n_2);
-    std::vector<double> rbear(3 * (size_t)n_rows);
-    std::vector<float> rscale(n_rows);
-    for (uint32_t r = 0; r < n_rows; ++r) {
-        const uint32_t i1 = row_idx_1[r];
-        std::copy(kp1_desc + 32 * (size_t)i1, kp1_desc + 32 * (size_t)i1 + 32, rdesc.begin() + 32 * (size_t)r);
-        std::copy(bearings_1 + 3 * (size_t)i1, bearings_1 + 3 * (size_t)i1 + 3, rbear.begin() + 3 * (size_t)r);
-        rstereo[r] = 0 <= x_right_1[i1];
-        rscale[r] = scale_factors_1[kp1_undist[i1].octave];
-    }
-    for (uint32_t i = 0; i < n_2; ++i) kstereo[i] = 0 <= x_right_2[i];
-
-    ArenaBump ar;
+    ArenaBump ar;  // inputs | work | outputs
     const size_t o_rd = ar.take(32 * (size_t)n_rows), o_cb = ar.take(4 * (size_t)n_rows), o_ce = ar.take(4 * (size_t)n_rows);
     const size_t o_it = ar.take(4 * (size_t)n_items), o_kd = ar.take(32 * (size_t)n_2), o_tk = ar.take(n_2);
     const size_t o_rb = ar.take(24 * (size_t)n_rows), o_kb = ar.take(24 * (size_t)n_2), o_rs = ar.take(n_rows), o_ks = ar.take(n_2);
-    const size_t o_rsc = ar.take(4 * (size_t)n_rows);
+    const size_t o_rsc = ar.take(4 * (size_t)n_rows), in_end = ar.off;
     const size_t o_tkey = ar.take(16 * (size_t)n_rows), o_tidx = ar.take(16 * (size_t)n_rows), o_m = ar.take(4 * (size_t)n_2);
-    const size_t o_ev = ar.take(8 * (size_t)n_rows), o_ne = ar.take(4);
-    uint8_t* dev = nullptr;
-    LPS_CUDA(scratch_alloc((void**)&dev, ar.off));
+    const size_t o_ne = ar.take(4), o_ev = ar.take(8 * (size_t)n_rows);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
     std::vector<int2> events;
     do {
-#define UP(off, src, bytes) if ((bytes) && (e = cudaMemcpy(dev + (off), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) break
-        UP(o_rd, rdesc.data(), 32 * (size_t)n_rows);
-        UP(o_cb, row_cand_begin, 4 * (size_t)n_rows);
-        UP(o_ce, row_cand_end, 4 * (size_t)n_rows);
-        UP(o_it, cand_items, 4 * (size_t)n_items);
-        UP(o_kd, kp2_desc, 32 * (size_t)n_2);
-        UP(o_tk, kp2_has_lm, n_2);
-        UP(o_rb, rbear.data(), 24 * (size_t)n_rows);
-        UP(o_kb, bearings_2, 24 * (size_t)n_2);
-        UP(o_rs, rstereo.data(), n_rows);
-        UP(o_ks, kstereo.data(), n_2);
-        UP(o_rsc, rscale.data(), 4 * (size_t)n_rows);
-#undef UP
+        // per-row copies of the keyframe-1 fields (rows are keyframe-1 keypoints in feature-vector order), written in place
+        uint8_t* rdesc = cs.host + o_rd;
+        double* rbear = (double*)(cs.host + o_rb);
+        uint8_t* rstereo = cs.host + o_rs;
+        float* rscale = (float*)(cs.host + o_rsc);
+        for (uint32_t r = 0; r < n_rows; ++r) {
+            const uint32_t i1 = row_idx_1[r];
+            memcpy(rdesc + 32 * (size_t)r, kp1_desc + 32 * (size_t)i1, 32);
+            memcpy(rbear + 3 * (size_t)r, bearings_1 + 3 * (size_t)i1, 24);
+            rstereo[r] = 0 <= x_right_1[i1];
+            rscale[r] = scale_factors_1[kp1_undist[i1].octave];
+        }
+        uint8_t* kstereo = cs.host + o_ks;
+        for (uint32_t i = 0; i < n_2; ++i) kstereo[i] = 0 <= x_right_2[i];
+        cs.put(o_cb, row_cand_begin, 4 * (size_t)n_rows);
+        cs.put(o_ce, row_cand_end, 4 * (size_t)n_rows);
+        cs.put(o_it, cand_items, 4 * (size_t)n_items);
+        cs.put(o_kd, kp2_desc, 32 * (size_t)n_2);
+        cs.put(o_tk, kp2_has_lm, n_2);
+        cs.put(o_kb, bearings_2, 24 * (size_t)n_2);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.mode = 3;
         a.tri = 1;
@@ -1456,17 +1785,15 @@ extern "C" int lpslam_match_triangulation(uint32_t n_rows, const uint32_t* row_i
         a.curr_match_last = (int32_t*)(dev + o_m);
         a.events = (int2*)(dev + o_ev);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_proj_topk<<<(n_rows + 127) / 128, 128>>>(a);
-        a.claim_in_smem = n_2 <= 10000;
-        k_lm_resolve<<<1, 32, ((n_2 + 31) / 32) * 4 + (a.claim_in_smem ? 4 * (size_t)n_2 : 0)>>>(a);
+        k_proj_topk<<<(n_rows + 3) / 4, 128, 0, cs.st>>>(a);
+        a.claim_in_smem = n_2 <= kResolveTableMax;
+        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
+        if ((e = launch_lm_resolve(a, n_2, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
-        if ((e = cudaMemcpy(&n_ev, dev + o_ne, 4, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        if (n_ev) {
-            events.resize(n_ev);
-            if ((e = cudaMemcpy(events.data(), dev + o_ev, 8 * (size_t)n_ev, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
-        }
+        if ((e = cs.download(o_ne, ar.off)) != cudaSuccess) break;
+        n_ev = *cs.out<uint32_t>(o_ne);
+        events.assign(cs.out<int2>(o_ev), cs.out<int2>(o_ev) + n_ev);
     } while (false);
-    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_triangulation", __FILE__, __LINE__);
     *n_matches = n_ev;
     std::vector<std::pair<float, int>> deltas;

@@ -48,4 +48,75 @@ void scratch_free(void* p) {
     if (p) cudaFree(p);
 }
 
+namespace {
+struct StageBuffers {
+    uint8_t* dev = nullptr;
+    uint8_t* host = nullptr;
+    size_t cap = 0;
+    cudaStream_t st = nullptr;
+    int device = -1;
+    bool busy = false;
+    void drop() {
+        if (dev) cudaFree(dev);
+        if (host) cudaFreeHost(host);
+        if (st) cudaStreamDestroy(st);
+        dev = host = nullptr;
+        st = nullptr;
+        cap = 0;
+    }
+    ~StageBuffers() { drop(); }  // at thread exit; errors after the runtime shut down are ignored
+};
+thread_local StageBuffers t_stage;
+
+cudaError_t stage_allocate(StageBuffers& b, size_t want) {
+    cudaError_t e;
+    if (!b.st && (e = cudaStreamCreateWithFlags(&b.st, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&b.dev, want)) != cudaSuccess) return e;
+    if ((e = cudaHostAlloc((void**)&b.host, want, cudaHostAllocDefault)) != cudaSuccess) return e;
+    b.cap = want;
+    return cudaSuccess;
+}
+}  // namespace
+
+cudaError_t CallStage::open(size_t bytes) {
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return e;
+    StageBuffers& b = t_stage;
+    if (b.busy) {  // nested use on one thread (none today): private buffers for this call
+        StageBuffers own;
+        if ((e = stage_allocate(own, align_up(bytes + 256, 1 << 12))) != cudaSuccess) return e;
+        dev = own.dev, host = own.host, st = own.st;
+        own.dev = own.host = nullptr;
+        own.st = nullptr;
+        owned_ = true;
+        return cudaSuccess;
+    }
+    if (b.device != device || b.cap < bytes) {
+        b.drop();
+        b.device = device;
+        if ((e = stage_allocate(b, align_up(bytes + bytes / 2 + 4096, 1 << 16))) != cudaSuccess) {
+            b.drop();
+            return e;
+        }
+    }
+    b.busy = true;
+    dev = b.dev, host = b.host, st = b.st;
+    return cudaSuccess;
+}
+
+CallStage::~CallStage() {
+    if (owned_) {
+        if (st) cudaStreamSynchronize(st);
+        cudaFree(dev);
+        cudaFreeHost(host);
+        if (st) cudaStreamDestroy(st);
+    }
+    else if (dev && dev == t_stage.dev) {
+        // a call that failed half-way may have left work queued on the stream: the buffers are reused by the next call
+        if (cudaStreamQuery(st) == cudaErrorNotReady) cudaStreamSynchronize(st);
+        t_stage.busy = false;
+    }
+}
+
 }  // namespace lps
