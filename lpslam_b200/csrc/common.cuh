@@ -59,6 +59,8 @@ struct CallStage {
     uint8_t* dev = nullptr;
     uint8_t* host = nullptr;
     cudaStream_t st = nullptr;
+    cudaStream_t side = nullptr;  // second stream of the thread, for a copy that runs beside kernels already queued on st
+    cudaEvent_t joined = nullptr;
     cudaError_t open(size_t bytes);
     void put(size_t off, const void* src, size_t bytes) {
         if (bytes) memcpy(host + off, src, bytes);
@@ -66,6 +68,14 @@ struct CallStage {
     void zero(size_t off, size_t bytes) { memset(host + off, 0, bytes); }
     cudaError_t upload(size_t begin, size_t end) {
         return end > begin ? cudaMemcpyAsync(dev + begin, host + begin, end - begin, cudaMemcpyHostToDevice, st) : cudaSuccess;
+    }
+    // a second input range copied on the side stream: what is queued on st so far does not wait for it, what follows does
+    cudaError_t upload_beside(size_t begin, size_t end) {
+        if (end <= begin) return cudaSuccess;
+        cudaError_t e = cudaMemcpyAsync(dev + begin, host + begin, end - begin, cudaMemcpyHostToDevice, side);
+        if (e == cudaSuccess) e = cudaEventRecord(joined, side);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(st, joined, 0);
+        return e;
     }
     cudaError_t download(size_t begin, size_t end) {
         if (end > begin) {

@@ -6,9 +6,12 @@
 // and claims its best. The claim makes the loop order-dependent, so the work is split:
 //   k_bf_topk     all rows in parallel: the 4 smallest keys (distance << 16 | index) of every row ignoring claims.
 //                 In key order, "best / second among unclaimed" is simply the first two unclaimed keys.
-//   k_bf_resolve  one warp replays the rows in order against a shared-memory claim bitmap, 32 rows per round (commit up to the
-//                 first conflict). A row whose top-4 list runs out of unclaimed entries before the decision is certain is
-//                 rescanned exactly by the warp.
+//   k_bf_resolve  replays the rows in order against the claim set. Order-exact parallel rounds in one block: a row whose first
+//                 unclaimed key no earlier unresolved row can take, and whose second is fixed or cannot flip the ratio test, is
+//                 decided as the sequential loop would and committed with all other such rows; a row whose top-4 list may run out
+//                 of unclaimed entries blocks the rows behind it and is rescanned exactly by the whole block when it is the first
+//                 unresolved row. Contended inputs fall back to a serial warp loop (32 rows per round, commit up to the first
+//                 conflict).
 #include "common.cuh"
 #include "ctx.h"
 

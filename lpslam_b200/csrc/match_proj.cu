@@ -2,16 +2,22 @@
 // (match/projection.cc:85-208) together with the grid of data/common.cc:97-186 / data/common.h:59-64 and the perspective
 // reprojection of camera/perspective.cc:151-169, over flat arrays.
 //
-//   k_grid_*        assign_keypoints_to_grid: CSR lists per cell, indices ascending inside a cell (= insertion order)
-//   k_proj_topk     one thread per last-frame landmark: reproject (double, no FMA), walk the cells x-outer / y-inner like
-//                   get_keypoints_in_cell, apply the octave / window / x_right gates and keep the 4 best (distance, visit order)
-//   k_lm_resolve    one warp replays the landmarks in order against the "already holds an observed landmark" bitmap; that
-//                   bitmap changes as matches are made (projection.cc:163-165,189), which is what makes the loop sequential.
-//                   32 rows are decided at a time and committed up to the first conflict; a landmark whose 4 candidates
-//                   do not settle its decision is rescanned exactly.
+//   k_grid_*        assign_keypoints_to_grid: CSR lists per cell, indices ascending inside a cell (= insertion order);
+//                   k_grid_build is the four steps in one block for per-frame sizes
+//   k_proj_topk     one warp per row (last-frame landmark / local landmark / frame-1 keypoint): reproject (double, no FMA),
+//                   the lanes split the cells of get_keypoints_in_cell's window (x-outer / y-inner), apply the octave / window /
+//                   x_right gates and keep the 4 best (distance, visit order)
+//   k_lm_resolve    replays the rows against the "already holds an observed landmark" set, which changes as matches are made
+//                   (projection.cc:163-165,189) - that is what makes the reference loop sequential. Order-exact parallel rounds
+//                   in one block (rows whose outcome no earlier unresolved row can change are committed together), a serial
+//                   warp loop for contended inputs; a row whose 4 candidates do not settle its decision is rescanned exactly.
+// Every host entry point packs its inputs into one page-locked staging buffer (CallStage, scratch.cu): one copy in, kernels, one
+// copy out, on a stream of the calling thread; the grid is built from the first part of the copy while the rest is in flight.
+// LPS_MATCH_TIMING=1 prints the host / device time split of lpslam_match_reprojected.
 #include "common.cuh"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 
@@ -87,7 +93,6 @@ struct ProjArgs {
     const uint8_t* kp_stereo;
     const float* row_scale;     // scale_factors_.at(keypt_1.octave)
     double E[9], epi[3];
-    int debug;  // LPS_RESOLVE_DEBUG: k_lm_resolve prints its round count
 };
 
 // robust.cc:323-341 check_epipolar_constraint: double arithmetic in source order, no contraction
@@ -188,6 +193,83 @@ __global__ void k_grid_sort(ProjArgs a) {
         }
         a.cell_items[j] = v;
     }
+}
+
+// The four grid kernels in one block for the per-frame sizes (a few thousand keypoints): three launches and their gaps
+// cost more than the work. Same arithmetic and the same CSR result.
+__global__ void __launch_bounds__(1024) k_grid_build(ProjArgs a) {
+    __shared__ uint32_t s_w[33];
+    const uint32_t n = a.cam.grid_cols * a.cam.grid_rows;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (uint32_t i = tid; i < a.n_curr; i += 1024) {
+        int cx, cy;
+        if (cell_of(a, a.kp[i], cx, cy)) atomicAdd(&a.cell_count[cx * a.cam.grid_rows + cy], 1u);
+    }
+    __syncthreads();
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + tid;
+        const uint32_t v = i < n ? a.cell_count[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_w[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = s_w[lane];
+            uint32_t wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            s_w[lane] = wi - w;
+            if (lane == 31) s_w[32] = wi;
+        }
+        __syncthreads();
+        if (i < n) {
+            a.cell_start[i] = carry + s_w[warp] + inc - v;
+            a.cell_fill[i] = 0;
+        }
+        carry += s_w[32];
+        __syncthreads();
+    }
+    if (tid == 0) a.cell_start[n] = carry;
+    __syncthreads();
+    for (uint32_t i = tid; i < a.n_curr; i += 1024) {
+        int cx, cy;
+        if (cell_of(a, a.kp[i], cx, cy)) {
+            const uint32_t c = cx * a.cam.grid_rows + cy;
+            a.cell_items[a.cell_start[c] + atomicAdd(&a.cell_fill[c], 1u)] = i;
+        }
+    }
+    __syncthreads();
+    for (uint32_t c = tid; c < n; c += 1024) {  // push_back order = ascending keypoint index
+        const uint32_t b = a.cell_start[c], e = a.cell_start[c + 1];
+        for (uint32_t i = b + 1; i < e; ++i) {
+            const uint32_t v = a.cell_items[i];
+            uint32_t j = i;
+            while (j > b && a.cell_items[j - 1] > v) {
+                a.cell_items[j] = a.cell_items[j - 1];
+                --j;
+            }
+            a.cell_items[j] = v;
+        }
+    }
+}
+
+void launch_grid(const ProjArgs& a, uint32_t n, uint32_t ncell, cudaStream_t st) {
+    if (n <= 16384) {
+        k_grid_build<<<1, 1024, 0, st>>>(a);
+        return;
+    }
+    k_grid_count<<<(n + 255) / 256, 256, 0, st>>>(a);
+    k_grid_scan<<<1, 1024, 0, st>>>(a);
+    k_grid_fill<<<(n + 255) / 256, 256, 0, st>>>(a);
+    k_grid_sort<<<(ncell + 255) / 256, 256, 0, st>>>(a);
 }
 
 struct Projected {
@@ -704,13 +786,13 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
     extern __shared__ uint32_t s_mem[];
     __shared__ uint32_t s_barrier, s_minrow, s_warp_tot[RESOLVE_THREADS / 32], s_done;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // versioned owner table + claim table (n_curr words each) while they fit, else a bitmap (serial loop only)
+    // versioned owner table + two claim tables (n_curr words each) while they fit, else a bitmap (serial loop only)
     const TakenSet tk = {s_mem, a.claim_in_smem != 0};
     uint32_t* s_claim = tk.versioned ? s_mem + a.n_curr : nullptr;
     if (tk.versioned) {
         for (uint32_t i = tid; i < a.n_curr; i += RESOLVE_THREADS) {
             s_mem[i] = a.curr_taken[i] ? 0u : EMPTY;
-            s_claim[i] = EMPTY;
+            s_claim[i] = s_claim[a.n_curr + i] = EMPTY;
         }
     }
     else {
@@ -725,11 +807,16 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
     bool fw = false, bw = false;
     if (a.mode == 0) motion_flags(a, fw, bw);
     // rows that can never match (no candidate, or the closest one beyond the threshold) are resolved here
-    for (uint32_t r = tid; r < a.n_last; r += RESOLVE_THREADS) {
-        const uint32_t k0 = a.top_key[r].x;
-        if (k0 == EMPTY || (k0 >> 20) > a.hamm_thr) {
-            reinterpret_cast<uint32_t*>(a.top_key)[4 * (size_t)r + 1] = EMPTY;
-            reinterpret_cast<uint32_t*>(a.top_key)[4 * (size_t)r] = EMPTY;
+    uint32_t todo = 0;  // bit j: row tid + j * RESOLVE_THREADS is unresolved (parallel rounds: at most 32 rows per thread)
+    {
+        uint32_t j = 0;
+        for (uint32_t r = tid; r < a.n_last; r += RESOLVE_THREADS, ++j) {
+            const uint32_t k0 = a.top_key[r].x;
+            if (k0 == EMPTY || (k0 >> 20) > a.hamm_thr) {
+                reinterpret_cast<uint32_t*>(a.top_key)[4 * (size_t)r + 1] = EMPTY;
+                reinterpret_cast<uint32_t*>(a.top_key)[4 * (size_t)r] = EMPTY;
+            }
+            else if (j < 32) todo |= 1u << j;
         }
     }
     if (tid == 0) {
@@ -740,17 +827,15 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
     __syncthreads();
 
     const bool parallel = s_claim != nullptr && a.n_last <= 32u * RESOLVE_THREADS;
+    uint32_t* clean_claim = s_claim;  // a claim table with every entry EMPTY, for the serial loop
     if (parallel) {
-        uint32_t todo = 0;  // bit j: row tid + j * RESOLVE_THREADS is unresolved
-        for (uint32_t j = 0; tid + j * RESOLVE_THREADS < a.n_last; ++j)
-            if (a.top_key[tid + j * RESOLVE_THREADS].x != EMPTY) todo |= 1u << j;
         int idle_rounds = 0, rounds = 0;
         for (;;) {
             const int active = __syncthreads_count(todo != 0);  // threads that still own an unresolved row
-            if (a.debug && tid == 0) printf("lm_resolve round %d: active threads %d\n", rounds, active);
-            ++rounds;
             if (active == 0) break;
             // A: claims on the candidates a row could take
+            uint32_t* const claim = (rounds & 1) ? s_claim : s_claim + a.n_curr;  // the other table is wiped during C
+            uint32_t* const other = (rounds & 1) ? s_claim + a.n_curr : s_claim;
             if (todo) atomicMin(&s_minrow, (uint32_t)tid + (uint32_t)(__ffs(todo) - 1) * RESOLVE_THREADS);
             for (uint32_t m = todo; m; m &= m - 1) {
                 const uint32_t r = tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS;
@@ -762,56 +847,61 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
                 for (int q = 0; q < K; ++q) {
                     if (k[q] == EMPTY || (k[q] >> 20) > a.hamm_thr) continue;
                     const int c = raw[q] & 0x00FFFFFF;
-                    if (!tk.taken(c, r)) atomicMin(&s_claim[c], r);
+                    if (!tk.taken(c, r)) atomicMin(&claim[c], r);
                 }
             }
             __syncthreads();
-            // B: the first row that may have to look beyond its kept four
+            // B: every row's verdict, and the first row that may have to look beyond its kept four
+            uint32_t clear = 0, accept = 0;
+            bool behind = false;
             for (uint32_t m = todo; m; m &= m - 1) {
-                const uint32_t r = tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS;
+                const int j = __ffs(m) - 1;
+                const uint32_t r = tid + (uint32_t)j * RESOLVE_THREADS;
                 const uint4 mk = a.top_key[r];
                 const int4 mi = a.top_idx[r];
                 const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
                 const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
-                if (eval_row(a, r, k, raw, tk, s_claim).may_rescan) {
+                const RowEval e = eval_row(a, r, k, raw, tk, claim);
+                if (e.clear) clear |= 1u << j;
+                if (e.d.accept) accept |= 1u << j;
+                if (e.may_rescan && !behind) {
                     atomicMin(&s_barrier, r);
-                    break;  // later rows of this thread are behind it
+                    behind = true;
                 }
+                if (behind) break;  // later rows of this thread are behind the barrier anyway
             }
             __syncthreads();
-            // C: decide against the bitmap of the round's start (updates wait for the barrier), record
+            // C: record the decided rows up to the barrier (the owner table is updated after the next barrier)
             const uint32_t barrier = s_barrier, minrow = s_minrow;
-            uint32_t done = 0;
+            uint32_t done = 0, took = 0;
             for (uint32_t m = todo; m; m &= m - 1) {
                 const int j = __ffs(m) - 1;
                 const uint32_t r = tid + (uint32_t)j * RESOLVE_THREADS;
                 if (r > barrier) break;
-                const uint4 mk = a.top_key[r];
-                const int4 mi = a.top_idx[r];
-                const uint32_t k[K] = {mk.x, mk.y, mk.z, mk.w};
-                const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
-                RowEval e = eval_row(a, r, k, raw, tk, s_claim);
-                if (!e.clear) {
-                    if (r != minrow) continue;
-                    e.d = rescan_row(a, r, fw, bw, tk);  // every earlier row is resolved: the exact list decides
+                RowDecision d = {true, false, -1};
+                if ((clear >> j) & 1u) {
+                    if ((accept >> j) & 1u) {  // the first free candidate
+                        const int4 mi = a.top_idx[r];
+                        const int raw[K] = {mi.x, mi.y, mi.z, mi.w};
+#pragma unroll
+                        for (int q = K - 1; q >= 0; --q)
+                            if (raw[q] >= 0 && !tk.taken(raw[q] & 0x00FFFFFF, r)) d.i1 = raw[q] & 0x00FFFFFF;
+                        d.accept = true;
+                    }
                 }
-                commit_row(a, r, e.d, tk, false);
+                else if (r == minrow) d = rescan_row(a, r, fw, bw, tk);  // every earlier row is resolved: the exact list decides
+                else continue;
+                commit_row(a, r, d, tk, false);
+                if (d.accept) took |= 1u << j;
                 done |= 1u << j;
             }
             if (done) atomicAdd(&s_done, (uint32_t)__popc(done));
+            for (uint32_t i = tid; i < a.n_curr; i += RESOLVE_THREADS) other[i] = EMPTY;
             __syncthreads();
-            // D: bitmap updates of the committed rows, claims withdrawn, re-arm
-            for (uint32_t m = done; m; m &= m - 1) {
+            // D: owner-table updates of the committed rows, re-arm
+            for (uint32_t m = took; m; m &= m - 1) {
                 const uint32_t r = tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS;
-                const uint32_t res = reinterpret_cast<const uint32_t*>(a.top_key)[4 * (size_t)r + 1];
-                if (res != EMPTY && (a.last_obs ? a.last_obs[r] != 0 : true)) tk.take(res, r);
-            }
-            for (uint32_t m = todo; m; m &= m - 1) {
-                const int4 mi = a.top_idx[tid + (uint32_t)(__ffs(m) - 1) * RESOLVE_THREADS];
-                if (mi.x >= 0) s_claim[mi.x & 0x00FFFFFF] = EMPTY;
-                if (mi.y >= 0) s_claim[mi.y & 0x00FFFFFF] = EMPTY;
-                if (mi.z >= 0) s_claim[mi.z & 0x00FFFFFF] = EMPTY;
-                if (mi.w >= 0) s_claim[mi.w & 0x00FFFFFF] = EMPTY;
+                if (a.last_obs ? a.last_obs[r] != 0 : true) tk.take(reinterpret_cast<const uint32_t*>(a.top_key)[4 * (size_t)r + 1], r);
             }
             todo &= ~done;
             const uint32_t n_done = s_done;
@@ -821,6 +911,8 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
                 s_minrow = EMPTY;
                 s_done = 0;
             }
+            ++rounds;
+            clean_claim = (rounds & 1) ? s_claim : s_claim + a.n_curr;
             // contended (hundreds of rows left, a handful per round): the serial loop commits up to 32 rows per step without block barriers
             idle_rounds = (n_done < 8 && active >= 64) ? idle_rounds + 1 : 0;
             if (idle_rounds >= 4) break;
@@ -836,7 +928,7 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
         }
     __syncthreads();
     // whatever is left (everything when the claim table did not fit), from the first unresolved row on
-    if (warp == 0 && s_minrow != EMPTY) resolve_serial(a, tk, s_claim, lane, fw, bw, s_minrow & ~31u);
+    if (warp == 0 && s_minrow != EMPTY) resolve_serial(a, tk, clean_claim, lane, fw, bw, s_minrow & ~31u);
     __syncthreads();
 
     // ordered event list and count: rows in order, 1024 at a time
@@ -847,12 +939,15 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
         const uint32_t bal = __ballot_sync(0xFFFFFFFFu, res >= 0);
         if (lane == 0) s_warp_tot[warp] = __popc(bal);
         __syncthreads();
-        uint32_t before = 0, total = 0;
-        for (int w = 0; w < RESOLVE_THREADS / 32; ++w) {
-            const uint32_t t = s_warp_tot[w];
-            before += w < warp ? t : 0;
-            total += t;
+        // every warp scans the 32 warp totals itself
+        const uint32_t wt = s_warp_tot[lane];
+        uint32_t inc = wt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= o) inc += t;
         }
+        const uint32_t before = __shfl_sync(0xFFFFFFFFu, inc - wt, warp), total = __shfl_sync(0xFFFFFFFFu, inc, 31);
         if (res >= 0 && a.events) a.events[num + before + __popc(bal & ((1u << lane) - 1u))] = make_int2((int)r, res);
         num += total;
         __syncthreads();
@@ -860,10 +955,10 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
     if (tid == 0) *a.n_events = num;
 }
 
-constexpr uint32_t kResolveTableMax = 25000;  // 2 x 4 B per keypoint of shared memory
+constexpr uint32_t kResolveTableMax = 16000;  // 3 x 4 B per keypoint of shared memory
 
 cudaError_t launch_lm_resolve(const ProjArgs& a, uint32_t n_kp, cudaStream_t st) {
-    const size_t smem = a.claim_in_smem ? 8 * (size_t)n_kp : ((n_kp + 31) / 32) * 4;
+    const size_t smem = a.claim_in_smem ? 12 * (size_t)n_kp : ((n_kp + 31) / 32) * 4;
     if (smem > 48 * 1024) {
         const cudaError_t e = cudaFuncSetAttribute(k_lm_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -1142,15 +1237,11 @@ extern "C" int lpslam_match_projection(const lpslam_camera* cam, const double* p
         a.curr_match_last = (int32_t*)(dev + o_m);
         a.events = (int2*)(dev + o_ev);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_grid_count<<<(n_curr + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
-        k_grid_fill<<<(n_curr + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        launch_grid(a, n_curr, ncell, cs.st);
         k_proj_topk<<<(n_last + 3) / 4, 128, 0, cs.st>>>(a);
         a.hamm_thr = HAMMING_DIST_THR_HIGH;
         a.use_ratio = 0;
         a.claim_in_smem = n_curr <= kResolveTableMax;
-        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
         if ((e = launch_lm_resolve(a, n_curr, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         // matches + event count, and the event list (at most one event per row) only when the orientation check wants it
@@ -1202,11 +1293,12 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
                 "landmark scale level out of range");
 
     const uint32_t ncell = cam->grid_cols * cam->grid_rows;
-    ArenaBump ar;  // inputs | zeroed counters | work | outputs
+    ArenaBump ar;  // keypoints + zeroed counters | landmark inputs | work | outputs
+    const size_t o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_kp), o_cc = ar.take(4 * (size_t)ncell), grid_end = ar.off;
     const size_t o_act = ar.take(n_lm), o_rp = ar.take(16 * (size_t)n_lm), o_lxr = ar.take(4 * (size_t)n_lm), o_lvl = ar.take(4 * (size_t)n_lm);
-    const size_t o_ld = ar.take(32 * (size_t)n_lm), o_obs = ar.take(n_lm), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n_kp);
+    const size_t o_ld = ar.take(32 * (size_t)n_lm), o_obs = ar.take(n_lm);
     const size_t o_desc = ar.take(32 * (size_t)n_kp), o_xr = ar.take(4 * (size_t)n_kp), o_tk = ar.take(n_kp);
-    const size_t o_sc = ar.take(4 * kMaxLevels), o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_sc = ar.take(4 * kMaxLevels), in_end = ar.off;
     const size_t o_cs = ar.take(4 * (size_t)(ncell + 1));
     const size_t o_cf = ar.take(4 * (size_t)ncell), o_ci = ar.take(4 * (size_t)n_kp), o_tkey = ar.take(16 * (size_t)n_lm);
     const size_t o_tidx = ar.take(16 * (size_t)n_lm), o_m = ar.take(4 * (size_t)n_kp), o_ne = ar.take(4), o_ev = ar.take(8 * (size_t)n_lm);
@@ -1216,20 +1308,17 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
     cudaError_t e = cudaSuccess;
     uint32_t n_ev = 0;
     std::vector<int2> events;
+    const bool dbg = getenv("LPS_MATCH_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t0 = now(), t1 = 0, t2 = 0, t3 = 0, t4 = 0, t5 = 0;
+    cudaEvent_t evs[4] = {};
+    if (dbg) for (auto& ev : evs) cudaEventCreate(&ev);
     do {
-        cs.put(o_act, lm_active, n_lm);
-        cs.put(o_rp, lm_reproj, 16 * (size_t)n_lm);
-        cs.put(o_lxr, lm_x_right, 4 * (size_t)n_lm);
-        cs.put(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
-        cs.put(o_ld, lm_desc, 32 * (size_t)n_lm);
-        if (lm_has_observation) cs.put(o_obs, lm_has_observation, n_lm);
+        // the grid only needs the keypoints: they go first, and the landmark arrays are packed while that copy and the grid
+        // kernel run
         cs.put(o_kp, kp_undist, sizeof(lpslam_keypoint) * (size_t)n_kp);
-        cs.put(o_desc, kp_desc, 32 * (size_t)n_kp);
-        cs.put(o_xr, kp_x_right, 4 * (size_t)n_kp);
-        cs.put(o_tk, kp_has_observed_lm, n_kp);
-        cs.put(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
         cs.zero(o_cc, 4 * (size_t)ncell);
-        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
+        if ((e = cs.upload(0, grid_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.cam = *cam;
         a.mode = 1;
@@ -1262,20 +1351,44 @@ extern "C" int lpslam_match_reprojected(const lpslam_camera* cam, const lpslam_r
         a.top_idx = (int4*)(dev + o_tidx);
         a.curr_match_last = (int32_t*)(dev + o_m);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_grid_count<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
-        k_grid_fill<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        t1 = now();
+        if (dbg) cudaEventRecord(evs[0], cs.st);
+        launch_grid(a, n_kp, ncell, cs.st);
+        if (dbg) cudaEventRecord(evs[1], cs.st);
+        cs.put(o_act, lm_active, n_lm);
+        cs.put(o_rp, lm_reproj, 16 * (size_t)n_lm);
+        cs.put(o_lxr, lm_x_right, 4 * (size_t)n_lm);
+        cs.put(o_lvl, lm_scale_level, 4 * (size_t)n_lm);
+        cs.put(o_ld, lm_desc, 32 * (size_t)n_lm);
+        if (lm_has_observation) cs.put(o_obs, lm_has_observation, n_lm);
+        cs.put(o_desc, kp_desc, 32 * (size_t)n_kp);
+        cs.put(o_xr, kp_x_right, 4 * (size_t)n_kp);
+        cs.put(o_tk, kp_has_observed_lm, n_kp);
+        cs.put(o_sc, scale_factors, 4 * (size_t)cam->num_scale_levels);
+        t2 = now();
+        if ((e = cs.upload_beside(grid_end, in_end)) != cudaSuccess) break;
+        if (dbg) cudaEventRecord(evs[2], cs.st);
         k_proj_topk<<<(n_lm + 3) / 4, 128, 0, cs.st>>>(a);
         a.claim_in_smem = n_kp <= kResolveTableMax;
-        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
         if ((e = launch_lm_resolve(a, n_kp, cs.st)) != cudaSuccess) break;
+        if (dbg) cudaEventRecord(evs[3], cs.st);
+        t3 = now();
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cs.download(o_m, lm_angle ? ar.off : o_ev)) != cudaSuccess) break;
+        t4 = now();
         memcpy(kp_match_lm, cs.out<int32_t>(o_m), 4 * (size_t)n_kp);
         n_ev = *cs.out<uint32_t>(o_ne);
         if (lm_angle) events.assign(cs.out<int2>(o_ev), cs.out<int2>(o_ev) + n_ev);
     } while (false);
+    t5 = now();
+    if (dbg) {
+        float g01 = 0, g12 = 0, g23 = 0;
+        cudaEventElapsedTime(&g01, evs[0], evs[1]);
+        cudaEventElapsedTime(&g12, evs[1], evs[2]);
+        cudaEventElapsedTime(&g23, evs[2], evs[3]);
+        fprintf(stderr, "reprojected: host pack1+enqueue %.1f, pack2 %.1f, enqueue rest %.1f, wait %.1f, unpack %.1f us | gpu grid %.1f, upload2 %.1f, topk+resolve %.1f us\n", t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4, g01 * 1e3, g12 * 1e3, g23 * 1e3);
+        for (auto& ev : evs) cudaEventDestroy(ev);
+    }
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_reprojected", __FILE__, __LINE__);
     *n_matches = n_ev;
     if (lm_angle) {  // angle_checker over (row angle - keypoint angle, keypoint), projection.cc:297-311
@@ -1339,10 +1452,7 @@ extern "C" int lpslam_frame_postprocess(const lpslam_perspective* model, const l
         a.cell_start = (uint32_t*)(dev + o_cs);
         a.cell_fill = (uint32_t*)(dev + o_cf);
         a.cell_items = (uint32_t*)(dev + o_ci);
-        k_grid_count<<<(n + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
-        k_grid_fill<<<(n + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        launch_grid(a, n, ncell, cs.st);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cs.download(o_out, ar.off)) != cudaSuccess) break;
         memcpy(undist_keypts, cs.out<uint8_t>(o_out), sizeof(lpslam_keypoint) * (size_t)n);
@@ -1368,10 +1478,10 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
     for (uint32_t i = 0; i < n1; ++i) matched_indices_2_in_frm_1[i] = -1;
     if (n1 == 0 || n2 == 0) return LPSLAM_OK;
     const uint32_t ncell = cam->grid_cols * cam->grid_rows;
-    ArenaBump ar;  // inputs | zeroed counters | work | outputs
+    ArenaBump ar;  // frame-2 keypoints + zeroed counters | other inputs | work | outputs
+    const size_t o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n2), o_cc = ar.take(4 * (size_t)ncell), grid_end = ar.off;
     const size_t o_use = ar.take(n1), o_pp = ar.take(8 * (size_t)n1), o_d1 = ar.take(32 * (size_t)n1), o_lvl = ar.take(4 * (size_t)n1);
-    const size_t o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)n2), o_d2 = ar.take(32 * (size_t)n2);
-    const size_t o_cc = ar.take(4 * (size_t)ncell), in_end = ar.off;
+    const size_t o_d2 = ar.take(32 * (size_t)n2), in_end = ar.off;
     const size_t o_cs = ar.take(4 * (size_t)(ncell + 1)), o_cf = ar.take(4 * (size_t)ncell);
     const size_t o_ci = ar.take(4 * (size_t)n2), o_tkey = ar.take(16 * (size_t)n1), o_tidx = ar.take(16 * (size_t)n1);
     const size_t o_m12 = ar.take(4 * (size_t)n2), o_m21 = ar.take(4 * (size_t)n1), o_ne = ar.take(8), o_ev = ar.take(8 * (size_t)n1);
@@ -1382,15 +1492,10 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
     std::vector<int2> events;
     uint32_t ne[2] = {0, 0};
     do {
-        uint8_t* use = cs.host + o_use;
-        for (uint32_t i = 0; i < n1; ++i) use[i] = kp1_undist[i].octave <= 0;  // area.cc:23-26
-        cs.put(o_pp, prev_matched_pts, 8 * (size_t)n1);
-        cs.put(o_d1, desc1, 32 * (size_t)n1);
-        cs.zero(o_lvl, 4 * (size_t)n1);
+        // the grid only needs the keypoints of frame 2: they go first, the rest is packed while that copy and the grid kernel run
         cs.put(o_kp, kp2_undist, sizeof(lpslam_keypoint) * (size_t)n2);
-        cs.put(o_d2, desc2, 32 * (size_t)n2);
         cs.zero(o_cc, 4 * (size_t)ncell);
-        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
+        if ((e = cs.upload(0, grid_end)) != cudaSuccess) break;
         ProjArgs a = {};
         a.cam = *cam;
         a.mode = 2;
@@ -1414,10 +1519,14 @@ extern "C" int lpslam_match_area(const lpslam_camera* cam, uint32_t n1, const lp
         a.match_1_of_2 = (int32_t*)(dev + o_m12);
         a.events = (int2*)(dev + o_ev);
         a.n_events = (uint32_t*)(dev + o_ne);
-        k_grid_count<<<(n2 + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
-        k_grid_fill<<<(n2 + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        launch_grid(a, n2, ncell, cs.st);
+        uint8_t* use = cs.host + o_use;
+        for (uint32_t i = 0; i < n1; ++i) use[i] = kp1_undist[i].octave <= 0;  // area.cc:23-26
+        cs.put(o_pp, prev_matched_pts, 8 * (size_t)n1);
+        cs.put(o_d1, desc1, 32 * (size_t)n1);
+        cs.zero(o_lvl, 4 * (size_t)n1);
+        cs.put(o_d2, desc2, 32 * (size_t)n2);
+        if ((e = cs.upload_beside(grid_end, in_end)) != cudaSuccess) break;
         k_proj_topk<<<(n1 + 3) / 4, 128, 0, cs.st>>>(a);
         const size_t smem = 8 * (size_t)n2;
         if (smem > 48 * 1024 &&
@@ -1510,7 +1619,6 @@ extern "C" int lpslam_match_candidates(uint32_t n_rows, const uint8_t* row_desc,
         a.n_events = (uint32_t*)(dev + o_ne);
         k_proj_topk<<<(n_rows + 3) / 4, 128, 0, cs.st>>>(a);
         a.claim_in_smem = n_kp <= kResolveTableMax;
-        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
         if ((e = launch_lm_resolve(a, n_kp, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cs.download(o_m, row_angle ? ar.off : o_ev)) != cudaSuccess) break;
@@ -1618,10 +1726,7 @@ static int rows_best_search(const char* who, uint32_t hamm_thr, const lpslam_cam
         a.top_idx = (int4*)(dev + o_tidx);
         a.row_best = (int32_t*)(dev + o_rb);
         a.row_dist = (uint32_t*)(dev + o_rd);
-        k_grid_count<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_scan<<<1, 1024, 0, cs.st>>>(a);
-        k_grid_fill<<<(n_kp + 255) / 256, 256, 0, cs.st>>>(a);
-        k_grid_sort<<<(ncell + 255) / 256, 256, 0, cs.st>>>(a);
+        launch_grid(a, n_kp, ncell, cs.st);
         k_proj_topk<<<(n_lm + 3) / 4, 128, 0, cs.st>>>(a);
         k_rows_best<<<(n_lm + 255) / 256, 256, 0, cs.st>>>(a);
         if ((e = cudaGetLastError()) != cudaSuccess) break;
@@ -1787,7 +1892,6 @@ extern "C" int lpslam_match_triangulation(uint32_t n_rows, const uint32_t* row_i
         a.n_events = (uint32_t*)(dev + o_ne);
         k_proj_topk<<<(n_rows + 3) / 4, 128, 0, cs.st>>>(a);
         a.claim_in_smem = n_2 <= kResolveTableMax;
-        a.debug = getenv("LPS_RESOLVE_DEBUG") != nullptr;
         if ((e = launch_lm_resolve(a, n_2, cs.st)) != cudaSuccess) break;
         if ((e = cudaGetLastError()) != cudaSuccess) break;
         if ((e = cs.download(o_ne, ar.off)) != cudaSuccess) break;

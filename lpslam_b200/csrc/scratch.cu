@@ -53,15 +53,19 @@ struct StageBuffers {
     uint8_t* dev = nullptr;
     uint8_t* host = nullptr;
     size_t cap = 0;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, side = nullptr;
+    cudaEvent_t joined = nullptr;
     int device = -1;
     bool busy = false;
     void drop() {
         if (dev) cudaFree(dev);
         if (host) cudaFreeHost(host);
         if (st) cudaStreamDestroy(st);
+        if (side) cudaStreamDestroy(side);
+        if (joined) cudaEventDestroy(joined);
         dev = host = nullptr;
-        st = nullptr;
+        st = side = nullptr;
+        joined = nullptr;
         cap = 0;
     }
     ~StageBuffers() { drop(); }  // at thread exit; errors after the runtime shut down are ignored
@@ -71,6 +75,8 @@ thread_local StageBuffers t_stage;
 cudaError_t stage_allocate(StageBuffers& b, size_t want) {
     cudaError_t e;
     if (!b.st && (e = cudaStreamCreateWithFlags(&b.st, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if (!b.side && (e = cudaStreamCreateWithFlags(&b.side, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if (!b.joined && (e = cudaEventCreateWithFlags(&b.joined, cudaEventDisableTiming)) != cudaSuccess) return e;
     if ((e = cudaMalloc((void**)&b.dev, want)) != cudaSuccess) return e;
     if ((e = cudaHostAlloc((void**)&b.host, want, cudaHostAllocDefault)) != cudaSuccess) return e;
     b.cap = want;
@@ -86,9 +92,10 @@ cudaError_t CallStage::open(size_t bytes) {
     if (b.busy) {  // nested use on one thread (none today): private buffers for this call
         StageBuffers own;
         if ((e = stage_allocate(own, align_up(bytes + 256, 1 << 12))) != cudaSuccess) return e;
-        dev = own.dev, host = own.host, st = own.st;
+        dev = own.dev, host = own.host, st = own.st, side = own.side, joined = own.joined;
         own.dev = own.host = nullptr;
-        own.st = nullptr;
+        own.st = own.side = nullptr;
+        own.joined = nullptr;
         owned_ = true;
         return cudaSuccess;
     }
@@ -101,20 +108,24 @@ cudaError_t CallStage::open(size_t bytes) {
         }
     }
     b.busy = true;
-    dev = b.dev, host = b.host, st = b.st;
+    dev = b.dev, host = b.host, st = b.st, side = b.side, joined = b.joined;
     return cudaSuccess;
 }
 
 CallStage::~CallStage() {
     if (owned_) {
         if (st) cudaStreamSynchronize(st);
+        if (side) cudaStreamSynchronize(side);
         cudaFree(dev);
         cudaFreeHost(host);
         if (st) cudaStreamDestroy(st);
+        if (side) cudaStreamDestroy(side);
+        if (joined) cudaEventDestroy(joined);
     }
     else if (dev && dev == t_stage.dev) {
         // a call that failed half-way may have left work queued on the stream: the buffers are reused by the next call
         if (cudaStreamQuery(st) == cudaErrorNotReady) cudaStreamSynchronize(st);
+        if (cudaStreamQuery(side) == cudaErrorNotReady) cudaStreamSynchronize(side);
         t_stage.busy = false;
     }
 }
