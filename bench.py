@@ -371,9 +371,25 @@ def latency_1pair(L, check, orb, match, host, local):
                                      xr.ctypes.data, dep.ctypes.data))
         ts.append((time.perf_counter() - t) * 1e3)
     ts = np.sort(ts[20:])
-    return {"call": "lpslam_stereo_frames, n_pairs = 1, pinned host images, results on the host", "calls": len(ts),
-            "median_ms": round(float(np.median(ts)), 4), "p99_ms": round(float(ts[int(0.99 * (len(ts) - 1))]), 4),
-            "frames_per_s_at_median": round(1e3 / float(np.median(ts)), 1)}
+    out = {"call": "lpslam_stereo_frames, n_pairs = 1, pinned host images, results on the host", "calls": len(ts),
+           "median_ms": round(float(np.median(ts)), 4), "p99_ms": round(float(ts[int(0.99 * (len(ts) - 1))]), 4),
+           "frames_per_s_at_median": round(1e3 / float(np.median(ts)), 1)}
+    # the same pair through the C++ drop-in classes (cpp/build/dropin_smoke, built where the reference headers are), the way
+    # data::frame's stereo constructor calls them
+    binary = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "build", "dropin_smoke")
+    if os.path.exists(binary):
+        import subprocess
+        import tempfile
+        with tempfile.TemporaryDirectory() as d:
+            host[0].tofile(os.path.join(d, "l.raw"))
+            host[1].tofile(os.path.join(d, "r.raw"))
+            env = dict(os.environ, LPSLAM_CUDA_DEVICE=str(local))
+            r = subprocess.run([binary, str(W), str(H), str(KPTS), os.path.join(d, "l.raw"), os.path.join(d, "r.raw"), "latency:200",
+                                repr(FX_B), repr(BASELINE)], capture_output=True, text=True, env=env, timeout=300)
+        out["dropin_cpp"] = json.loads(r.stdout) if r.returncode == 0 else {"unavailable": (r.stderr or "failed")[-200:]}
+    else:
+        out["dropin_cpp"] = {"unavailable": "cpp/build/dropin_smoke not built"}
+    return out
 
 
 def config_line(L, check, orb, match, replay, torch, local, w, h, kpts, batch, matcher, props, peak, cpu_frames_per_core):

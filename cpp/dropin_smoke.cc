@@ -3,6 +3,13 @@
 // tests/test_dropin_gpu.py. Built by cpp/Makefile against the oracle's minimal cv:: shim because the OpenCV SDK is not
 // installed in this image; with a real OpenCV the same sources compile unchanged.
 //   usage: dropin_smoke <w> <h> <max_kpts> <left.raw> <right.raw> <out.bin> <fx_b> <baseline>
+//          dropin_smoke <w> <h> <max_kpts> <left.raw> <right.raw> latency:<reps> <fx_b> <baseline>
+//              -> one JSON line: median / p99 wall time of what data::frame's stereo constructor does per frame
+//                 (frame.cc:55-93: two extract calls on two threads, then match::stereo::compute)
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <thread>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -37,6 +44,34 @@ int main(int argc, char** argv) {
     orb_extractor* ext_r = new orb_extractor(max_kpts, 2 * max_kpts, 1.2f, 8, 20, 7);
     std::vector<cv::KeyPoint> kl, kr;
     cv::Mat dl, dr;
+    if (std::strncmp(argv[6], "latency:", 8) == 0) {
+        const int reps = std::atoi(argv[6] + 8);
+        const std::vector<float> sf = ext_l->get_scale_factors(), isf = ext_l->get_inv_scale_factors();
+        std::vector<double> ms, ms_extract;
+        for (int i = 0; i < reps + 10; ++i) {
+            const auto t0 = std::chrono::steady_clock::now();
+            std::thread tl([&] { ext_l->extract(left, cv::Mat(), kl, dl); });   // frame.cc:60-63
+            std::thread tr([&] { ext_r->extract(right, cv::Mat(), kr, dr); });
+            tl.join();
+            tr.join();
+            const auto t1 = std::chrono::steady_clock::now();
+            std::vector<float> xr_, depth_;
+            openvslam::match::stereo m(ext_l->image_pyramid_, ext_r->image_pyramid_, kl, kr, dl, dr, sf, isf, fx_b, baseline);
+            m.compute(xr_, depth_);
+            if (i >= 10) {
+                ms.push_back(std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+                ms_extract.push_back(std::chrono::duration<double, std::milli>(t1 - t0).count());
+            }
+        }
+        std::sort(ms.begin(), ms.end());
+        std::sort(ms_extract.begin(), ms_extract.end());
+        std::printf("{\"call\": \"drop-in orb_extractor::extract x 2 (two threads) + match::stereo::compute, image_pyramid_ filled\", "
+                    "\"calls\": %d, \"median_ms\": %.4f, \"p99_ms\": %.4f, \"extract_median_ms\": %.4f, \"keypoints_left\": %zu}\n",
+                    reps, ms[ms.size() / 2], ms[static_cast<size_t>(0.99 * (ms.size() - 1))], ms_extract[ms_extract.size() / 2], kl.size());
+        delete ext_l;
+        delete ext_r;
+        return 0;
+    }
     ext_l->extract(left, cv::Mat(), kl, dl);
     ext_r->extract(right, cv::Mat(), kr, dr);
     std::vector<float> xr, depth;
@@ -63,6 +98,25 @@ int main(int argc, char** argv) {
     std::fwrite(&pw, 4, 1, f);
     std::fwrite(&ph, 4, 1, f);
     for (int y = 0; y < ph; ++y) std::fwrite(p3.ptr(y), 1, static_cast<size_t>(pw), f);
+    // a copy of the extractor (the reference's class is copyable) gives the same keypoints; its pyramid levels 1.. follow
+    {
+        orb_extractor copy(*ext_l);
+        std::vector<cv::KeyPoint> kc;
+        cv::Mat dc;
+        copy.extract(left, cv::Mat(), kc, dc);
+        int32_t same = kc.size() == kl.size();
+        for (size_t i = 0; same && i < kc.size(); ++i)
+            same = kc[i].pt.x == kl[i].pt.x && kc[i].pt.y == kl[i].pt.y && kc[i].octave == kl[i].octave
+                   && std::memcmp(dc.ptr(static_cast<int>(i)), dl.ptr(static_cast<int>(i)), 32) == 0;
+        std::fwrite(&same, 4, 1, f);
+        for (size_t level = 1; level < copy.image_pyramid_.size(); ++level) {
+            const cv::Mat& m = copy.image_pyramid_.at(level);
+            const int32_t mw = m.cols, mh = m.rows;
+            std::fwrite(&mw, 4, 1, f);
+            std::fwrite(&mh, 4, 1, f);
+            for (int y = 0; y < mh; ++y) std::fwrite(m.ptr(y), 1, static_cast<size_t>(mw), f);
+        }
+    }
     std::fclose(f);
     delete ext_l;
     delete ext_r;

@@ -34,8 +34,10 @@ public:
     //! Destructor: releases the CUDA context (the reference's is defaulted; ownership by raw pointer is unchanged)
     virtual ~orb_extractor();
 
-    orb_extractor(const orb_extractor&) = delete;
-    orb_extractor& operator=(const orb_extractor&) = delete;
+    //! Copyable like the reference's (implicitly defaulted) class: a copy gets its own device context with the same parameters
+    //! and shares the image_pyramid_ headers of the source, as copied cv::Mat members do
+    orb_extractor(const orb_extractor& other);
+    orb_extractor& operator=(const orb_extractor& other);
 
     //! Extract keypoints and each descriptor of them (orb_extractor.cc:71-147)
     void extract(const cv::_InputArray& in_image, const cv::_InputArray& in_image_mask,
@@ -58,8 +60,10 @@ public:
     std::vector<float> get_inv_level_sigma_sq() const;
 
     //! Image pyramid (orb_extractor.h:76): host copies of the device pyramid of the last extract; level 0 aliases the
-    //! caller's image as in the reference (orb_extractor.cc:267). Filled by extract() because match::stereo and other
-    //! users read it (data/frame.cc:78); set LPSLAM_CUDA_LAZY_PYRAMID=1 to skip the copy when nobody does.
+    //! caller's image as in the reference (orb_extractor.cc:267). Levels 1.. arrive in ONE device-to-host copy into a single
+    //! allocation that the cv::Mat headers share; as in the reference, the next extract of the same image size overwrites them
+    //! in place. Filled by extract() because match::stereo and other users read it (data/frame.cc:78); set
+    //! LPSLAM_CUDA_LAZY_PYRAMID=1 to skip the copy when nobody does.
     std::vector<cv::Mat> image_pyramid_;
 
     //! CUDA device the instance runs on (default 0, or the LPSLAM_CUDA_DEVICE environment variable)
@@ -70,6 +74,7 @@ private:
     std::vector<float> table(int which) const;
 
     orb_params orb_params_;
+    cv::Mat pyramid_storage_;  //!< levels 1.. of image_pyramid_, packed
     lpslam_orb_ctx* ctx_ = nullptr;
     int device_ = 0;
 };

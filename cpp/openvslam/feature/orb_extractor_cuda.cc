@@ -1,8 +1,11 @@
 // Host side of the drop-in openvslam::feature::orb_extractor: flattens the cv:: arguments and calls liblpslam_cuda.
 // Replaces orb_extractor.cc + orb_extractor_node.cc of the reference build. No pixel is touched on the host.
 #include "openvslam/feature/orb_extractor.h"
+#include "openvslam/feature/orb_device_pyramid.h"
 
 #include "lpslam_cuda.h"
+
+#include <mutex>
 
 #include <cstdlib>
 #include <cstring>
@@ -16,7 +19,41 @@ namespace {
 void check(int rc, const char* what) {
     if (rc < 0) throw std::runtime_error(std::string("liblpslam_cuda: ") + what + ": " + lpslam_cuda_last_error());
 }
+
+struct resident {
+    lpslam_orb_ctx* ctx;
+    const unsigned char *level0, *level1;
+};
+std::mutex resident_mutex;
+std::vector<resident> residents;  // one entry per live extractor that has extracted: a handful
 } // namespace
+
+namespace cuda_detail {
+void publish_pyramid(lpslam_orb_ctx* ctx, const unsigned char* level0, const unsigned char* level1) {
+    std::lock_guard<std::mutex> lock(resident_mutex);
+    for (auto& r : residents)
+        if (r.ctx == ctx) {
+            r.level0 = level0;
+            r.level1 = level1;
+            return;
+        }
+    residents.push_back({ctx, level0, level1});
+}
+void retire_pyramid(lpslam_orb_ctx* ctx) {
+    std::lock_guard<std::mutex> lock(resident_mutex);
+    for (size_t i = 0; i < residents.size(); ++i)
+        if (residents[i].ctx == ctx) {
+            residents.erase(residents.begin() + static_cast<long>(i));
+            return;
+        }
+}
+lpslam_orb_ctx* resident_pyramid(const unsigned char* level0, const unsigned char* level1) {
+    std::lock_guard<std::mutex> lock(resident_mutex);
+    for (const auto& r : residents)
+        if (r.level0 == level0 && r.level1 == level1) return r.ctx;
+    return nullptr;
+}
+} // namespace cuda_detail
 
 orb_extractor::orb_extractor(const unsigned int max_num_keypts, const unsigned int ini_min_num_keypts,
                              const float scale_factor, const unsigned int num_levels,
@@ -31,7 +68,26 @@ orb_extractor::orb_extractor(const orb_params& orb_params)
 }
 
 orb_extractor::~orb_extractor() {
+    cuda_detail::retire_pyramid(ctx_);
     lpslam_orb_destroy(ctx_);
+}
+
+orb_extractor::orb_extractor(const orb_extractor& other)
+    : image_pyramid_(other.image_pyramid_), orb_params_(other.orb_params_), device_(other.device_) {
+    create_context();
+}
+
+orb_extractor& orb_extractor::operator=(const orb_extractor& other) {
+    if (this != &other) {
+        cuda_detail::retire_pyramid(ctx_);
+        lpslam_orb_destroy(ctx_);
+        ctx_ = nullptr;
+        image_pyramid_ = other.image_pyramid_;
+        orb_params_ = other.orb_params_;
+        device_ = other.device_;
+        create_context();
+    }
+    return *this;
 }
 
 void orb_extractor::create_context() {
@@ -56,6 +112,7 @@ void orb_extractor::extract(const cv::_InputArray& in_image, const cv::_InputArr
     }
     const cv::Mat image = in_image.getMat();
     assert(image.type() == CV_8UC1);
+    cuda_detail::retire_pyramid(ctx_);  // the device pyramid is about to be replaced
     cv::Mat mask;
     if (!in_image_mask.empty()) {
         mask = in_image_mask.getMat();  // orb_extractor.cc:93-97: the image mask has priority over the rectangle mask
@@ -93,14 +150,23 @@ void orb_extractor::extract(const cv::_InputArray& in_image, const cv::_InputArr
     image_pyramid_.resize(orb_params_.num_levels_);
     image_pyramid_.at(0) = image;
     const char* lazy = std::getenv("LPSLAM_CUDA_LAZY_PYRAMID");
-    if (!(lazy && lazy[0] == '1')) {
-        for (unsigned int level = 1; level < orb_params_.num_levels_; ++level) {
+    if (!(lazy && lazy[0] == '1') && orb_params_.num_levels_ > 1) {
+        const unsigned int n = orb_params_.num_levels_ - 1;
+        std::vector<size_t> offsets(n);
+        size_t total = 0;
+        lpslam_orb_pyramid_levels(ctx_, 0, 1, nullptr, 0, offsets.data(), &total);  // sizes only
+        // like the reference, which resizes into the existing image_pyramid_ matrices (orb_extractor.cc:270-273), the levels of the
+        // previous extract are overwritten in place while the image size stays the same
+        if (pyramid_storage_.cols != static_cast<int>(total)) pyramid_storage_.create(1, static_cast<int>(total), CV_8UC1);
+        cv::Mat& storage = pyramid_storage_;
+        check(lpslam_orb_pyramid_levels(ctx_, 0, 1, storage.data, total, offsets.data(), &total), "lpslam_orb_pyramid_levels");
+        for (unsigned int level = 1; level <= n; ++level) {
             int w = 0, h = 0;
             check(lpslam_orb_level_size(ctx_, level, &w, &h), "lpslam_orb_level_size");
-            cv::Mat& m = image_pyramid_.at(level);
-            m.create(h, w, CV_8UC1);
-            check(lpslam_orb_pyramid(ctx_, 0, level, 0, m.data, m.step), "lpslam_orb_pyramid");
+            const int begin = static_cast<int>(offsets[level - 1]);
+            image_pyramid_.at(level) = storage.colRange(begin, begin + w * h).reshape(1, h);  // shares storage's reference count
         }
+        cuda_detail::publish_pyramid(ctx_, image.data, image_pyramid_.at(1).data);
     }
 }
 

@@ -2,8 +2,11 @@
 // stereo.h is used UNCHANGED; compile this file instead of match/stereo.cc. compute() flattens the members the reference
 // constructor stored and calls lpslam_match_stereo; the private helpers of the reference class are never called.
 #include "openvslam/match/stereo.h"
+#include "openvslam/feature/orb_device_pyramid.h"
 
 #include "lpslam_cuda.h"
+
+#include <cstdlib>
 
 #include <stdexcept>
 #include <string>
@@ -40,6 +43,21 @@ void stereo::compute(std::vector<float>& stereo_x_right, std::vector<float>& dep
     depths.assign(num_keypts_, -1.0f);
     static_assert(sizeof(cv::KeyPoint) == sizeof(lpslam_keypoint), "cv::KeyPoint layout");
     uint32_t n_matches = 0;
+    // both pyramids still on the device (they are the image_pyramid_ of two drop-in extractors' last extract): match there
+    const char* force_upload = std::getenv("LPSLAM_CUDA_STEREO_UPLOAD");
+    if (levels >= 2 && !(force_upload && force_upload[0] == '1')) {
+        lpslam_orb_ctx* cl = feature::cuda_detail::resident_pyramid(pl[0], pl[1]);
+        lpslam_orb_ctx* cr = feature::cuda_detail::resident_pyramid(pr[0], pr[1]);
+        if (cl && cr && cl != cr) {
+            const int rc = lpslam_match_stereo_ctx(cl, cr, reinterpret_cast<const lpslam_keypoint*>(keypts_left_.data()),
+                                                   static_cast<uint32_t>(keypts_left_.size()),
+                                                   reinterpret_cast<const lpslam_keypoint*>(keypts_right_.data()),
+                                                   static_cast<uint32_t>(keypts_right_.size()), descs_left_.data, descs_right_.data,
+                                                   focal_x_baseline_, true_baseline_, stereo_x_right.data(), depths.data(), &n_matches);
+            if (rc < 0) throw std::runtime_error(std::string("liblpslam_cuda: lpslam_match_stereo_ctx: ") + lpslam_cuda_last_error());
+            return;
+        }
+    }
     // descriptor matrices are n x 32 CV_8U and continuous (created by orb_extractor::extract)
     const int rc = lpslam_match_stereo(pl.data(), pr.data(), lw.data(), lh.data(), sl.data(), sr.data(), levels,
                                        reinterpret_cast<const lpslam_keypoint*>(keypts_left_.data()), static_cast<uint32_t>(keypts_left_.size()),

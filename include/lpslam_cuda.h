@@ -124,6 +124,12 @@ void* lpslam_orb_stream(lpslam_orb_ctx* ctx); /* cudaStream_t of the context */
  * blurred != 0 returns the Gaussian-blurred level the descriptors were sampled from (test hook). */
 int lpslam_orb_level_size(const lpslam_orb_ctx* ctx, uint32_t level, int* width, int* height);
 int lpslam_orb_pyramid(lpslam_orb_ctx* ctx, uint32_t frame, uint32_t level, int blurred, uint8_t* dst, size_t pitch);
+/* Levels first_level .. num_levels - 1 of frame `frame` in ONE device-to-host copy: every level tightly packed (row pitch =
+ * level width) at dst + offsets[i], i = level - first_level; *total = bytes needed. LPSLAM_ERR_CAPACITY (with *total and
+ * offsets set) when cap is too small or dst is null. What the drop-in extractor fills image_pyramid_ levels 1.. from
+ * (feature/orb_extractor.cc:266-275 leaves them in image_pyramid_; data/frame.cc:78 hands them to match::stereo). */
+int lpslam_orb_pyramid_levels(lpslam_orb_ctx* ctx, uint32_t frame, uint32_t first_level, uint8_t* dst, size_t cap, size_t* offsets,
+                              size_t* total);
 
 /* test hooks: intermediates of the last extract for frame `frame` — FAST candidates handed to the quadtree
  * (feature/orb_extractor.cc:352-369) and the keypoints it selected (:378), as (x, y, score) int32 triplets in
@@ -163,6 +169,14 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
                         const uint8_t* desc_l, const uint8_t* desc_r, const float* scale_factors,
                         const float* inv_scale_factors, float focal_x_baseline, float true_baseline,
                         float* stereo_x_right, float* depths, uint32_t* n_matches);
+
+/* The same on the pyramids two extractor contexts still hold on the device from their last lpslam_orb_extract (left eye on
+ * ctx_l, right eye on ctx_r; same device, same image size and level count): nothing but keypoints and descriptors travels.
+ * The scale tables are the contexts' own. Used by the drop-in match::stereo when it is handed the image_pyramid_ of two
+ * drop-in extractors (data/frame.cc:78). LPSLAM_ERR_STATE when a context has not extracted yet. */
+int lpslam_match_stereo_ctx(lpslam_orb_ctx* ctx_l, lpslam_orb_ctx* ctx_r, const lpslam_keypoint* kp_l, uint32_t nl,
+                            const lpslam_keypoint* kp_r, uint32_t nr, const uint8_t* desc_l, const uint8_t* desc_r,
+                            float focal_x_baseline, float true_baseline, float* stereo_x_right, float* depths, uint32_t* n_matches);
 
 /* fused stereo frames — data::frame's stereo constructor (data/frame.cc:55-93: two extractions + match::stereo) for
  * n_pairs stereo pairs in one pass, without the pyramid round trip: both eyes are extracted on the device by ONE context

@@ -11,6 +11,23 @@ const std::string& get_error();
 }
 using namespace lps;
 
+namespace {
+struct PackArgs {
+    const uint8_t* src[kMaxLevels];
+    int w[kMaxLevels], h[kMaxLevels], pitch[kMaxLevels];
+    size_t off[kMaxLevels];
+};
+
+// rows of several levels gathered into one tightly packed buffer (row pitch = level width)
+__global__ void k_pack_levels(PackArgs a, uint8_t* __restrict__ dst) {
+    const int l = blockIdx.y;
+    const uint8_t* __restrict__ src = a.src[l];
+    uint8_t* out = dst + a.off[l];
+    for (int y = blockIdx.x; y < a.h[l]; y += gridDim.x)
+        for (int x = threadIdx.x; x < a.w[l]; x += blockDim.x) out[(size_t)y * a.w[l] + x] = src[(size_t)y * a.pitch[l] + x];
+}
+}  // namespace
+
 extern "C" {
 
 int lpslam_cuda_abi_version(void) { return LPSLAM_CUDA_ABI_VERSION; }
@@ -105,6 +122,8 @@ void lpslam_orb_destroy(lpslam_orb_ctx* c) {
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->side) cudaStreamDestroy(c->side);
     if (c->h_frame_off) cudaFreeHost(c->h_frame_off);
+    if (c->pack_dev) cudaFree(c->pack_dev);
+    if (c->pack_host) cudaFreeHost(c->pack_host);
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -373,6 +392,51 @@ int lpslam_orb_pyramid(lpslam_orb_ctx* c, uint32_t frame, uint32_t level, int bl
     const uint8_t* src = (blurred ? g.blur : g.img) + frame * g.frame_stride;
     LPS_CUDA(cudaMemcpy2DAsync(dst, pitch, src, g.pitch, g.w, g.h, cudaMemcpyDeviceToHost, c->stream));
     LPS_CUDA(cudaStreamSynchronize(c->stream));
+    return LPSLAM_OK;
+}
+
+int lpslam_orb_pyramid_levels(lpslam_orb_ctx* c, uint32_t frame, uint32_t first_level, uint8_t* dst, size_t cap, size_t* offsets,
+                              size_t* total) {
+    LPS_ARG(c && offsets && total, "null argument");
+    if (!c->has_result) {
+        set_error("no extraction has run on this context");
+        return LPSLAM_ERR_STATE;
+    }
+    LPS_ARG(first_level < c->num_levels && frame < c->last_batch, "level / frame out of range");
+    PackArgs a = {};
+    const uint32_t n = c->num_levels - first_level;
+    size_t bytes = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const LevelGeom& g = c->lv[first_level + i];
+        a.src[i] = g.img + frame * g.frame_stride;
+        a.w[i] = g.w;
+        a.h[i] = g.h;
+        a.pitch[i] = g.pitch;
+        a.off[i] = offsets[i] = bytes;
+        bytes += (size_t)g.w * g.h;
+    }
+    *total = bytes;
+    if (!dst || cap < bytes) {
+        set_error("destination smaller than the packed levels");
+        return LPSLAM_ERR_CAPACITY;
+    }
+    LPS_CUDA(cudaSetDevice(c->device));
+    // packed on the device, fetched into the context's page-locked landing buffer in one copy (a copy straight into pageable
+    // memory runs at a fraction of the link rate), then handed over
+    if (c->pack_cap < bytes) {
+        if (c->pack_dev) cudaFree(c->pack_dev);
+        if (c->pack_host) cudaFreeHost(c->pack_host);
+        c->pack_dev = c->pack_host = nullptr;
+        c->pack_cap = 0;
+        LPS_CUDA(cudaMalloc((void**)&c->pack_dev, bytes));
+        LPS_CUDA(cudaHostAlloc((void**)&c->pack_host, bytes, cudaHostAllocDefault));
+        c->pack_cap = bytes;
+    }
+    k_pack_levels<<<dim3(64, n), 256, 0, c->stream>>>(a, c->pack_dev);
+    LPS_CUDA(cudaGetLastError());
+    LPS_CUDA(cudaMemcpyAsync(c->pack_host, c->pack_dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+    LPS_CUDA(cudaStreamSynchronize(c->stream));
+    memcpy(dst, c->pack_host, bytes);
     return LPSLAM_OK;
 }
 

@@ -328,4 +328,82 @@ int lpslam_match_stereo(const uint8_t* const* pyr_l, const uint8_t* const* pyr_r
     return LPSLAM_OK;
 }
 
+int lpslam_match_stereo_ctx(lpslam_orb_ctx* cl, lpslam_orb_ctx* cr, const lpslam_keypoint* kp_l, uint32_t nl, const lpslam_keypoint* kp_r,
+                            uint32_t nr, const uint8_t* desc_l, const uint8_t* desc_r, float focal_x_baseline, float true_baseline,
+                            float* stereo_x_right, float* depths, uint32_t* n_matches) {
+    LPS_ARG(cl && cr, "null context");
+    LPS_ARG(nl == 0 || (kp_l && desc_l && stereo_x_right && depths), "null left-eye argument");
+    LPS_ARG(nr == 0 || (kp_r && desc_r), "null right-eye argument");
+    if (n_matches) *n_matches = 0;
+    if (!cl->has_result || !cr->has_result) {
+        set_error("no extraction has run on one of the contexts");
+        return LPSLAM_ERR_STATE;
+    }
+    LPS_ARG(cl->device == cr->device && cl->w == cr->w && cl->h == cr->h && cl->num_levels == cr->num_levels,
+            "the two contexts must hold pyramids of the same geometry on the same device");
+    if (nl == 0) return LPSLAM_OK;
+    const uint32_t num_levels = cl->num_levels;
+    for (uint32_t i = 0; i < nl; ++i) LPS_ARG(kp_l[i].octave >= 0 && (uint32_t)kp_l[i].octave < num_levels, "left octave out of range");
+    for (uint32_t i = 0; i < nr; ++i) LPS_ARG(kp_r[i].octave >= 0 && (uint32_t)kp_r[i].octave < num_levels, "right octave out of range");
+    LPS_CUDA(cudaSetDevice(cl->device));
+    // the level table of the left context with "the next frame" = the same level of the right context: the kernels address the
+    // right eye as img + frame_stride (pointer difference, modulo 2^64)
+    LevelGeom lv[kMaxLevels];
+    memset(lv, 0, sizeof lv);
+    for (uint32_t l = 0; l < num_levels; ++l) {
+        lv[l] = cl->lv[l];
+        LPS_ARG(cl->lv[l].pitch == cr->lv[l].pitch, "level pitch differs between the contexts");
+        lv[l].frame_stride = (size_t)(cr->lv[l].img - cl->lv[l].img);
+    }
+    const uint32_t rows = nl + nr;
+    ArenaBump ar;
+    const size_t o_lv = ar.take(sizeof lv), o_kp = ar.take(sizeof(lpslam_keypoint) * (size_t)rows);
+    const size_t o_desc = ar.take(32 * (size_t)rows), o_off = ar.take(12), in_end = ar.off;
+    const size_t o_rec = ar.take(8 * (size_t)rows), o_corr = ar.take(4 * (size_t)rows), o_perm = ar.take(16 * (size_t)rows);
+    const size_t o_rows = ar.take(4 * (size_t)(cl->h + 1)), o_xr = ar.take(4 * (size_t)rows), o_dep = ar.take(4 * (size_t)rows);
+    CallStage cs;
+    LPS_CUDA(cs.open(ar.off));
+    uint8_t* const dev = cs.dev;
+    cudaError_t e = cudaSuccess;
+    do {
+        const uint32_t h_off[3] = {0, nl, rows};
+        cs.put(o_lv, lv, sizeof lv);
+        cs.put(o_kp, kp_l, sizeof(lpslam_keypoint) * (size_t)nl);
+        cs.put(o_kp + sizeof(lpslam_keypoint) * (size_t)nl, kp_r, sizeof(lpslam_keypoint) * (size_t)nr);
+        cs.put(o_desc, desc_l, 32 * (size_t)nl);
+        cs.put(o_desc + 32 * (size_t)nl, desc_r, 32 * (size_t)nr);
+        cs.put(o_off, h_off, sizeof h_off);
+        if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
+        StereoArgs a{};
+        a.lv = (const LevelGeom*)(dev + o_lv);
+        a.num_levels = (int)num_levels;
+        a.n_pairs = 1;
+        a.kp = (const lpslam_keypoint*)(dev + o_kp);
+        a.desc = dev + o_desc;
+        a.frame_off = (const uint32_t*)(dev + o_off);
+        a.max_rows = rows;
+        a.rec = (uint2*)(dev + o_rec);
+        a.x_right = (float*)(dev + o_xr);
+        a.depth = (float*)(dev + o_dep);
+        a.corr = (int*)(dev + o_corr);
+        a.perm = (uint4*)(dev + o_perm);
+        a.row_start = (uint32_t*)(dev + o_rows);
+        a.focal_x_baseline = focal_x_baseline;
+        a.true_baseline = true_baseline;
+        a.rows0 = cl->h;
+        launch_stereo(a, cs.st);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cs.download(o_xr, ar.off)) != cudaSuccess) break;
+        memcpy(stereo_x_right, cs.out<float>(o_xr), 4 * (size_t)nl);
+        memcpy(depths, cs.out<float>(o_dep), 4 * (size_t)nl);
+        if (n_matches) {
+            uint32_t n = 0;
+            for (uint32_t i = 0; i < nl; ++i) n += !(depths[i] == -1.0f && stereo_x_right[i] == -1.0f);
+            *n_matches = n;
+        }
+    } while (false);
+    if (e != cudaSuccess) return cuda_fail(e, "lpslam_match_stereo_ctx", __FILE__, __LINE__);
+    return LPSLAM_OK;
+}
+
 }  // extern "C"

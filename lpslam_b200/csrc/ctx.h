@@ -54,6 +54,12 @@ struct lpslam_orb_ctx {
 
     // pinned host staging
     uint32_t* h_frame_off = nullptr;  // max_batch + 2 (last = overflow flag)
+    // lpslam_orb_pyramid_levels: packed levels on the device and their page-locked landing buffer. Owned by the context, not the
+    // calling thread: data::frame runs every extract on a thread of its own (frame.cc:60-63), thread-local buffers would be
+    // allocated and freed per frame
+    uint8_t* pack_dev = nullptr;
+    uint8_t* pack_host = nullptr;
+    size_t pack_cap = 0;
     uint32_t last_batch = 0;
     bool has_result = false;
 

@@ -122,6 +122,19 @@ public:
         m.channels_ = cn;
         return m;
     }
+    // reshape(cn, rows): a continuous matrix (here: one row, or rows packed back to back) seen with another row count
+    Mat reshape(int cn, int new_rows) const {
+        if (new_rows == 0) return reshape(cn);
+        if (rows > 1 && step != static_cast<size_t>(cols) * elem() * channels_) throw std::invalid_argument("cv::Mat::reshape: not continuous");
+        const size_t total = static_cast<size_t>(rows) * cols * channels_;
+        if (total % (static_cast<size_t>(new_rows) * cn) != 0) throw std::invalid_argument("cv::Mat::reshape: bad row count");
+        Mat m(*this);
+        m.rows = new_rows;
+        m.cols = static_cast<int>(total / (static_cast<size_t>(new_rows) * cn));
+        m.channels_ = cn;
+        m.step = static_cast<size_t>(m.cols) * elem() * cn;
+        return m;
+    }
     int channels() const { return channels_; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     int type() const { return type_; }

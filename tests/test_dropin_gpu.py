@@ -36,7 +36,12 @@ def test_dropin_classes_match_oracle(oracle, tmp_path):
     xr = np.frombuffer(raw, np.float32, nl, o); o += 4 * nl
     dep = np.frombuffer(raw, np.float32, nl, o); o += 4 * nl
     pw, ph = np.frombuffer(raw, np.int32, 2, o); o += 8
-    p3 = np.frombuffer(raw, np.uint8, pw * ph, o).reshape(ph, pw)
+    p3 = np.frombuffer(raw, np.uint8, pw * ph, o).reshape(ph, pw); o += pw * ph
+    same_after_copy = np.frombuffer(raw, np.int32, 1, o)[0]; o += 4
+    copy_levels = []
+    for _ in range(1, 8):
+        mw, mh = np.frombuffer(raw, np.int32, 2, o); o += 8
+        copy_levels.append(np.frombuffer(raw, np.uint8, mw * mh, o).reshape(mh, mw)); o += mw * mh
 
     ol, orr = oracle.extractor(max_kpts=n), oracle.extractor(max_kpts=n)
     okl, odl = ol.extract(left)
@@ -47,6 +52,9 @@ def test_dropin_classes_match_oracle(oracle, tmp_path):
     assert np.abs(kl["angle"] - okl["angle"]).max() <= 1e-4 * 180 / np.pi
     assert (dl == odl).all(axis=1).mean() >= 0.999 and (dr == odr).all(axis=1).mean() >= 0.999
     assert np.array_equal(p3, ol.level(3))  # image_pyramid_ side effect (orb_extractor.h:76)
+    assert same_after_copy == 1  # a copy-constructed extractor (own device context) extracts the same keypoints and descriptors
+    for level, m in enumerate(copy_levels, 1):  # levels 1..7 arrive in one copy into one allocation
+        assert np.array_equal(m, ol.level(level)), level
     oxr, odep = oracle.match_stereo([ol.level(l) for l in range(8)], [orr.level(l) for l in range(8)], okl, okr, odl, odr,
                                     ol.table(0), ol.table(1), FX_B, B)
     if (dl == odl).all() and (dr == odr).all():
