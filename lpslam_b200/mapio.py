@@ -77,14 +77,17 @@ def keyframe_descriptors(doc):
 def landmark_observations(doc):
     """data/map_database.cc:358-380: returns (landmark ids ascending, obs_descs (total, 32) uint8, offsets (n + 1,) uint32);
     ids missing from "landmarks" are skipped like the reference does (with its warning), landmarks nobody observes get an
-    empty range."""
+    empty range, a landmark referenced twice from one keyframe keeps its first keypoint only."""
     known = sorted(int(k) for k in doc["landmarks"].keys())
     slot = {lm: i for i, lm in enumerate(known)}
     per_lm = [[] for _ in known]
     for _, descs, lm_ids in keyframe_descriptors(doc):
-        for idx in np.nonzero(lm_ids >= 0)[0]:
-            s = slot.get(int(lm_ids[idx]))
-            if s is not None:
+        seen = set()  # landmark::add_observation (data/landmark.cc:45-50) ignores a keyframe that already observes the landmark:
+        for idx in np.nonzero(lm_ids >= 0)[0]:  # of several keypoints of one keyframe carrying the same id, the first one counts
+            lm = int(lm_ids[idx])
+            s = slot.get(lm)
+            if s is not None and lm not in seen:
+                seen.add(lm)
                 per_lm[s].append(descs[idx])
     offsets = np.zeros(len(known) + 1, np.uint32)
     offsets[1:] = np.cumsum([len(p) for p in per_lm])

@@ -57,13 +57,26 @@ def test_message_pack_round_trip_and_association(tmp_path):
         assert np.array_equal(descs, truth[kid][0]) and np.array_equal(lm_ids, truth[kid][1])
     ids, obs, offsets = mapio.landmark_observations(doc)
     assert list(ids) == list(range(40)) and offsets[-1] == len(obs)
-    for s, lm in enumerate(ids):  # observations in keyframe-id then keypoint order; ids 40..42 are not in the file
-        want = [truth[kid][0][i] for kid in sorted(truth) for i in np.nonzero(truth[kid][1] == lm)[0]]
+    for s, lm in enumerate(ids):  # observations in keyframe-id order, one per keyframe (the first keypoint carrying the id,
+        # data/landmark.cc:45-50); ids 40..42 are not in the file
+        want = [truth[kid][0][i] for kid in sorted(truth) for i in np.nonzero(truth[kid][1] == lm)[0][:1]]
         got = obs[offsets[s]:offsets[s + 1]]
         assert len(got) == len(want) and all(np.array_equal(a, b) for a, b in zip(got, want))
     doc["keyframes"]["1"]["n_keypts"] += 1
     with pytest.raises(ValueError):
         mapio.keyframe_descriptors(doc)
+
+
+def test_landmark_referenced_twice_from_one_keyframe_keeps_its_first_keypoint():
+    """landmark::add_observation (data/landmark.cc:45-50) returns early when the keyframe already observes the landmark"""
+    rng = np.random.default_rng(3)
+    d0, d1 = rng.integers(0, 256, (4, 32), dtype=np.uint8), rng.integers(0, 256, (3, 32), dtype=np.uint8)
+    doc = {"landmarks": {"5": {}, "9": {}},
+           "keyframes": {"0": {"n_keypts": 4, "descs": mapio.convert_descriptors_to_json(d0), "lm_ids": [5, 9, 5, -1]},
+                         "1": {"n_keypts": 3, "descs": mapio.convert_descriptors_to_json(d1), "lm_ids": [9, 9, 5]}}}
+    ids, obs, offsets = mapio.landmark_observations(doc)
+    assert list(ids) == [5, 9] and list(offsets) == [0, 2, 4]
+    assert np.array_equal(obs, np.stack([d0[0], d1[2], d0[1], d1[0]]))
 
 
 @pytest.mark.gpu
