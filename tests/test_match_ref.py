@@ -135,12 +135,16 @@ def _fake_match(port):
     return m
 
 
+# cases that drive a device-resident extractor context itself (nothing to replay through the port)
+DEVICE_ONLY = {"test_match_consecutive_frames"}
+
+
 def _gpu_cases():
     import test_match_gpu as tm  # its tests carry the gpu mark; here they are replayed on the CPU
     out = []
     for name in sorted(dir(tm)):
         fn = getattr(tm, name)
-        if not name.startswith("test_") or not callable(fn):
+        if not name.startswith("test_") or not callable(fn) or name in DEVICE_ONLY:
             continue
         marks = [mk for mk in getattr(fn, "pytestmark", []) if mk.name == "parametrize"]
         if not marks:
