@@ -132,6 +132,7 @@ void lpslam_orb_destroy(lpslam_orb_ctx* c) {
 
 int lpslam_orb_set_param(lpslam_orb_ctx* c, int which, double value) {
     LPS_ARG(c, "null context");
+    c->drop_pair_graph();  // kernel arguments change
     switch (which) {
         case LPSLAM_ORB_MAX_NUM_KEYPTS: c->max_kpts = (uint32_t)value; break;
         case LPSLAM_ORB_SCALE_FACTOR:

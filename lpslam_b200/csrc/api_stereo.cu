@@ -2,6 +2,8 @@
 // match::stereo drop-in that takes host pyramids (match/stereo.h:18-29).
 #include "ctx.h"
 
+#include <cstdlib>
+
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -54,11 +56,56 @@ int lpslam_stereo_frames(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const 
         LPS_CUDA(cudaMemcpy2DAsync(g0.img + (2 * p + 1) * g0.frame_stride, g0.pitch, imgs_r[p], pitch, width, height,
                                    cudaMemcpyHostToDevice, c->stream));
     }
-    rc = lpslam_stereo_frames_dev(c, g0.img, n_pairs, width, height, g0.pitch, focal_x_baseline, true_baseline);
-    if (rc) return rc;
     const uint32_t nf = 2 * n_pairs;
-    LPS_CUDA(cudaMemcpyAsync(c->h_frame_off, c->desc.frame_off, sizeof(uint32_t) * (c->max_batch + 2), cudaMemcpyDeviceToHost,
-                             c->stream));
+    // the live tracker's call pattern (one pair per call, data/frame.cc:55-93) is launch-bound: ~20 small kernels. They are
+    // replayed as one CUDA graph from the third call of a setting on
+    static const bool graphs_on = [] {
+        const char* e = getenv("LPSLAM_CUDA_GRAPH");
+        return !(e && e[0] == '0');
+    }();
+    const bool want_graph = graphs_on && n_pairs == 1 && !c->timing && !c->pair_graph_off;
+    if (c->pair_graph && (!want_graph || c->pair_graph_fxb != focal_x_baseline || c->pair_graph_tb != true_baseline)) c->drop_pair_graph();
+    if (want_graph && c->pair_graph) {
+        LPS_CUDA(cudaGraphLaunch(c->pair_graph, c->stream));
+        c->last_batch = nf;
+        c->has_result = true;
+    }
+    else {
+        const bool capture = want_graph && c->pair_graph_warm >= 1;
+        if (capture && cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+            cudaGetLastError();
+            c->pair_graph_off = true;
+        }
+        const bool capturing = capture && !c->pair_graph_off;
+        rc = lpslam_stereo_frames_dev(c, g0.img, n_pairs, width, height, g0.pitch, focal_x_baseline, true_baseline);
+        cudaError_t ce = cudaSuccess;
+        if (!rc)
+            ce = cudaMemcpyAsync(c->h_frame_off, c->desc.frame_off, sizeof(uint32_t) * (c->max_batch + 2), cudaMemcpyDeviceToHost, c->stream);
+        if (capturing) {
+            cudaGraph_t g = nullptr;
+            const cudaError_t end = cudaStreamEndCapture(c->stream, &g);
+            if (!rc && ce == cudaSuccess && end == cudaSuccess && g && cudaGraphInstantiate(&c->pair_graph, g, 0) == cudaSuccess) {
+                c->pair_graph_fxb = focal_x_baseline;
+                c->pair_graph_tb = true_baseline;
+            }
+            else {  // not capturable on this driver / configuration: stay with plain launches for this context
+                cudaGetLastError();
+                c->pair_graph = nullptr;
+                c->pair_graph_off = true;
+            }
+            if (g) cudaGraphDestroy(g);
+            if (c->pair_graph_off) {  // nothing ran: do it launch by launch
+                rc = lpslam_stereo_frames_dev(c, g0.img, n_pairs, width, height, g0.pitch, focal_x_baseline, true_baseline);
+                ce = rc ? cudaSuccess
+                        : cudaMemcpyAsync(c->h_frame_off, c->desc.frame_off, sizeof(uint32_t) * (c->max_batch + 2), cudaMemcpyDeviceToHost,
+                                          c->stream);
+            }
+            else LPS_CUDA(cudaGraphLaunch(c->pair_graph, c->stream));
+        }
+        if (rc) return rc;
+        LPS_CUDA(ce);
+        if (want_graph) ++c->pair_graph_warm;
+    }
     LPS_CUDA(cudaStreamSynchronize(c->stream));
     const uint32_t total = c->h_frame_off[nf];
     for (uint32_t f = 0; f <= nf; ++f) offsets[f] = c->h_frame_off[f];

@@ -122,7 +122,14 @@ void lpslam_orb_ctx::release_async() {
     landing_bytes = 0;
 }
 
+void lpslam_orb_ctx::drop_pair_graph() {
+    if (pair_graph) cudaGraphExecDestroy(pair_graph);
+    pair_graph = nullptr;
+    pair_graph_warm = 0;
+}
+
 void lpslam_orb_ctx::release_geometry() {
+    drop_pair_graph();
     release_async();
     lps::blur_plan_destroy(blur_plan);
     blur_plan = nullptr;

@@ -57,6 +57,14 @@ struct lpslam_orb_ctx {
     // lpslam_orb_pyramid_levels: packed levels on the device and their page-locked landing buffer. Owned by the context, not the
     // calling thread: data::frame runs every extract on a thread of its own (frame.cc:60-63), thread-local buffers would be
     // allocated and freed per frame
+    // lpslam_stereo_frames with one pair: the whole per-frame pipeline (pyramid .. stereo matcher + the offsets read-back) as one
+    // CUDA graph. The first call of a (geometry, parameters, stereo constants) setting runs launch by launch (tables and masks are
+    // built on first use), the second is captured, later ones relaunch the graph. LPSLAM_CUDA_GRAPH=0 turns it off.
+    cudaGraphExec_t pair_graph = nullptr;
+    float pair_graph_fxb = 0.f, pair_graph_tb = 0.f;
+    int pair_graph_warm = 0;
+    bool pair_graph_off = false;
+    void drop_pair_graph();
     uint8_t* pack_dev = nullptr;
     uint8_t* pack_host = nullptr;
     size_t pack_cap = 0;

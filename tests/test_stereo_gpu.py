@@ -81,3 +81,37 @@ def test_stereo_frames_submit_collect():
     # the blocking entry point still works on the same context afterwards
     again = match.stereo_frames(e, [p[0] for p in batches[0]], [p[1] for p in batches[0]], 84.0, 0.12)
     assert again[0]["keypts_left"].tobytes() == want[0][0]["keypts_left"].tobytes()
+
+
+def test_single_pair_calls_replay_a_graph():
+    """lpslam_stereo_frames with one pair per call (data/frame.cc:55-93's pattern): the first call of a setting runs launch by launch,
+    the second is captured into a CUDA graph, later ones replay it. Every call must give what a fresh context gives for the same
+    pair; changing a parameter or the stereo constants in between drops the graph."""
+    from lpslam_b200 import match, orb
+    pairs = [synth_stereo_pair(360, 640, 7000 + k) for k in range(6)]
+    e = orb.orb_extractor(max_num_keypts=700, max_batch=2)
+
+    def fresh(pair, n, fxb):
+        f = orb.orb_extractor(max_num_keypts=n, max_batch=2)
+        return match.stereo_frames(f, [pair[0]], [pair[1]], fxb, B)[0]
+
+    def same(a, b):
+        return all(a[k].tobytes() == b[k].tobytes() for k in a)
+
+    for k, pair in enumerate(pairs):  # calls 0, 1: plain / capture, 2..5: graph replays on new images
+        got = match.stereo_frames(e, [pair[0]], [pair[1]], FX_B, B)[0]
+        assert same(got, fresh(pair, 700, FX_B)), k
+    e.set_max_num_keypoints(500)  # kernel arguments change: the graph is dropped and rebuilt
+    for k, pair in enumerate(pairs[:4]):
+        assert same(match.stereo_frames(e, [pair[0]], [pair[1]], FX_B, B)[0], fresh(pair, 500, FX_B)), k
+    for k, pair in enumerate(pairs[:4]):  # other stereo constants
+        assert same(match.stereo_frames(e, [pair[0]], [pair[1]], 2 * FX_B, B)[0], fresh(pair, 500, 2 * FX_B)), k
+    # a two-pair call in between runs without the graph and leaves it usable
+    two = orb.orb_extractor(max_num_keypts=500, max_batch=4)
+    want = match.stereo_frames(two, [pairs[0][0], pairs[1][0]], [pairs[0][1], pairs[1][1]], 2 * FX_B, B)
+    e4 = orb.orb_extractor(max_num_keypts=500, max_batch=4)
+    for _ in range(3):
+        match.stereo_frames(e4, [pairs[2][0]], [pairs[2][1]], 2 * FX_B, B)
+    got = match.stereo_frames(e4, [pairs[0][0], pairs[1][0]], [pairs[0][1], pairs[1][1]], 2 * FX_B, B)
+    assert all(same(a, b) for a, b in zip(got, want))
+    assert same(match.stereo_frames(e4, [pairs[2][0]], [pairs[2][1]], 2 * FX_B, B)[0], fresh(pairs[2], 500, 2 * FX_B))
