@@ -273,6 +273,24 @@ size_t lpslam_imadjust_scratch_bytes(uint32_t n_images);
 int lpslam_imadjust_dev(const uint8_t* src_dev, int width, int height, size_t pitch, size_t frame_stride, uint32_t n_images,
                         int auto_limits, double low_in, double high_in, double low_out, double high_out, uint8_t* dst_dev,
                         size_t dst_pitch, size_t dst_frame_stride, void* scratch_dev, void* stream);
+/* No counterpart in the reference: lpslam_imadjust_dev for hosts that may not allocate device memory while they run. That is
+ * a camera callback on a real-time tracking thread (a cudaMalloc takes driver locks and can stall the whole device for an
+ * unbounded time), and a plugin in a process whose own pool claimed the device memory at start-up (a later cudaMalloc there
+ * fails). Such a caller can neither make the scratch_dev buffer of lpslam_imadjust_dev nor use lpslam_imadjust, which
+ * allocates for it. Here the histograms and value maps live in a fixed array inside the library image: 80 KiB on every GPU
+ * that loads the library, held until the process exits. The call allocates and frees nothing; it only enqueues on `stream`.
+ *  - Same arithmetic, arguments and output as lpslam_imadjust_dev (without scratch_dev). limits_dev (nullable, device,
+ *    2 x n_images doubles) receives low / high input limits per image.
+ *  - n_images <= LPSLAM_IMADJUST_STATIC_MAX_IMAGES, else LPSLAM_ERR_ARG with the limit named in lpslam_cuda_last_error().
+ *  - It works on the device that is current in the calling thread. The first call on each device looks the array's device
+ *    address up (once, kept afterwards): make that first call during start-up, before any stream capture begins.
+ *  - All calls on a device share the one array and it keeps what the last call left; the call clears the histogram part it is
+ *    about to use itself. Two calls that overlap on the GPU (different streams without an ordering between them, or two host
+ *    threads) race on it and produce wrong images: order them, or give all but one of them lpslam_imadjust_dev. */
+#define LPSLAM_IMADJUST_STATIC_MAX_IMAGES 64
+int lpslam_imadjust_dev_static(const uint8_t* src_dev, int width, int height, size_t pitch, size_t frame_stride, uint32_t n_images,
+                               int auto_limits, double low_in, double high_in, double low_out, double high_out, uint8_t* dst_dev,
+                               size_t dst_pitch, size_t dst_frame_stride, double* limits_dev, void* stream);
 /* LpSlam::ImageProcessing::Undistort::undistort (src/Utils/ImageProcessing.h:245-249): cv::remap(INTER_LINEAR,
  * BORDER_CONSTANT 0) with the cached CV_32FC1 maps of cv::initUndistortRectifyMap (map_pitch in floats; the maps have the
  * destination size and are shared by all n_images frames). */

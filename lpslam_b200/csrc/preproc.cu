@@ -13,6 +13,7 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <mutex>
 
 namespace lps {
 namespace {
@@ -357,3 +358,78 @@ int lpslam_remap_linear(const uint8_t* src, int src_width, int src_height, size_
 }
 
 }  // extern "C"
+
+// ---- imadjust without any allocation (lpslam_imadjust_dev_static) ----
+// Some hosts of this library are not allowed to allocate device memory once they run: a camera callback of a real-time tracking
+// thread (cudaMalloc takes driver locks and may synchronise the whole device, so its latency has no bound), or a plugin inside a
+// process whose own pool reserved the device memory at start-up, where a later cudaMalloc simply fails. lpslam_imadjust_dev asks
+// such a caller for a scratch buffer it cannot produce, and lpslam_imadjust allocates on its behalf. This variant keeps the
+// histograms and value maps in an array that is part of the library image instead: kAdjustStaticBytes (80 KiB) of every GPU that
+// loads liblpslam_cuda.so, from module load until the process ends.
+constexpr size_t kAdjustPerImage = 256 * sizeof(uint32_t) + 256;  // hist u32[256] + lut u8[256]
+constexpr size_t kAdjustStaticBytes = (size_t)LPSLAM_IMADJUST_STATIC_MAX_IMAGES * kAdjustPerImage;
+// Layout: hist u32[256 x MAX] | lut u8[256 x MAX]. Shared by every call on the device; holds whatever the last call left.
+static __device__ __align__(256) uint8_t g_adjust_static[kAdjustStaticBytes];
+
+namespace lps {
+namespace {
+
+constexpr int kAdjustMaxDevices = 64;
+std::mutex g_adjust_mutex;
+uint8_t* g_adjust_ptr[kAdjustMaxDevices] = {};  // device address of g_adjust_static, per device ordinal
+
+// In host code `g_adjust_static` is only a handle for the runtime, not an address a kernel can use: the address differs per
+// device and has to be asked for with that device current. Looked up once per device, then cached.
+int adjust_static_ptr(uint8_t** out) {
+    int dev = -1;
+    LPS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kAdjustMaxDevices) {
+        set_error("lpslam_imadjust_dev_static: device ordinal beyond the " + std::to_string(kAdjustMaxDevices) + " this entry point tracks");
+        return LPSLAM_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lock(g_adjust_mutex);
+    if (!g_adjust_ptr[dev]) {
+        void* p = nullptr;
+        LPS_CUDA(cudaGetSymbolAddress(&p, g_adjust_static));
+        g_adjust_ptr[dev] = (uint8_t*)p;
+    }
+    *out = g_adjust_ptr[dev];
+    return LPSLAM_OK;
+}
+
+}  // namespace
+}  // namespace lps
+
+extern "C" int lpslam_imadjust_dev_static(const uint8_t* src_dev, int width, int height, size_t pitch, size_t frame_stride,
+                                          uint32_t n_images, int auto_limits, double low_in, double high_in, double low_out,
+                                          double high_out, uint8_t* dst_dev, size_t dst_pitch, size_t dst_frame_stride,
+                                          double* limits_dev, void* stream) {
+    LPS_ARG(src_dev && dst_dev, "null pointer");
+    LPS_ARG(width > 0 && height > 0 && pitch >= (size_t)width && dst_pitch >= (size_t)width && n_images >= 1, "bad image geometry");
+    if (n_images > LPSLAM_IMADJUST_STATIC_MAX_IMAGES) {
+        set_error("lpslam_imadjust_dev_static: " + std::to_string(n_images) + " images in one call, the built-in scratch holds "
+                  + std::to_string(LPSLAM_IMADJUST_STATIC_MAX_IMAGES) + " (LPSLAM_IMADJUST_STATIC_MAX_IMAGES); split the batch or use "
+                  "lpslam_imadjust_dev with a scratch buffer of your own");
+        return LPSLAM_ERR_ARG;
+    }
+    uint8_t* base = nullptr;
+    if (int rc = adjust_static_ptr(&base)) return rc;  // first call on this device: one symbol lookup, nothing allocated
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t* hist = (uint32_t*)base;
+    uint8_t* lut = base + 256 * sizeof(uint32_t) * (size_t)LPSLAM_IMADJUST_STATIC_MAX_IMAGES;
+    const int vec = aligned(src_dev, 16) && pitch % 16 == 0 && frame_stride % 16 == 0;
+    const int vec_out = vec && aligned(dst_dev, 16) && dst_pitch % 16 == 0 && dst_frame_stride % 16 == 0;
+    if (auto_limits) {
+        // the previous call's counts are still in the array: the histograms this call adds into start from zero
+        LPS_CUDA(cudaMemsetAsync(hist, 0, 256 * sizeof(uint32_t) * (size_t)n_images, st));
+        const long units = (long)(vec ? (width + 15) / 16 : width) * height;
+        const int blocks = (int)std::min<long>(std::max<long>((units + 256 * 8 - 1) / (256 * 8), 1), 148 * 4);
+        k_hist<<<dim3(blocks, n_images), 256, 0, st>>>(src_dev, width, height, pitch, frame_stride, hist, vec);
+    }
+    AdjustArgs a{auto_limits, low_in, high_in, low_out, high_out, (uint32_t)(width * height)};
+    k_lut<<<n_images, 256, 0, st>>>(hist, a, lut, limits_dev);  // every lut entry of images 0..n-1 is rewritten, nothing to clear
+    dim3 blk(64, 4), grd((width + 64 * 16 - 1) / (64 * 16), (height + 3) / 4, n_images);
+    k_apply_lut<<<grd, blk, 0, st>>>(src_dev, width, height, pitch, frame_stride, lut, dst_dev, dst_pitch, dst_frame_stride, vec_out);
+    LPS_CUDA(cudaGetLastError());
+    return LPSLAM_OK;
+}

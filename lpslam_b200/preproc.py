@@ -15,6 +15,11 @@ register("lpslam_imadjust", C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_size_t, 
 register("lpslam_imadjust_scratch_bytes", C.c_size_t, [C.c_uint32])
 register("lpslam_imadjust_dev", C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_uint32, C.c_int, C.c_double,
                                           C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p])
+# no reference counterpart: imadjust with the scratch in a fixed array inside the library, for hosts that may not allocate
+register("lpslam_imadjust_dev_static", C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_uint32, C.c_int, C.c_double,
+                                                 C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p,
+                                                 C.c_void_p])
+IMADJUST_STATIC_MAX_IMAGES = 64  # LPSLAM_IMADJUST_STATIC_MAX_IMAGES in include/lpslam_cuda.h
 register("lpslam_remap_linear", C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
                                           C.c_int, C.c_int, C.c_size_t])
 register("lpslam_remap_linear_dev", C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t,
