@@ -480,8 +480,11 @@ int lpslam_orb_ctx::configure(int width, int height) {
     {
         static const bool blur_v1 = getenv("LPS_BLUR_V1") != nullptr;  // A/B switch: the ld.global version of blur.cu
         if (!blur_v1) {
+            // nullptr (a tensor map could not be encoded for this geometry) = the ld.global blur of blur.cu, as pyr_plan
+            // does below: same results, and configure() still completes so that later calls do not rebuild the arena
             blur_plan = blur_plan_create(lv, L, (int)max_batch);
-            if (!blur_plan) return LPSLAM_ERR_CUDA;
+            if (!blur_plan) fprintf(stderr, "liblpslam_cuda: TMA blur unavailable for %dx%d (%s), using the ld.global blur\n", width, height,
+                                    lpslam_cuda_last_error());
         }
         pyr_plan = pyramid_plan_create(lv, L, (int)max_batch);  // nullptr = geometry outside the kernel's range
     }
