@@ -57,8 +57,8 @@ def test_dropin_classes_match_oracle(oracle, tmp_path):
         assert np.array_equal(m, ol.level(level)), level
     oxr, odep = oracle.match_stereo([ol.level(l) for l in range(8)], [orr.level(l) for l in range(8)], okl, okr, odl, odr,
                                     ol.table(0), ol.table(1), FX_B, B)
-    if (dl == odl).all() and (dr == odr).all():
-        assert np.array_equal(xr, oxr) and np.array_equal(dep, odep)
+    assert (dl == odl).all() and (dr == odr).all()
+    assert np.array_equal(xr, oxr) and np.array_equal(dep, odep)
     assert (xr >= 0).sum() > 50
 
 

@@ -47,9 +47,7 @@ def test_stereo_frames(name):
     r = match.stereo_frames(e, [left], [right], FX_B, B)[0]
     assert np.array_equal(np.stack([r["keypts_left"]["x"], r["keypts_left"]["y"]], 1), g["kp_l_xy"])
     assert np.array_equal(np.stack([r["keypts_right"]["x"], r["keypts_right"]["y"]], 1), g["kp_r_xy"])
-    if crc(r["descs_left"]) == int(g["desc_l_crc"]) and crc(r["descs_right"]) == int(g["desc_r_crc"]):
-        assert np.array_equal(r["stereo_x_right"], g["stereo_x_right"])
-        assert np.array_equal(r["depths"], g["depths"])
-    else:  # a descriptor bit differs within the 0.1 % allowance: matches may move, so compare loosely
-        same = (r["stereo_x_right"] == g["stereo_x_right"]).mean()
-        assert same >= 0.99
+    # descriptors are identical to the reference build's on every fixture, so the matcher is held bit for bit
+    assert crc(r["descs_left"]) == int(g["desc_l_crc"]) and crc(r["descs_right"]) == int(g["desc_r_crc"])
+    assert np.array_equal(r["stereo_x_right"], g["stereo_x_right"])
+    assert np.array_equal(r["depths"], g["depths"])
