@@ -74,7 +74,9 @@ typedef enum {
     LPSLAM_ORB_SCALE_FACTOR = 1,
     LPSLAM_ORB_NUM_LEVELS = 2,
     LPSLAM_ORB_INI_FAST_THR = 3,
-    LPSLAM_ORB_MIN_FAST_THR = 4
+    LPSLAM_ORB_MIN_FAST_THR = 4,
+    /* read only, no reference counterpart: how many times this context replayed its one-pair CUDA graph (lpslam_stereo_frames) */
+    LPSLAM_ORB_DEBUG_GRAPH_LAUNCHES = 100
 } lpslam_orb_param_id;
 int lpslam_orb_set_param(lpslam_orb_ctx* ctx, int which, double value);
 int lpslam_orb_get_param(const lpslam_orb_ctx* ctx, int which, double* value);

@@ -89,6 +89,7 @@ int lpslam_orb_create(lpslam_orb_ctx** out, const lpslam_orb_params* p, int devi
     if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_greatest);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_reader, cudaEventDisableTiming);
     for (int i = 0; i < 3 && e == cudaSuccess; ++i) {
         e = cudaStreamCreateWithPriority(&c->chain[i], cudaStreamNonBlocking, prio_greatest);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_chain_join[i], cudaEventDisableTiming);
@@ -120,6 +121,7 @@ void lpslam_orb_destroy(lpslam_orb_ctx* c) {
     c->release_geometry();
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->ev_reader) cudaEventDestroy(c->ev_reader);
     if (c->side) cudaStreamDestroy(c->side);
     if (c->h_frame_off) cudaFreeHost(c->h_frame_off);
     if (c->pack_dev) cudaFree(c->pack_dev);
@@ -169,6 +171,7 @@ int lpslam_orb_get_param(const lpslam_orb_ctx* c, int which, double* value) {
         case LPSLAM_ORB_NUM_LEVELS: *value = c->num_levels; break;
         case LPSLAM_ORB_INI_FAST_THR: *value = c->ini_thr; break;
         case LPSLAM_ORB_MIN_FAST_THR: *value = c->min_thr; break;
+        case LPSLAM_ORB_DEBUG_GRAPH_LAUNCHES: *value = (double)c->pair_graph_launches; break;
         default: LPS_ARG(false, "unknown parameter id");
     }
     return LPSLAM_OK;

@@ -67,6 +67,7 @@ int lpslam_stereo_frames(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const 
     if (c->pair_graph && (!want_graph || c->pair_graph_fxb != focal_x_baseline || c->pair_graph_tb != true_baseline)) c->drop_pair_graph();
     if (want_graph && c->pair_graph) {
         LPS_CUDA(cudaGraphLaunch(c->pair_graph, c->stream));
+        ++c->pair_graph_launches;
         c->last_batch = nf;
         c->has_result = true;
     }
@@ -100,7 +101,10 @@ int lpslam_stereo_frames(lpslam_orb_ctx* c, const uint8_t* const* imgs_l, const 
                         : cudaMemcpyAsync(c->h_frame_off, c->desc.frame_off, sizeof(uint32_t) * (c->max_batch + 2), cudaMemcpyDeviceToHost,
                                           c->stream);
             }
-            else LPS_CUDA(cudaGraphLaunch(c->pair_graph, c->stream));
+            else {
+                LPS_CUDA(cudaGraphLaunch(c->pair_graph, c->stream));
+                ++c->pair_graph_launches;
+            }
         }
         if (rc) return rc;
         LPS_CUDA(ce);
@@ -128,9 +132,11 @@ namespace {
 // packed results of a finished batch -> the slot's own arrays (exact sizes are only known on the device)
 __global__ void k_copy_results(const lpslam_keypoint* __restrict__ kp, const uint8_t* __restrict__ desc, const float* __restrict__ xr,
                                const float* __restrict__ dep, const uint32_t* __restrict__ off, uint32_t nf, uint32_t n_off,
-                               lpslam_keypoint* __restrict__ kp_o, uint8_t* __restrict__ desc_o, float* __restrict__ xr_o,
+                               uint32_t out_cap, lpslam_keypoint* __restrict__ kp_o, uint8_t* __restrict__ desc_o, float* __restrict__ xr_o,
                                float* __restrict__ dep_o, uint32_t* __restrict__ off_o) {
-    const uint32_t total = off[nf];
+    // off[nf] is the raw carry: beyond out_cap it only says by how much the batch overflowed (collect() then reports
+    // LPSLAM_ERR_CAPACITY from the overflow word); the slot arrays hold out_cap rows, as the packed arrays k_describe wrote
+    const uint32_t total = min(off[nf], out_cap);
     const uint32_t stride = gridDim.x * blockDim.x, i0 = blockIdx.x * blockDim.x + threadIdx.x;
     for (uint32_t i = i0; i < n_off; i += stride) off_o[i] = off[i];
     const uint32_t* ks = reinterpret_cast<const uint32_t*>(kp);
@@ -214,7 +220,7 @@ int submit_frames(lpslam_orb_ctx* c, const uint8_t* const* frames, uint32_t nf, 
     if (rc) return rc;
     // (extraction only: the stereo arrays are copied too, rows of an earlier stereo call or never-read scratch)
     k_copy_results<<<256, 256, 0, c->stream>>>(c->desc.kp, c->desc.desc, c->stereo.x_right, c->stereo.depth, c->desc.frame_off, nf,
-                                               c->max_batch + 2, sl.kp, sl.desc, sl.xr, sl.dep, sl.off_dev);
+                                               c->max_batch + 2, c->out_cap, sl.kp, sl.desc, sl.xr, sl.dep, sl.off_dev);
     LPS_CUDA(cudaMemcpyAsync(sl.h_off, sl.off_dev, 4 * (size_t)(c->max_batch + 2), cudaMemcpyDeviceToHost, c->stream));
     LPS_CUDA(cudaEventRecord(sl.ev_done, c->stream));
     sl.busy = true;
@@ -421,6 +427,14 @@ int lpslam_match_stereo_ctx(lpslam_orb_ctx* cl, lpslam_orb_ctx* cr, const lpslam
         cs.put(o_desc + 32 * (size_t)nl, desc_r, 32 * (size_t)nr);
         cs.put(o_off, h_off, sizeof h_off);
         if ((e = cs.upload(0, in_end)) != cudaSuccess) break;
+        // the pyramids may still be in the making on the contexts' own streams (the enqueue-only and submit forms set
+        // has_result without waiting): the call's stream runs after whatever they hold now
+        if ((e = cudaEventRecord(cl->ev_reader, cl->stream)) != cudaSuccess) break;
+        if ((e = cudaStreamWaitEvent(cs.st, cl->ev_reader, 0)) != cudaSuccess) break;
+        if (cr != cl) {
+            if ((e = cudaEventRecord(cr->ev_reader, cr->stream)) != cudaSuccess) break;
+            if ((e = cudaStreamWaitEvent(cs.st, cr->ev_reader, 0)) != cudaSuccess) break;
+        }
         StereoArgs a{};
         a.lv = (const LevelGeom*)(dev + o_lv);
         a.num_levels = (int)num_levels;

@@ -11,6 +11,8 @@ struct lpslam_orb_ctx {
     // side stream: level-0 apron + blur run beside FAST and the quadtree (they only depend on the pyramid)
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // marks "everything enqueued on `stream` so far" for a reader on another stream (lpslam_match_stereo_ctx)
+    cudaEvent_t ev_reader = nullptr;
     // the pyramid of a batch is built as up to 4 independent chains of frames on their own streams, so that the small
     // levels of one chain run beside the large levels of another (each level launch alone leaves most SMs idle at its tail)
     cudaStream_t chain[3] = {};
@@ -64,6 +66,7 @@ struct lpslam_orb_ctx {
     float pair_graph_fxb = 0.f, pair_graph_tb = 0.f;
     int pair_graph_warm = 0;
     bool pair_graph_off = false;
+    uint64_t pair_graph_launches = 0;  // cudaGraphLaunch calls over the context's life (LPSLAM_ORB_DEBUG_GRAPH_LAUNCHES)
     void drop_pair_graph();
     uint8_t* pack_dev = nullptr;
     uint8_t* pack_host = nullptr;

@@ -11,6 +11,8 @@ register("lpslam_match_stereo", C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_v
                                           szp, szp, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p,
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                           _lib.u32p])
+register("lpslam_match_stereo_ctx", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p,
+                                              C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p, _lib.u32p])
 register("lpslam_stereo_frames", C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_uint32, C.c_int,
                                            C.c_int, C.c_size_t, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_uint32,
                                            C.c_void_p, C.c_void_p, C.c_void_p])
@@ -56,6 +58,21 @@ class stereo:
                                         self.isf.ctypes.data, self.fx_b, self.b, xr.ctypes.data, dep.ctypes.data,
                                         C.byref(nm)))
         return xr, dep
+
+
+def stereo_on_contexts(extractor_left, extractor_right, keypts_left, keypts_right, descs_left, descs_right, focal_x_baseline,
+                       true_baseline):
+    """match::stereo::compute (match/stereo.cc:18-249) on the pyramids the two extractors still hold on the device from their last
+    extraction (lpslam_match_stereo_ctx: what the drop-in match::stereo does with two drop-in extractors, data/frame.cc:78)."""
+    kl, kr = np.ascontiguousarray(keypts_left, KP_DTYPE), np.ascontiguousarray(keypts_right, KP_DTYPE)
+    dl, dr = np.ascontiguousarray(descs_left, np.uint8), np.ascontiguousarray(descs_right, np.uint8)
+    xr = np.full(len(kl), -1.0, np.float32)
+    dep = np.full(len(kl), -1.0, np.float32)
+    nm = C.c_uint32(0)
+    check(lib().lpslam_match_stereo_ctx(extractor_left._h, extractor_right._h, kl.ctypes.data, len(kl), kr.ctypes.data, len(kr),
+                                        dl.ctypes.data, dr.ctypes.data, float(focal_x_baseline), float(true_baseline), xr.ctypes.data,
+                                        dep.ctypes.data, C.byref(nm)))
+    return xr, dep
 
 
 def stereo_frames(extractor, lefts, rights, focal_x_baseline, true_baseline, cap_per_frame=None):
