@@ -116,6 +116,13 @@ int main(int argc, char** argv) {
             std::fwrite(&mh, 4, 1, f);
             for (int y = 0; y < mh; ++y) std::fwrite(m.ptr(y), 1, static_cast<size_t>(mw), f);
         }
+        // an empty input image returns at once and leaves the caller's keypoints and descriptors as they were (orb_extractor.cc:73-75)
+        const size_t n_before = kc.size();
+        const int rows_before = dc.rows;
+        const uint8_t* data_before = dc.data;
+        copy.extract(cv::Mat(), cv::Mat(), kc, dc);
+        const int32_t untouched = kc.size() == n_before && n_before > 0 && dc.rows == rows_before && dc.data == data_before;
+        std::fwrite(&untouched, 4, 1, f);
     }
     std::fclose(f);
     delete ext_l;

@@ -344,8 +344,10 @@ int lpslam_knn_unpack(const uint64_t* merged_dev, uint32_t nq, int64_t* best_idx
     LPS_ARG(nq == 0 || (merged_dev && best_idx && best_dist && second_dist), "null argument");
     if (nq == 0) return LPSLAM_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    // the calling thread's grow-only scratch (scratch.cu): a relocalisation query no longer pays a cudaMalloc + cudaFree
+    // (two device synchronisations) per call; the stream is drained below before the buffer is handed back
     uint8_t* dev = nullptr;
-    LPS_CUDA(cudaMalloc(&dev, (size_t)nq * 16));
+    LPS_CUDA(scratch_alloc((void**)&dev, (size_t)nq * 16));
     int64_t* bi = (int64_t*)dev;
     uint32_t* bd = (uint32_t*)(dev + (size_t)nq * 8);
     uint32_t* sd = bd + nq;
@@ -355,7 +357,7 @@ int lpslam_knn_unpack(const uint64_t* merged_dev, uint32_t nq, int64_t* best_idx
     if (e == cudaSuccess) e = cudaMemcpyAsync(best_dist, bd, (size_t)nq * 4, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(second_dist, sd, (size_t)nq * 4, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    cudaFree(dev);
+    scratch_free(dev);
     if (e != cudaSuccess) return cuda_fail(e, "lpslam_knn_unpack", __FILE__, __LINE__);
     return LPSLAM_OK;
 }

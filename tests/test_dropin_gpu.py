@@ -42,6 +42,8 @@ def test_dropin_classes_match_oracle(oracle, tmp_path):
     for _ in range(1, 8):
         mw, mh = np.frombuffer(raw, np.int32, 2, o); o += 8
         copy_levels.append(np.frombuffer(raw, np.uint8, mw * mh, o).reshape(mh, mw)); o += mw * mh
+    empty_image_untouched = np.frombuffer(raw, np.int32, 1, o)[0]; o += 4
+    assert o == len(raw)
 
     ol, orr = oracle.extractor(max_kpts=n), oracle.extractor(max_kpts=n)
     okl, odl = ol.extract(left)
@@ -52,6 +54,7 @@ def test_dropin_classes_match_oracle(oracle, tmp_path):
     assert np.abs(kl["angle"] - okl["angle"]).max() <= 1e-4 * 180 / np.pi
     assert (dl == odl).all(axis=1).mean() >= 0.999 and (dr == odr).all(axis=1).mean() >= 0.999
     assert np.array_equal(p3, ol.level(3))  # image_pyramid_ side effect (orb_extractor.h:76)
+    assert empty_image_untouched == 1  # orb_extractor.cc:73-75 through the drop-in class: outputs keep what they held
     assert same_after_copy == 1  # a copy-constructed extractor (own device context) extracts the same keypoints and descriptors
     for level, m in enumerate(copy_levels, 1):  # levels 1..7 arrive in one copy into one allocation
         assert np.array_equal(m, ol.level(level)), level

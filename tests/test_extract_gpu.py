@@ -143,3 +143,28 @@ def test_repeatable_under_shared_memory_protocols(orb):
             first = sig
         assert sig == first, f"run {rep} differs from run 0"
         e.extract_batch(other)
+
+
+def test_empty_image_leaves_outputs_untouched(orb):
+    """feature/orb_extractor.cc:73-75: `if (in_image.empty()) return;` — through lpslam_orb_extract an image without pixels (null
+    pointer, zero width or zero height) is LPSLAM_OK with *n_out = 0 and not one byte of the output buffers written; the context
+    stays usable."""
+    import ctypes as C
+    from lpslam_b200._lib import KP_DTYPE, lib
+    e = orb.orb_extractor(max_num_keypts=300)
+    img = synth_image(240, 320, 11)
+    want_kp, want_desc = e.extract(img)
+    assert len(want_kp) > 50
+    kp = np.zeros(64, KP_DTYPE)
+    kp["octave"] = 0x5A5A5A5A
+    desc = np.full((64, 32), 0xA5, np.uint8)
+    kp0, desc0 = kp.copy(), desc.copy()
+    for ptr, w, h in ((img.ctypes.data, 0, 240), (img.ctypes.data, 320, 0), (None, 320, 240), (None, 0, 0)):
+        n = C.c_uint32(77)
+        rc = lib().lpslam_orb_extract(e._h, ptr, w, h, 320, None, 0, kp.ctypes.data, desc.ctypes.data, 64, C.byref(n))
+        assert rc == 0 and n.value == 0
+        assert kp.tobytes() == kp0.tobytes() and desc.tobytes() == desc0.tobytes()
+    got_kp, got_desc = e.extract(np.zeros((0, 0), np.uint8))  # the Python mirror of the same branch
+    assert len(got_kp) == 0 and got_desc is None
+    again_kp, again_desc = e.extract(img)
+    assert again_kp.tobytes() == want_kp.tobytes() and np.array_equal(again_desc, want_desc)
