@@ -782,7 +782,7 @@ __device__ void resolve_serial(const ProjArgs& a, const TakenSet& tk, uint32_t* 
 
 constexpr int RESOLVE_THREADS = 1024;
 
-__global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(ProjArgs a) {
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_lm_resolve(const __grid_constant__ ProjArgs a) {
     extern __shared__ uint32_t s_mem[];
     __shared__ uint32_t s_barrier, s_minrow, s_warp_tot[RESOLVE_THREADS / 32], s_done;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
