@@ -122,13 +122,16 @@ void orb_extractor::extract(const cv::_InputArray& in_image, const cv::_InputArr
 
     // the keypoint count is not bounded by max_num_keypts (a breadth pass of the quadtree is always finished)
     uint32_t cap = 4 * orb_params_.max_num_keypts_ + 1024, n = 0;
-    std::vector<uint8_t> desc;
+    // landing buffers of the calling thread, kept between calls: a fresh std::vector of `cap` keypoints and cap x 32 descriptor
+    // bytes would be value-initialised (0.5 MB of stores) on every frame only to be overwritten by the copy from the device
+    thread_local std::vector<lpslam_keypoint> kp_land;
+    thread_local std::vector<uint8_t> desc_land;
     for (int attempt = 0; attempt < 2; ++attempt) {
-        keypts.resize(cap);
-        desc.resize(static_cast<size_t>(cap) * 32);
+        if (kp_land.size() < cap) kp_land.resize(cap);
+        if (desc_land.size() < static_cast<size_t>(cap) * 32) desc_land.resize(static_cast<size_t>(cap) * 32);
         const int rc = lpslam_orb_extract(ctx_, image.data, image.cols, image.rows, image.step,
                                           mask.empty() ? nullptr : mask.data, mask.empty() ? 0 : mask.step,
-                                          reinterpret_cast<lpslam_keypoint*>(keypts.data()), desc.data(), cap, &n);
+                                          kp_land.data(), desc_land.data(), cap, &n);
         if (rc == LPSLAM_ERR_CAPACITY && n > cap && attempt == 0) {
             cap = n;
             continue;
@@ -137,13 +140,19 @@ void orb_extractor::extract(const cv::_InputArray& in_image, const cv::_InputArr
         break;
     }
     keypts.resize(n);
+    if (n) std::memcpy(static_cast<void*>(keypts.data()), kp_land.data(), sizeof(lpslam_keypoint) * static_cast<size_t>(n));
     if (n == 0) {
         out_descriptors.release();  // orb_extractor.cc:115-117
     }
     else {
         out_descriptors.create(static_cast<int>(n), 32, CV_8U);
         cv::Mat d = out_descriptors.getMat();
-        for (uint32_t i = 0; i < n; ++i) std::memcpy(d.ptr(static_cast<int>(i)), desc.data() + static_cast<size_t>(i) * 32, 32);
+        if (d.isContinuous()) {
+            std::memcpy(d.data, desc_land.data(), static_cast<size_t>(n) * 32);
+        }
+        else {
+            for (uint32_t i = 0; i < n; ++i) std::memcpy(d.ptr(static_cast<int>(i)), desc_land.data() + static_cast<size_t>(i) * 32, 32);
+        }
     }
 
     // image_pyramid_ (orb_extractor.h:76): level 0 aliases the input, the other levels are copied back from the device

@@ -137,6 +137,7 @@ public:
     }
     int channels() const { return channels_; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+    bool isContinuous() const { return rows <= 1 || step == static_cast<size_t>(cols) * elem(); }
     int type() const { return type_; }
     size_t elem() const { return type_ == CV_32F ? 4 : 1; }
     size_t step1() const { return step / elem(); }
